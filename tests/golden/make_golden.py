@@ -1,0 +1,222 @@
+#!/usr/bin/env python
+"""Generate the golden fixtures in this directory FROM THE REFERENCE ITSELF.
+
+Run in the build container only (needs /root/reference, read-only):
+
+    PYTHONDONTWRITEBYTECODE=1 python tests/golden/make_golden.py
+
+The reference ships no tests or golden vectors, so parity is pinned on
+outputs of the unmodified reference code run here with this environment's torch CPU
+kernels (torch 2.11.0, oneDNN, fp32; fp64 re-run stored beside it as the tie-breaker):
+
+  weights_<ckpt>.npz   the shipped checkpoints' tensors, verbatim fp32, original key names
+                       (/root/reference/ckpts/*.pth; data, not source - they must travel
+                       to the GPU box where /root/reference does not exist)
+  forward_<ckpt>.npz   seeded inputs -> StofNet.forward masks (fp32 + fp64) and
+                       mask2coords / get_maxima_positions outputs for th in
+                       {None, checkpoint th, 0.5}
+  peaks_cases.npz      hand-made stage-4 edge cases -> reference indices / coords
+  espcn_<ckpt>.npz     ESPCN_1D forward masks
+  metrics_cases.npz    toa_rmse / coords2mask / find_threshold known answers
+
+Nothing here is imported by the product; tests/ read the .npz files only.
+"""
+import os
+import sys
+import glob
+
+sys.dont_write_bytecode = True
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+REF = "/root/reference"
+sys.path.insert(0, REF)
+
+import numpy as np
+import torch
+
+from stofnet_b200.synth import synth_waveforms  # our generator (inputs only)
+
+from models.stofnet import StofNet  # noqa: E402  (reference)
+from models.espcn_1d import ESPCN_1D  # noqa: E402
+from utils.mask2samples import mask2coords, get_maxima_positions, coords2mask, nms_1d  # noqa: E402
+from utils.metrics import toa_rmse  # noqa: E402
+from utils.threshold import find_threshold  # noqa: E402
+from utils.sample_shuffle import SampleShuffle1D  # noqa: E402
+
+torch.manual_seed(0)
+torch.set_num_threads(8)
+
+# checkpoint -> (rf_scale_factor, benchmark threshold) from bash_scripts/array_*_params.txt
+STOF = {
+    "different-armadillo": (10, None),
+    "clean-serenity": (10, None),
+    "graceful-snow": (20, 0.015),
+    "breezy-violet": (20, 2.3),
+}
+ESPCN = {"vital-puddle": (10, None), "wobbly-sponge": (20, 0.2)}
+
+
+def ckpt_path(prefix):
+    (p,) = glob.glob(os.path.join(REF, "ckpts", prefix + "*.pth"))
+    return p
+
+
+def load_sd(prefix):
+    return torch.load(ckpt_path(prefix), weights_only=True, map_location="cpu")
+
+
+def th_key(th):
+    return "none" if th is None else ("%g" % th).replace(".", "p").replace("-", "m")
+
+
+def peaks_dict(prefix, masks, th, out):
+    """Store reference stage-4 outputs for one (masks, th)."""
+    idx = get_maxima_positions(masks, 20, th)
+    co = mask2coords(masks, 20, th, upsample_factor=4)
+    out[prefix + "_idx_" + th_key(th)] = idx.numpy().astype(np.int64)
+    out[prefix + "_coords_" + th_key(th)] = co.numpy().astype(np.float32)
+
+
+def gen_forward():
+    for name, (rf, th) in STOF.items():
+        sd = load_sd(name)
+        np.savez(os.path.join(HERE, "weights_%s.npz" % name),
+                 **{k: v.numpy() for k, v in sd.items()})
+        has_sgb = any(k.startswith("semi_global_block") for k in sd)
+        model = StofNet(upsample_factor=4, semi_global_scale=80 if has_sgb else 1).eval()
+        print(name, model.load_state_dict(sd))
+        model64 = StofNet(upsample_factor=4, semi_global_scale=80 if has_sgb else 1).double().eval()
+        model64.load_state_dict({k: v.double() for k, v in sd.items()})
+        out = {"rf": np.int64(rf), "th": np.float64(np.nan if th is None else th)}
+        cases = [(3, 160, 11), (2, 2578, 3008), (2, 256 * rf, 3008), (1, 320, 1)]
+        out["cases"] = np.array(cases, dtype=np.int64)
+        for ci, (N, L, seed) in enumerate(cases):
+            x = torch.from_numpy(synth_waveforms(N, L, seed=seed, rf=rf)).unsqueeze(1)
+            with torch.no_grad():
+                m = model(x)
+                m64 = model64(x.double())
+            p = "c%d" % ci
+            out[p + "_x"] = x.squeeze(1).numpy()
+            out[p + "_mask"] = m.squeeze(1).numpy()
+            out[p + "_mask64"] = m64.squeeze(1).numpy()
+            for t in sorted({None, th, 0.5}, key=lambda v: (v is not None, v or 0)):
+                peaks_dict(p, m, t, out)
+            print("  case", ci, N, L, "mask range", float(m.min()), float(m.max()),
+                  "max|fp32-fp64|", float((m.double() - m64).abs().max()))
+        np.savez_compressed(os.path.join(HERE, "forward_%s.npz" % name), **out)
+
+    for name, (rf, th) in ESPCN.items():
+        sd = load_sd(name)
+        np.savez(os.path.join(HERE, "weights_%s.npz" % name),
+                 **{k: v.numpy() for k, v in sd.items()})
+        model = ESPCN_1D(4).eval()
+        print(name, model.load_state_dict(sd))
+        out = {"rf": np.int64(rf), "th": np.float64(np.nan if th is None else th)}
+        cases = [(3, 160, 11), (2, 256 * rf, 3008), (1, 37, 2)]
+        out["cases"] = np.array(cases, dtype=np.int64)
+        for ci, (N, L, seed) in enumerate(cases):
+            x = torch.from_numpy(synth_waveforms(N, L, seed=seed, rf=rf)).unsqueeze(1)
+            with torch.no_grad():
+                m = model(x)
+            p = "c%d" % ci
+            out[p + "_x"] = x.squeeze(1).numpy()
+            out[p + "_mask"] = m.squeeze(1).numpy()
+            for t in sorted({None, th, 0.5}, key=lambda v: (v is not None, v or 0)):
+                peaks_dict(p, m, t, out)
+        np.savez_compressed(os.path.join(HERE, "espcn_%s.npz" % name), **out)
+
+
+def gen_peaks_cases():
+    rng = np.random.default_rng(7)
+    cases = {}
+
+    def add(name, scores, th, win=20, r=4):
+        s = torch.from_numpy(np.ascontiguousarray(scores, dtype=np.float32))
+        idx = get_maxima_positions(s.clone(), win, th)
+        co = mask2coords(s.clone(), win, th, upsample_factor=r)
+        sup = nms_1d(s.clone(), win)
+        cases[name + "_scores"] = s.numpy()
+        cases[name + "_th"] = np.float64(np.nan if th is None else th)
+        cases[name + "_win"] = np.int64(win)
+        cases[name + "_r"] = np.int64(r)
+        cases[name + "_idx"] = idx.numpy().astype(np.int64)
+        cases[name + "_coords"] = co.numpy().astype(np.float32)
+        cases[name + "_nms"] = sup.numpy().astype(np.float32)
+        names.append(name)
+
+    names = []
+    add("allzero_none", np.zeros((3, 1, 64)), None)
+    add("allzero_th", np.zeros((3, 1, 64)), 0.5)
+    add("allneg_none", -2.5 * np.ones((2, 1, 48)), None)
+    add("allneg_th", -2.5 * np.ones((2, 1, 48)), 0.5)
+    add("allpos_const_th", 1.5 * np.ones((2, 1, 48)), 0.5)
+    x = np.zeros((2, 1, 100)); x[0, 0, 30] = 2.0; x[0, 0, 36] = 2.0; x[1, 0, 50] = 1.0; x[1, 0, 70] = 1.0
+    add("ties_in_window_th", x, 0.5)
+    add("ties_in_window_none", x, None)
+    x = np.zeros((2, 1, 100)); x[0, 0, 0] = 3.0; x[0, 0, 99] = 3.0; x[1, 0, 10] = 0.7; x[1, 0, 20] = 0.7; x[1, 0, 31] = 0.6
+    add("edges_th", x, 0.5)
+    add("edges_none", x, None)
+    add("n1_th", rng.normal(size=(1, 1, 400)), 0.5)
+    add("n1_none", rng.normal(size=(1, 1, 400)), None)
+    add("th_zero_is_none", rng.normal(size=(3, 1, 257)), 0.0)
+    add("neg_th", rng.normal(size=(3, 1, 257)), -0.25)
+    x = rng.normal(size=(4, 1, 300)).astype(np.float32)
+    x[0, 0, 17] = np.nan; x[1, 0, 40] = np.inf; x[2, 0, 5] = -np.inf; x[3, 0, 299] = np.nan; x[3, 0, 100] = np.inf
+    add("nonfinite_th", x, 0.5)
+    add("nonfinite_none", x, None)
+    add("noise_th", rng.normal(size=(16, 1, 4096)), 1.0)
+    add("noise_none", rng.normal(size=(16, 1, 4096)), None)
+    add("noise_win4", rng.normal(size=(5, 1, 1000)), 0.3, win=4, r=1)
+    add("noise_win1", rng.normal(size=(5, 1, 333)), 0.3, win=1, r=2)
+    add("noise_win63", rng.normal(size=(5, 1, 777)), 0.1, win=63, r=10)
+    add("short_row", rng.normal(size=(4, 1, 7)), 0.1)
+    x = np.abs(rng.normal(size=(6, 1, 2048))); x[2] = 0; x[4] = -x[4]
+    add("mixed_rows_th", x, 1.5)
+    add("mixed_rows_none", x, None)
+    # plateaus and quantised values: many exact ties
+    add("quantised_th", np.round(rng.normal(size=(8, 1, 1500)) * 2) / 2, 0.5)
+    add("quantised_none", np.round(rng.normal(size=(8, 1, 1500)) * 2) / 2, None)
+    cases["names"] = np.array(names)
+    np.savez_compressed(os.path.join(HERE, "peaks_cases.npz"), **cases)
+    print("peaks cases:", len(names))
+
+
+def gen_metrics_cases():
+    rng = np.random.default_rng(21)
+    out = {}
+    # toa_rmse (utils/metrics.py:9-41): etol compares with the SQUARED distance
+    gt = rng.uniform(10, 500, size=(6, 4)).astype(np.float32)
+    gt[1, 2:] = 0; gt[3, :] = 0; gt[4, 1] = np.nan
+    es = gt + rng.normal(0, 0.8, size=gt.shape).astype(np.float32)
+    es = np.concatenate([es, rng.uniform(10, 500, size=(6, 2)).astype(np.float32)], axis=1)
+    es[2, :] = 0; es[5, 4] = np.inf
+    for tol in (1.0, 0.25, 4.0):
+        r = toa_rmse(torch.from_numpy(gt.copy()), torch.from_numpy(es.copy()), tol=tol)
+        out["rmse_tol%s" % th_key(tol)] = r.numpy()
+    out["rmse_gt"] = gt; out["rmse_es"] = es
+    # coords2mask (utils/mask2samples.py:139-148)
+    ref = torch.zeros((3, 1, 64))
+    samples = torch.tensor([[[5, 9, 0]], [[-3, 63, 63]], [[0, 0, 0]]], dtype=torch.long)
+    out["c2m_samples"] = samples.numpy().copy()
+    out["c2m_mask"] = coords2mask(samples.clone(), ref).numpy()
+    # find_threshold (utils/threshold.py:6-28): row 0 only
+    pred = torch.from_numpy(rng.normal(size=(2, 1, 512)).astype(np.float32))
+    true = torch.zeros((2, 1, 512)); true[0, 0, [40, 200, 333]] = 1; true[1, 0, [5]] = 1
+    pred[0, 0, [40, 200, 333]] += 3
+    out["ft_pred"] = pred.numpy(); out["ft_true"] = true.numpy()
+    out["ft_th"] = np.float64(find_threshold(pred, true, 20))
+    out["ft_th_norm"] = np.float64(find_threshold(pred, true, 20, norm_opt=True))
+    # SampleShuffle1D (utils/sample_shuffle.py:10-28)
+    x = torch.arange(2 * 8 * 5, dtype=torch.float32).reshape(2, 8, 5)
+    out["shuffle_x"] = x.numpy()
+    out["shuffle_r4"] = SampleShuffle1D(4)(x).numpy()
+    out["shuffle_r2"] = SampleShuffle1D(2)(x).numpy()
+    np.savez_compressed(os.path.join(HERE, "metrics_cases.npz"), **out)
+
+
+if __name__ == "__main__":
+    gen_forward()
+    gen_peaks_cases()
+    gen_metrics_cases()
+    print("done")

@@ -1,0 +1,125 @@
+"""Pin the CPU oracle (oracle/) against the reference's own outputs (tests/golden/*.npz)."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import STOF_CKPTS, ESPCN_CKPTS, th_key, th_list
+from oracle import c_oracle, torch_port
+
+
+@pytest.mark.parametrize("name", STOF_CKPTS)
+def test_c_forward_matches_reference(golden, name):
+    sd = golden("weights_%s.npz" % name)
+    g = golden("forward_%s.npz" % name)
+    W = c_oracle.pack_weights(sd)
+    for ci, (N, L, seed) in enumerate(g["cases"]):
+        if L > 3000 and ci != 2:
+            continue
+        x = g["c%d_x" % ci]
+        m = c_oracle.forward(W, x, acc64=True)
+        ref64 = g["c%d_mask64" % ci]
+        ref32 = g["c%d_mask" % ci]
+        scale = np.abs(ref64).max()
+        # double-accumulating C restatement vs the reference run in fp64: fp32 storage noise only
+        assert np.abs(m - ref64).max() <= 2e-5 * scale
+        assert np.abs(m - ref32).max() <= 1e-5 * scale + np.abs(ref32 - ref64).max() * 2
+        # the detections the reference makes on its own mask are reproduced on the oracle's mask
+        for th in th_list(g):
+            idx, _ = c_oracle.get_maxima_positions(m, 20, th)
+            assert np.array_equal(idx, g["c%d_idx_%s" % (ci, th_key(th))]), (name, ci, th)
+
+
+@pytest.mark.parametrize("name", STOF_CKPTS)
+def test_c_forward_fp32_accumulate(golden, name):
+    sd = golden("weights_%s.npz" % name)
+    g = golden("forward_%s.npz" % name)
+    x = g["c0_x"]
+    m = c_oracle.forward(sd, x, acc64=False)
+    ref = g["c0_mask"]
+    assert np.abs(m - ref).max() <= 2e-5 * np.abs(ref).max()
+
+
+@pytest.mark.parametrize("name", STOF_CKPTS)
+def test_torch_port_is_bitwise_reference(golden, name):
+    sd = torch_port.to_torch_sd(golden("weights_%s.npz" % name))
+    g = golden("forward_%s.npz" % name)
+    for ci, (N, L, seed) in enumerate(g["cases"]):
+        x = torch.from_numpy(g["c%d_x" % ci]).unsqueeze(1)
+        with torch.no_grad():
+            m = torch_port.stofnet_forward(sd, x)
+        ref = torch.from_numpy(g["c%d_mask" % ci])
+        # same ATen kernels in the same order; thread-count dependent blocking may differ in the last bits
+        assert (m.squeeze(1) - ref).abs().max() <= 2e-5 * ref.abs().max()
+        for th in th_list(g):
+            co = torch_port.mask2coords(ref.unsqueeze(1), 20, th, 4)
+            assert np.array_equal(co.numpy(), g["c%d_coords_%s" % (ci, th_key(th))])
+            idx = torch_port.get_maxima_positions(ref.unsqueeze(1), 20, th)
+            assert np.array_equal(idx.numpy(), g["c%d_idx_%s" % (ci, th_key(th))])
+
+
+@pytest.mark.parametrize("name", ESPCN_CKPTS)
+def test_espcn_oracles(golden, name):
+    sd = golden("weights_%s.npz" % name)
+    g = golden("espcn_%s.npz" % name)
+    tsd = torch_port.to_torch_sd(sd)
+    for ci, (N, L, seed) in enumerate(g["cases"]):
+        x = g["c%d_x" % ci]
+        ref = g["c%d_mask" % ci]
+        m = c_oracle.espcn_forward(sd, x)
+        assert np.abs(m - ref).max() <= 5e-6      # sigmoid output in (0,1); tanhf/expf libm vs ATen vectorised
+        with torch.no_grad():
+            mt = torch_port.espcn_forward(tsd, torch.from_numpy(x).unsqueeze(1)).squeeze(1).numpy()
+        assert np.abs(mt - ref).max() <= 1e-6
+
+
+def test_stage4_bit_exact_on_reference_masks(golden):
+    """Stage 4 involves no rounding: oracle indices/coords must equal the reference's exactly."""
+    for name in STOF_CKPTS:
+        g = golden("forward_%s.npz" % name)
+        for ci in range(len(g["cases"])):
+            ref = g["c%d_mask" % ci]
+            for th in th_list(g):
+                idx, counts = c_oracle.get_maxima_positions(ref, 20, th)
+                assert np.array_equal(idx, g["c%d_idx_%s" % (ci, th_key(th))])
+                co = c_oracle.mask2coords(ref[:, None, :], 20, th, 4)
+                gc = g["c%d_coords_%s" % (ci, th_key(th))]
+                assert co.shape == gc.shape and np.array_equal(co, gc)
+
+
+def test_stage4_edge_cases(golden):
+    g = golden("peaks_cases.npz")
+    for name in g["names"]:
+        s = g[name + "_scores"]
+        th = float(g[name + "_th"])
+        th = None if np.isnan(th) else th
+        win, r = int(g[name + "_win"]), int(g[name + "_r"])
+        nms = c_oracle.nms_1d(s, win)
+        assert np.array_equal(nms, g[name + "_nms"], equal_nan=True), name
+        idx, _ = c_oracle.get_maxima_positions(s, win, th)
+        assert np.array_equal(idx, g[name + "_idx"]), name
+        co = c_oracle.mask2coords(s, win, th, r)
+        assert co.shape == g[name + "_coords"].shape, name
+        assert np.array_equal(co, g[name + "_coords"]), name
+        ts = torch.from_numpy(s)
+        assert np.array_equal(torch_port.mask2coords(ts, win, th, r).numpy(), g[name + "_coords"]), name
+
+
+def test_bad_lengths_raise(golden):
+    sd = golden("weights_different-armadillo.npz")
+    for L in (79, 161, 1001):
+        with pytest.raises(RuntimeError):
+            c_oracle.forward(sd, np.zeros((1, L), np.float32))
+    # without the semi-global block any length works (reference: no pooling constraint)
+    sd2 = golden("weights_clean-serenity.npz")
+    assert c_oracle.forward(sd2, np.zeros((1, 37), np.float32)).shape == (1, 148)
+
+
+def test_aux_ops(golden):
+    g = golden("metrics_cases.npz")
+    assert np.array_equal(c_oracle.sample_shuffle(g["shuffle_x"], 4), g["shuffle_r4"])
+    assert np.array_equal(c_oracle.sample_shuffle(g["shuffle_x"], 2), g["shuffle_r2"])
+    assert np.array_equal(c_oracle.coords2mask(g["c2m_samples"], 64), g["c2m_mask"])
+    for tol in (1.0, 0.25, 4.0):
+        ref = g["rmse_tol%s" % th_key(tol)]
+        out = c_oracle.toa_rmse(g["rmse_gt"], g["rmse_es"], tol)
+        assert np.allclose(out, ref, rtol=1e-5, atol=1e-6, equal_nan=True), tol
