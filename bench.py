@@ -1,0 +1,317 @@
+#!/usr/bin/env python
+"""bench.py - echo waveforms/s of the StofNet inference path (forward + ToF extraction) on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Contract (see the task statement): one JSON line on rank 0.  A "step" is one pass of the hot path
+over one batch of synthetic waveforms: StofNet.forward (conv stack + semi-global block + sub-pixel
+shuffle) followed by mask2coords (NMS + threshold + ToF table).
+
+Workload (config.workload): BASELINE.json configs[1] - StofNet rf_scale_factor=20, 4096 waveforms of
+L = 5120 samples per GPU, checkpoint graceful-snow-1553 (the StofNet rf-scale-20 checkpoint; the
+literally named wobbly-sponge file is an ESPCN_1D checkpoint), th = 0.015,
+nms_win_size = 20.  Rows are independent, so N GPUs each process their own 4096 rows (weak scaling)
+and the only collective is the final ToF gather (max-reduce of K_max + all_gather of the table).
+
+  value     waveforms/s, all ranks, inputs resident in HBM (device timed, max over ranks)
+  e2e       same metric through the host-buffer C-ABI call stof_infer_host: pinned host input,
+            H2D + forward + peaks + D2H of the ToF table inside the timed region
+  roofline  dominant kernel (conv2..conv12 class, 65 % of the FLOPs): algorithmic FLOPs per launch /
+            mean launch duration from CUDA events recorded on the launch stream inside the timed steps
+  cpu_baseline  the oracle's torch-CPU port of the reference path on this box's host cores
+            (bounded row sample)
+
+--impl reference times that CPU port alone, all host threads, on a bounded sample per step.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np
+import torch
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+CKPT = "graceful-snow"
+ROWS, L, RF, TH, WIN, R = 4096, 5120, 20, 0.015, 20, 4
+CAP = 128
+# algorithmic work per row: MACs = 480,576 L + 163,840 floor(L/80)
+FLOP_PER_ROW = 2.0 * (480576 * L + 163840 * (L // 80))
+MID_FLOP_PER_POS = 2.0 * 64 * 64 * 7         # one conv2..conv12 layer, per position
+
+
+def peaks_file():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f), "measured"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        self.t.join(timeout=2)
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 7 and r[3 + i].lower().startswith("active")
+                                                         for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": reasons}
+
+
+def load_sd():
+    with np.load(os.path.join(GOLD, "weights_%s.npz" % CKPT)) as z:
+        return {k: torch.from_numpy(np.ascontiguousarray(z[k])) for k in z.files}
+
+
+def make_inputs(n_unique, seed):
+    """(n_unique, L) base rows from the seeded numpy generator; batches are built by tiling + per-row
+    gain so that every row differs (data: synthetic)."""
+    from stofnet_b200.synth import synth_waveforms
+    return torch.from_numpy(synth_waveforms(n_unique, L, seed=seed, rf=RF))
+
+
+def expand_batch(base, rows, shift):
+    reps = (rows + base.shape[0] - 1) // base.shape[0]
+    x = base.repeat(reps, 1)[:rows].clone()
+    x = torch.roll(x, shifts=shift, dims=0)
+    return x
+
+
+def cpu_port_rate(sd, rows, repeats, threads):
+    """waveforms/s of the oracle's torch-CPU port (forward + mask2coords) on `rows` rows."""
+    from oracle import torch_port
+    torch.set_num_threads(threads)
+    x = make_inputs(rows, 11).unsqueeze(1)
+    torch_port.infer(sd, x[:max(1, rows // 4)], WIN, TH)       # warm-up
+    ts = []
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        torch_port.infer(sd, x, WIN, TH)
+        ts.append(time.perf_counter() - t0)
+    return rows / float(np.median(ts)), float(np.median(ts))
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    sd = load_sd()
+    threads = os.cpu_count() or 1
+    rows = 64
+    torch.set_num_threads(threads)
+    from oracle import torch_port
+    x = make_inputs(rows, 11).unsqueeze(1)
+    for _ in range(max(1, args.warmup)):
+        torch_port.infer(sd, x[:16], WIN, TH)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        torch_port.infer(sd, x, WIN, TH)
+    dt = time.perf_counter() - t0
+    val = rows * args.steps / dt
+    line = {
+        "impl": "reference", "metric": "echo waveforms/sec", "value": val, "unit": "waveforms/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args.gpus),
+        "cpu_baseline": {"value": val, "unit": "waveforms/s", "cores": threads, "kind": "port",
+                         "sample": "%d rows of L=%d per step (forward + mask2coords), torch %s CPU, oracle/torch_port.py"
+                                   % (rows, L, torch.__version__)},
+        "e2e": {"value": val, "unit": "waveforms/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+def workload_config(gpus):
+    return {"workload": "StofNet rf_scale_factor=20 inference (forward + mask2coords), ckpt graceful-snow-1553, "
+                        "%d waveforms x L=%d per GPU, th=%g, nms_win_size=%d, upsample_factor=%d"
+                        % (ROWS, L, TH, WIN, R),
+            "rows_per_gpu": ROWS, "L": L, "rf_scale_factor": RF, "th": TH, "parallelism": "rows sharded x%d" % gpus,
+            "l2": "3 distinct input batches rotated (252 MB) and >1 GiB of activations per chunk: working set >> 126 MB L2"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch.distributed as dist
+    import stofnet_b200 as sb
+    from stofnet_b200._lib import lib, check, PROF_CLASSES, PROF_NAMES
+    from stofnet_b200.engine import stream_ptr
+
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU path)"
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    sd = load_sd()
+    model = sb.build_model(sd, dev)
+    eng = model._engine
+    base = make_inputs(256, 3008 + rank)
+    batches_host = [expand_batch(base, ROWS, s).pin_memory() for s in (0, 7, 13)]
+    batches_dev = [b.to(dev).unsqueeze(1).contiguous() for b in batches_host]
+
+    coords = torch.empty((ROWS, CAP), dtype=torch.float32, device=dev)
+    counts = torch.empty((ROWS,), dtype=torch.int32, device=dev)
+    stats = torch.zeros((2,), dtype=torch.int64, device=dev)
+    gathered = torch.empty((world * ROWS, CAP), dtype=torch.float32, device=dev) if world > 1 else None
+    kmax_t = torch.zeros((1,), dtype=torch.int64, device=dev)
+
+    def step(i):
+        x = batches_dev[i % len(batches_dev)]
+        mask = eng.forward(model, x)
+        stats.zero_()
+        check(lib.stof_peaks(mask.data_ptr(), ROWS, R * L, WIN, 0, TH, R, coords.data_ptr(), None, CAP,
+                             counts.data_ptr(), stats.data_ptr(), stream_ptr(dev)))
+        if world > 1:     # final ToF gather: global K_max + fixed-stride table (north_star)
+            kmax_t.copy_(stats[:1])
+            dist.all_reduce(kmax_t, op=dist.ReduceOp.MAX)
+            dist.all_gather_into_tensor(gathered, coords)
+        return mask
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with torch.no_grad():
+        for i in range(args.warmup):
+            step(i)
+        barrier()
+        check(lib.stof_profile_enable(eng.handle, 1))
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+        l0 = lib.stof_launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        for i in range(args.steps):
+            step(args.warmup + i)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        launches = lib.stof_launch_count() - l0
+        prof_ms = (C.c_double * PROF_CLASSES)()
+        prof_n = (C.c_int64 * PROF_CLASSES)()
+        check(lib.stof_profile_collect(eng.handle, prof_ms, prof_n))
+        check(lib.stof_profile_enable(eng.handle, 0))
+
+        # ---- e2e: host buffers through stof_infer_host (H2D + forward + peaks + D2H inside the timing)
+        coords_h = torch.empty((ROWS, CAP), dtype=torch.float32).pin_memory()
+        counts_h = torch.empty((ROWS,), dtype=torch.int32).pin_memory()
+        kmax = C.c_int(0)
+
+        def e2e_step(i):
+            xh = batches_host[i % len(batches_host)]
+            check(lib.stof_infer_host(eng.handle, xh.data_ptr(), ROWS, L, WIN, 0, TH, coords_h.data_ptr(), CAP,
+                                      counts_h.data_ptr(), None, C.byref(kmax)))
+
+        for i in range(max(1, args.warmup - 1)):
+            e2e_step(i)
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(args.steps):
+            e2e_step(i)
+        torch.cuda.synchronize()
+        e2e_s = time.perf_counter() - t0
+        clocks = sampler.stop() if rank == 0 else None
+
+    t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = float(t[0]), float(t[1])
+    value = ROWS * world * args.steps / (ms / 1e3)
+    e2e_val = ROWS * world * args.steps / (e2e_ms / 1e3)
+
+    if rank == 0:
+        peaks, peak_src = peaks_file()
+        mid_n = int(prof_n[4])
+        mid_ms = float(prof_ms[4]) / max(1, mid_n)
+        # positions per conv_mid launch = chunk rows * L; chunk = launches per step / 11 layers
+        chunks_per_step = max(1, mid_n // (11 * args.steps))
+        pos_per_launch = ROWS * L / chunks_per_step
+        achieved_tf = MID_FLOP_PER_POS * pos_per_launch / (mid_ms / 1e3) / 1e12 if mid_n else 0.0
+        peak_tf = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops")))
+        share = {PROF_NAMES[c]: round(float(prof_ms[c]) / args.steps, 3) for c in range(PROF_CLASSES) if prof_n[c]}
+        line = {
+            "metric": "echo waveforms/sec", "value": value, "unit": "waveforms/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": workload_config(world),
+            "e2e": {"value": e2e_val, "unit": "waveforms/s", "h2d_bytes_per_step": ROWS * L * 4,
+                    "d2h_bytes_per_step": ROWS * CAP * 4 + ROWS * 4 + 16, "ms_per_step": e2e_ms / args.steps},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "tensor", "kernel": "conv_mid (conv2..conv12, 64->64 k7; fp32 FFMA kernel this round)",
+                         "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
+                         "frac": achieved_tf / peak_tf if peak_tf else None, "traffic": None,
+                         "peak_source": "%s bf16 sustained (MEASURED_PEAKS.json); tf32 peak not measured" % peak_src,
+                         "launch_ms": mid_ms, "launches": mid_n,
+                         "algorithmic_flops_per_launch": MID_FLOP_PER_POS * pos_per_launch},
+            "kernel_ms_per_step": share,
+            "algorithmic_tflops": FLOP_PER_ROW * value / 1e12,
+        }
+        if not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            rows = 64
+            rate, med = cpu_port_rate(sd, rows, 3, threads)
+            line["cpu_baseline"] = {"value": rate, "unit": "waveforms/s", "cores": threads, "kind": "port",
+                                    "sample": "%d rows of L=%d, forward + mask2coords, median of 3 (%.2f s each), "
+                                              "torch %s CPU via oracle/torch_port.py" % (rows, L, med, torch.__version__)}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

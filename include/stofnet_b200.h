@@ -1,0 +1,145 @@
+/*
+ * stofnet_b200.h - C ABI of the B200-native StofNet echo-waveform inference path.
+ *
+ * Drop-in boundary for ONE hot path of hahnec/stofnet: StofNet.forward -> sub-pixel shuffle ->
+ * NMS / threshold / time-of-flight extraction.  The reference is pure Python on PyTorch and has
+ * no FFI of its own; each entry point below names the reference call site it replaces (paths
+ * relative to the reference repository root).  INTEGRATION.md shows the ctypes stub a maintainer
+ * of the reference would add.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; `stream` is a cudaStream_t passed as void* (NULL = default)
+ *   - *_dev pointers are device memory owned by the caller (e.g. torch's caching allocator);
+ *     *_host pointers are host memory (pinned recommended)
+ *   - every call is asynchronous on `stream` unless stated otherwise
+ *   - returns 0 on success, a negative STOF_E_* code otherwise; stof_last_error() gives the text
+ *   - there is no CPU fallback: without a CUDA device every compute call returns STOF_E_CUDA
+ *   - a model handle is not thread-safe; use one handle per device / stream
+ */
+#ifndef STOFNET_B200_H
+#define STOFNET_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define STOF_OK            0
+#define STOF_E_INVALID    -1   /* bad argument (null pointer, non-positive size, unsupported shape) */
+#define STOF_E_LENGTH     -2   /* L < scale: pooled length would be 0 (torch raises in max_pool1d; models/stofnet.py:91) */
+#define STOF_E_LENGTH_ODD -3   /* (L mod scale) odd: reference fails at torch.add (models/stofnet.py:111-115) */
+#define STOF_E_WORKSPACE  -4   /* workspace too small */
+#define STOF_E_CUDA       -5   /* CUDA runtime error (text in stof_last_error) */
+#define STOF_E_NCCL       -6   /* reserved: collective error */
+#define STOF_E_UNSUPPORTED -7  /* architecture of the checkpoint not supported by the kernels */
+
+#define STOF_MAX_MID_CONVS 16
+
+/* Model kinds */
+#define STOF_KIND_STOFNET 0    /* models/stofnet.py  */
+#define STOF_KIND_ESPCN   1    /* models/espcn_1d.py */
+
+/* Host-side description of a checkpoint: fp32 tensors in PyTorch's (Cout, Cin, K) layout exactly
+ * as stored in the reference's .pth state_dict (main.py:174-177).  Pointers are host memory and
+ * are only read during stof_model_create / stof_model_set_weights.                              */
+typedef struct stof_weights {
+    int kind;                   /* STOF_KIND_* */
+    /* StofNet (models/stofnet.py:11-40) */
+    const float *conv1_w, *conv1_b;                 /* (F,1,9), (F)            :23 */
+    int n_mid;                                      /* num_blocks-2 = 11 convs: conv2..conv12 */
+    const float *mid_w[STOF_MAX_MID_CONVS];         /* (F,F,7)                 :30-31 */
+    const float *mid_b[STOF_MAX_MID_CONVS];
+    const float *last_w, *last_b;                   /* (r,F,3), (r)            :24 */
+    const float *contract_w, *contract_b;           /* (8F,F,5) or NULL        :88 */
+    const float *expand_w, *expand_b;               /* (F,8F,5) or NULL        :94 */
+    int num_features;                               /* F = 64 */
+    int upsample_factor;                            /* r = conv_last.out_channels (4); NOT rf_scale_factor */
+    int k_first, k_mid, k_last;                     /* 9, 7, 3 */
+    int sgb_scale, sgb_feat, sgb_k;                 /* 80, 512, 5 ; sgb_scale = 1 when no semi-global block (:27) */
+    /* ESPCN_1D (models/espcn_1d.py:12-14): conv1 (64,1,5) -> conv1_w/b, conv2 (32,64,3) -> mid_w[0]/mid_b[0],
+     * conv3 (r,32,3) -> last_w/b */
+} stof_weights;
+
+typedef struct stof_model stof_model;   /* opaque: device-resident repacked weights */
+
+/* Library / device probes (no GPU work) */
+const char *stof_version(void);
+const char *stof_last_error(void);
+int stof_device_count(void);            /* 0 when no CUDA device is visible */
+
+/* Replaces StofNet(...).to(device) + load_state_dict (main.py:133-134,173-177).  Synchronous. */
+int stof_model_create(const stof_weights *w, int device, stof_model **out);
+/* Re-upload weights into an existing handle (after an optimizer step).  Synchronous. */
+int stof_model_set_weights(stof_model *m, const stof_weights *w);
+void stof_model_destroy(stof_model *m);
+
+/* Rows processed per internal chunk and the workspace this needs.  chunk_rows <= 0 picks a default. */
+int stof_forward_workspace_bytes(const stof_model *m, int N, int L, int chunk_rows, size_t *bytes);
+
+/* Replaces `masks_pred = model(frame)` (main.py:221,314; models/stofnet.py:42-67 incl. the
+ * SampleShuffle1D of utils/sample_shuffle.py:10-28 fused into the last conv's store).
+ *   x_dev    (N, 1, L) fp32 contiguous
+ *   mask_dev (N, 1, r*L) fp32 contiguous
+ *   ws_dev   workspace of at least stof_forward_workspace_bytes(...) bytes                     */
+int stof_forward(stof_model *m, const float *x_dev, int N, int L, float *mask_dev,
+                 void *ws_dev, size_t ws_bytes, int chunk_rows, void *stream);
+
+/* Replaces utils/mask2samples.py: nms_1d (:5-11) + thresholding (:14-23) + torch.nonzero (:32) +
+ * bincount / ragged pack / divide by upsample_factor of mask2coords (:92-112).
+ *   scores_dev (N, M) fp32 contiguous (M = r*L)
+ *   window      nms window (made odd like the reference: window/2*2+1)
+ *   th_is_none  1 = "threshold is None or 0.0" branch (keep entries equal to the row max)
+ *   coords_dev (N, cap) fp32 or NULL: ascending position / upsample_factor, zero padded
+ *   pos_dev    (N, cap) int32 or NULL: ascending integer positions, -1 padded
+ *   counts_dev (N) int32: detections per row (may exceed cap: caller re-runs with a larger cap)
+ *   stats_dev  (2) int64: [0] = max_k counts_k (K_max, :93), [1] = total detections K; must be
+ *               zeroed by the caller before the call                                            */
+int stof_peaks(const float *scores_dev, int N, int M, int window, int th_is_none, float th,
+               int upsample_factor, float *coords_dev, int32_t *pos_dev, int cap,
+               int32_t *counts_dev, int64_t *stats_dev, void *stream);
+
+/* (K,2) int64 [row, position] list of get_maxima_positions (utils/mask2samples.py:26-34) from the
+ * per-row output of stof_peaks.  offsets_dev (N) int64 scratch.  K = stats[1].                   */
+int stof_peaks_indices(const int32_t *pos_dev, const int32_t *counts_dev, int N, int cap,
+                       int64_t *offsets_dev, int64_t *idx_dev, void *stream);
+
+/* Replaces nms_1d alone (utils/mask2samples.py:5-11): out = (s == window_max(s)) * s. */
+int stof_nms_1d(const float *scores_dev, int N, int M, int window, float *out_dev, void *stream);
+
+/* End-to-end call with HOST buffers: the reference's eval step `model(frame)` + `mask2coords`
+ * (main.py:307-320) including the host->device copy of the waveforms and the device->host copy
+ * of the time-of-flight table.  Synchronous; rows are pipelined in chunks over internal streams.
+ *   x_host (N, L) fp32; coords_host (N, cap) fp32; counts_host (N) int32; mask_host (N, r*L) or NULL
+ *   kmax_out: max detections in any row (if > cap the table is truncated: re-run with cap >= kmax) */
+int stof_infer_host(stof_model *m, const float *x_host, int N, int L, int window, int th_is_none,
+                    float th, float *coords_host, int cap, int32_t *counts_host, float *mask_host,
+                    int *kmax_out);
+
+/* SampleShuffle1D.forward (utils/sample_shuffle.py:10-28) as a standalone operator:
+ * x (B, r*Cl, W) -> out (B, Cl, r*W), out[b,c,w*r+u] = x[b,u*Cl+c,w].                           */
+int stof_sample_shuffle(const float *x_dev, int B, int Cs, int W, int r, float *out_dev, void *stream);
+
+/* Per-kernel-class device timing for bench.py's roofline: when enabled, stof_forward /
+ * stof_infer_host record a CUDA-event pair on the launch stream around every kernel launch;
+ * stof_profile_collect waits for them and returns summed milliseconds and launch counts per class.
+ * (The reference has only a host process_time() pair around model(frame), main.py:313-315.)      */
+#define STOF_PROF_FIRST    0   /* conv1 + ReLU */
+#define STOF_PROF_CONTRACT 1   /* contract conv + LeakyReLU + max-pool */
+#define STOF_PROF_EXPAND   2   /* expand conv + LeakyReLU */
+#define STOF_PROF_SGB_ADD  3   /* nearest upsample + pad + skip add */
+#define STOF_PROF_MID      4   /* conv2..conv12 */
+#define STOF_PROF_LAST     5   /* conv_last + sample shuffle */
+#define STOF_PROF_PEAKS    6   /* nms + threshold + compaction (stof_infer_host only) */
+#define STOF_PROF_CLASSES  8
+int stof_profile_enable(stof_model *m, int on);
+int stof_profile_collect(stof_model *m, double *ms_by_class, int64_t *launches_by_class);
+
+/* Counter of kernels launched by this library since load (bench.py's gpu_launches). */
+uint64_t stof_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* STOFNET_B200_H */

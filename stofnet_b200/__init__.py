@@ -1,0 +1,15 @@
+"""stofnet_b200 - B200-native (sm_100a) StofNet echo-waveform inference path.
+
+Drop-in for the hot path of hahnec/stofnet: ``models.stofnet.StofNet`` forward, the sub-pixel
+shuffle, and ``utils.mask2samples`` time-of-flight extraction, behind the reference's own Python
+surface (same module / class / function names and signatures).  All compute runs in hand-written
+CUDA kernels reached through the C ABI of ``libstofnet_b200.so`` (include/stofnet_b200.h).
+"""
+from .models.stofnet import StofNet, SemiGlobalBlock          # noqa: F401
+from .models.espcn_1d import ESPCN_1D                          # noqa: F401
+from .utils.sample_shuffle import SampleShuffle1D              # noqa: F401
+from .utils.mask2samples import (mask2coords, get_maxima_positions, nms_1d, thresholding,  # noqa: F401
+                                 coords2mask)
+from .checkpoint import load_checkpoint, load_config, build_model  # noqa: F401
+
+__version__ = "0.1"

@@ -1,0 +1,420 @@
+// C ABI of libstofnet_b200.so: model handle, weight repack, forward orchestration, host-buffer
+// end-to-end call.  See include/stofnet_b200.h for the contract of every entry point.
+#include <stdarg.h>
+#include <stdlib.h>
+#include <string.h>
+#include <vector>
+
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace stof {
+
+static thread_local char g_err[512] = "";
+std::atomic<unsigned long long> g_launches{0};
+
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char *what, const char *file, int line) {
+    set_error("CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), file, line, what);
+    return STOF_E_CUDA;
+}
+
+// Device-resident weights in the layouts the kernels read (all fp32):
+//   first : [K][64]            w[t][co]        = W[co][0][t]
+//   mid   : [64][K][64]        w[ci][t][co]    = W[co][ci][t]          (conv2..conv12, contract tiles)
+//   expand: [512][5][64]       w[ci][t][co]
+//   last  : [CIN][3][4]        w[ci][t][u]     = W[u][ci][t]
+struct DevConv {
+    float *w = nullptr;
+    float *b = nullptr;
+};
+
+}  // namespace stof
+
+struct stof_model {
+    int device = 0;
+    int kind = STOF_KIND_STOFNET;
+    int F = 64, r = 4, n_mid = 0;
+    int k_first = 9, k_mid = 7, k_last = 3;
+    int sgb_scale = 1, sgb_feat = 0, sgb_k = 0;
+    stof::DevConv first, last, contract, expand;
+    stof::DevConv mid[STOF_MAX_MID_CONVS];
+    // scratch of stof_infer_host (grow-only)
+    static constexpr int kPipe = 2;
+    cudaStream_t streams[kPipe] = {nullptr, nullptr};
+    void *scratch[kPipe] = {nullptr, nullptr};
+    size_t scratch_bytes[kPipe] = {0, 0};
+    int64_t *h_stats = nullptr;   // pinned, kPipe * 2
+    // optional per-kernel-class CUDA-event timing (stof_profile_*): pairs recorded on the launch stream
+    bool profiling = false;
+    std::vector<cudaEvent_t> ev_pool;                 // start/stop pairs
+    std::vector<int> ev_class;                        // class of pair i
+    size_t ev_used = 0;
+};
+
+namespace stof {
+
+static int upload(DevConv &c, const std::vector<float> &w, const float *b, int nb) {
+    if (!c.w) STOF_CUDA(cudaMalloc(&c.w, w.size() * sizeof(float)));
+    if (!c.b) STOF_CUDA(cudaMalloc(&c.b, (size_t)nb * sizeof(float)));
+    STOF_CUDA(cudaMemcpy(c.w, w.data(), w.size() * sizeof(float), cudaMemcpyHostToDevice));
+    STOF_CUDA(cudaMemcpy(c.b, b, (size_t)nb * sizeof(float), cudaMemcpyHostToDevice));
+    return STOF_OK;
+}
+
+// (Cout, Cin, K) -> [Cin][K][Cout]
+static std::vector<float> repack_cikco(const float *w, int Cout, int Cin, int K) {
+    std::vector<float> o((size_t)Cout * Cin * K);
+    for (int co = 0; co < Cout; ++co)
+        for (int ci = 0; ci < Cin; ++ci)
+            for (int t = 0; t < K; ++t) o[((size_t)ci * K + t) * Cout + co] = w[((size_t)co * Cin + ci) * K + t];
+    return o;
+}
+
+static int validate(const stof_weights *w) {
+    STOF_REQUIRE(w != nullptr, STOF_E_INVALID, "weights: NULL");
+    STOF_REQUIRE(w->conv1_w && w->conv1_b && w->last_w && w->last_b, STOF_E_INVALID, "weights: missing conv1/conv_last");
+    if (w->kind == STOF_KIND_STOFNET) {
+        STOF_REQUIRE(w->num_features == 64 && w->upsample_factor == 4 && w->k_first == 9 && w->k_mid == 7 && w->k_last == 3,
+                     STOF_E_UNSUPPORTED, "StofNet kernels are built for F=64, r=4, kernel_sizes=[9,7,3] (got F=%d r=%d k=%d,%d,%d)",
+                     w->num_features, w->upsample_factor, w->k_first, w->k_mid, w->k_last);
+        STOF_REQUIRE(w->n_mid >= 3 && w->n_mid <= STOF_MAX_MID_CONVS && (w->n_mid % 2) == 1, STOF_E_UNSUPPORTED,
+                     "StofNet: n_mid=%d (num_blocks-2) must be odd and in [3,%d]", w->n_mid, STOF_MAX_MID_CONVS);
+        for (int i = 0; i < w->n_mid; ++i)
+            STOF_REQUIRE(w->mid_w[i] && w->mid_b[i], STOF_E_INVALID, "weights: conv%d missing", i + 2);
+        if (w->contract_w) {
+            STOF_REQUIRE(w->contract_b && w->expand_w && w->expand_b, STOF_E_INVALID, "weights: incomplete semi-global block");
+            STOF_REQUIRE(w->sgb_scale == 80 && w->sgb_feat == 512 && w->sgb_k == 5, STOF_E_UNSUPPORTED,
+                         "semi-global block kernels are built for scale=80, 512 features, k=5 (got %d, %d, %d)",
+                         w->sgb_scale, w->sgb_feat, w->sgb_k);
+        }
+    } else if (w->kind == STOF_KIND_ESPCN) {
+        STOF_REQUIRE(w->upsample_factor == 4 && w->mid_w[0] && w->mid_b[0], STOF_E_UNSUPPORTED,
+                     "ESPCN_1D kernels are built for upscale_factor=4");
+    } else {
+        STOF_REQUIRE(false, STOF_E_INVALID, "weights: unknown kind %d", w->kind);
+    }
+    return STOF_OK;
+}
+
+static int set_weights(stof_model *m, const stof_weights *w) {
+    int rc = validate(w);
+    if (rc) return rc;
+    STOF_CUDA(cudaSetDevice(m->device));
+    m->kind = w->kind;
+    m->r = w->upsample_factor;
+    if (w->kind == STOF_KIND_ESPCN) {
+        m->F = 64; m->n_mid = 1; m->k_first = 5; m->k_mid = 3; m->k_last = 3; m->sgb_scale = 1;
+        if ((rc = upload(m->first, repack_cikco(w->conv1_w, 64, 1, 5), w->conv1_b, 64))) return rc;
+        if ((rc = upload(m->mid[0], repack_cikco(w->mid_w[0], 32, 64, 3), w->mid_b[0], 32))) return rc;
+        if ((rc = upload(m->last, repack_cikco(w->last_w, 4, 32, 3), w->last_b, 4))) return rc;
+        return STOF_OK;
+    }
+    m->F = w->num_features; m->n_mid = w->n_mid;
+    m->k_first = w->k_first; m->k_mid = w->k_mid; m->k_last = w->k_last;
+    if ((rc = upload(m->first, repack_cikco(w->conv1_w, 64, 1, 9), w->conv1_b, 64))) return rc;
+    for (int i = 0; i < w->n_mid; ++i)
+        if ((rc = upload(m->mid[i], repack_cikco(w->mid_w[i], 64, 64, 7), w->mid_b[i], 64))) return rc;
+    if ((rc = upload(m->last, repack_cikco(w->last_w, 4, 64, 3), w->last_b, 4))) return rc;
+    if (w->contract_w) {
+        m->sgb_scale = w->sgb_scale; m->sgb_feat = w->sgb_feat; m->sgb_k = w->sgb_k;
+        // 8 cout tiles of 64, each [ci][t][co]
+        std::vector<float> cw((size_t)512 * 64 * 5);
+        for (int ct = 0; ct < 8; ++ct) {
+            std::vector<float> t = repack_cikco(w->contract_w + (size_t)ct * 64 * 64 * 5, 64, 64, 5);
+            memcpy(cw.data() + (size_t)ct * 64 * 64 * 5, t.data(), t.size() * sizeof(float));
+        }
+        if ((rc = upload(m->contract, cw, w->contract_b, 512))) return rc;
+        if ((rc = upload(m->expand, repack_cikco(w->expand_w, 64, 512, 5), w->expand_b, 64))) return rc;
+    } else {
+        m->sgb_scale = 1; m->sgb_feat = 0; m->sgb_k = 0;
+    }
+    return STOF_OK;
+}
+
+static void free_conv(DevConv &c) {
+    if (c.w) cudaFree(c.w);
+    if (c.b) cudaFree(c.b);
+    c.w = c.b = nullptr;
+}
+
+// ---- workspace layout of one chunk of rows -----------------------------------------------------
+struct Plan {
+    int chunk;          // rows per chunk
+    int P;              // pooled length
+    size_t act;         // floats per activation buffer (chunk * 64 * L)
+    size_t pooled, e;   // floats
+    size_t total_bytes;
+};
+
+static size_t align256(size_t b) { return (b + 255) & ~(size_t)255; }
+
+static int make_plan(const stof_model *m, int N, int L, int chunk_rows, Plan *p) {
+    STOF_REQUIRE(m != nullptr, STOF_E_INVALID, "model: NULL");
+    STOF_REQUIRE(N > 0 && L > 0, STOF_E_INVALID, "forward: N=%d L=%d must be positive", N, L);
+    const bool sgb = m->kind == STOF_KIND_STOFNET && m->sgb_scale != 1;
+    if (sgb) {
+        STOF_REQUIRE(L >= m->sgb_scale, STOF_E_LENGTH,
+                     "forward: L=%d shorter than the semi-global pooling window %d (reference: max_pool1d output size 0)",
+                     L, m->sgb_scale);
+        STOF_REQUIRE(((L % m->sgb_scale) & 1) == 0, STOF_E_LENGTH_ODD,
+                     "forward: (L mod %d) = %d is odd; the reference pads (p//2, p//2) and fails at torch.add",
+                     m->sgb_scale, L % m->sgb_scale);
+    }
+    int chunk = chunk_rows;
+    if (chunk <= 0) {
+        // default: ~4 Mi positions per chunk (>= 100 CTA tiles per SM-wave several times over, and
+        // 3 activation buffers of 1 GiB each)
+        long long c = (4ll << 20) / L;
+        if (c < 1) c = 1;
+        chunk = (int)c;
+    }
+    if (chunk > N) chunk = N;
+    p->chunk = chunk;
+    p->P = sgb ? L / m->sgb_scale : 0;
+    p->act = (size_t)chunk * 64 * L;
+    p->pooled = sgb ? (size_t)chunk * 512 * p->P : 0;
+    p->e = sgb ? (size_t)chunk * 64 * p->P : 0;
+    p->total_bytes = 3 * align256(p->act * 4) + align256(p->pooled * 4) + align256(p->e * 4);
+    return STOF_OK;
+}
+
+// RAII: records an event pair around the launches issued while it is alive (profiling only)
+struct ProfScope {
+    stof_model *m; cudaStream_t st; size_t slot; bool on;
+    ProfScope(stof_model *m_, int cls, cudaStream_t st_) : m(m_), st(st_), slot(0), on(m_->profiling) {
+        if (!on) return;
+        if (m->ev_used + 2 > m->ev_pool.size()) {
+            cudaEvent_t a, b;
+            if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) { on = false; return; }
+            m->ev_pool.push_back(a); m->ev_pool.push_back(b); m->ev_class.push_back(cls);
+        } else {
+            m->ev_class[m->ev_used / 2] = cls;
+        }
+        slot = m->ev_used; m->ev_used += 2;
+        cudaEventRecord(m->ev_pool[slot], st);
+    }
+    ~ProfScope() { if (on) cudaEventRecord(m->ev_pool[slot + 1], st); }
+};
+
+static int forward_chunk(stof_model *m, const float *x, int n, int L, float *mask, char *ws, const Plan &pl,
+                         cudaStream_t st) {
+    float *B0 = reinterpret_cast<float *>(ws);
+    float *B1 = reinterpret_cast<float *>(ws + align256(pl.act * 4));
+    float *B2 = reinterpret_cast<float *>(ws + 2 * align256(pl.act * 4));
+    float *pooled = reinterpret_cast<float *>(ws + 3 * align256(pl.act * 4));
+    float *e = reinterpret_cast<float *>(ws + 3 * align256(pl.act * 4) + align256(pl.pooled * 4));
+    int rc;
+    if (m->kind == STOF_KIND_ESPCN) {
+        // models/espcn_1d.py:31-36
+        { ProfScope p(m, STOF_PROF_FIRST, st); if ((rc = launch_conv_first(x, n, L, m->first.w, m->first.b, B0, 5, 1, st))) return rc; }
+        { ProfScope p(m, STOF_PROF_MID, st); if ((rc = launch_espcn_conv2(B0, B1, m->mid[0].w, m->mid[0].b, n, L, st))) return rc; }
+        ProfScope p(m, STOF_PROF_LAST, st);
+        return launch_conv_last(B1, mask, m->last.w, m->last.b, n, L, 32, 1, st);
+    }
+    // models/stofnet.py:45
+    { ProfScope p(m, STOF_PROF_FIRST, st); if ((rc = launch_conv_first(x, n, L, m->first.w, m->first.b, B0, 9, 0, st))) return rc; }
+    // :48 semi-global block
+    if (m->sgb_scale != 1) {
+        { ProfScope p(m, STOF_PROF_CONTRACT, st); if ((rc = launch_contract_pool_simt(B0, pooled, m->contract.w, m->contract.b, n, L, pl.P, st))) return rc; }
+        { ProfScope p(m, STOF_PROF_EXPAND, st); if ((rc = launch_expand(pooled, e, m->expand.w, m->expand.b, n, pl.P, st))) return rc; }
+        const int off = (L - pl.P * m->sgb_scale) / 2;
+        { ProfScope p(m, STOF_PROF_SGB_ADD, st); if ((rc = launch_sgb_add(B0, e, n, L, pl.P, m->sgb_scale, off, st))) return rc; }
+    }
+    // :51-58  conv2 .. conv{nb-2}: even index -> LeakyReLU, odd index (>= 3) -> res + conv, res = x
+    const float *cur = B0;     // x
+    const float *res = B0;     // short skip (B0 stays intact as res1, the long skip)
+    for (int i = 2; i <= m->n_mid; ++i) {          // layer index i uses mid[i-2]; last one (i = n_mid+1) below
+        const DevConv &c = m->mid[i - 2];
+        ProfScope p(m, STOF_PROF_MID, st);
+        if (i % 2 == 0) {
+            if ((rc = launch_conv_mid_simt(cur, nullptr, B1, c.w, c.b, n, L, 0, st))) return rc;
+            cur = B1;
+        } else {
+            if ((rc = launch_conv_mid_simt(cur, res, B2, c.w, c.b, n, L, 1, st))) return rc;   // in place on B2 after the first
+            cur = B2; res = B2;
+        }
+    }
+    // :61-62  x = res1 + conv{nb-1}(x)
+    {
+        const DevConv &c = m->mid[m->n_mid - 1];
+        float *dst = (cur == B1) ? B2 : B1;
+        ProfScope p(m, STOF_PROF_MID, st);
+        if ((rc = launch_conv_mid_simt(cur, B0, dst, c.w, c.b, n, L, 1, st))) return rc;
+        cur = dst;
+    }
+    // :65 conv_last + sample shuffle
+    ProfScope p(m, STOF_PROF_LAST, st);
+    return launch_conv_last(cur, mask, m->last.w, m->last.b, n, L, 64, 0, st);
+}
+
+}  // namespace stof
+
+extern "C" const char *stof_version(void) { return "stofnet_b200 0.1 (sm_100a)"; }
+extern "C" const char *stof_last_error(void) { return stof::g_err; }
+extern "C" uint64_t stof_launch_count(void) { return stof::g_launches.load(); }
+
+extern "C" int stof_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+extern "C" int stof_model_create(const stof_weights *w, int device, stof_model **out) {
+    STOF_REQUIRE(out != nullptr, STOF_E_INVALID, "stof_model_create: out is NULL");
+    *out = nullptr;
+    int rc = stof::validate(w);
+    if (rc) return rc;
+    int ndev = 0;
+    STOF_CUDA(cudaGetDeviceCount(&ndev));
+    STOF_REQUIRE(device >= 0 && device < ndev, STOF_E_INVALID, "stof_model_create: device %d of %d", device, ndev);
+    stof_model *m = new stof_model();
+    m->device = device;
+    rc = stof::set_weights(m, w);
+    if (rc) { stof_model_destroy(m); return rc; }
+    *out = m;
+    return STOF_OK;
+}
+
+extern "C" int stof_model_set_weights(stof_model *m, const stof_weights *w) {
+    STOF_REQUIRE(m != nullptr, STOF_E_INVALID, "stof_model_set_weights: model is NULL");
+    STOF_REQUIRE(w != nullptr && w->kind == m->kind, STOF_E_INVALID, "stof_model_set_weights: kind mismatch");
+    STOF_REQUIRE((w->contract_w != nullptr) == (m->sgb_scale != 1) || m->kind != STOF_KIND_STOFNET, STOF_E_INVALID,
+                 "stof_model_set_weights: semi-global block presence differs from the handle");
+    return stof::set_weights(m, w);
+}
+
+extern "C" void stof_model_destroy(stof_model *m) {
+    if (!m) return;
+    cudaSetDevice(m->device);
+    stof::free_conv(m->first); stof::free_conv(m->last); stof::free_conv(m->contract); stof::free_conv(m->expand);
+    for (int i = 0; i < STOF_MAX_MID_CONVS; ++i) stof::free_conv(m->mid[i]);
+    for (int i = 0; i < stof_model::kPipe; ++i) {
+        if (m->scratch[i]) cudaFree(m->scratch[i]);
+        if (m->streams[i]) cudaStreamDestroy(m->streams[i]);
+    }
+    if (m->h_stats) cudaFreeHost(m->h_stats);
+    for (cudaEvent_t e : m->ev_pool) cudaEventDestroy(e);
+    delete m;
+}
+
+extern "C" int stof_forward_workspace_bytes(const stof_model *m, int N, int L, int chunk_rows, size_t *bytes) {
+    STOF_REQUIRE(bytes != nullptr, STOF_E_INVALID, "stof_forward_workspace_bytes: bytes is NULL");
+    stof::Plan pl;
+    int rc = stof::make_plan(m, N, L, chunk_rows, &pl);
+    if (rc) return rc;
+    *bytes = pl.total_bytes;
+    return STOF_OK;
+}
+
+extern "C" int stof_forward(stof_model *m, const float *x_dev, int N, int L, float *mask_dev, void *ws_dev,
+                            size_t ws_bytes, int chunk_rows, void *stream) {
+    stof::Plan pl;
+    int rc = stof::make_plan(m, N, L, chunk_rows, &pl);
+    if (rc) return rc;
+    STOF_REQUIRE(x_dev && mask_dev && ws_dev, STOF_E_INVALID, "stof_forward: NULL buffer");
+    STOF_REQUIRE(ws_bytes >= pl.total_bytes, STOF_E_WORKSPACE, "stof_forward: workspace %zu < %zu bytes", ws_bytes, pl.total_bytes);
+    STOF_REQUIRE((reinterpret_cast<uintptr_t>(ws_dev) & 255) == 0 && (reinterpret_cast<uintptr_t>(mask_dev) & 15) == 0,
+                 STOF_E_INVALID, "stof_forward: workspace must be 256-byte and mask 16-byte aligned");
+    cudaStream_t st = (cudaStream_t)stream;
+    for (int n0 = 0; n0 < N; n0 += pl.chunk) {
+        const int n = (N - n0 < pl.chunk) ? N - n0 : pl.chunk;
+        rc = stof::forward_chunk(m, x_dev + (size_t)n0 * L, n, L, mask_dev + (size_t)n0 * L * m->r, (char *)ws_dev, pl, st);
+        if (rc) return rc;
+    }
+    return STOF_OK;
+}
+
+extern "C" int stof_infer_host(stof_model *m, const float *x_host, int N, int L, int window, int th_is_none, float th,
+                               float *coords_host, int cap, int32_t *counts_host, float *mask_host, int *kmax_out) {
+    STOF_REQUIRE(m && x_host && coords_host && counts_host && cap > 0, STOF_E_INVALID, "stof_infer_host: bad arguments");
+    stof::Plan pl;
+    int rc = stof::make_plan(m, N, L, 0, &pl);
+    if (rc) return rc;
+    STOF_CUDA(cudaSetDevice(m->device));
+    constexpr int kPipe = stof_model::kPipe;
+    // split into at least kPipe chunks so copies overlap compute
+    int chunk = pl.chunk;
+    if (N >= 2 * kPipe && chunk > (N + kPipe - 1) / kPipe) chunk = (N + kPipe - 1) / kPipe;
+    rc = stof::make_plan(m, N, L, chunk, &pl);
+    if (rc) return rc;
+    const size_t Mr = (size_t)L * m->r;
+    const size_t x_b = stof::align256((size_t)pl.chunk * L * 4), mask_b = stof::align256((size_t)pl.chunk * Mr * 4);
+    const size_t coords_b = stof::align256((size_t)pl.chunk * cap * 4), counts_b = stof::align256((size_t)pl.chunk * 4);
+    const size_t need = pl.total_bytes + x_b + mask_b + coords_b + counts_b + 256;
+    if (!m->h_stats) STOF_CUDA(cudaMallocHost(&m->h_stats, sizeof(int64_t) * 2 * kPipe));
+    for (int i = 0; i < kPipe; ++i) {
+        if (!m->streams[i]) STOF_CUDA(cudaStreamCreateWithFlags(&m->streams[i], cudaStreamNonBlocking));
+        if (m->scratch_bytes[i] < need) {
+            if (m->scratch[i]) STOF_CUDA(cudaFree(m->scratch[i]));
+            m->scratch[i] = nullptr; m->scratch_bytes[i] = 0;
+            STOF_CUDA(cudaMalloc(&m->scratch[i], need));
+            m->scratch_bytes[i] = need;
+        }
+    }
+    long long kmax = 0;
+    int it = 0;
+    for (int n0 = 0; n0 < N; n0 += pl.chunk, ++it) {
+        const int s = it % kPipe;
+        const int n = (N - n0 < pl.chunk) ? N - n0 : pl.chunk;
+        cudaStream_t st = m->streams[s];
+        if (it >= kPipe) {      // the slot's previous chunk must be done before its stats are read / buffers reused
+            STOF_CUDA(cudaStreamSynchronize(st));
+            if (m->h_stats[2 * s] > kmax) kmax = m->h_stats[2 * s];
+        }
+        char *base = (char *)m->scratch[s];
+        char *ws = base;
+        float *x_d = (float *)(base + pl.total_bytes);
+        float *mask_d = (float *)(base + pl.total_bytes + x_b);
+        float *coords_d = (float *)(base + pl.total_bytes + x_b + mask_b);
+        int32_t *counts_d = (int32_t *)(base + pl.total_bytes + x_b + mask_b + coords_b);
+        int64_t *stats_d = (int64_t *)(base + pl.total_bytes + x_b + mask_b + coords_b + counts_b);
+        STOF_CUDA(cudaMemcpyAsync(x_d, x_host + (size_t)n0 * L, (size_t)n * L * 4, cudaMemcpyHostToDevice, st));
+        STOF_CUDA(cudaMemsetAsync(stats_d, 0, 16, st));
+        if ((rc = stof::forward_chunk(m, x_d, n, L, mask_d, ws, pl, st))) return rc;
+        {
+            stof::ProfScope p(m, STOF_PROF_PEAKS, st);
+            if ((rc = stof_peaks(mask_d, n, (int)Mr, window, th_is_none, th, m->r, coords_d, nullptr, cap, counts_d, stats_d, st)))
+                return rc;
+        }
+        STOF_CUDA(cudaMemcpyAsync(coords_host + (size_t)n0 * cap, coords_d, (size_t)n * cap * 4, cudaMemcpyDeviceToHost, st));
+        STOF_CUDA(cudaMemcpyAsync(counts_host + n0, counts_d, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+        STOF_CUDA(cudaMemcpyAsync(m->h_stats + 2 * s, stats_d, 16, cudaMemcpyDeviceToHost, st));
+        if (mask_host)
+            STOF_CUDA(cudaMemcpyAsync(mask_host + (size_t)n0 * Mr, mask_d, (size_t)n * Mr * 4, cudaMemcpyDeviceToHost, st));
+    }
+    for (int s = 0; s < kPipe && s < it; ++s) {
+        STOF_CUDA(cudaStreamSynchronize(m->streams[s]));
+        if (m->h_stats[2 * s] > kmax) kmax = m->h_stats[2 * s];
+    }
+    if (kmax_out) *kmax_out = (int)kmax;
+    return STOF_OK;
+}
+
+extern "C" int stof_profile_enable(stof_model *m, int on) {
+    STOF_REQUIRE(m != nullptr, STOF_E_INVALID, "stof_profile_enable: model is NULL");
+    m->profiling = on != 0;
+    m->ev_used = 0;
+    return STOF_OK;
+}
+
+extern "C" int stof_profile_collect(stof_model *m, double *ms_by_class, int64_t *launches_by_class) {
+    STOF_REQUIRE(m && ms_by_class && launches_by_class, STOF_E_INVALID, "stof_profile_collect: NULL argument");
+    for (int c = 0; c < STOF_PROF_CLASSES; ++c) { ms_by_class[c] = 0.0; launches_by_class[c] = 0; }
+    for (size_t i = 0; i + 1 < m->ev_used; i += 2) {
+        STOF_CUDA(cudaEventSynchronize(m->ev_pool[i + 1]));
+        float ms = 0.f;
+        STOF_CUDA(cudaEventElapsedTime(&ms, m->ev_pool[i], m->ev_pool[i + 1]));
+        const int c = m->ev_class[i / 2];
+        ms_by_class[c] += ms;
+        launches_by_class[c] += 1;
+    }
+    m->ev_used = 0;
+    return STOF_OK;
+}

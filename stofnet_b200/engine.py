@@ -1,0 +1,152 @@
+"""Host-side glue between torch tensors and the C ABI (device memory, streams: plumbing only)."""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import lib, check
+
+
+def _np32(t):
+    return np.ascontiguousarray(t.detach().to("cpu", torch.float32).numpy())
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def stream_ptr(device):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def require_cuda(t, what):
+    if not t.is_cuda:
+        raise RuntimeError("stofnet_b200: %s must be a CUDA tensor - this build has no CPU path (got %s)"
+                           % (what, t.device))
+
+
+class Engine:
+    """Owns one stof_model handle and a grow-only workspace for one nn.Module instance."""
+
+    def __init__(self, kind):
+        self.kind = kind
+        self.handle = None
+        self.device = None
+        self.key = None
+        self.ws = None
+        self.chunk_rows = 0     # 0 = library default
+
+    def close(self):
+        if self.handle is not None:
+            lib.stof_model_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- weights ---------------------------------------------------------------------------
+    def _pack(self, sd):
+        """sd: mapping with the reference's state_dict key names -> ctypes struct (+ keep-alive)."""
+        W = _lib.Weights()
+        keep = {k: _np32(v) for k, v in sd.items()}
+        W.kind = self.kind
+        W.conv1_w, W.conv1_b = _ptr(keep["conv1.weight"]), _ptr(keep["conv1.bias"])
+        if self.kind == _lib.KIND_ESPCN:
+            W.n_mid = 1
+            W.mid_w[0], W.mid_b[0] = _ptr(keep["conv2.weight"]), _ptr(keep["conv2.bias"])
+            W.last_w, W.last_b = _ptr(keep["conv3.weight"]), _ptr(keep["conv3.bias"])
+            W.upsample_factor = keep["conv3.weight"].shape[0]
+            W.num_features = 64
+            W.k_first, W.k_mid, W.k_last = 5, 3, 3
+            W.sgb_scale = 1
+            return W, keep
+        mids = sorted(int(k[4:-7]) for k in keep
+                      if k.startswith("conv") and k.endswith(".weight") and k[4:-7].isdigit() and k != "conv1.weight")
+        W.n_mid = len(mids)
+        for j, i in enumerate(mids):
+            W.mid_w[j], W.mid_b[j] = _ptr(keep["conv%d.weight" % i]), _ptr(keep["conv%d.bias" % i])
+        W.last_w, W.last_b = _ptr(keep["conv_last.weight"]), _ptr(keep["conv_last.bias"])
+        W.num_features = keep["conv1.weight"].shape[0]
+        W.upsample_factor = keep["conv_last.weight"].shape[0]
+        W.k_first = keep["conv1.weight"].shape[2]
+        W.k_mid = keep["conv2.weight"].shape[2]
+        W.k_last = keep["conv_last.weight"].shape[2]
+        p = "semi_global_block."
+        if p + "contract_conv.weight" in keep:
+            cw = keep[p + "contract_conv.weight"]
+            W.contract_w, W.contract_b = _ptr(cw), _ptr(keep[p + "contract_conv.bias"])
+            W.expand_w, W.expand_b = _ptr(keep[p + "expand_conv.weight"]), _ptr(keep[p + "expand_conv.bias"])
+            W.sgb_feat, W.sgb_k = cw.shape[0], cw.shape[2]
+            W.sgb_scale = sd.sgb_scale if hasattr(sd, "sgb_scale") else 10 * (cw.shape[0] // cw.shape[1])
+        else:
+            W.sgb_scale, W.sgb_feat, W.sgb_k = 1, 0, 0
+        return W, keep
+
+    def sync(self, module, device):
+        """(Re)upload the module's parameters when they changed (load_state_dict, optimizer step)."""
+        params = dict(module.state_dict(keep_vars=True))
+        key = (device.index, tuple((k, v.data_ptr(), v._version) for k, v in params.items()))
+        if self.handle is not None and key == self.key:
+            return
+        W, keep = self._pack(params)
+        if getattr(module, "semi_global_block", None) is not None:
+            W.sgb_scale = int(module.semi_global_block.sample_scale)
+        if self.handle is not None and self.device == device:
+            check(lib.stof_model_set_weights(self.handle, C.byref(W)))
+        else:
+            self.close()
+            h = C.c_void_p()
+            check(lib.stof_model_create(C.byref(W), device.index if device.index is not None else 0, C.byref(h)))
+            self.handle, self.device = h, device
+        self.key = key
+        del keep
+
+    # -- forward ---------------------------------------------------------------------------
+    def forward(self, module, x):
+        require_cuda(x, "input")
+        if x.dim() != 3 or x.shape[1] != 1:
+            raise RuntimeError("stofnet_b200: expected input of shape (N, 1, L), got %s" % (tuple(x.shape),))
+        dev = x.device
+        self.sync(module, dev)
+        x = x.detach().to(torch.float32).contiguous()
+        N, _, L = x.shape
+        r = module.upsample_factor
+        with torch.cuda.device(dev):
+            need = C.c_size_t()
+            check(lib.stof_forward_workspace_bytes(self.handle, N, L, self.chunk_rows, C.byref(need)))
+            if self.ws is None or self.ws.numel() < need.value or self.ws.device != dev:
+                self.ws = None
+                self.ws = torch.empty(need.value, dtype=torch.uint8, device=dev)
+            out = torch.empty((N, 1, r * L), dtype=torch.float32, device=dev)
+            check(lib.stof_forward(self.handle, x.data_ptr(), N, L, out.data_ptr(), self.ws.data_ptr(),
+                                   self.ws.numel(), self.chunk_rows, stream_ptr(dev)))
+        return out
+
+    def infer_host(self, module, x_host, window_size, threshold, cap=64, want_mask=False, device=None):
+        """End-to-end eval step on HOST tensors (pinned recommended): H2D + forward + peaks + D2H."""
+        dev = device if device is not None else next(module.parameters()).device
+        if dev.type != "cuda":
+            raise RuntimeError("stofnet_b200: module must live on a CUDA device (no CPU path)")
+        self.sync(module, dev)
+        x_host = x_host.detach().to(torch.float32).contiguous()
+        if x_host.dim() == 3:
+            x_host = x_host[:, 0, :]
+        N, L = x_host.shape
+        r = module.upsample_factor
+        none = (threshold is None) or (not threshold)
+        while True:
+            coords = torch.empty((N, cap), dtype=torch.float32).pin_memory()
+            counts = torch.empty((N,), dtype=torch.int32).pin_memory()
+            mask = torch.empty((N, 1, r * L), dtype=torch.float32).pin_memory() if want_mask else None
+            kmax = C.c_int(0)
+            check(lib.stof_infer_host(self.handle, x_host.data_ptr(), N, L, int(window_size), int(none),
+                                      0.0 if none else float(threshold), coords.data_ptr(), cap, counts.data_ptr(),
+                                      mask.data_ptr() if want_mask else None, C.byref(kmax)))
+            if kmax.value <= cap:
+                break
+            cap = kmax.value
+        return coords, counts, kmax.value, mask

@@ -1,0 +1,147 @@
+"""Time-of-flight extraction with the reference's operator surface
+(/root/reference/utils/mask2samples.py), computed by libstofnet_b200.so.
+
+``get_maxima_positions`` / ``mask2coords`` run ONE fused kernel (stof_peaks: sliding-window NMS,
+threshold / row-max selection, ordered per-row compaction, division by ``upsample_factor``)
+instead of the reference's max_pool1d + elementwise passes + torch.nonzero + bincount + per-row
+Python pack loop (:92-102).  Return shapes follow the reference exactly, including the
+``zeros((N, C, 1))`` result when nothing is detected anywhere (:87-88) and right zero padding.
+"""
+import ctypes as C
+
+import torch
+
+from .._lib import lib, check
+from ..engine import require_cuda, stream_ptr
+
+_DEFAULT_CAP = 64
+
+
+def _as_rows(scores):
+    require_cuda(scores, "scores")
+    s = scores.detach().to(torch.float32)
+    if s.dim() == 3:
+        if s.shape[1] != 1:
+            raise ValueError("stofnet_b200: scores must have a single channel, got shape %s" % (tuple(s.shape),))
+        rows = s[:, 0, :]
+    elif s.dim() == 2:
+        rows = s
+    else:
+        raise ValueError("stofnet_b200: scores must be (N, 1, M), got shape %s" % (tuple(s.shape),))
+    return rows.contiguous()
+
+
+def _th(threshold):
+    none = (threshold is None) or (not threshold)      # `if threshold:` (reference :16)
+    return int(none), 0.0 if none else float(threshold)
+
+
+def _run_peaks(rows, window_size, threshold, upsample_factor, want_pos, cap):
+    N, M = rows.shape
+    dev = rows.device
+    none, th = _th(threshold)
+    while True:
+        coords = torch.empty((N, cap), dtype=torch.float32, device=dev)
+        pos = torch.empty((N, cap), dtype=torch.int32, device=dev) if want_pos else None
+        counts = torch.empty((N,), dtype=torch.int32, device=dev)
+        stats = torch.zeros((2,), dtype=torch.int64, device=dev)
+        with torch.cuda.device(dev):
+            check(lib.stof_peaks(rows.data_ptr(), N, M, int(window_size), none, th, int(upsample_factor),
+                                 coords.data_ptr(), pos.data_ptr() if want_pos else None, cap,
+                                 counts.data_ptr(), stats.data_ptr(), stream_ptr(dev)))
+        kmax, total = (int(v) for v in stats.tolist())        # the one host sync (reference :93)
+        if kmax <= cap:
+            return coords, pos, counts, kmax, total
+        cap = kmax
+
+
+def nms_1d(scores, window_size):
+    """(scores == max_pool1d(scores, odd(window), 1, pad)).float() * scores   (reference :5-11)."""
+    rows = _as_rows(scores)
+    out = torch.empty_like(rows)
+    with torch.cuda.device(rows.device):
+        check(lib.stof_nms_1d(rows.data_ptr(), rows.shape[0], rows.shape[1], int(window_size), out.data_ptr(),
+                              stream_ptr(rows.device)))
+    return out.view(scores.shape)
+
+
+def thresholding(scores, threshold=None):
+    """Reference :14-23.  Standalone convenience (inside mask2coords it is fused into the kernel);
+    elementwise on the caller's device with torch, in place for a float threshold like the reference."""
+    if threshold:
+        scores[scores < threshold] = 0
+    else:
+        max_vals = torch.max(scores, dim=-1, keepdim=True)[0]
+        scores = scores.masked_fill(scores < max_vals, 0)
+    return scores
+
+
+def get_maxima_positions(scores, window_size, threshold=None):
+    """(K, 2) int64 [row, position], row-major ascending (reference :26-34)."""
+    rows = _as_rows(scores)
+    N = rows.shape[0]
+    _, pos, counts, kmax, total = _run_peaks(rows, window_size, threshold, 1, True, _DEFAULT_CAP)
+    idx = torch.empty((total, 2), dtype=torch.int64, device=rows.device)
+    if total:
+        offsets = torch.empty((N,), dtype=torch.int64, device=rows.device)
+        with torch.cuda.device(rows.device):
+            check(lib.stof_peaks_indices(pos.data_ptr(), counts.data_ptr(), N, pos.shape[1], offsets.data_ptr(),
+                                         idx.data_ptr(), stream_ptr(rows.device)))
+    return idx
+
+
+def mask2coords(scores, window_size, threshold=None, upsample_factor=1, echo_max=None):
+    """(N, K_max) fp32 time-of-flight table: ascending positions / upsample_factor, zero padded
+    (reference :81-114)."""
+    rows = _as_rows(scores)
+    N = rows.shape[0]
+    int_r = isinstance(upsample_factor, int) or float(upsample_factor).is_integer()
+    coords, _, counts, kmax, _ = _run_peaks(rows, window_size, threshold, int(upsample_factor) if int_r else 1,
+                                            False, _DEFAULT_CAP)
+    if kmax == 0:
+        return torch.zeros((scores.shape[0], scores.shape[1] if scores.dim() == 3 else 1, 1), device=scores.device)
+    coords = coords[:, :kmax].contiguous()
+    if echo_max:
+        # reference :105-110 applies the amplitude selection BEFORE dividing by upsample_factor
+        if echo_max < coords.shape[-1]:
+            if int_r:
+                coords = coords * int(upsample_factor)
+            amplitudes = get_amplitudes(scores, coords)
+            coords = reduce_echoes(torch.dstack([coords, amplitudes]), echo_max=echo_max)[..., 0]
+            coords = coords / upsample_factor
+            return coords
+        elif echo_max > coords.shape[-1]:
+            pad = torch.zeros(coords.shape[0], echo_max - coords.shape[-1], device=coords.device, dtype=coords.dtype)
+            coords = torch.cat([coords, pad], dim=-1)
+    if not int_r:
+        coords /= upsample_factor
+    return coords
+
+
+def reduce_echoes(samples_and_amps, echo_max=100):
+    """Keep the echo_max largest-amplitude echoes, re-sorted by time (reference :117-132; off the hot
+    path: main.py never passes echo_max)."""
+    echo_num = samples_and_amps.shape[1]
+    channel_num = samples_and_amps.shape[-1]
+    echoes = samples_and_amps
+    if echo_num > echo_max:
+        idcs = torch.argsort(samples_and_amps[..., 1], descending=True, dim=1)
+        echoes = torch.gather(samples_and_amps, dim=1, index=idcs[..., None].repeat(1, 1, channel_num))[:, :echo_max]
+        idcs = torch.argsort(echoes[..., 0], descending=False, dim=1)
+        echoes = torch.gather(echoes, dim=1, index=idcs[..., None].repeat(1, 1, channel_num))
+    return echoes
+
+
+def get_amplitudes(frames, samples):
+    return torch.gather(frames.squeeze(), -1, torch.round(samples).long())
+
+
+def coords2mask(samples, ref):
+    """One-hot ground-truth mask for the loss (reference :139-148): scatter ones at the (clamped)
+    sample indices, then clear column 0 (placeholder for absent echoes).  Loss-side helper, off the
+    inference path; plain tensor indexing on the caller's device."""
+    empty_mask = torch.zeros_like(ref)
+    samples[samples < 0] = 0
+    empty_mask.scatter_(2, samples, 1)
+    empty_mask[..., :1] = 0
+    return empty_mask
