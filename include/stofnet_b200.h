@@ -136,6 +136,23 @@ int stof_sample_shuffle(const float *x_dev, int B, int Cs, int W, int r, float *
 int stof_profile_enable(stof_model *m, int on);
 int stof_profile_collect(stof_model *m, double *ms_by_class, int64_t *launches_by_class);
 
+/* Arithmetic path of the 64->64 conv stack (models/stofnet.py:51-65).
+ *   STOF_PATH_TC    tcgen05/TMEM implicit GEMM; every fp32 operand is carried as an fp16 hi/lo pair (22 significand
+ *                   bits, fp32 accumulation): fp32-faithful results at fp16 tensor-core rate.  Default for StofNet.
+ *   STOF_PATH_SIMT  plain fp32 FFMA kernels (bring-up / cross-check path; also what ESPCN_1D uses).
+ * layers_per_launch > 0 sets how many conv layers one fused chain launch covers (1..6, default 4).     */
+#define STOF_PATH_SIMT 0
+#define STOF_PATH_TC   1
+int stof_model_set_path(stof_model *m, int path, int layers_per_launch);
+
+/* One fused chain launch on caller-provided activations (test hook for single layers / segments):
+ * layers [first, first+count) of the list conv2 .. conv{nb-1}, conv_last.
+ *   in_planes_dev  (N, 2, 8, L, 8) fp16: plane 0 = fp16(v), plane 1 = fp16((v - plane0) * 2^11), channel c at [c/8][l][c%8]
+ *   x0_planes_dev  same layout: the long-skip tensor res1 (needed when the range contains conv{nb-1}); may be NULL otherwise
+ *   out_dev        same layout, or the (N, r*L) fp32 mask when the range ends with conv_last                 */
+int stof_chain_segment(stof_model *m, int first, int count, const void *in_planes_dev, const void *x0_planes_dev,
+                       void *out_dev, int N, int L, void *stream);
+
 /* Counter of kernels launched by this library since load (bench.py's gpu_launches). */
 uint64_t stof_launch_count(void);
 

@@ -11,6 +11,7 @@ LIB_PATH = os.path.join(_HERE, "libstofnet_b200.so")
 
 MAX_MID = 16
 KIND_STOFNET, KIND_ESPCN = 0, 1
+PATH_SIMT, PATH_TC = 0, 1
 
 E_INVALID, E_LENGTH, E_LENGTH_ODD, E_WORKSPACE, E_CUDA, E_NCCL, E_UNSUPPORTED = -1, -2, -3, -4, -5, -6, -7
 
@@ -53,6 +54,8 @@ _SIGS = {
     "stof_nms_1d": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "stof_infer_host": (_i, [_vp, _vp, _i, _i, _i, _i, _f, _vp, _i, _vp, _vp, C.POINTER(_i)]),
     "stof_sample_shuffle": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
+    "stof_model_set_path": (_i, [_vp, _i, _i]),
+    "stof_chain_segment": (_i, [_vp, _i, _i, _vp, _vp, _vp, _i, _i, _vp]),
     "stof_profile_enable": (_i, [_vp, _i]),
     "stof_profile_collect": (_i, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
 }

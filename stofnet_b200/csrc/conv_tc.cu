@@ -1,0 +1,508 @@
+// Tensor-core (tcgen05 / TMEM) kernels of the StofNet conv stack (models/stofnet.py:30-31,51-65).
+//
+// chain_tc_kernel runs a SEGMENT of consecutive layers of the 64->64 k7 stack (conv2..conv12) and,
+// optionally, conv_last + SampleShuffle1D, on one tile of a row without leaving the SM:
+//
+//   * a Conv1d layer is an implicit GEMM  D[position, co] = sum_tap sum_ci X[position + tap - pad, ci] * W_tap[co, ci]
+//     with M = 128 positions (TMEM lanes), N = output channels (TMEM columns), K = 64 input channels per tap.
+//     Activations live in shared memory as "rows x 8-channel" 16-byte vectors (layout [plane][c8][row][8] fp16), which
+//     is exactly the no-swizzle K-major UMMA operand layout with SBO = 128 B: a one-sample tap shift is a 16-byte
+//     shift of the descriptor start address, so the 7 taps are 7 descriptors into the same tile (no im2col copy).
+//   * fp32 accuracy on fp16 tensor cores: every fp32 value v is carried as two fp16 planes, hi = fp16(v) and
+//     lo = fp16((v - hi) * 2^11) (22 significand bits); weights likewise.  Per K-step two MMAs are issued,
+//          [D0 | D1] (+)= X_hi * [W_hi ; W_lo]^T      (N = 128)
+//               D1    += X_lo * W_hi^T                 (N = 64)
+//     and the epilogue forms D0 + 2^-11 * D1 (the dropped lo*lo term is 2^-22 relative).  Stacking W_hi and W_lo along N
+//     halves the shared-memory operand traffic per MAC, which is what bounds N = 64 MMAs.
+//   * the epilogue (4 warps, one TMEM lane = one position per thread) adds bias / residual, applies LeakyReLU, zeroes
+//     positions outside the row (per-layer zero padding), re-splits to hi/lo fp16 and writes the next layer's operand
+//     straight back to shared memory; block grids of successive layers are skewed by the layer's padding so block b of
+//     layer k+1 only depends on blocks <= b of layer k and the tensor pipe never waits for a whole layer.
+//   * weights stream through a 4-stage ring of 16 KB taps filled by bulk async copies (TMA engine) on mbarriers.
+//
+// Roles: warp 0 = producer (input tile + weight ring), warp 1 = MMA issuer + TMEM owner, warps 2-5 = epilogue.
+#include <cuda_fp16.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "kernels.cuh"
+#include "tc_ptx.cuh"
+
+namespace stof {
+
+using namespace ptx;
+
+constexpr int TC_THREADS = 192;
+constexpr int TC_R = 280;                              // smem rows per (plane, c8) slab
+constexpr int TC_SLAB = TC_R * 16;                     // bytes of one (plane, c8) slab
+constexpr int TC_PLANE = 8 * TC_SLAB;                  // one fp16 plane (hi or lo): 64 channels
+constexpr int TC_BUF = 2 * TC_PLANE;                   // hi + lo
+constexpr int TC_STAGES = 4;
+constexpr int TC_STAGE_BYTES = 16384;                  // one k7 tap: [8 c8][128 n][8] fp16
+constexpr int TC_GROUP = 4;                            // taps issued per block before switching block (<= stages)
+constexpr float TC_LO_SCALE = 2048.0f;                 // 2^11
+constexpr float TC_LO_INV = 1.0f / 2048.0f;
+
+// shared memory map (dynamic, 1024-aligned base)
+constexpr int TC_OFF_P = 0;
+constexpr int TC_OFF_Q = TC_BUF;
+constexpr int TC_OFF_W = 2 * TC_BUF;
+constexpr int TC_OFF_BIAS = TC_OFF_W + TC_STAGES * TC_STAGE_BYTES;          // [TC_MAX_LAYERS][64] fp32
+constexpr int TC_OFF_BAR = TC_OFF_BIAS + TC_MAX_LAYERS * 64 * 4;
+// barriers (8 B each): w_full[4] w_empty[4] acc_full[4] acc_empty[4] act_ready[TC_MAX_LAYERS][2] in_full tile_free
+constexpr int TC_NBAR = 16 + 2 * TC_MAX_LAYERS + 2;
+constexpr int TC_OFF_TMEM = TC_OFF_BAR + TC_NBAR * 8;
+constexpr int TC_SMEM_BYTES = TC_OFF_TMEM + 16;
+
+static_assert(TC_SMEM_BYTES <= 232448, "chain kernel exceeds the 227 KB shared-memory limit");
+
+__device__ __forceinline__ uint32_t pack_half2(float a, float b) {
+    __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t *>(&h);
+}
+
+// v -> (hi, lo) with hi = fp16(v) (saturated to the finite range), lo = fp16((v - hi) * 2^11)
+__device__ __forceinline__ void split_hi_lo(float v, float &hi, float &lo) {
+    const float c = fminf(fmaxf(v, -65504.0f), 65504.0f);
+    hi = __half2float(__float2half_rn(c));
+    lo = (c - hi) * TC_LO_SCALE;
+}
+
+__device__ __forceinline__ void unpack8(const uint4 &u, float (&f)[8]) {
+    const __half2 *h = reinterpret_cast<const __half2 *>(&u);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float2 t = __half22float2(h[i]);
+        f[2 * i] = t.x;
+        f[2 * i + 1] = t.y;
+    }
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const uint32_t sbase = smem_u32(smem);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t bar0 = sbase + TC_OFF_BAR;
+    auto BAR_W_FULL = [&](int s) { return bar0 + 8 * s; };
+    auto BAR_W_EMPTY = [&](int s) { return bar0 + 8 * (4 + s); };
+    auto BAR_ACC_FULL = [&](int s) { return bar0 + 8 * (8 + s); };
+    auto BAR_ACC_EMPTY = [&](int s) { return bar0 + 8 * (12 + s); };
+    auto BAR_ACT = [&](int k, int b) { return bar0 + 8 * (16 + 2 * k + b); };
+    const uint32_t BAR_IN_FULL = bar0 + 8 * (16 + 2 * TC_MAX_LAYERS);
+    const uint32_t BAR_TILE_FREE = BAR_IN_FULL + 8;
+    float *s_bias = reinterpret_cast<float *>(smem + TC_OFF_BIAS);
+    volatile uint32_t *s_tmem = reinterpret_cast<volatile uint32_t *>(smem + TC_OFF_TMEM);
+
+    // ---- one-time setup ------------------------------------------------------------------------------
+    for (int i = threadIdx.x; i < p.n_layers * 64; i += TC_THREADS) {
+        const int k = i >> 6, c = i & 63;
+        s_bias[i] = (c < p.layer[k].n_out) ? __ldg(p.layer[k].bias + c) : 0.0f;
+    }
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < 4; ++s) {
+            mbar_init(BAR_W_FULL(s), 1);
+            mbar_init(BAR_W_EMPTY(s), 1);
+            mbar_init(BAR_ACC_FULL(s), 1);
+            mbar_init(BAR_ACC_EMPTY(s), 4);
+        }
+        for (int k = 0; k < TC_MAX_LAYERS; ++k) {
+            mbar_init(BAR_ACT(k, 0), 4);
+            mbar_init(BAR_ACT(k, 1), 4);
+        }
+        mbar_init(BAR_IN_FULL, 1);
+        mbar_init(BAR_TILE_FREE, 4);
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc(sbase + TC_OFF_TMEM, 512);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem0 = *s_tmem;
+
+    const int n_layers = p.n_layers;
+    const int r_in = p.r_in;                 // input rows staged per tile
+
+    if (warp == 0) {
+        // =================================== producer ===================================================
+        uint32_t seq = 0;
+        int it = 0;
+        for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+            const int n = tile / p.tiles_per_row;
+            const int l0 = (tile - n * p.tiles_per_row) * p.t_out;
+            const int l_org = l0 - p.l_shift;
+            // the previous tile must be completely consumed before its input buffer is overwritten
+            mbar_wait(BAR_TILE_FREE, (uint32_t)(it & 1) ^ 1u);
+            const int r_lo = max(0, -l_org), r_hi = min(r_in, p.L - l_org);
+            // rows outside the waveform are the conv's zero padding
+            for (int idx = lane; idx < 16 * r_in; idx += 32) {
+                const int slab = idx / r_in, r = idx - slab * r_in;
+                if (r < r_lo || r >= r_hi)
+                    *reinterpret_cast<uint4 *>(smem + TC_OFF_P + slab * TC_SLAB + r * 16) = make_uint4(0, 0, 0, 0);
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+                const uint32_t bytes = (uint32_t)(r_hi - r_lo) * 16u;
+                mbar_arrive_expect_tx(BAR_IN_FULL, bytes * 16u);
+                const __half *src = reinterpret_cast<const __half *>(p.in) + (size_t)n * 16 * p.L * 8;
+                for (int slab = 0; slab < 16; ++slab)
+                    bulk_g2s(sbase + TC_OFF_P + slab * TC_SLAB + r_lo * 16, src + ((size_t)slab * p.L + l_org + r_lo) * 8, bytes,
+                             BAR_IN_FULL);
+                // weight ring: every tap of every layer of this tile, in issue order
+                for (int k = 0; k < n_layers; ++k) {
+                    const TcLayer &ly = p.layer[k];
+                    for (int t = 0; t < ly.taps; ++t, ++seq) {
+                        const int s = seq & 3;
+                        mbar_wait(BAR_W_EMPTY(s), ((seq >> 2) & 1u) ^ 1u);
+                        mbar_arrive_expect_tx(BAR_W_FULL(s), (uint32_t)ly.stage_bytes);
+                        bulk_g2s(sbase + TC_OFF_W + s * TC_STAGE_BYTES,
+                                 reinterpret_cast<const uint8_t *>(ly.w) + (size_t)t * ly.stage_bytes, (uint32_t)ly.stage_bytes,
+                                 BAR_W_FULL(s));
+                    }
+                }
+            }
+            __syncwarp();
+        }
+    } else if (warp == 1) {
+        // =================================== MMA issuer ==================================================
+        if (lane == 0) {
+            uint32_t seq0 = 0, q0 = 0;
+            int it = 0;
+            for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+                mbar_wait(BAR_IN_FULL, (uint32_t)(it & 1));
+                tc_fence_after_sync();
+                for (int k = 0; k < n_layers; ++k) {
+                    const TcLayer &ly = p.layer[k];
+                    const uint32_t in_base = sbase + ((k & 1) ? TC_OFF_Q : TC_OFF_P);
+                    const uint32_t idesc_a = umma_idesc_f16(128, ly.n_stack);
+                    const uint32_t idesc_b = umma_idesc_f16(128, ly.n_lo);
+                    const uint32_t w_lbo = (uint32_t)ly.w_rows * 16u;          // K-chunk stride of the weight stage
+                    for (int g0 = 0; g0 < ly.taps; g0 += TC_GROUP) {
+                        const int g1 = min(ly.taps, g0 + TC_GROUP);
+                        for (int b = 0; b < 2; ++b) {
+                            const uint32_t q = q0 + b;
+                            const uint32_t d_tmem = tmem0 + (q & 3u) * 128u;
+                            if (g0 == 0) {
+                                mbar_wait(BAR_ACC_EMPTY(q & 3u), ((q >> 2) & 1u) ^ 1u);
+                                if (k > 0) mbar_wait(BAR_ACT(k - 1, b), (uint32_t)(it & 1));
+                                tc_fence_after_sync();
+                            }
+                            const int row0 = p.b_row[k] + 128 * b - ly.pad;
+                            for (int t = g0; t < g1; ++t) {
+                                const uint32_t seq = seq0 + t;
+                                const int s = seq & 3;
+                                mbar_wait(BAR_W_FULL(s), (seq >> 2) & 1u);
+                                tc_fence_after_sync();
+                                const uint32_t a_row = in_base + (uint32_t)(row0 + t) * 16u;
+                                const uint32_t w_st = sbase + TC_OFF_W + s * TC_STAGE_BYTES;
+#pragma unroll
+                                for (int ks = 0; ks < 4; ++ks) {
+                                    const uint64_t a_hi = umma_desc(a_row + 2 * ks * TC_SLAB, TC_SLAB, 128);
+                                    const uint64_t a_lo = umma_desc(a_row + TC_PLANE + 2 * ks * TC_SLAB, TC_SLAB, 128);
+                                    const uint64_t b_all = umma_desc(w_st + 2 * ks * w_lbo, w_lbo, 128);
+                                    const uint64_t b_hi = umma_desc(w_st + 2 * ks * w_lbo + (uint32_t)ly.lo_row * 16u, w_lbo, 128);
+                                    umma_f16(d_tmem, a_hi, b_all, idesc_a, (t > 0 || ks > 0) ? 1u : 0u);
+                                    umma_f16(d_tmem + (uint32_t)ly.lo_col, a_lo, b_hi, idesc_b, 1u);
+                                }
+                                if (b == 1) umma_commit(BAR_W_EMPTY(s));
+                            }
+                            if (g1 == ly.taps) umma_commit(BAR_ACC_FULL(q & 3u));
+                        }
+                    }
+                    seq0 += ly.taps;
+                    q0 += 2;
+                }
+            }
+        }
+        __syncwarp();
+    } else {
+        // =================================== epilogue ====================================================
+        const int quad = warp & 3;
+        const int trow = 32 * quad + lane;                       // TMEM lane = row within the 128-block
+        const uint32_t lane_addr = (uint32_t)(32 * quad) << 16;
+        uint32_t q0 = 0;
+        int it = 0;
+        for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+            const int n = tile / p.tiles_per_row;
+            const int l0 = (tile - n * p.tiles_per_row) * p.t_out;
+            const int l_org = l0 - p.l_shift;
+            const int l_end = min(l0 + p.t_out, p.L);
+            for (int k = 0; k < n_layers; ++k) {
+                const TcLayer &ly = p.layer[k];
+                const bool last_in_seg = (k == n_layers - 1);
+                uint8_t *outbuf = smem + ((k & 1) ? TC_OFF_P : TC_OFF_Q);
+                const float *bias = s_bias + 64 * k;
+                for (int b = 0; b < 2; ++b) {
+                    const uint32_t q = q0 + b;
+                    const int r = p.b_row[k] + 128 * b + trow;
+                    const int l = l_org + r;
+                    const bool inside = (l >= 0) && (l < p.L);
+                    mbar_wait(BAR_ACC_FULL(q & 3u), (q >> 2) & 1u);
+                    tc_fence_after_sync();
+                    const uint32_t d_tmem = tmem0 + (q & 3u) * 128u + lane_addr;
+                    if (ly.type == TC_LAST) {
+                        // conv_last + SampleShuffle1D: mask[n][4 l + u] = D0[u] + 2^-11 D1[u] + bias[u]
+                        uint32_t d[16];
+                        tmem_ld16(d_tmem, d);
+                        tmem_ld_wait();
+                        tc_fence_before_sync();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(BAR_ACC_EMPTY(q & 3u));
+                        if (l >= l0 && l < l_end) {
+                            float4 o;
+                            o.x = (__uint_as_float(d[0]) + TC_LO_INV * __uint_as_float(d[8])) + bias[0];
+                            o.y = (__uint_as_float(d[1]) + TC_LO_INV * __uint_as_float(d[9])) + bias[1];
+                            o.z = (__uint_as_float(d[2]) + TC_LO_INV * __uint_as_float(d[10])) + bias[2];
+                            o.w = (__uint_as_float(d[3]) + TC_LO_INV * __uint_as_float(d[11])) + bias[3];
+                            reinterpret_cast<float4 *>(p.out_mask)[(size_t)n * p.L + l] = o;
+                        }
+                        continue;
+                    }
+                    const bool store_global = last_in_seg && (l >= l0) && (l < l_end);
+#pragma unroll 1
+                    for (int c16 = 0; c16 < 4; ++c16) {
+                        uint32_t d0[16], d1[16];
+                        tmem_ld16(d_tmem + 16 * c16, d0);
+                        tmem_ld16(d_tmem + 64 + 16 * c16, d1);
+                        tmem_ld_wait();
+                        if (c16 == 3) {                                  // accumulator fully read: hand it back
+                            tc_fence_before_sync();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(BAR_ACC_EMPTY(q & 3u));
+                        }
+                        float v[16];
+#pragma unroll
+                        for (int i = 0; i < 16; ++i)
+                            v[i] = (__uint_as_float(d0[i]) + TC_LO_INV * __uint_as_float(d1[i])) + bias[16 * c16 + i];
+                        if (ly.type == TC_LEAKY) {
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], kLeakySlope * v[i]);
+                        } else {
+                            // residual: short skip = value stored at this row of the output buffer (x two layers back);
+                            // long skip (res1) = x0 planes in global memory
+#pragma unroll
+                            for (int h = 0; h < 2; ++h) {
+                                const int c8 = 2 * c16 + h;
+                                uint4 rh, rl;
+                                if (ly.type == TC_RES) {
+                                    rh = *reinterpret_cast<const uint4 *>(outbuf + c8 * TC_SLAB + r * 16);
+                                    rl = *reinterpret_cast<const uint4 *>(outbuf + TC_PLANE + c8 * TC_SLAB + r * 16);
+                                } else if (inside) {
+                                    const uint4 *x0 = reinterpret_cast<const uint4 *>(p.x0) + (size_t)n * 16 * p.L;
+                                    rh = __ldg(x0 + (size_t)c8 * p.L + l);
+                                    rl = __ldg(x0 + (size_t)(8 + c8) * p.L + l);
+                                } else {
+                                    rh = make_uint4(0, 0, 0, 0);
+                                    rl = rh;
+                                }
+                                float fh[8], fl[8];
+                                unpack8(rh, fh);
+                                unpack8(rl, fl);
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) v[8 * h + i] += fh[i] + TC_LO_INV * fl[i];
+                            }
+                        }
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            float hi[8], lo[8];
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                split_hi_lo(inside ? v[8 * h + i] : 0.0f, hi[i], lo[i]);
+                            }
+                            uint4 uh, ul;
+                            uh.x = pack_half2(hi[0], hi[1]); uh.y = pack_half2(hi[2], hi[3]);
+                            uh.z = pack_half2(hi[4], hi[5]); uh.w = pack_half2(hi[6], hi[7]);
+                            ul.x = pack_half2(lo[0], lo[1]); ul.y = pack_half2(lo[2], lo[3]);
+                            ul.z = pack_half2(lo[4], lo[5]); ul.w = pack_half2(lo[6], lo[7]);
+                            const int c8 = 2 * c16 + h;
+                            if (!last_in_seg) {
+                                *reinterpret_cast<uint4 *>(outbuf + c8 * TC_SLAB + r * 16) = uh;
+                                *reinterpret_cast<uint4 *>(outbuf + TC_PLANE + c8 * TC_SLAB + r * 16) = ul;
+                            } else if (store_global) {
+                                uint4 *dst = reinterpret_cast<uint4 *>(p.out_planes) + (size_t)n * 16 * p.L;
+                                dst[(size_t)c8 * p.L + l] = uh;
+                                dst[(size_t)(8 + c8) * p.L + l] = ul;
+                            }
+                        }
+                    }
+                    if (!last_in_seg) {
+                        fence_proxy_async_smem();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(BAR_ACT(k, b));
+                    }
+                }
+                q0 += 2;
+            }
+            // every read of this tile's buffers by this warp is done
+            __syncwarp();
+            if (lane == 0) mbar_arrive(BAR_TILE_FREE);
+        }
+    }
+
+    // ---- teardown --------------------------------------------------------------------------------------
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after_sync();
+        tmem_dealloc(tmem0, 512);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// x0 = act(conv_first(x)) [+ E upsampled x scale, centred, zero outside]  ->  split planes.
+// conv1 (1 -> 64, k9) has K = 9: CUDA-core FMAs, HBM-bound (4 B in, 256 B out per position).
+// (models/stofnet.py:23,45 and :96,108-115)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+x0_split_kernel(const float *__restrict__ x, const float *__restrict__ e, int N, int L, int P, int scale, int off,
+                const float *__restrict__ w /*[9][64]*/, const float *__restrict__ b, uint4 *__restrict__ planes) {
+    __shared__ float4 ws[9 * 16];
+    __shared__ float4 bs[16];
+    for (int i = threadIdx.x; i < 9 * 16; i += 256) ws[i] = reinterpret_cast<const float4 *>(w)[i];
+    if (threadIdx.x < 16) bs[threadIdx.x] = reinterpret_cast<const float4 *>(b)[threadIdx.x];
+    __syncthreads();
+    const int n = blockIdx.y;
+    const int l = blockIdx.x * 256 + threadIdx.x;
+    if (l >= L) return;
+    const float *xr = x + (size_t)n * L;
+    float xv[9];
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+        const int g = l + t - 4;
+        xv[t] = (g >= 0 && g < L) ? __ldg(xr + g) : 0.0f;
+    }
+    const int j = l - off;
+    const bool has_e = (e != nullptr) && j >= 0 && j < scale * P;
+    const float *er = has_e ? e + (size_t)n * 64 * P + j / scale : nullptr;
+    uint4 *dst = planes + (size_t)n * 16 * L + l;
+#pragma unroll 2
+    for (int c8 = 0; c8 < 8; ++c8) {
+        float v[8];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            float4 a = bs[2 * c8 + h];
+#pragma unroll
+            for (int t = 0; t < 9; ++t) {
+                const float4 wv = ws[t * 16 + 2 * c8 + h];
+                a.x = fmaf(wv.x, xv[t], a.x); a.y = fmaf(wv.y, xv[t], a.y);
+                a.z = fmaf(wv.z, xv[t], a.z); a.w = fmaf(wv.w, xv[t], a.w);
+            }
+            v[4 * h + 0] = fmaxf(a.x, 0.f); v[4 * h + 1] = fmaxf(a.y, 0.f);
+            v[4 * h + 2] = fmaxf(a.z, 0.f); v[4 * h + 3] = fmaxf(a.w, 0.f);
+        }
+        if (has_e) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] += __ldg(er + (size_t)(8 * c8 + i) * P);
+        }
+        float hi[8], lo[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) split_hi_lo(v[i], hi[i], lo[i]);
+        uint4 uh, ul;
+        uh.x = pack_half2(hi[0], hi[1]); uh.y = pack_half2(hi[2], hi[3]); uh.z = pack_half2(hi[4], hi[5]); uh.w = pack_half2(hi[6], hi[7]);
+        ul.x = pack_half2(lo[0], lo[1]); ul.y = pack_half2(lo[2], lo[3]); ul.z = pack_half2(lo[4], lo[5]); ul.w = pack_half2(lo[6], lo[7]);
+        dst[(size_t)c8 * L] = uh;
+        dst[(size_t)(8 + c8) * L] = ul;
+    }
+}
+
+// fp32 C4L4 [n][c/4][l][4]  <->  split planes [n][plane][c8][l][8]
+__global__ void __launch_bounds__(256)
+c4l4_to_planes_kernel(const float4 *__restrict__ act, uint4 *__restrict__ planes, int N, int L) {
+    const int n = blockIdx.z, c8 = blockIdx.y;
+    const int l = blockIdx.x * 256 + threadIdx.x;
+    if (l >= L) return;
+    const float4 a0 = act[((size_t)n * 16 + 2 * c8) * L + l], a1 = act[((size_t)n * 16 + 2 * c8 + 1) * L + l];
+    const float v[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+    float hi[8], lo[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) split_hi_lo(v[i], hi[i], lo[i]);
+    uint4 uh, ul;
+    uh.x = pack_half2(hi[0], hi[1]); uh.y = pack_half2(hi[2], hi[3]); uh.z = pack_half2(hi[4], hi[5]); uh.w = pack_half2(hi[6], hi[7]);
+    ul.x = pack_half2(lo[0], lo[1]); ul.y = pack_half2(lo[2], lo[3]); ul.z = pack_half2(lo[4], lo[5]); ul.w = pack_half2(lo[6], lo[7]);
+    planes[((size_t)n * 16 + c8) * L + l] = uh;
+    planes[((size_t)n * 16 + 8 + c8) * L + l] = ul;
+}
+
+__global__ void __launch_bounds__(256)
+planes_to_c4l4_kernel(const uint4 *__restrict__ planes, float4 *__restrict__ act, int N, int L) {
+    const int n = blockIdx.z, c8 = blockIdx.y;
+    const int l = blockIdx.x * 256 + threadIdx.x;
+    if (l >= L) return;
+    float fh[8], fl[8];
+    unpack8(planes[((size_t)n * 16 + c8) * L + l], fh);
+    unpack8(planes[((size_t)n * 16 + 8 + c8) * L + l], fl);
+    float v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = fh[i] + TC_LO_INV * fl[i];
+    act[((size_t)n * 16 + 2 * c8) * L + l] = make_float4(v[0], v[1], v[2], v[3]);
+    act[((size_t)n * 16 + 2 * c8 + 1) * L + l] = make_float4(v[4], v[5], v[6], v[7]);
+}
+
+// ------------------------------------------------------------------------------------------------ launchers
+int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void *x0, void *out_planes, float *out_mask,
+                    int N, int L, cudaStream_t st) {
+    STOF_REQUIRE(count >= 1 && count <= TC_MAX_LAYERS, STOF_E_INVALID, "chain_tc: %d layers per segment (max %d)", count, TC_MAX_LAYERS);
+    static bool attr = false;
+    if (!attr) {
+        STOF_CUDA(cudaFuncSetAttribute(chain_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+        attr = true;
+    }
+    TcParams p;
+    memset(&p, 0, sizeof(p));
+    int S = 0, Sp = 0;
+    for (int k = 0; k < count; ++k) {
+        p.layer[k] = layers[k];
+        S += layers[k].pad;
+        if (k > 0) Sp += layers[k].pad;
+        STOF_REQUIRE(layers[k].type != TC_LAST || k == count - 1, STOF_E_INVALID, "chain_tc: conv_last must end a segment");
+        STOF_REQUIRE(layers[k].type != TC_RES || k >= 1, STOF_E_INVALID, "chain_tc: a short-skip layer cannot start a segment");
+        STOF_REQUIRE(layers[k].type != TC_LONGSKIP || x0 != nullptr, STOF_E_INVALID, "chain_tc: long skip needs x0");
+    }
+    const int OFF = S + 3;
+    p.n_layers = count;
+    int acc = 0;
+    for (int k = 0; k < count; ++k) {
+        acc += layers[k].pad;
+        p.b_row[k] = OFF - acc;
+    }
+    p.r_in = OFF + 256;
+    STOF_REQUIRE(p.r_in <= TC_R, STOF_E_INVALID, "chain_tc: segment too deep for the smem tile (%d rows)", p.r_in);
+    p.l_shift = p.b_row[0] + Sp;
+    p.t_out = 256 - 2 * Sp;
+    p.tiles_per_row = (L + p.t_out - 1) / p.t_out;
+    const long long total = (long long)N * p.tiles_per_row;
+    STOF_REQUIRE(total < (1ll << 31), STOF_E_INVALID, "chain_tc: too many tiles");
+    p.total_tiles = (int)total;
+    p.N = N; p.L = L;
+    p.in = in; p.x0 = x0; p.out_planes = out_planes; p.out_mask = out_mask;
+    const bool ends_last = layers[count - 1].type == TC_LAST;
+    STOF_REQUIRE(ends_last ? out_mask != nullptr : out_planes != nullptr, STOF_E_INVALID, "chain_tc: missing output buffer");
+    const int grid = (int)(total < kSMs ? total : kSMs);
+    chain_tc_kernel<<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(p);
+    STOF_LAUNCH_CHECK();
+    return STOF_OK;
+}
+
+int launch_x0_split(const float *x, const float *e, int N, int L, int P, int scale, int off, const float *w, const float *b,
+                    void *planes, cudaStream_t st) {
+    dim3 grid((L + 255) / 256, N);
+    x0_split_kernel<<<grid, 256, 0, st>>>(x, e, N, L, P, scale, off, w, b, reinterpret_cast<uint4 *>(planes));
+    STOF_LAUNCH_CHECK();
+    return STOF_OK;
+}
+
+int launch_c4l4_to_planes(const float *act, void *planes, int N, int L, cudaStream_t st) {
+    dim3 grid((L + 255) / 256, 8, N);
+    c4l4_to_planes_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float4 *>(act), reinterpret_cast<uint4 *>(planes), N, L);
+    STOF_LAUNCH_CHECK();
+    return STOF_OK;
+}
+
+int launch_planes_to_c4l4(const void *planes, float *act, int N, int L, cudaStream_t st) {
+    dim3 grid((L + 255) / 256, 8, N);
+    planes_to_c4l4_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const uint4 *>(planes), reinterpret_cast<float4 *>(act), N, L);
+    STOF_LAUNCH_CHECK();
+    return STOF_OK;
+}
+
+}  // namespace stof

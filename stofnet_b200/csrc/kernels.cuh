@@ -18,4 +18,44 @@ int launch_conv_last(const float *in, float *mask, const float *w, const float *
                      cudaStream_t st);
 int launch_espcn_conv2(const float *in, float *out, const float *w, const float *b, int N, int L, cudaStream_t st);
 
+// conv_tc.cu (tcgen05 / TMEM path) ---------------------------------------------------------------
+constexpr int TC_MAX_LAYERS = 6;
+enum TcLayerType { TC_LEAKY = 0, TC_RES = 1, TC_LONGSKIP = 2, TC_LAST = 3 };
+
+struct TcLayer {
+    const void *w;        // packed fp16 taps: [tap][c8][w_rows][8]
+    const float *bias;
+    int taps, pad, type;
+    int stage_bytes;      // bytes of one tap
+    int n_out;            // real output channels (64, or r = 4 for conv_last)
+    int n_stack, n_lo;    // N of the stacked [W_hi; W_lo] MMA and of the X_lo * W_hi MMA
+    int lo_row, lo_col;   // first weight row of the W_hi block used by the second MMA; its first accumulator column
+    int w_rows;           // rows per c8 chunk of a tap
+};
+
+struct TcParams {
+    TcLayer layer[TC_MAX_LAYERS];
+    int n_layers;
+    int b_row[TC_MAX_LAYERS];   // first smem row computed by layer k
+    int r_in;                   // input rows staged per tile
+    int l_shift;                // position of smem row 0 relative to the tile's first output position
+    int t_out;                  // valid output positions per tile
+    int tiles_per_row, total_tiles;
+    int N, L;
+    const void *in;             // split planes [N][2][8][L][8] fp16
+    const void *x0;             // split planes of the long-skip tensor (TC_LONGSKIP), or NULL
+    void *out_planes;           // segment output (split planes) unless the segment ends with TC_LAST
+    float *out_mask;            // (N, 4L) when the segment ends with TC_LAST
+};
+
+// layers[first .. first+count) of the spec list; returns STOF_E_* on error
+int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void *x0, void *out_planes, float *out_mask,
+                    int N, int L, cudaStream_t st);
+// x (N, L) fp32 -> split planes of x0 = act(conv_first(x)) [+ nearest-upsampled E, centred]  (models/stofnet.py:45,96-115)
+int launch_x0_split(const float *x, const float *e, int N, int L, int P, int scale, int off, const float *w, const float *b,
+                    void *planes, cudaStream_t st);
+// fp32 C4L4 activations <-> split planes (debug / hand-over between the SIMT and tensor paths)
+int launch_c4l4_to_planes(const float *act, void *planes, int N, int L, cudaStream_t st);
+int launch_planes_to_c4l4(const void *planes, float *act, int N, int L, cudaStream_t st);
+
 }  // namespace stof

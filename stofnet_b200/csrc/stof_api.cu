@@ -5,6 +5,8 @@
 #include <string.h>
 #include <vector>
 
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 #include "kernels.cuh"
 
@@ -45,6 +47,12 @@ struct stof_model {
     int sgb_scale = 1, sgb_feat = 0, sgb_k = 0;
     stof::DevConv first, last, contract, expand;
     stof::DevConv mid[STOF_MAX_MID_CONVS];
+    // tensor-core path (conv_tc.cu): packed fp16 hi/lo taps of conv2..conv{nb-1} + conv_last, one allocation
+    int path = STOF_PATH_TC;
+    int seg_len = 4;                                  // layers fused per chain launch
+    void *tc_w = nullptr;
+    stof::TcLayer tc_layer[STOF_MAX_MID_CONVS + 1];   // spec list: mid convs then conv_last
+    int n_tc = 0;
     // scratch of stof_infer_host (grow-only)
     static constexpr int kPipe = 2;
     cudaStream_t streams[kPipe] = {nullptr, nullptr};
@@ -75,6 +83,61 @@ static std::vector<float> repack_cikco(const float *w, int Cout, int Cin, int K)
         for (int ci = 0; ci < Cin; ++ci)
             for (int t = 0; t < K; ++t) o[((size_t)ci * K + t) * Cout + co] = w[((size_t)co * Cin + ci) * K + t];
     return o;
+}
+
+
+// ---- tensor-core weight pack ------------------------------------------------------------------------
+// fp32 w -> hi = fp16(w), lo = fp16((w - hi) * 2^11); one tap = [c8][rows][8] fp16 (K-major, no-swizzle core matrices)
+static void split_w(float w, __half &hi, __half &lo) {
+    hi = __float2half_rn(w);
+    lo = __float2half_rn((w - __half2float(hi)) * 2048.0f);
+}
+
+static int upload_tc(stof_model *m, const stof_weights *w) {
+    const int n_mid = w->n_mid;
+    const size_t mid_tap = 8 * 128 * 8, last_tap = 8 * 32 * 8;          // halves per tap
+    std::vector<__half> buf((size_t)n_mid * 7 * mid_tap + 3 * last_tap, __float2half_rn(0.0f));
+    for (int j = 0; j < n_mid; ++j)
+        for (int t = 0; t < 7; ++t) {
+            __half *tap = buf.data() + ((size_t)j * 7 + t) * mid_tap;
+            for (int co = 0; co < 64; ++co)
+                for (int ci = 0; ci < 64; ++ci) {
+                    __half hi, lo;
+                    split_w(w->mid_w[j][((size_t)co * 64 + ci) * 7 + t], hi, lo);
+                    tap[((size_t)(ci >> 3) * 128 + co) * 8 + (ci & 7)] = hi;
+                    tap[((size_t)(ci >> 3) * 128 + 64 + co) * 8 + (ci & 7)] = lo;
+                }
+        }
+    __half *lastp = buf.data() + (size_t)n_mid * 7 * mid_tap;
+    for (int t = 0; t < 3; ++t)
+        for (int u = 0; u < 4; ++u)
+            for (int ci = 0; ci < 64; ++ci) {
+                __half hi, lo;
+                split_w(w->last_w[((size_t)u * 64 + ci) * 3 + t], hi, lo);
+                __half *tap = lastp + (size_t)t * last_tap;
+                tap[((size_t)(ci >> 3) * 32 + u) * 8 + (ci & 7)] = hi;          // rows 0-3   : W_hi   (first MMA, D0)
+                tap[((size_t)(ci >> 3) * 32 + 8 + u) * 8 + (ci & 7)] = lo;      // rows 8-11  : W_lo   (first MMA, D1)
+                tap[((size_t)(ci >> 3) * 32 + 16 + u) * 8 + (ci & 7)] = hi;     // rows 16-19 : W_hi   (second MMA, D1)
+            }
+    if (!m->tc_w) STOF_CUDA(cudaMalloc(&m->tc_w, buf.size() * sizeof(__half)));
+    STOF_CUDA(cudaMemcpy(m->tc_w, buf.data(), buf.size() * sizeof(__half), cudaMemcpyHostToDevice));
+    const __half *base = reinterpret_cast<const __half *>(m->tc_w);
+    for (int j = 0; j < n_mid; ++j) {
+        TcLayer &l = m->tc_layer[j];
+        l.w = base + (size_t)j * 7 * mid_tap;
+        l.bias = m->mid[j].b;
+        l.taps = 7; l.pad = 3;
+        // models/stofnet.py:51-62: conv index i = j + 2; even i -> LeakyReLU, odd i -> res + conv, last -> res1 + conv
+        l.type = (j == n_mid - 1) ? TC_LONGSKIP : ((j & 1) ? TC_RES : TC_LEAKY);
+        l.stage_bytes = 16384; l.n_out = 64; l.n_stack = 128; l.n_lo = 64; l.lo_row = 0; l.lo_col = 64; l.w_rows = 128;
+    }
+    TcLayer &l = m->tc_layer[n_mid];
+    l.w = base + (size_t)n_mid * 7 * mid_tap;
+    l.bias = m->last.b;
+    l.taps = 3; l.pad = 1; l.type = TC_LAST;
+    l.stage_bytes = 4096; l.n_out = 4; l.n_stack = 16; l.n_lo = 16; l.lo_row = 16; l.lo_col = 8; l.w_rows = 32;
+    m->n_tc = n_mid + 1;
+    return STOF_OK;
 }
 
 static int validate(const stof_weights *w) {
@@ -122,6 +185,7 @@ static int set_weights(stof_model *m, const stof_weights *w) {
     for (int i = 0; i < w->n_mid; ++i)
         if ((rc = upload(m->mid[i], repack_cikco(w->mid_w[i], 64, 64, 7), w->mid_b[i], 64))) return rc;
     if ((rc = upload(m->last, repack_cikco(w->last_w, 4, 64, 3), w->last_b, 4))) return rc;
+    if ((rc = upload_tc(m, w))) return rc;
     if (w->contract_w) {
         m->sgb_scale = w->sgb_scale; m->sgb_feat = w->sgb_feat; m->sgb_k = w->sgb_k;
         // 8 cout tiles of 64, each [ci][t][co]
@@ -203,6 +267,41 @@ struct ProfScope {
     ~ProfScope() { if (on) cudaEventRecord(m->ev_pool[slot + 1], st); }
 };
 
+// Tensor-core path: conv1 (+ semi-global block) on CUDA cores / SIMT, then the 64->64 stack and conv_last +
+// shuffle as fused tcgen05 chain segments (conv_tc.cu).  B0/B1/B2 hold split fp16 planes (same bytes as fp32 C4L4).
+static int forward_chunk_tc(stof_model *m, const float *x, int n, int L, float *mask, float *B0, float *B1, float *B2,
+                            float *pooled, float *e, const Plan &pl, cudaStream_t st) {
+    int rc;
+    const bool sgb = m->sgb_scale != 1;
+    int off = 0;
+    if (sgb) {
+        // models/stofnet.py:45,98-107: E = LeakyReLU(expand(maxpool80(LeakyReLU(contract(relu(conv1 x))))))
+        { ProfScope p(m, STOF_PROF_FIRST, st); if ((rc = launch_conv_first(x, n, L, m->first.w, m->first.b, B0, 9, 0, st))) return rc; }
+        { ProfScope p(m, STOF_PROF_CONTRACT, st); if ((rc = launch_contract_pool_simt(B0, pooled, m->contract.w, m->contract.b, n, L, pl.P, st))) return rc; }
+        { ProfScope p(m, STOF_PROF_EXPAND, st); if ((rc = launch_expand(pooled, e, m->expand.w, m->expand.b, n, pl.P, st))) return rc; }
+        off = (L - pl.P * m->sgb_scale) / 2;
+    }
+    // x0 = relu(conv1 x) + upsample(E) as split planes (:45,108-115); also the long skip res1 (:51,62)
+    { ProfScope p(m, STOF_PROF_SGB_ADD, st);
+      if ((rc = launch_x0_split(x, sgb ? e : nullptr, n, L, pl.P, m->sgb_scale, off, m->first.w, m->first.b, B1, st))) return rc; }
+    const void *cur = B1;
+    void *pp[2] = {B2, B0};
+    int which = 0;
+    int j = 0;
+    while (j < m->n_tc) {
+        int cnt = m->seg_len < m->n_tc - j ? m->seg_len : m->n_tc - j;
+        // a segment may not start on a short-skip layer: its residual lives in the previous segment's tile
+        if (j + cnt < m->n_tc && m->tc_layer[j + cnt].type == TC_RES) cnt = (cnt > 1) ? cnt - 1 : cnt + 1;
+        const bool ends = (j + cnt == m->n_tc);
+        ProfScope p(m, ends ? STOF_PROF_LAST : STOF_PROF_MID, st);
+        if ((rc = launch_chain_tc(m->tc_layer + j, cnt, cur, B1, ends ? nullptr : pp[which], ends ? mask : nullptr, n, L, st))) return rc;
+        cur = pp[which];
+        which ^= 1;
+        j += cnt;
+    }
+    return STOF_OK;
+}
+
 static int forward_chunk(stof_model *m, const float *x, int n, int L, float *mask, char *ws, const Plan &pl,
                          cudaStream_t st) {
     float *B0 = reinterpret_cast<float *>(ws);
@@ -218,6 +317,7 @@ static int forward_chunk(stof_model *m, const float *x, int n, int L, float *mas
         ProfScope p(m, STOF_PROF_LAST, st);
         return launch_conv_last(B1, mask, m->last.w, m->last.b, n, L, 32, 1, st);
     }
+    if (m->path == STOF_PATH_TC) return forward_chunk_tc(m, x, n, L, mask, B0, B1, B2, pooled, e, pl, st);
     // models/stofnet.py:45
     { ProfScope p(m, STOF_PROF_FIRST, st); if ((rc = launch_conv_first(x, n, L, m->first.w, m->first.b, B0, 9, 0, st))) return rc; }
     // :48 semi-global block
@@ -299,6 +399,7 @@ extern "C" void stof_model_destroy(stof_model *m) {
         if (m->scratch[i]) cudaFree(m->scratch[i]);
         if (m->streams[i]) cudaStreamDestroy(m->streams[i]);
     }
+    if (m->tc_w) cudaFree(m->tc_w);
     if (m->h_stats) cudaFreeHost(m->h_stats);
     for (cudaEvent_t e : m->ev_pool) cudaEventDestroy(e);
     delete m;
@@ -417,4 +518,29 @@ extern "C" int stof_profile_collect(stof_model *m, double *ms_by_class, int64_t 
     }
     m->ev_used = 0;
     return STOF_OK;
+}
+
+extern "C" int stof_model_set_path(stof_model *m, int path, int layers_per_launch) {
+    STOF_REQUIRE(m != nullptr, STOF_E_INVALID, "stof_model_set_path: model is NULL");
+    STOF_REQUIRE(path == STOF_PATH_SIMT || path == STOF_PATH_TC, STOF_E_INVALID, "stof_model_set_path: path %d", path);
+    STOF_REQUIRE(path == STOF_PATH_SIMT || m->kind == STOF_KIND_STOFNET, STOF_E_UNSUPPORTED,
+                 "stof_model_set_path: the tensor-core path covers StofNet only");
+    if (layers_per_launch > 0) {
+        STOF_REQUIRE(layers_per_launch <= stof::TC_MAX_LAYERS, STOF_E_INVALID, "stof_model_set_path: at most %d layers per launch",
+                     stof::TC_MAX_LAYERS);
+        m->seg_len = layers_per_launch;
+    }
+    m->path = path;
+    return STOF_OK;
+}
+
+extern "C" int stof_chain_segment(stof_model *m, int first, int count, const void *in_planes_dev, const void *x0_planes_dev,
+                                  void *out_dev, int N, int L, void *stream) {
+    STOF_REQUIRE(m != nullptr && m->kind == STOF_KIND_STOFNET, STOF_E_INVALID, "stof_chain_segment: needs a StofNet model");
+    STOF_REQUIRE(first >= 0 && count >= 1 && first + count <= m->n_tc, STOF_E_INVALID,
+                 "stof_chain_segment: layers [%d, %d) of %d", first, first + count, m->n_tc);
+    STOF_REQUIRE(in_planes_dev && out_dev && N > 0 && L > 0, STOF_E_INVALID, "stof_chain_segment: bad arguments");
+    const bool ends = m->tc_layer[first + count - 1].type == stof::TC_LAST;
+    return stof::launch_chain_tc(m->tc_layer + first, count, in_planes_dev, x0_planes_dev, ends ? nullptr : out_dev,
+                                 ends ? reinterpret_cast<float *>(out_dev) : nullptr, N, L, (cudaStream_t)stream);
 }

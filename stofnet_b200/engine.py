@@ -36,6 +36,8 @@ class Engine:
         self.key = None
         self.ws = None
         self.chunk_rows = 0     # 0 = library default
+        self.path = None        # None = library default (tensor-core path for StofNet)
+        self.layers_per_launch = 0
 
     def close(self):
         if self.handle is not None:
@@ -102,8 +104,40 @@ class Engine:
             h = C.c_void_p()
             check(lib.stof_model_create(C.byref(W), device.index if device.index is not None else 0, C.byref(h)))
             self.handle, self.device = h, device
+            self._applied_path = None
         self.key = key
         del keep
+
+    def set_path(self, path, layers_per_launch=0):
+        """path: _lib.PATH_TC (tcgen05, fp16 hi/lo split operands) or _lib.PATH_SIMT (fp32 FFMA)."""
+        self.path, self.layers_per_launch = path, layers_per_launch
+        self._applied_path = None
+
+    def _apply_path(self):
+        want = (self.path, self.layers_per_launch)
+        if self.path is not None and getattr(self, "_applied_path", None) != want:
+            check(lib.stof_model_set_path(self.handle, int(self.path), int(self.layers_per_launch)))
+            self._applied_path = want
+
+    def chain_segment(self, module, first, count, in_planes, x0_planes=None):
+        """Test hook: layers [first, first+count) of conv2..conv{nb-1}, conv_last on split fp16 planes
+        (N, 2, 8, L, 8); returns planes, or the (N, 1, r*L) mask when the range ends with conv_last."""
+        require_cuda(in_planes, "in_planes")
+        dev = in_planes.device
+        self.sync(module, dev)
+        N, _, _, L, _ = in_planes.shape
+        n_tc = module.num_blocks - 1
+        ends = first + count == n_tc
+        in_planes = in_planes.contiguous()
+        if ends:
+            out = torch.empty((N, 1, module.upsample_factor * L), dtype=torch.float32, device=dev)
+        else:
+            out = torch.empty_like(in_planes)
+        with torch.cuda.device(dev):
+            check(lib.stof_chain_segment(self.handle, first, count, in_planes.data_ptr(),
+                                         x0_planes.data_ptr() if x0_planes is not None else None, out.data_ptr(),
+                                         N, L, stream_ptr(dev)))
+        return out
 
     # -- forward ---------------------------------------------------------------------------
     def forward(self, module, x):
@@ -112,6 +146,7 @@ class Engine:
             raise RuntimeError("stofnet_b200: expected input of shape (N, 1, L), got %s" % (tuple(x.shape),))
         dev = x.device
         self.sync(module, dev)
+        self._apply_path()
         x = x.detach().to(torch.float32).contiguous()
         N, _, L = x.shape
         r = module.upsample_factor
@@ -132,6 +167,7 @@ class Engine:
         if dev.type != "cuda":
             raise RuntimeError("stofnet_b200: module must live on a CUDA device (no CPU path)")
         self.sync(module, dev)
+        self._apply_path()
         x_host = x_host.detach().to(torch.float32).contiguous()
         if x_host.dim() == 3:
             x_host = x_host[:, 0, :]

@@ -1,0 +1,135 @@
+"""GPU tests of the tcgen05 chain kernel (conv_tc.cu) through the C ABI.
+
+Layer-level checks feed split fp16 hi/lo planes into stof_chain_segment and compare with a float64 torch restatement of
+the same layers (models/stofnet.py:51-65 of the reference); end-to-end checks live in test_gpu_parity.py, which runs the
+tensor-core path by default."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from conftest import STOF_CKPTS
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 2e-5      # of max |reference|: fp32 accumulation-order noise + 2^-22 operand split
+
+
+@pytest.fixture(scope="module")
+def sb():
+    import stofnet_b200
+    assert torch.cuda.is_available()
+    return stofnet_b200
+
+
+@pytest.fixture(scope="module")
+def dev():
+    return torch.device("cuda:0")
+
+
+def to_planes(a):
+    """(N, 64, L) fp32 -> (N, 2, 8, L, 8) fp16 hi/lo planes."""
+    N, C, L = a.shape
+    c = a.clamp(-65504.0, 65504.0)
+    hi = c.half()
+    lo = ((c - hi.float()) * 2048.0).half()
+
+    def lay(h):
+        return h.view(N, 8, 8, L).permute(0, 1, 3, 2)
+    return torch.stack([lay(hi), lay(lo)], 1).contiguous()
+
+
+def from_planes(p):
+    N, _, _, L, _ = p.shape
+    v = p[:, 0].float() + p[:, 1].float() / 2048.0
+    return v.permute(0, 1, 3, 2).reshape(N, 64, L)
+
+
+def ref_layers(model, x, x0, first, count):
+    """float64 reference of layers [first, first+count) on CPU; x, x0: (N, 64, L)."""
+    n_mid = model.num_blocks - 2
+    x = x.double().cpu()
+    x0 = x0.double().cpu() if x0 is not None else None
+    res = x.clone()          # only used when the range starts on an even (LeakyReLU) layer: res = its input
+    for j in range(first, first + count):
+        if j == n_mid:
+            w, b = model.conv_last.weight.double().cpu(), model.conv_last.bias.double().cpu()
+            y = F.conv1d(x, w, b, padding=1)                     # (N, 4, L)
+            return y.permute(0, 2, 1).reshape(y.shape[0], 1, -1)  # sample shuffle, C_long = 1
+        conv = getattr(model, "conv%d" % (j + 2))
+        y = F.conv1d(x, conv.weight.double().cpu(), conv.bias.double().cpu(), padding=3)
+        if j == n_mid - 1:
+            x = x0 + y
+        elif j % 2 == 0:
+            res = x
+            x = F.leaky_relu(y, 0.01)
+        else:
+            x = res + y
+    return x
+
+
+def _model(sb, golden, name, dev):
+    sd = {k: torch.from_numpy(v) for k, v in golden("weights_%s.npz" % name).items()}
+    return sb.build_model(sd, dev)
+
+
+def _check(got, ref, what):
+    ref = ref.float()
+    err = (got.cpu() - ref).abs().max().item() / ref.abs().max().item()
+    assert err <= REL_TOL, (what, err)
+
+
+@pytest.mark.parametrize("first,count,L", [(0, 1, 700), (0, 2, 700), (0, 4, 1300), (4, 4, 256), (2, 2, 250), (0, 6, 999)])
+def test_chain_mid_layers(sb, dev, golden, first, count, L):
+    model = _model(sb, golden, "different-armadillo", dev)
+    g = torch.Generator().manual_seed(100 * first + count)
+    x = torch.randn(3, 64, L, generator=g) * 2.0
+    out = model._engine.chain_segment(model, first, count, to_planes(x.to(dev)))
+    torch.cuda.synchronize()
+    _check(from_planes(out), ref_layers(model, x, None, first, count), (first, count, L))
+
+
+@pytest.mark.parametrize("name", ["different-armadillo", "breezy-violet"])
+@pytest.mark.parametrize("first,count", [(10, 2), (8, 4), (10, 1), (11, 1)])
+def test_chain_tail_with_long_skip_and_shuffle(sb, dev, golden, name, first, count):
+    model = _model(sb, golden, name, dev)
+    L = 900
+    g = torch.Generator().manual_seed(7)
+    x = torch.randn(2, 64, L, generator=g)
+    x0 = torch.randn(2, 64, L, generator=g)
+    out = model._engine.chain_segment(model, first, count, to_planes(x.to(dev)), to_planes(x0.to(dev)))
+    torch.cuda.synchronize()
+    ref = ref_layers(model, x, x0, first, count)
+    if first + count == model.num_blocks - 1:
+        assert out.shape == (2, 1, 4 * L)
+        _check(out, ref, (name, first, count))
+    else:
+        _check(from_planes(out), ref, (name, first, count))
+
+
+def test_chain_large_magnitude_and_edges(sb, dev, golden):
+    """values beyond the fp16 normal range of the lo plane, exact zeros, and a row shorter than one tile"""
+    model = _model(sb, golden, "graceful-snow", dev)
+    for L in (80, 129, 239):
+        g = torch.Generator().manual_seed(L)
+        x = torch.randn(5, 64, L, generator=g) * torch.tensor([1e-4, 1.0, 50.0, 0.0, 3.0]).view(5, 1, 1)
+        out = model._engine.chain_segment(model, 0, 4, to_planes(x.to(dev)))
+        torch.cuda.synchronize()
+        _check(from_planes(out), ref_layers(model, x, None, 0, 4), L)
+
+
+@pytest.mark.parametrize("name", STOF_CKPTS)
+@pytest.mark.parametrize("seg", [1, 2, 4, 6])
+def test_forward_tc_matches_simt(sb, dev, golden, name, seg):
+    from stofnet_b200 import _lib
+    from stofnet_b200.synth import synth_waveforms
+    model = _model(sb, golden, name, dev)
+    x = torch.from_numpy(synth_waveforms(6, 1280, seed=3, rf=10)).unsqueeze(1).to(dev)
+    with torch.no_grad():
+        model._engine.set_path(_lib.PATH_SIMT)
+        a = model(x)
+        model._engine.set_path(_lib.PATH_TC, seg)
+        b = model(x)
+    torch.cuda.synchronize()
+    err = (a - b).abs().max().item() / a.abs().max().item()
+    assert err <= REL_TOL, (name, seg, err)
