@@ -20,7 +20,8 @@
 //     layer k+1 only depends on blocks <= b of layer k and the tensor pipe never waits for a whole layer.
 //   * weights stream through a 4-stage ring of 16 KB taps filled by bulk async copies (TMA engine) on mbarriers.
 //
-// Roles: warp 0 = producer (input tile + weight ring), warp 1 = MMA issuer + TMEM owner, warps 2-5 = epilogue.
+// Roles: warp 0 = producer (input tile + weight ring), warps 1-2 = MMA issuers (one per 128-row block; warp 1 owns
+// TMEM), warps 3-10 = epilogue.
 #include <cuda_fp16.h>
 #include <string.h>
 
@@ -32,14 +33,15 @@ namespace stof {
 
 using namespace ptx;
 
-constexpr int TC_THREADS = 192;
+constexpr int TC_THREADS = 352;                         // 1 producer + 2 MMA issuers + 8 epilogue warps
+constexpr int TC_EPI_WARPS = 8;
 constexpr int TC_R = 280;                              // smem rows per (plane, c8) slab
 constexpr int TC_SLAB = TC_R * 16;                     // bytes of one (plane, c8) slab
 constexpr int TC_PLANE = 8 * TC_SLAB;                  // one fp16 plane (hi or lo): 64 channels
 constexpr int TC_BUF = 2 * TC_PLANE;                   // hi + lo
 constexpr int TC_STAGES = 4;
 constexpr int TC_STAGE_BYTES = 16384;                  // one k7 tap: [8 c8][128 n][8] fp16
-constexpr int TC_GROUP = 4;                            // taps issued per block before switching block (<= stages)
+constexpr int TC_GROUP = 4;                            // max taps issued per block before switching block (<= stages)
 constexpr float TC_LO_SCALE = 2048.0f;                 // 2^11
 constexpr float TC_LO_INV = 1.0f / 2048.0f;
 
@@ -61,6 +63,19 @@ __device__ __forceinline__ uint32_t pack_half2(float a, float b) {
     return *reinterpret_cast<uint32_t *>(&h);
 }
 
+// two fp32 -> packed fp16x2 (round to nearest, saturated to the finite fp16 range); a in the low half
+__device__ __forceinline__ uint32_t cvt_sat_half2(float a, float b) {
+    uint32_t r;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+    return r;
+}
+// (v0, v1) -> packed hi = fp16(v), packed lo = fp16((v - hi) * 2^11)
+__device__ __forceinline__ void split_pair(float v0, float v1, uint32_t &hi, uint32_t &lo) {
+    hi = cvt_sat_half2(v0, v1);
+    const float2 h = __half22float2(*reinterpret_cast<const __half2 *>(&hi));
+    lo = cvt_sat_half2((v0 - h.x) * TC_LO_SCALE, (v1 - h.y) * TC_LO_SCALE);
+}
+
 // v -> (hi, lo) with hi = fp16(v) (saturated to the finite range), lo = fp16((v - hi) * 2^11)
 __device__ __forceinline__ void split_hi_lo(float v, float &hi, float &lo) {
     const float c = fminf(fmaxf(v, -65504.0f), 65504.0f);
@@ -77,6 +92,17 @@ __device__ __forceinline__ void unpack8(const uint4 &u, float (&f)[8]) {
         f[2 * i + 1] = t.y;
     }
 }
+
+// optional timeline (stof_debug_set_timeline): CTA 0 appends (code, clock64) pairs; code = role<<24 | k<<16 | b<<8 | what
+__device__ __forceinline__ void tl_event(unsigned long long *tl, int cap, uint32_t code) {
+    if (tl == nullptr || blockIdx.x != 0) return;
+    const unsigned long long i = atomicAdd(tl, 1ull);
+    if ((int)i < cap) {
+        tl[1 + 2 * i] = code;
+        tl[2 + 2 * i] = (unsigned long long)clock64();
+    }
+}
+#define TL(role, k, b, what) tl_event(p.timeline, p.timeline_cap, ((role) << 24) | ((uint32_t)(k) << 16) | ((uint32_t)(b) << 8) | (what))
 
 __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -101,16 +127,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
     if (threadIdx.x == 0) {
         for (int s = 0; s < 4; ++s) {
             mbar_init(BAR_W_FULL(s), 1);
-            mbar_init(BAR_W_EMPTY(s), 1);
+            mbar_init(BAR_W_EMPTY(s), 2);
             mbar_init(BAR_ACC_FULL(s), 1);
-            mbar_init(BAR_ACC_EMPTY(s), 4);
+            mbar_init(BAR_ACC_EMPTY(s), TC_EPI_WARPS);
         }
         for (int k = 0; k < TC_MAX_LAYERS; ++k) {
-            mbar_init(BAR_ACT(k, 0), 4);
-            mbar_init(BAR_ACT(k, 1), 4);
+            mbar_init(BAR_ACT(k, 0), TC_EPI_WARPS);
+            mbar_init(BAR_ACT(k, 1), TC_EPI_WARPS);
         }
         mbar_init(BAR_IN_FULL, 1);
-        mbar_init(BAR_TILE_FREE, 4);
+        mbar_init(BAR_TILE_FREE, TC_EPI_WARPS);
         fence_mbar_init();
     }
     if (warp == 1) tmem_alloc(sbase + TC_OFF_TMEM, 512);
@@ -133,11 +159,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
             // the previous tile must be completely consumed before its input buffer is overwritten
             mbar_wait(BAR_TILE_FREE, (uint32_t)(it & 1) ^ 1u);
             const int r_lo = max(0, -l_org), r_hi = min(r_in, p.L - l_org);
-            // rows outside the waveform are the conv's zero padding
-            for (int idx = lane; idx < 16 * r_in; idx += 32) {
-                const int slab = idx / r_in, r = idx - slab * r_in;
-                if (r < r_lo || r >= r_hi)
-                    *reinterpret_cast<uint4 *>(smem + TC_OFF_P + slab * TC_SLAB + r * 16) = make_uint4(0, 0, 0, 0);
+            // rows outside the waveform are the conv's zero padding (only tiles at the ends of a row have any)
+            if (r_lo > 0 || r_hi < r_in) {
+                for (int slab = 0; slab < 16; ++slab) {
+                    uint8_t *sl = smem + TC_OFF_P + slab * TC_SLAB;
+                    for (int r = lane; r < r_lo; r += 32) *reinterpret_cast<uint4 *>(sl + r * 16) = make_uint4(0, 0, 0, 0);
+                    for (int r = r_hi + lane; r < r_in; r += 32) *reinterpret_cast<uint4 *>(sl + r * 16) = make_uint4(0, 0, 0, 0);
+                }
             }
             fence_proxy_async_smem();
             __syncwarp();
@@ -163,92 +191,107 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
             }
             __syncwarp();
         }
-    } else if (warp == 1) {
-        // =================================== MMA issuer ==================================================
-        if (lane == 0) {
-            uint32_t seq0 = 0, q0 = 0;
-            int it = 0;
-            for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
-                mbar_wait(BAR_IN_FULL, (uint32_t)(it & 1));
-                tc_fence_after_sync();
-                for (int k = 0; k < n_layers; ++k) {
-                    const TcLayer &ly = p.layer[k];
-                    const uint32_t in_base = sbase + ((k & 1) ? TC_OFF_Q : TC_OFF_P);
-                    const uint32_t idesc_a = umma_idesc_f16(128, ly.n_stack);
-                    const uint32_t idesc_b = umma_idesc_f16(128, ly.n_lo);
-                    const uint32_t w_lbo = (uint32_t)ly.w_rows * 16u;          // K-chunk stride of the weight stage
-                    for (int g0 = 0; g0 < ly.taps; g0 += TC_GROUP) {
-                        const int g1 = min(ly.taps, g0 + TC_GROUP);
-                        for (int b = 0; b < 2; ++b) {
-                            const uint32_t q = q0 + b;
-                            const uint32_t d_tmem = tmem0 + (q & 3u) * 128u;
-                            if (g0 == 0) {
-                                mbar_wait(BAR_ACC_EMPTY(q & 3u), ((q >> 2) & 1u) ^ 1u);
-                                if (k > 0) mbar_wait(BAR_ACT(k - 1, b), (uint32_t)(it & 1));
-                                tc_fence_after_sync();
-                            }
-                            const int row0 = p.b_row[k] + 128 * b - ly.pad;
-                            for (int t = g0; t < g1; ++t) {
-                                const uint32_t seq = seq0 + t;
-                                const int s = seq & 3;
-                                mbar_wait(BAR_W_FULL(s), (seq >> 2) & 1u);
-                                tc_fence_after_sync();
-                                const uint32_t a_row = in_base + (uint32_t)(row0 + t) * 16u;
-                                const uint32_t w_st = sbase + TC_OFF_W + s * TC_STAGE_BYTES;
-#pragma unroll
-                                for (int ks = 0; ks < 4; ++ks) {
-                                    const uint64_t a_hi = umma_desc(a_row + 2 * ks * TC_SLAB, TC_SLAB, 128);
-                                    const uint64_t a_lo = umma_desc(a_row + TC_PLANE + 2 * ks * TC_SLAB, TC_SLAB, 128);
-                                    const uint64_t b_all = umma_desc(w_st + 2 * ks * w_lbo, w_lbo, 128);
-                                    const uint64_t b_hi = umma_desc(w_st + 2 * ks * w_lbo + (uint32_t)ly.lo_row * 16u, w_lbo, 128);
-                                    umma_f16(d_tmem, a_hi, b_all, idesc_a, (t > 0 || ks > 0) ? 1u : 0u);
-                                    umma_f16(d_tmem + (uint32_t)ly.lo_col, a_lo, b_hi, idesc_b, 1u);
-                                }
-                                if (b == 1) umma_commit(BAR_W_EMPTY(s));
-                            }
-                            if (g1 == ly.taps) umma_commit(BAR_ACC_FULL(q & 3u));
-                        }
-                    }
-                    seq0 += ly.taps;
-                    q0 += 2;
+    } else if (warp <= 2) {
+        // =================================== MMA issuers =================================================
+        // Two issuing warps, one per 128-row block of the tile (warp 1 -> block 0, warp 2 -> block 1).  The tensor pipe's
+        // queue is shallow, so a single issuing thread exposes its own barrier waits and descriptor arithmetic; two
+        // independent streams (different accumulators) hide each other's issue gaps and the lagging stream's MMAs cover
+        // the leading stream's epilogue wait.  The weight ring bounds the lag to TC_STAGES taps.
+        // Each warp runs warp-uniform control flow (descriptors stay in uniform registers); one elected lane issues.
+        // Descriptor low word = (addr >> 4) | (LBO >> 4) << 16; the high word (SBO = 128 B, version 1) is constant.
+        constexpr uint32_t kDescHi = (128u >> 4) | (1u << 14);
+        constexpr uint32_t kALoBase = (uint32_t)(TC_SLAB >> 4) << 16;            // A: LBO = one slab
+        const int b = warp - 1;
+        uint32_t seq0 = 0, lseq = 0;
+        int it = 0;
+        for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+            if (b == 0 && lane == 0) TL(1u, 0, 0, 1);
+            mbar_wait(BAR_IN_FULL, (uint32_t)(it & 1));
+            tc_fence_after_sync();
+            if (b == 0 && lane == 0) TL(1u, 0, 0, 2);
+            for (int k = 0; k < n_layers; ++k, ++lseq) {
+                const TcLayer &ly = p.layer[k];
+                const int taps = ly.taps;
+                const uint32_t a_base = (((sbase + ((k & 1) ? TC_OFF_Q : TC_OFF_P)) >> 4) | kALoBase) +
+                                        (uint32_t)(p.b_row[k] - ly.pad + 128 * b);
+                const uint32_t idesc_a = umma_idesc_f16(128, ly.n_stack);
+                const uint32_t idesc_b = umma_idesc_f16(128, ly.n_lo);
+                const uint32_t w_rows = (uint32_t)ly.w_rows;                    // K-chunk stride of a weight stage / 16
+                const uint32_t w_hi_off = (uint32_t)ly.lo_row;
+                const uint32_t lo_col = (uint32_t)ly.lo_col;
+                const uint32_t set = (uint32_t)b + 2u * (lseq & 1u);
+                const uint32_t d_tmem = tmem0 + set * 128u;
+                if (lane == 0) TL(1u + b, k, b, 3);
+                mbar_wait(BAR_ACC_EMPTY(set), ((lseq >> 1) & 1u) ^ 1u);
+                if (k > 0) {
+                    mbar_wait(BAR_ACT(k - 1, 0), (uint32_t)(it & 1));
+                    if (b == 1) mbar_wait(BAR_ACT(k - 1, 1), (uint32_t)(it & 1));
                 }
+                tc_fence_after_sync();
+                for (int t = 0; t < taps; ++t) {
+                    const uint32_t seq = seq0 + t;
+                    const uint32_t s = seq & 3u;
+                    mbar_wait(BAR_W_FULL(s), (seq >> 2) & 1u);
+                    tc_fence_after_sync();
+                    if (elect_one()) {
+                        const uint32_t a_lo = a_base + (uint32_t)t;
+                        const uint32_t w_lo = ((sbase + TC_OFF_W + s * TC_STAGE_BYTES) >> 4) | (w_rows << 16);
+#pragma unroll
+                        for (int ks = 0; ks < 4; ++ks) {
+                            const uint64_t da_hi = make_desc(a_lo + 2 * ks * TC_R, kDescHi);
+                            const uint64_t da_lo = make_desc(a_lo + (8 + 2 * ks) * TC_R, kDescHi);
+                            const uint64_t db_all = make_desc(w_lo + 2 * ks * w_rows, kDescHi);
+                            const uint64_t db_hi = make_desc(w_lo + 2 * ks * w_rows + w_hi_off, kDescHi);
+                            umma_f16(d_tmem, da_hi, db_all, idesc_a, (t > 0 || ks > 0) ? 1u : 0u);
+                            umma_f16(d_tmem + lo_col, da_lo, db_hi, idesc_b, 1u);
+                        }
+                        umma_commit(BAR_W_EMPTY(s));                             // this stream is done with the stage
+                        if (t == taps - 1) umma_commit(BAR_ACC_FULL(set));
+                    }
+                    __syncwarp();
+                }
+                seq0 += taps;
             }
         }
-        __syncwarp();
     } else {
         // =================================== epilogue ====================================================
+        // 8 warps: warp quadrant (warp & 3) selects the 32 TMEM lanes, group (0/1) the 32-channel half of the block.
         const int quad = warp & 3;
+        const int egrp = (warp - 3) >> 2;
         const int trow = 32 * quad + lane;                       // TMEM lane = row within the 128-block
         const uint32_t lane_addr = (uint32_t)(32 * quad) << 16;
-        uint32_t q0 = 0;
+        uint32_t lseq = 0;
         int it = 0;
         for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
             const int n = tile / p.tiles_per_row;
             const int l0 = (tile - n * p.tiles_per_row) * p.t_out;
             const int l_org = l0 - p.l_shift;
             const int l_end = min(l0 + p.t_out, p.L);
-            for (int k = 0; k < n_layers; ++k) {
+            for (int k = 0; k < n_layers; ++k, ++lseq) {
                 const TcLayer &ly = p.layer[k];
+                const int type = ly.type;
                 const bool last_in_seg = (k == n_layers - 1);
                 uint8_t *outbuf = smem + ((k & 1) ? TC_OFF_P : TC_OFF_Q);
                 const float *bias = s_bias + 64 * k;
                 for (int b = 0; b < 2; ++b) {
-                    const uint32_t q = q0 + b;
+                    const uint32_t set = (uint32_t)b + 2u * (lseq & 1u);
                     const int r = p.b_row[k] + 128 * b + trow;
                     const int l = l_org + r;
                     const bool inside = (l >= 0) && (l < p.L);
-                    mbar_wait(BAR_ACC_FULL(q & 3u), (q >> 2) & 1u);
+                    mbar_wait(BAR_ACC_FULL(set), (lseq >> 1) & 1u);
                     tc_fence_after_sync();
-                    const uint32_t d_tmem = tmem0 + (q & 3u) * 128u + lane_addr;
-                    if (ly.type == TC_LAST) {
-                        // conv_last + SampleShuffle1D: mask[n][4 l + u] = D0[u] + 2^-11 D1[u] + bias[u]
+                    const uint32_t d_tmem = tmem0 + set * 128u + lane_addr;
+                    if (type == TC_LAST) {
+                        // conv_last + SampleShuffle1D: mask[n][4 l + u] = D0[u] + 2^-11 D1[u] + bias[u]   (group 0 only)
                         uint32_t d[16];
-                        tmem_ld16(d_tmem, d);
-                        tmem_ld_wait();
+                        if (egrp == 0) {
+                            tmem_ld16(d_tmem, d);
+                            tmem_ld_wait();
+                        }
                         tc_fence_before_sync();
                         __syncwarp();
-                        if (lane == 0) mbar_arrive(BAR_ACC_EMPTY(q & 3u));
-                        if (l >= l0 && l < l_end) {
+                        if (lane == 0) mbar_arrive(BAR_ACC_EMPTY(set));
+                        if (egrp == 0 && l >= l0 && l < l_end) {
                             float4 o;
                             o.x = (__uint_as_float(d[0]) + TC_LO_INV * __uint_as_float(d[8])) + bias[0];
                             o.y = (__uint_as_float(d[1]) + TC_LO_INV * __uint_as_float(d[9])) + bias[1];
@@ -259,70 +302,63 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                         continue;
                     }
                     const bool store_global = last_in_seg && (l >= l0) && (l < l_end);
-#pragma unroll 1
-                    for (int c16 = 0; c16 < 4; ++c16) {
-                        uint32_t d0[16], d1[16];
-                        tmem_ld16(d_tmem + 16 * c16, d0);
-                        tmem_ld16(d_tmem + 64 + 16 * c16, d1);
-                        tmem_ld_wait();
-                        if (c16 == 3) {                                  // accumulator fully read: hand it back
-                            tc_fence_before_sync();
-                            __syncwarp();
-                            if (lane == 0) mbar_arrive(BAR_ACC_EMPTY(q & 3u));
-                        }
-                        float v[16];
+                    // this group's 32 channels: columns [32 egrp, +32) of D0 and of D1 (at +64)
+                    uint32_t d0[32], d1[32];
+                    tmem_ld16(d_tmem + 32 * egrp, *reinterpret_cast<uint32_t(*)[16]>(&d0[0]));
+                    tmem_ld16(d_tmem + 32 * egrp + 16, *reinterpret_cast<uint32_t(*)[16]>(&d0[16]));
+                    tmem_ld16(d_tmem + 64 + 32 * egrp, *reinterpret_cast<uint32_t(*)[16]>(&d1[0]));
+                    tmem_ld16(d_tmem + 64 + 32 * egrp + 16, *reinterpret_cast<uint32_t(*)[16]>(&d1[16]));
+                    tmem_ld_wait();
+                    tc_fence_before_sync();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(BAR_ACC_EMPTY(set));              // accumulator read: hand it back
 #pragma unroll
-                        for (int i = 0; i < 16; ++i)
-                            v[i] = (__uint_as_float(d0[i]) + TC_LO_INV * __uint_as_float(d1[i])) + bias[16 * c16 + i];
-                        if (ly.type == TC_LEAKY) {
+                    for (int h = 0; h < 4; ++h) {                                  // 4 chunks of 8 channels
+                        const int c8 = 4 * egrp + h;
+                        float v[8];
 #pragma unroll
-                            for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], kLeakySlope * v[i]);
+                        for (int i = 0; i < 8; ++i)
+                            v[i] = (__uint_as_float(d0[8 * h + i]) + TC_LO_INV * __uint_as_float(d1[8 * h + i])) + bias[8 * c8 + i];
+                        if (type == TC_LEAKY) {
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], kLeakySlope * v[i]);
                         } else {
                             // residual: short skip = value stored at this row of the output buffer (x two layers back);
                             // long skip (res1) = x0 planes in global memory
-#pragma unroll
-                            for (int h = 0; h < 2; ++h) {
-                                const int c8 = 2 * c16 + h;
-                                uint4 rh, rl;
-                                if (ly.type == TC_RES) {
-                                    rh = *reinterpret_cast<const uint4 *>(outbuf + c8 * TC_SLAB + r * 16);
-                                    rl = *reinterpret_cast<const uint4 *>(outbuf + TC_PLANE + c8 * TC_SLAB + r * 16);
-                                } else if (inside) {
-                                    const uint4 *x0 = reinterpret_cast<const uint4 *>(p.x0) + (size_t)n * 16 * p.L;
-                                    rh = __ldg(x0 + (size_t)c8 * p.L + l);
-                                    rl = __ldg(x0 + (size_t)(8 + c8) * p.L + l);
-                                } else {
-                                    rh = make_uint4(0, 0, 0, 0);
-                                    rl = rh;
-                                }
-                                float fh[8], fl[8];
-                                unpack8(rh, fh);
-                                unpack8(rl, fl);
-#pragma unroll
-                                for (int i = 0; i < 8; ++i) v[8 * h + i] += fh[i] + TC_LO_INV * fl[i];
+                            uint4 rh, rl;
+                            if (type == TC_RES) {
+                                rh = *reinterpret_cast<const uint4 *>(outbuf + c8 * TC_SLAB + r * 16);
+                                rl = *reinterpret_cast<const uint4 *>(outbuf + TC_PLANE + c8 * TC_SLAB + r * 16);
+                            } else if (inside) {
+                                const uint4 *x0 = reinterpret_cast<const uint4 *>(p.x0) + (size_t)n * 16 * p.L;
+                                rh = __ldg(x0 + (size_t)c8 * p.L + l);
+                                rl = __ldg(x0 + (size_t)(8 + c8) * p.L + l);
+                            } else {
+                                rh = make_uint4(0, 0, 0, 0);
+                                rl = rh;
                             }
+                            float fh[8], fl[8];
+                            unpack8(rh, fh);
+                            unpack8(rl, fl);
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) v[i] += fh[i] + TC_LO_INV * fl[i];
                         }
+                        if (!inside) {
 #pragma unroll
-                        for (int h = 0; h < 2; ++h) {
-                            float hi[8], lo[8];
-#pragma unroll
-                            for (int i = 0; i < 8; ++i) {
-                                split_hi_lo(inside ? v[8 * h + i] : 0.0f, hi[i], lo[i]);
-                            }
-                            uint4 uh, ul;
-                            uh.x = pack_half2(hi[0], hi[1]); uh.y = pack_half2(hi[2], hi[3]);
-                            uh.z = pack_half2(hi[4], hi[5]); uh.w = pack_half2(hi[6], hi[7]);
-                            ul.x = pack_half2(lo[0], lo[1]); ul.y = pack_half2(lo[2], lo[3]);
-                            ul.z = pack_half2(lo[4], lo[5]); ul.w = pack_half2(lo[6], lo[7]);
-                            const int c8 = 2 * c16 + h;
-                            if (!last_in_seg) {
-                                *reinterpret_cast<uint4 *>(outbuf + c8 * TC_SLAB + r * 16) = uh;
-                                *reinterpret_cast<uint4 *>(outbuf + TC_PLANE + c8 * TC_SLAB + r * 16) = ul;
-                            } else if (store_global) {
-                                uint4 *dst = reinterpret_cast<uint4 *>(p.out_planes) + (size_t)n * 16 * p.L;
-                                dst[(size_t)c8 * p.L + l] = uh;
-                                dst[(size_t)(8 + c8) * p.L + l] = ul;
-                            }
+                            for (int i = 0; i < 8; ++i) v[i] = 0.0f;               // per-layer zero padding outside the row
+                        }
+                        uint4 uh, ul;
+                        split_pair(v[0], v[1], uh.x, ul.x);
+                        split_pair(v[2], v[3], uh.y, ul.y);
+                        split_pair(v[4], v[5], uh.z, ul.z);
+                        split_pair(v[6], v[7], uh.w, ul.w);
+                        if (!last_in_seg) {
+                            *reinterpret_cast<uint4 *>(outbuf + c8 * TC_SLAB + r * 16) = uh;
+                            *reinterpret_cast<uint4 *>(outbuf + TC_PLANE + c8 * TC_SLAB + r * 16) = ul;
+                        } else if (store_global) {
+                            uint4 *dst = reinterpret_cast<uint4 *>(p.out_planes) + (size_t)n * 16 * p.L;
+                            dst[(size_t)c8 * p.L + l] = uh;
+                            dst[(size_t)(8 + c8) * p.L + l] = ul;
                         }
                     }
                     if (!last_in_seg) {
@@ -330,8 +366,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                         __syncwarp();
                         if (lane == 0) mbar_arrive(BAR_ACT(k, b));
                     }
+                    if (warp == 3 && lane == 0) TL(3u, k, b, 3);
                 }
-                q0 += 2;
             }
             // every read of this tile's buffers by this warp is done
             __syncwarp();
@@ -439,6 +475,10 @@ planes_to_c4l4_kernel(const uint4 *__restrict__ planes, float4 *__restrict__ act
 }
 
 // ------------------------------------------------------------------------------------------------ launchers
+static unsigned long long *g_timeline = nullptr;
+static int g_timeline_cap = 0;
+void set_chain_timeline(void *dev_buf, int cap) { g_timeline = reinterpret_cast<unsigned long long *>(dev_buf); g_timeline_cap = cap; }
+
 int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void *x0, void *out_planes, float *out_mask,
                     int N, int L, cudaStream_t st) {
     STOF_REQUIRE(count >= 1 && count <= TC_MAX_LAYERS, STOF_E_INVALID, "chain_tc: %d layers per segment (max %d)", count, TC_MAX_LAYERS);
@@ -475,6 +515,7 @@ int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void
     p.total_tiles = (int)total;
     p.N = N; p.L = L;
     p.in = in; p.x0 = x0; p.out_planes = out_planes; p.out_mask = out_mask;
+    p.timeline = g_timeline; p.timeline_cap = g_timeline_cap;
     const bool ends_last = layers[count - 1].type == TC_LAST;
     STOF_REQUIRE(ends_last ? out_mask != nullptr : out_planes != nullptr, STOF_E_INVALID, "chain_tc: missing output buffer");
     const int grid = (int)(total < kSMs ? total : kSMs);

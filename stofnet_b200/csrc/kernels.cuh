@@ -46,7 +46,10 @@ struct TcParams {
     const void *x0;             // split planes of the long-skip tensor (TC_LONGSKIP), or NULL
     void *out_planes;           // segment output (split planes) unless the segment ends with TC_LAST
     float *out_mask;            // (N, 4L) when the segment ends with TC_LAST
+    unsigned long long *timeline;   // debug: [0] = event count, then (code, clock64) pairs written by CTA 0; or NULL
+    int timeline_cap;
 };
+void set_chain_timeline(void *dev_buf, int cap);
 
 // layers[first .. first+count) of the spec list; returns STOF_E_* on error
 int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void *x0, void *out_planes, float *out_mask,
@@ -54,6 +57,9 @@ int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void
 // x (N, L) fp32 -> split planes of x0 = act(conv_first(x)) [+ nearest-upsampled E, centred]  (models/stofnet.py:45,96-115)
 int launch_x0_split(const float *x, const float *e, int N, int L, int P, int scale, int off, const float *w, const float *b,
                     void *planes, cudaStream_t st);
+// contract_tc.cu: pooled = maxpool80(LeakyReLU(contract_conv(relu(conv1 x)))) on tcgen05, conv1 recomputed per tile
+int launch_contract_pool_tc(const float *x, const void *w, const float *bias, const float *w1, const float *b1, float *pooled,
+                            int N, int L, int P, cudaStream_t st);
 // fp32 C4L4 activations <-> split planes (debug / hand-over between the SIMT and tensor paths)
 int launch_c4l4_to_planes(const float *act, void *planes, int N, int L, cudaStream_t st);
 int launch_planes_to_c4l4(const void *planes, float *act, int N, int L, cudaStream_t st);

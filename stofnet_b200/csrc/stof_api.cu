@@ -51,6 +51,7 @@ struct stof_model {
     int path = STOF_PATH_TC;
     int seg_len = 4;                                  // layers fused per chain launch
     void *tc_w = nullptr;
+    void *tc_contract_w = nullptr;                    // contract conv: [4 slices][5 taps][8 c8][W_hi 128 | W_lo 128][8] fp16
     stof::TcLayer tc_layer[STOF_MAX_MID_CONVS + 1];   // spec list: mid convs then conv_last
     int n_tc = 0;
     // scratch of stof_infer_host (grow-only)
@@ -196,6 +197,22 @@ static int set_weights(stof_model *m, const stof_weights *w) {
         }
         if ((rc = upload(m->contract, cw, w->contract_b, 512))) return rc;
         if ((rc = upload(m->expand, repack_cikco(w->expand_w, 64, 512, 5), w->expand_b, 64))) return rc;
+        {
+            std::vector<__half> buf((size_t)4 * 5 * 8 * 256 * 8);
+            for (int sl = 0; sl < 4; ++sl)
+                for (int t = 0; t < 5; ++t) {
+                    __half *tap = buf.data() + ((size_t)sl * 5 + t) * 8 * 256 * 8;
+                    for (int r = 0; r < 128; ++r)
+                        for (int ci = 0; ci < 64; ++ci) {
+                            __half hi, lo;
+                            split_w(w->contract_w[((size_t)(sl * 128 + r) * 64 + ci) * 5 + t], hi, lo);
+                            tap[((size_t)(ci >> 3) * 256 + r) * 8 + (ci & 7)] = hi;
+                            tap[((size_t)(ci >> 3) * 256 + 128 + r) * 8 + (ci & 7)] = lo;
+                        }
+                }
+            if (!m->tc_contract_w) STOF_CUDA(cudaMalloc(&m->tc_contract_w, buf.size() * sizeof(__half)));
+            STOF_CUDA(cudaMemcpy(m->tc_contract_w, buf.data(), buf.size() * sizeof(__half), cudaMemcpyHostToDevice));
+        }
     } else {
         m->sgb_scale = 1; m->sgb_feat = 0; m->sgb_k = 0;
     }
@@ -276,8 +293,8 @@ static int forward_chunk_tc(stof_model *m, const float *x, int n, int L, float *
     int off = 0;
     if (sgb) {
         // models/stofnet.py:45,98-107: E = LeakyReLU(expand(maxpool80(LeakyReLU(contract(relu(conv1 x))))))
-        { ProfScope p(m, STOF_PROF_FIRST, st); if ((rc = launch_conv_first(x, n, L, m->first.w, m->first.b, B0, 9, 0, st))) return rc; }
-        { ProfScope p(m, STOF_PROF_CONTRACT, st); if ((rc = launch_contract_pool_simt(B0, pooled, m->contract.w, m->contract.b, n, L, pl.P, st))) return rc; }
+        { ProfScope p(m, STOF_PROF_CONTRACT, st);
+          if ((rc = launch_contract_pool_tc(x, m->tc_contract_w, m->contract.b, m->first.w, m->first.b, pooled, n, L, pl.P, st))) return rc; }
         { ProfScope p(m, STOF_PROF_EXPAND, st); if ((rc = launch_expand(pooled, e, m->expand.w, m->expand.b, n, pl.P, st))) return rc; }
         off = (L - pl.P * m->sgb_scale) / 2;
     }
@@ -400,6 +417,7 @@ extern "C" void stof_model_destroy(stof_model *m) {
         if (m->streams[i]) cudaStreamDestroy(m->streams[i]);
     }
     if (m->tc_w) cudaFree(m->tc_w);
+    if (m->tc_contract_w) cudaFree(m->tc_contract_w);
     if (m->h_stats) cudaFreeHost(m->h_stats);
     for (cudaEvent_t e : m->ev_pool) cudaEventDestroy(e);
     delete m;
@@ -543,4 +561,9 @@ extern "C" int stof_chain_segment(stof_model *m, int first, int count, const voi
     const bool ends = m->tc_layer[first + count - 1].type == stof::TC_LAST;
     return stof::launch_chain_tc(m->tc_layer + first, count, in_planes_dev, x0_planes_dev, ends ? nullptr : out_dev,
                                  ends ? reinterpret_cast<float *>(out_dev) : nullptr, N, L, (cudaStream_t)stream);
+}
+
+extern "C" int stof_debug_set_timeline(void *dev_buf, int capacity_events) {
+    stof::set_chain_timeline(dev_buf, dev_buf ? capacity_events : 0);
+    return STOF_OK;
 }
