@@ -9,14 +9,15 @@
 // Weight-stationary schedule: a CTA owns one 128-channel slice of the 512 output channels and keeps that slice's five taps
 // (fp16 hi/lo pairs, 160 KB) resident in shared memory for the whole launch; it streams 240-position tiles (3 pooling
 // windows = two 128-row MMA blocks) of waveform rows through them.  conv1 (1 -> 64, k9, K = 9: CUDA-core work) is recomputed
-// per tile by four loader warps straight into the UMMA operand layout, so the kernel reads 4 B and writes 6.4 B per
+// per tile by eight loader warps straight into the UMMA operand layout, so the kernel reads 4 B and writes 6.4 B per
 // position and moves no weights after start-up.
 //
 // fp32 accuracy on fp16 tensor cores as in conv_tc.cu: v = hi + 2^-11 lo;  per K-step
 //     [D0 | D1] (+)= X_hi [W_hi ; W_lo]^T   (N = 256),      D1 += X_lo W_hi^T   (N = 128),      result D0 + 2^-11 D1.
 //
-// Roles: warp 0 = weight loader (bulk copies, once), warp 1 = MMA issuer + TMEM owner, warps 2-5 = conv1 loaders,
-// warps 6-13 = pooling epilogue (warp & 3 = TMEM lane quadrant, (warp - 6) >> 2 = 64-channel half).
+// Roles: warp 0 = weight loader (bulk copies, once), warp 1 = MMA issuer + TMEM owner, warps 2-9 = conv1 loaders
+// (one thread per row and 32-channel half), warps 10-17 = pooling epilogue (warp & 3 = TMEM lane quadrant,
+// (warp - 10) >> 2 = 64-channel half).
 #include <cuda_fp16.h>
 #include <limits.h>
 
@@ -28,7 +29,7 @@ namespace stof {
 
 using namespace ptx;
 
-constexpr int CT_THREADS = 448;
+constexpr int CT_THREADS = 576;                       // 2 + 8 loader + 8 epilogue warps
 constexpr int CT_TILE = 240;                         // positions per tile = 3 pooling windows of 80
 constexpr int CT_WINDOW = 80;
 constexpr int CT_ROWS0 = 132;                        // operand rows of block 0: positions [-2, 130) of the tile
@@ -61,6 +62,54 @@ __device__ __forceinline__ int float_key(float v) {
     return b ^ ((b >> 31) & 0x7fffffff);
 }
 __device__ __forceinline__ float key_float(int k) { return __int_as_float(k ^ ((k >> 31) & 0x7fffffff)); }
+
+// Warp "transpose-reduce": every lane holds 32 column values of its own row; afterwards lane j holds the maximum over the
+// rows (lanes) of its segment for column j (FULL: one 32-lane segment; otherwise two 16-lane segments and lane j holds
+// columns 2 * (j & 15) + {0, 1} in v[0], v[1]).  log-step butterfly: 31 (30) shuffles instead of 32 warp reductions.
+template <bool FULL>
+__device__ __forceinline__ void transpose_max(float (&v)[32], int lane) {
+    if (FULL) {
+        const bool up = lane & 16;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const float send = up ? v[i] : v[i + 16], keep = up ? v[i + 16] : v[i];
+            v[i] = fmaxf(keep, __shfl_xor_sync(0xffffffffu, send, 16));
+        }
+    }
+    constexpr int N0 = FULL ? 16 : 32;
+    {
+        const bool up = lane & 8;
+#pragma unroll
+        for (int i = 0; i < N0 / 2; ++i) {
+            const float send = up ? v[i] : v[i + N0 / 2], keep = up ? v[i + N0 / 2] : v[i];
+            v[i] = fmaxf(keep, __shfl_xor_sync(0xffffffffu, send, 8));
+        }
+    }
+    {
+        const bool up = lane & 4;
+#pragma unroll
+        for (int i = 0; i < N0 / 4; ++i) {
+            const float send = up ? v[i] : v[i + N0 / 4], keep = up ? v[i + N0 / 4] : v[i];
+            v[i] = fmaxf(keep, __shfl_xor_sync(0xffffffffu, send, 4));
+        }
+    }
+    {
+        const bool up = lane & 2;
+#pragma unroll
+        for (int i = 0; i < N0 / 8; ++i) {
+            const float send = up ? v[i] : v[i + N0 / 8], keep = up ? v[i + N0 / 8] : v[i];
+            v[i] = fmaxf(keep, __shfl_xor_sync(0xffffffffu, send, 2));
+        }
+    }
+    {
+        const bool up = lane & 1;
+#pragma unroll
+        for (int i = 0; i < N0 / 16; ++i) {
+            const float send = up ? v[i] : v[i + N0 / 16], keep = up ? v[i + N0 / 16] : v[i];
+            v[i] = fmaxf(keep, __shfl_xor_sync(0xffffffffu, send, 1));
+        }
+    }
+}
 
 struct ContractParams {
     const float *x;          // (N, L) fp32
@@ -97,7 +146,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
     if (threadIdx.x == 0) {
         mbar_init(BAR_W_FULL, 1);
         for (int b = 0; b < 2; ++b) {
-            mbar_init(BAR_A_FULL(b), 4);
+            mbar_init(BAR_A_FULL(b), 8);
             mbar_init(BAR_A_EMPTY(b), 1);
             mbar_init(BAR_ACC_FULL(b), 1);
             mbar_init(BAR_ACC_EMPTY(b), 8);
@@ -151,10 +200,11 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
                 __syncwarp();
             }
         }
-    } else if (warp < 6) {
+    } else if (warp < 10) {
         // =================================== conv1 loaders ===============================================
-        // x0[l][c] = relu(b1[c] + sum_t w1[c][t] x[l + t - 4]) for 0 <= l < L, 0 outside (the contract conv's zero padding)
-        const int tid = threadIdx.x - 64;               // 0..127
+        // x0[l][c] = relu(b1[c] + sum_t w1[c][t] x[l + t - 4]) for 0 <= l < L, 0 outside (the contract conv's zero padding).
+        // Work item = (row, 32-channel half); 256 threads.
+        const int tid = threadIdx.x - 64;               // 0..255
         const float4 *w4 = reinterpret_cast<const float4 *>(s_w1);
         int it = 0;
         for (int tile = worker; tile < p.total_tiles; tile += workers, ++it) {
@@ -166,7 +216,9 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
                 const int rows = b ? CT_ROWS1 : CT_ROWS0;
                 uint8_t *abuf = smem + (b ? CT_OFF_A1 : CT_OFF_A0);
                 mbar_wait(BAR_A_EMPTY(b), (uint32_t)(it & 1) ^ 1u);
-                for (int row = tid; row < rows; row += 128) {
+                for (int item = tid; item < 2 * rows; item += 256) {
+                    const int half = item >= rows ? 1 : 0;
+                    const int row = item - half * rows;
                     const int l = l_tile + 128 * b - 2 + row;
                     const bool inside = (l >= 0) && (l < p.L);
                     float xv[9];
@@ -176,7 +228,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
                         xv[t] = (inside && g >= 0 && g < p.L) ? __ldg(xr + g) : 0.0f;
                     }
 #pragma unroll 2
-                    for (int c8 = 0; c8 < 8; ++c8) {
+                    for (int j = 0; j < 4; ++j) {
+                        const int c8 = 4 * half + j;
                         float v[8];
 #pragma unroll
                         for (int h = 0; h < 2; ++h) {
@@ -207,8 +260,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
     } else {
         // =================================== pooling epilogue ============================================
         const int quad = warp & 3;
-        const int grp = (warp - 6) >> 2;                 // channel half: co [64 grp, +64) of the slice
-        const int etid = threadIdx.x - 192;              // 0..255
+        const int grp = (warp - 10) >> 2;                // channel half: co [64 grp, +64) of the slice
+        const int etid = threadIdx.x - 320;              // 0..255
         const uint32_t lane_addr = (uint32_t)(32 * quad) << 16;
         int it = 0;
         for (int tile = worker; tile < p.total_tiles; tile += workers, ++it) {
@@ -220,37 +273,42 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
                 const int row = 128 * b + 32 * quad + lane;             // row within the tile
                 const int win = row / CT_WINDOW;                        // 0..3 (3 = beyond the tile)
                 const bool valid = (row < CT_TILE) && (p0 + win < p.P);
-                const int w_first = (128 * b + 32 * quad) / CT_WINDOW;
-                const int w_last = min(2, (128 * b + 32 * quad + 31) / CT_WINDOW);
+                // the only warp whose rows belong to two pooling windows of the tile: rows 64..95 (split at lane 16)
+                const bool split = (b == 0) && (quad == 2);
                 mbar_wait(BAR_ACC_FULL(b), (uint32_t)(it & 1));
                 tc_fence_after_sync();
                 const uint32_t d_tmem = tmem0 + 256u * b + lane_addr + 64u * grp;
 #pragma unroll 1
-                for (int c16 = 0; c16 < 4; ++c16) {
-                    uint32_t d0[16], d1[16];
-                    tmem_ld16(d_tmem + 16 * c16, d0);
-                    tmem_ld16(d_tmem + 128 + 16 * c16, d1);
+                for (int c32 = 0; c32 < 2; ++c32) {
+                    uint32_t d0[32], d1[32];
+                    tmem_ld16(d_tmem + 32 * c32, *reinterpret_cast<uint32_t(*)[16]>(&d0[0]));
+                    tmem_ld16(d_tmem + 32 * c32 + 16, *reinterpret_cast<uint32_t(*)[16]>(&d0[16]));
+                    tmem_ld16(d_tmem + 128 + 32 * c32, *reinterpret_cast<uint32_t(*)[16]>(&d1[0]));
+                    tmem_ld16(d_tmem + 128 + 32 * c32 + 16, *reinterpret_cast<uint32_t(*)[16]>(&d1[16]));
                     tmem_ld_wait();
-                    if (c16 == 3) {
+                    if (c32 == 1) {
                         tc_fence_before_sync();
                         __syncwarp();
                         if (lane == 0) mbar_arrive(BAR_ACC_EMPTY(b));
                     }
-                    // lanes 0-15 collect window w_first, lanes 16-31 window w_first + 1 (a warp spans at most two windows)
-                    int mine = INT_MIN;
+                    float v[32];
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        const float v = __uint_as_float(d0[i]) + (1.0f / 2048.0f) * __uint_as_float(d1[i]);
-                        const int key = float_key(v);
-                        const int m0 = __reduce_max_sync(0xffffffffu, (valid && win == w_first) ? key : INT_MIN);
-                        if (lane == i) mine = m0;
-                        if (w_last > w_first) {
-                            const int m1 = __reduce_max_sync(0xffffffffu, (valid && win == w_first + 1) ? key : INT_MIN);
-                            if (lane == 16 + i) mine = m1;
-                        }
+                    for (int i = 0; i < 32; ++i) {
+                        const float t = __uint_as_float(d0[i]) + (1.0f / 2048.0f) * __uint_as_float(d1[i]);
+                        v[i] = valid ? t : -INFINITY;
                     }
-                    const int w = w_first + (lane >> 4);
-                    if (w <= w_last && mine != INT_MIN) atomicMax(&s_pool[w * 128 + 64 * grp + 16 * c16 + (lane & 15)], mine);
+                    const int co0 = 64 * grp + 32 * c32;
+                    if (!split) {
+                        transpose_max<true>(v, lane);                   // lane j: max over the warp's rows of column j
+                        const int w = (128 * b + 32 * quad) / CT_WINDOW;
+                        if (v[0] != -INFINITY) atomicMax(&s_pool[w * 128 + co0 + lane], float_key(v[0]));
+                    } else {
+                        transpose_max<false>(v, lane);                  // lane j: columns 2 (j & 15) + {0, 1} of its 16-row half
+                        const int w = lane >> 4;                        // rows 64..79 -> window 0, rows 80..95 -> window 1
+                        const int c = 2 * (lane & 15);
+                        if (v[0] != -INFINITY) atomicMax(&s_pool[w * 128 + co0 + c], float_key(v[0]));
+                        if (v[1] != -INFINITY) atomicMax(&s_pool[w * 128 + co0 + c + 1], float_key(v[1]));
+                    }
                 }
             }
             // all 8 epilogue warps have folded both blocks: publish bias + LeakyReLU of the window maxima, reset the pool

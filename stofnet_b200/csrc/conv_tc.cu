@@ -176,6 +176,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                 for (int slab = 0; slab < 16; ++slab)
                     bulk_g2s(sbase + TC_OFF_P + slab * TC_SLAB + r_lo * 16, src + ((size_t)slab * p.L + l_org + r_lo) * 8, bytes,
                              BAR_IN_FULL);
+                // pull the next tile's input rows into L2 while this tile computes
+                {
+                    const int tile2 = tile + gridDim.x;
+                    if (tile2 < p.total_tiles) {
+                        const int n2 = tile2 / p.tiles_per_row;
+                        const int lo2 = (tile2 - n2 * p.tiles_per_row) * p.t_out - p.l_shift;
+                        const int a2 = max(0, lo2), b2 = min(p.L, lo2 + r_in);
+                        const __half *src2 = reinterpret_cast<const __half *>(p.in) + (size_t)n2 * 16 * p.L * 8;
+                        for (int slab = 0; slab < 16; ++slab)
+                            bulk_prefetch_l2(src2 + ((size_t)slab * p.L + a2) * 8, (uint32_t)(b2 - a2) * 16u);
+                    }
+                }
                 // weight ring: every tap of every layer of this tile, in issue order
                 for (int k = 0; k < n_layers; ++k) {
                     const TcLayer &ly = p.layer[k];

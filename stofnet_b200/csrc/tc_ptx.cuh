@@ -50,6 +50,11 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void *src_gmem
                  : "memory");
 }
 
+// L2 prefetch of a global range (bytes % 16 == 0)
+__device__ __forceinline__ void bulk_prefetch_l2(const void *src_gmem, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(__cvta_generic_to_global(src_gmem)), "r"(bytes) : "memory");
+}
+
 // ---- TMEM ------------------------------------------------------------------------------------------
 // whole warp; writes the TMEM base address to *dst_smem
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
