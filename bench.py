@@ -16,8 +16,8 @@ and the only collective is the final ToF gather (max-reduce of K_max + all_gathe
   value     waveforms/s, all ranks, inputs resident in HBM (device timed, max over ranks)
   e2e       same metric through the host-buffer C-ABI call stof_infer_host: pinned host input,
             H2D + forward + peaks + D2H of the ToF table inside the timed region
-  roofline  dominant kernel (conv2..conv12 class, 65 % of the FLOPs): algorithmic FLOPs per launch /
-            mean launch duration from CUDA events recorded on the launch stream inside the timed steps
+  roofline  dominant kernel (chain_tc_kernel: conv2..conv12 + conv_last, 65 % of the FLOPs): algorithmic FLOPs
+            per launch / mean launch duration from CUDA events recorded on the launch stream inside the timed steps
   cpu_baseline  the oracle's torch-CPU port of the reference path on this box's host cores
             (bounded row sample)
 
@@ -45,6 +45,7 @@ CAP = 128
 # algorithmic work per row: MACs = 480,576 L + 163,840 floor(L/80)
 FLOP_PER_ROW = 2.0 * (480576 * L + 163840 * (L // 80))
 MID_FLOP_PER_POS = 2.0 * 64 * 64 * 7         # one conv2..conv12 layer, per position
+CHAIN_FLOP_PER_POS = 11 * MID_FLOP_PER_POS + 2.0 * 64 * 4 * 3     # conv2..conv12 + conv_last (K5 + K6)
 
 
 def peaks_file():
@@ -275,13 +276,21 @@ def main():
 
     if rank == 0:
         peaks, peak_src = peaks_file()
-        mid_n = int(prof_n[4])
-        mid_ms = float(prof_ms[4]) / max(1, mid_n)
-        # positions per conv_mid launch = chunk rows * L; chunk = launches per step / 11 layers
-        chunks_per_step = max(1, mid_n // (11 * args.steps))
-        pos_per_launch = ROWS * L / chunks_per_step
-        achieved_tf = MID_FLOP_PER_POS * pos_per_launch / (mid_ms / 1e3) / 1e12 if mid_n else 0.0
+        # dominant kernel = chain_tc_kernel: the fused 64->64 k7 stack (conv2..conv12) + conv_last/shuffle, launched
+        # per segment of layers (profile classes conv_mid = segments of mid layers, conv_last = the tail segment)
+        ch_n = int(prof_n[4]) + int(prof_n[5])
+        ch_ms = (float(prof_ms[4]) + float(prof_ms[5])) / max(1, ch_n)
+        chain_flops_step = CHAIN_FLOP_PER_POS * ROWS * L                    # algorithmic, per step
+        flops_per_launch = chain_flops_step * args.steps / max(1, ch_n)
+        achieved_tf = flops_per_launch / (ch_ms / 1e3) / 1e12 if ch_n else 0.0
         peak_tf = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops")))
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "chain_traffic.json")
+        if os.path.exists(tpath):
+            with open(tpath) as f:
+                tj = json.load(f)
+            # ncu dram bytes (read + write) per position summed over the chain launches of one forward, averaged per launch
+            traffic = float(tj["dram_bytes_per_position_all_segments"]) * ROWS * L * args.steps / max(1, ch_n)
         share = {PROF_NAMES[c]: round(float(prof_ms[c]) / args.steps, 3) for c in range(PROF_CLASSES) if prof_n[c]}
         line = {
             "metric": "echo waveforms/sec", "value": value, "unit": "waveforms/s", "n_gpus": world,
@@ -292,12 +301,17 @@ def main():
                     "d2h_bytes_per_step": ROWS * CAP * 4 + ROWS * 4 + 16, "ms_per_step": e2e_ms / args.steps},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"bound": "tensor", "kernel": "conv_mid (conv2..conv12, 64->64 k7; fp32 FFMA kernel this round)",
+            "roofline": {"bound": "tensor",
+                         "kernel": "chain_tc_kernel (conv2..conv12 64->64 k7 + conv_last/shuffle; tcgen05 kind::f16, fp32 "
+                                   "operands as fp16 hi/lo pairs: 3 issued MMA FLOPs per algorithmic FLOP)",
                          "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
-                         "frac": achieved_tf / peak_tf if peak_tf else None, "traffic": None,
-                         "peak_source": "%s bf16 sustained (MEASURED_PEAKS.json); tf32 peak not measured" % peak_src,
-                         "launch_ms": mid_ms, "launches": mid_n,
-                         "algorithmic_flops_per_launch": MID_FLOP_PER_POS * pos_per_launch},
+                         "frac": achieved_tf / peak_tf if peak_tf else None, "traffic": traffic,
+                         "issued_tflops": 3.0 * achieved_tf, "issued_frac": 3.0 * achieved_tf / peak_tf if peak_tf else None,
+                         "peak_source": "%s: dense 16-bit tensor peak, sustained figure of MEASURED_PEAKS.json (kernel timed "
+                                        "inside a long step); 'achieved' counts algorithmic FLOPs, 'issued' the fp16 MMAs "
+                                        "the exact-fp32 split needs" % peak_src,
+                         "launch_ms": ch_ms, "launches": ch_n,
+                         "algorithmic_flops_per_launch": flops_per_launch},
             "kernel_ms_per_step": share,
             "algorithmic_tflops": FLOP_PER_ROW * value / 1e12,
         }

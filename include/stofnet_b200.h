@@ -153,8 +153,9 @@ int stof_model_set_path(stof_model *m, int path, int layers_per_launch);
 int stof_chain_segment(stof_model *m, int first, int count, const void *in_planes_dev, const void *x0_planes_dev,
                        void *out_dev, int N, int L, void *stream);
 
-/* Debug: chain launches issued after this call make CTA 0 append (code, clock64) event pairs to dev_buf
- * (uint64[1 + 2*capacity]: [0] = count; must be zeroed by the caller).  NULL switches it off.        */
+/* Debug: chain launches issued after this call make four warps of CTA 0 (producer, the two MMA issuers, one epilogue
+ * warp) append (code, clock64) event pairs to dev_buf (uint64[4 + 2*capacity]: [role] = event count of that role, then
+ * four regions of capacity/4 pairs; must be zeroed by the caller).  NULL switches it off.                  */
 int stof_debug_set_timeline(void *dev_buf, int capacity_events);
 
 /* Counter of kernels launched by this library since load (bench.py's gpu_launches). */

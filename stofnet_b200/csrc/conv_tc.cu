@@ -93,21 +93,27 @@ __device__ __forceinline__ void unpack8(const uint4 &u, float (&f)[8]) {
     }
 }
 
-// optional timeline (stof_debug_set_timeline): CTA 0 appends (code, clock64) pairs; code = role<<24 | k<<16 | b<<8 | what
-__device__ __forceinline__ void tl_event(unsigned long long *tl, int cap, uint32_t code) {
+// optional timeline (stof_debug_set_timeline): roles 0..3 (producer, MMA issuer 0 / 1, epilogue warp 3) of CTA 0 each append
+// (code, clock64) pairs to a private quarter of the buffer with a register counter (no atomics: the probe must not stall
+// the warp it observes); code = role<<24 | k<<16 | b<<8 | what.  tl[role] receives the role's event count at kernel end.
+__device__ __forceinline__ void tl_event(unsigned long long *tl, int cap, uint32_t role, uint32_t code, int &cnt) {
     if (tl == nullptr || blockIdx.x != 0) return;
-    const unsigned long long i = atomicAdd(tl, 1ull);
-    if ((int)i < cap) {
-        tl[1 + 2 * i] = code;
-        tl[2 + 2 * i] = (unsigned long long)clock64();
+    const int capr = cap >> 2;
+    if (cnt < capr) {
+        unsigned long long *e = tl + 4 + 2 * ((size_t)role * capr + cnt);
+        e[0] = code;
+        e[1] = (unsigned long long)clock64();
     }
+    ++cnt;
 }
-#define TL(role, k, b, what) tl_event(p.timeline, p.timeline_cap, ((role) << 24) | ((uint32_t)(k) << 16) | ((uint32_t)(b) << 8) | (what))
+#define TL(role, k, b, what) tl_event(p.timeline, p.timeline_cap, (role), ((role) << 24) | ((uint32_t)(k) << 16) | ((uint32_t)(b) << 8) | (what), tl_cnt)
+#define TL_FLUSH(role) do { if (p.timeline != nullptr && blockIdx.x == 0) p.timeline[(role)] = (unsigned long long)tl_cnt; } while (0)
 
 __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     const uint32_t sbase = smem_u32(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int tl_cnt = 0;
     const uint32_t bar0 = sbase + TC_OFF_BAR;
     auto BAR_W_FULL = [&](int s) { return bar0 + 8 * s; };
     auto BAR_W_EMPTY = [&](int s) { return bar0 + 8 * (4 + s); };
@@ -158,6 +164,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
             const int l_org = l0 - p.l_shift;
             // the previous tile must be completely consumed before its input buffer is overwritten
             mbar_wait(BAR_TILE_FREE, (uint32_t)(it & 1) ^ 1u);
+            if (lane == 0) TL(0u, 0, 0, 1);
             const int r_lo = max(0, -l_org), r_hi = min(r_in, p.L - l_org);
             // rows outside the waveform are the conv's zero padding (only tiles at the ends of a row have any)
             if (r_lo > 0 || r_hi < r_in) {
@@ -194,6 +201,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                     for (int t = 0; t < ly.taps; ++t, ++seq) {
                         const int s = seq & 3;
                         mbar_wait(BAR_W_EMPTY(s), ((seq >> 2) & 1u) ^ 1u);
+                        TL(0u, k, 0, 16 + t);
                         mbar_arrive_expect_tx(BAR_W_FULL(s), (uint32_t)ly.stage_bytes);
                         bulk_g2s(sbase + TC_OFF_W + s * TC_STAGE_BYTES,
                                  reinterpret_cast<const uint8_t *>(ly.w) + (size_t)t * ly.stage_bytes, (uint32_t)ly.stage_bytes,
@@ -203,6 +211,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
             }
             __syncwarp();
         }
+        if (lane == 0) TL_FLUSH(0u);
     } else if (warp <= 2) {
         // =================================== MMA issuers =================================================
         // Two issuing warps, one per 128-row block of the tile (warp 1 -> block 0, warp 2 -> block 1).  The tensor pipe's
@@ -245,6 +254,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                     const uint32_t s = seq & 3u;
                     mbar_wait(BAR_W_FULL(s), (seq >> 2) & 1u);
                     tc_fence_after_sync();
+                    if (lane == 0) TL(1u + b, k, b, 16 + t);
                     if (elect_one()) {
                         const uint32_t a_lo = a_base + (uint32_t)t;
                         const uint32_t w_lo = ((sbase + TC_OFF_W + s * TC_STAGE_BYTES) >> 4) | (w_rows << 16);
@@ -265,6 +275,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                 seq0 += taps;
             }
         }
+        if (lane == 0) TL_FLUSH(1u + b);
     } else {
         // =================================== epilogue ====================================================
         // 8 warps: warp quadrant (warp & 3) selects the 32 TMEM lanes, group (0/1) the 32-channel half of the block.
@@ -292,6 +303,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                     const bool inside = (l >= 0) && (l < p.L);
                     mbar_wait(BAR_ACC_FULL(set), (lseq >> 1) & 1u);
                     tc_fence_after_sync();
+                    if (warp == 3 && lane == 0) TL(3u, k, b, 1);
                     const uint32_t d_tmem = tmem0 + set * 128u + lane_addr;
                     if (type == TC_LAST) {
                         // conv_last + SampleShuffle1D: mask[n][4 l + u] = D0[u] + 2^-11 D1[u] + bias[u]   (group 0 only)
@@ -385,6 +397,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
             __syncwarp();
             if (lane == 0) mbar_arrive(BAR_TILE_FREE);
         }
+        if (warp == 3 && lane == 0) TL_FLUSH(3u);
     }
 
     // ---- teardown --------------------------------------------------------------------------------------

@@ -16,19 +16,25 @@ eng = model._engine
 for _ in range(2):
     eng.chain_segment(model, first, count, x, x0)
 torch.cuda.synchronize()
-cap = 20000
-tl = torch.zeros(1 + 2 * cap, dtype=torch.int64, device=dev)
+cap = 40000
+tl = torch.zeros(4 + 2 * cap, dtype=torch.int64, device=dev)
 check(lib.stof_debug_set_timeline(tl.data_ptr(), cap))
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record(); eng.chain_segment(model, first, count, x, x0); e1.record()
 torch.cuda.synchronize()
 check(lib.stof_debug_set_timeline(None, 0))
 t = tl.cpu().numpy()
-n = min(int(t[0]), cap)
-ev = sorted((int(t[2 + 2 * i]), int(t[1 + 2 * i])) for i in range(n))
+capr = cap // 4
+ev = []
+for role in range(4):
+    for i in range(min(int(t[role]), capr)):
+        o = 4 + 2 * (role * capr + i)
+        ev.append((int(t[o + 1]), int(t[o])))
+ev.sort()
+n = len(ev)
 print("kernel ms", e0.elapsed_time(e1), "events", n)
 t0 = ev[0][0]
-names = {1: "MMA0", 2: "MMA1", 3: "EPI"}
+names = {0: "PROD", 1: "MMA0", 2: "MMA1", 3: "EPI"}
 lim = int(sys.argv[4]) if len(sys.argv) > 4 else 400
 for c, code in ev[:lim]:
     role, k, b, what = code >> 24, (code >> 16) & 255, (code >> 8) & 255, code & 255
