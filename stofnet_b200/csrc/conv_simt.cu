@@ -209,48 +209,125 @@ contract_pool_simt_kernel(const float *__restrict__ in, float *__restrict__ pool
 
 // ------------------------------------------------------------------------------------------------
 // expand conv: Conv1d(512 -> 64, k5, pad 2) + LeakyReLU on the pooled tensor (N,512,P)
-// (models/stofnet.py:94-95,106-107).  0.4 % of the FLOPs; one CTA per (row, 64-position tile).
+// (models/stofnet.py:94-95,106-107).  0.4 % of the FLOPs, on CUDA cores as a register-tiled fp32 GEMM:
+// the rows of a chunk are laid end to end in "slots", each row padded by 2 zero slots on both sides (the conv's zero
+// padding), so the 5 taps are plain slot shifts and a 128-slot CTA tile may span several short rows.  Thread tile = 8 slots
+// x 4 output channels; the 512 input channels stream through shared memory in double-buffered chunks of 8 (register
+// prefetch of the next chunk while the current one is multiplied).
 // ------------------------------------------------------------------------------------------------
 constexpr int EX_THREADS = 256;
-constexpr int EX_TP = 64;
+constexpr int EX_TS = 128;                 // output slots per CTA
+constexpr int EX_KC = 8;                   // input channels per shared-memory chunk
+constexpr int EX_AP = 136;                 // pitch of one channel's slot line (EX_TS + 4 used, 16-byte aligned)
+constexpr int EX_A_ELEMS = EX_KC * (EX_TS + 4);          // 1056
+constexpr int EX_A_PER_THREAD = (EX_A_ELEMS + EX_THREADS - 1) / EX_THREADS;   // 5
+constexpr int EX_W_VEC = EX_KC * 5 * 64 / 4;             // 640 float4
+constexpr int EX_W_PER_THREAD = (EX_W_VEC + EX_THREADS - 1) / EX_THREADS;     // 3
 
-__global__ void __launch_bounds__(EX_THREADS)
+__global__ void __launch_bounds__(EX_THREADS, 3)
 expand_simt_kernel(const float *__restrict__ pooled /*[N][512][P]*/, float *__restrict__ e /*[N][64][P]*/,
                    const float *__restrict__ w /*[512][5][64]*/, const float *__restrict__ b, int N, int P) {
-    extern __shared__ __align__(16) float ex_smem[];   // [512][EX_TP + 4]
-    constexpr int PITCH = EX_TP + 4;
-    const int n = blockIdx.y, p0 = blockIdx.x * EX_TP;
-    for (int idx = threadIdx.x; idx < 512 * PITCH; idx += EX_THREADS) {
-        const int ci = idx / PITCH, j = idx - ci * PITCH;
-        const int p = p0 - 2 + j;
-        ex_smem[idx] = (p >= 0 && p < P) ? __ldg(pooled + ((size_t)n * 512 + ci) * P + p) : 0.0f;
+    __shared__ __align__(16) float As[2][EX_KC][EX_AP];
+    __shared__ __align__(16) float Ws[2][EX_KC * 5 * 64];
+    const int PP = P + 4;
+    const long long S = (long long)N * PP;                     // slots in this launch
+    const long long q0 = (long long)blockIdx.x * EX_TS;
+    const int tid = threadIdx.x;
+    const int sg = tid >> 4, cg = tid & 15;                    // slots [8 sg, +8), channels [4 cg, +4)
+
+    // fixed (slot, channel-in-chunk) -> global offset of this thread's share of an A chunk (-1: zero padding)
+    int a_off[EX_A_PER_THREAD];               // < 2^31: checked by the launcher
+    int a_dst[EX_A_PER_THREAD];
+#pragma unroll
+    for (int i = 0; i < EX_A_PER_THREAD; ++i) {
+        const int el = tid + i * EX_THREADS;
+        a_off[i] = -1;
+        a_dst[i] = -1;
+        if (el < EX_A_ELEMS) {
+            const int ci = el / (EX_TS + 4), sl = el - ci * (EX_TS + 4);
+            a_dst[i] = ci * EX_AP + sl;
+            const long long q = q0 - 2 + sl;
+            if (q >= 0 && q < S) {
+                const long long row = q / PP;
+                const int j = (int)(q - row * PP);
+                if (j >= 2 && j < P + 2) a_off[i] = (int)((row * 512 + ci) * P + (j - 2));
+            }
+        }
     }
+    float a_reg[EX_A_PER_THREAD];
+    float4 w_reg[EX_W_PER_THREAD];
+    auto fetch = [&](int ci0) {
+#pragma unroll
+        for (int i = 0; i < EX_A_PER_THREAD; ++i)
+            a_reg[i] = (a_off[i] >= 0) ? __ldg(pooled + a_off[i] + ci0 * P) : 0.0f;
+        const float4 *wsrc = reinterpret_cast<const float4 *>(w + (size_t)ci0 * 320);
+#pragma unroll
+        for (int i = 0; i < EX_W_PER_THREAD; ++i) {
+            const int v = tid + i * EX_THREADS;
+            if (v < EX_W_VEC) w_reg[i] = __ldg(wsrc + v);
+        }
+    };
+    auto stage = [&](int buf) {
+        float *ad = &As[buf][0][0];
+#pragma unroll
+        for (int i = 0; i < EX_A_PER_THREAD; ++i)
+            if (a_dst[i] >= 0) ad[a_dst[i]] = a_reg[i];
+        float4 *wd = reinterpret_cast<float4 *>(&Ws[buf][0]);
+#pragma unroll
+        for (int i = 0; i < EX_W_PER_THREAD; ++i) {
+            const int v = tid + i * EX_THREADS;
+            if (v < EX_W_VEC) wd[v] = w_reg[i];
+        }
+    };
+
+    float acc[8][4];
+    {
+        const float4 bc = __ldg(reinterpret_cast<const float4 *>(b) + cg);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { acc[j][0] = bc.x; acc[j][1] = bc.y; acc[j][2] = bc.z; acc[j][3] = bc.w; }
+    }
+    fetch(0);
+    stage(0);
     __syncthreads();
-    const int co = threadIdx.x & 63, pg = threadIdx.x >> 6;     // 4 groups x 16 positions
-    float acc[16];
-    const float bc = __ldg(b + co);
+    for (int c = 0; c < 512 / EX_KC; ++c) {
+        const int buf = c & 1;
+        if (c + 1 < 512 / EX_KC) fetch((c + 1) * EX_KC);
 #pragma unroll
-    for (int j = 0; j < 16; ++j) acc[j] = bc;
-#pragma unroll 2
-    for (int ci = 0; ci < 512; ++ci) {
-        float xv[20];
-        const float4 *xp = reinterpret_cast<const float4 *>(ex_smem + ci * PITCH + 16 * pg);
+        for (int ci = 0; ci < EX_KC; ++ci) {
+            float xv[12];
+            const float4 *xp = reinterpret_cast<const float4 *>(&As[buf][ci][8 * sg]);
 #pragma unroll
-        for (int q = 0; q < 5; ++q) {
-            const float4 t = xp[q];
-            xv[4 * q] = t.x; xv[4 * q + 1] = t.y; xv[4 * q + 2] = t.z; xv[4 * q + 3] = t.w;
+            for (int q = 0; q < 3; ++q) {
+                const float4 t = xp[q];
+                xv[4 * q] = t.x; xv[4 * q + 1] = t.y; xv[4 * q + 2] = t.z; xv[4 * q + 3] = t.w;
+            }
+#pragma unroll
+            for (int t = 0; t < 5; ++t) {
+                const float4 wv = *reinterpret_cast<const float4 *>(&Ws[buf][(ci * 5 + t) * 64 + 4 * cg]);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    acc[j][0] = fmaf(wv.x, xv[j + t], acc[j][0]);
+                    acc[j][1] = fmaf(wv.y, xv[j + t], acc[j][1]);
+                    acc[j][2] = fmaf(wv.z, xv[j + t], acc[j][2]);
+                    acc[j][3] = fmaf(wv.w, xv[j + t], acc[j][3]);
+                }
+            }
         }
-#pragma unroll
-        for (int t = 0; t < 5; ++t) {
-            const float wv = __ldg(w + (ci * 5 + t) * 64 + co);
-#pragma unroll
-            for (int j = 0; j < 16; ++j) acc[j] = fmaf(wv, xv[j + t], acc[j]);
-        }
+        if (c + 1 < 512 / EX_KC) stage(buf ^ 1);
+        __syncthreads();
     }
 #pragma unroll
-    for (int j = 0; j < 16; ++j) {
-        const int p = p0 + 16 * pg + j;
-        if (p < P) e[((size_t)n * 64 + co) * P + p] = leaky(acc[j]);
+    for (int j = 0; j < 8; ++j) {
+        const long long q = q0 + 8 * sg + j;
+        if (q >= S) continue;
+        const long long row = q / PP;
+        const int jj = (int)(q - row * PP);
+        if (jj < 2 || jj >= P + 2) continue;
+        float *dst = e + ((size_t)row * 64 + 4 * cg) * P + (jj - 2);
+        dst[0] = leaky(acc[j][0]);
+        dst[(size_t)P] = leaky(acc[j][1]);
+        dst[2 * (size_t)P] = leaky(acc[j][2]);
+        dst[3 * (size_t)P] = leaky(acc[j][3]);
     }
 }
 
@@ -419,14 +496,11 @@ int launch_contract_pool_simt(const float *in, float *pooled, const float *w, co
 }
 
 int launch_expand(const float *pooled, float *e, const float *w, const float *b, int N, int P, cudaStream_t st) {
-    static bool attr = false;
-    const size_t smem = sizeof(float) * 512 * (EX_TP + 4);
-    if (!attr) {
-        STOF_CUDA(cudaFuncSetAttribute(expand_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr = true;
-    }
-    dim3 grid((P + EX_TP - 1) / EX_TP, N);
-    expand_simt_kernel<<<grid, EX_THREADS, smem, st>>>(pooled, e, w, b, N, P);
+    const long long slots = (long long)N * (P + 4);
+    const long long grid = (slots + EX_TS - 1) / EX_TS;
+    STOF_REQUIRE(grid < (1ll << 31) && (long long)N * 512 * P < (1ll << 31), STOF_E_INVALID,
+                 "expand: chunk of %d rows x %d pooled positions too large (use a smaller chunk_rows)", N, P);
+    expand_simt_kernel<<<(unsigned)grid, EX_THREADS, 0, st>>>(pooled, e, w, b, N, P);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }

@@ -14,11 +14,14 @@
 //               D1    += X_lo * W_hi^T                 (N = 64)
 //     and the epilogue forms D0 + 2^-11 * D1 (the dropped lo*lo term is 2^-22 relative).  Stacking W_hi and W_lo along N
 //     halves the shared-memory operand traffic per MAC, which is what bounds N = 64 MMAs.
-//   * the epilogue (4 warps, one TMEM lane = one position per thread) adds bias / residual, applies LeakyReLU, zeroes
+//   * the epilogue (8 warps, one TMEM lane = one position per thread) adds bias / residual, applies LeakyReLU, zeroes
 //     positions outside the row (per-layer zero padding), re-splits to hi/lo fp16 and writes the next layer's operand
 //     straight back to shared memory; block grids of successive layers are skewed by the layer's padding so block b of
 //     layer k+1 only depends on blocks <= b of layer k and the tensor pipe never waits for a whole layer.
-//   * weights stream through a 4-stage ring of 16 KB taps filled by bulk async copies (TMA engine) on mbarriers.
+//   * weights stream through a 5-stage ring of 16 KB taps filled by bulk async copies (TMA engine) on mbarriers.
+//
+//   * the short skip of a segment's LAST layer is parked as fp32 in spare TMEM columns by the previous layer's epilogue, so
+//     the input buffer is free one layer before the tile ends and the next tile's input load hides behind that layer.
 //
 // Roles: warp 0 = producer (input tile + weight ring), warps 1-2 = MMA issuers (one per 128-row block; warp 1 owns
 // TMEM), warps 3-10 = epilogue.
@@ -39,9 +42,8 @@ constexpr int TC_R = 280;                              // smem rows per (plane, 
 constexpr int TC_SLAB = TC_R * 16;                     // bytes of one (plane, c8) slab
 constexpr int TC_PLANE = 8 * TC_SLAB;                  // one fp16 plane (hi or lo): 64 channels
 constexpr int TC_BUF = 2 * TC_PLANE;                   // hi + lo
-constexpr int TC_STAGES = 4;
+constexpr int TC_STAGES = 5;
 constexpr int TC_STAGE_BYTES = 16384;                  // one k7 tap: [8 c8][128 n][8] fp16
-constexpr int TC_GROUP = 4;                            // max taps issued per block before switching block (<= stages)
 constexpr float TC_LO_SCALE = 2048.0f;                 // 2^11
 constexpr float TC_LO_INV = 1.0f / 2048.0f;
 
@@ -51,8 +53,8 @@ constexpr int TC_OFF_Q = TC_BUF;
 constexpr int TC_OFF_W = 2 * TC_BUF;
 constexpr int TC_OFF_BIAS = TC_OFF_W + TC_STAGES * TC_STAGE_BYTES;          // [TC_MAX_LAYERS][64] fp32
 constexpr int TC_OFF_BAR = TC_OFF_BIAS + TC_MAX_LAYERS * 64 * 4;
-// barriers (8 B each): w_full[4] w_empty[4] acc_full[4] acc_empty[4] act_ready[TC_MAX_LAYERS][2] in_full tile_free
-constexpr int TC_NBAR = 16 + 2 * TC_MAX_LAYERS + 2;
+// barriers (8 B each): w_full[STAGES] w_empty[STAGES] acc_full[2] acc_empty[2] act_ready[TC_MAX_LAYERS][2] in_full p_free
+constexpr int TC_NBAR = 2 * TC_STAGES + 4 + 2 * TC_MAX_LAYERS + 2;
 constexpr int TC_OFF_TMEM = TC_OFF_BAR + TC_NBAR * 8;
 constexpr int TC_SMEM_BYTES = TC_OFF_TMEM + 16;
 
@@ -116,12 +118,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
     int tl_cnt = 0;
     const uint32_t bar0 = sbase + TC_OFF_BAR;
     auto BAR_W_FULL = [&](int s) { return bar0 + 8 * s; };
-    auto BAR_W_EMPTY = [&](int s) { return bar0 + 8 * (4 + s); };
-    auto BAR_ACC_FULL = [&](int s) { return bar0 + 8 * (8 + s); };
-    auto BAR_ACC_EMPTY = [&](int s) { return bar0 + 8 * (12 + s); };
-    auto BAR_ACT = [&](int k, int b) { return bar0 + 8 * (16 + 2 * k + b); };
-    const uint32_t BAR_IN_FULL = bar0 + 8 * (16 + 2 * TC_MAX_LAYERS);
-    const uint32_t BAR_TILE_FREE = BAR_IN_FULL + 8;
+    auto BAR_W_EMPTY = [&](int s) { return bar0 + 8 * (TC_STAGES + s); };
+    auto BAR_ACC_FULL = [&](int b) { return bar0 + 8 * (2 * TC_STAGES + b); };
+    auto BAR_ACC_EMPTY = [&](int b) { return bar0 + 8 * (2 * TC_STAGES + 2 + b); };
+    auto BAR_ACT = [&](int k, int b) { return bar0 + 8 * (2 * TC_STAGES + 4 + 2 * k + b); };
+    const uint32_t BAR_IN_FULL = bar0 + 8 * (2 * TC_STAGES + 4 + 2 * TC_MAX_LAYERS);
+    const uint32_t BAR_P_FREE = BAR_IN_FULL + 8;
     float *s_bias = reinterpret_cast<float *>(smem + TC_OFF_BIAS);
     volatile uint32_t *s_tmem = reinterpret_cast<volatile uint32_t *>(smem + TC_OFF_TMEM);
 
@@ -131,18 +133,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
         s_bias[i] = (c < p.layer[k].n_out) ? __ldg(p.layer[k].bias + c) : 0.0f;
     }
     if (threadIdx.x == 0) {
-        for (int s = 0; s < 4; ++s) {
+        for (int s = 0; s < TC_STAGES; ++s) {
             mbar_init(BAR_W_FULL(s), 1);
-            mbar_init(BAR_W_EMPTY(s), 2);
-            mbar_init(BAR_ACC_FULL(s), 1);
-            mbar_init(BAR_ACC_EMPTY(s), TC_EPI_WARPS);
+            mbar_init(BAR_W_EMPTY(s), 2);                 // one issuing warp per block consumes a tap
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(BAR_ACC_FULL(b), 1);
+            mbar_init(BAR_ACC_EMPTY(b), TC_EPI_WARPS);
         }
         for (int k = 0; k < TC_MAX_LAYERS; ++k) {
             mbar_init(BAR_ACT(k, 0), TC_EPI_WARPS);
             mbar_init(BAR_ACT(k, 1), TC_EPI_WARPS);
         }
         mbar_init(BAR_IN_FULL, 1);
-        mbar_init(BAR_TILE_FREE, TC_EPI_WARPS);
+        mbar_init(BAR_P_FREE, TC_EPI_WARPS);
         fence_mbar_init();
     }
     if (warp == 1) tmem_alloc(sbase + TC_OFF_TMEM, 512);
@@ -156,14 +160,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
 
     if (warp == 0) {
         // =================================== producer ===================================================
-        uint32_t seq = 0;
-        int it = 0;
-        for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+        // Input tile j of this CTA goes into buffer P as soon as tile j-1 no longer touches P (BAR_P_FREE, arrived by the
+        // epilogue after layer p.free_layer); with an even number of layers that is one whole layer before the tile
+        // ends, so the load of the next tile hides behind the last layer.  Weights: every tap of every layer in issue order.
+        auto issue_input = [&](int tile, int j) {
             const int n = tile / p.tiles_per_row;
-            const int l0 = (tile - n * p.tiles_per_row) * p.t_out;
-            const int l_org = l0 - p.l_shift;
-            // the previous tile must be completely consumed before its input buffer is overwritten
-            mbar_wait(BAR_TILE_FREE, (uint32_t)(it & 1) ^ 1u);
+            const int l_org = (tile - n * p.tiles_per_row) * p.t_out - p.l_shift;
+            if (j > 0) mbar_wait(BAR_P_FREE, (uint32_t)(j - 1) & 1u);
             if (lane == 0) TL(0u, 0, 0, 1);
             const int r_lo = max(0, -l_org), r_hi = min(r_in, p.L - l_org);
             // rows outside the waveform are the conv's zero padding (only tiles at the ends of a row have any)
@@ -183,53 +186,66 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                 for (int slab = 0; slab < 16; ++slab)
                     bulk_g2s(sbase + TC_OFF_P + slab * TC_SLAB + r_lo * 16, src + ((size_t)slab * p.L + l_org + r_lo) * 8, bytes,
                              BAR_IN_FULL);
-                // pull the next tile's input rows into L2 while this tile computes
-                {
-                    const int tile2 = tile + gridDim.x;
-                    if (tile2 < p.total_tiles) {
-                        const int n2 = tile2 / p.tiles_per_row;
-                        const int lo2 = (tile2 - n2 * p.tiles_per_row) * p.t_out - p.l_shift;
-                        const int a2 = max(0, lo2), b2 = min(p.L, lo2 + r_in);
-                        const __half *src2 = reinterpret_cast<const __half *>(p.in) + (size_t)n2 * 16 * p.L * 8;
-                        for (int slab = 0; slab < 16; ++slab)
-                            bulk_prefetch_l2(src2 + ((size_t)slab * p.L + a2) * 8, (uint32_t)(b2 - a2) * 16u);
-                    }
+            }
+            __syncwarp();
+        };
+        int s = 0;
+        uint32_t ph = 0;
+        int it = 0;
+        if ((int)blockIdx.x < p.total_tiles) issue_input(blockIdx.x, 0);
+        for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+            const int next = tile + gridDim.x;
+            for (int k = 0; k < n_layers; ++k) {
+                const TcLayer &ly = p.layer[k];
+                if (ly.type == TC_LONGSKIP && k > 0 && lane == 0) {
+                    // pull this tile's rows of the long-skip tensor into L2 one layer before the epilogue reads them
+                    const int n = tile / p.tiles_per_row;
+                    const int l0 = (tile - n * p.tiles_per_row) * p.t_out;
+                    const int a0 = max(0, l0 - 16), a1 = min(p.L, l0 + p.t_out + 16);
+                    const __half *src = reinterpret_cast<const __half *>(p.x0) + (size_t)n * 16 * p.L * 8;
+                    for (int slab = 0; slab < 16; ++slab)
+                        bulk_prefetch_l2(src + ((size_t)slab * p.L + a0) * 8, (uint32_t)(a1 - a0) * 16u);
                 }
-                // weight ring: every tap of every layer of this tile, in issue order
-                for (int k = 0; k < n_layers; ++k) {
-                    const TcLayer &ly = p.layer[k];
-                    for (int t = 0; t < ly.taps; ++t, ++seq) {
-                        const int s = seq & 3;
-                        mbar_wait(BAR_W_EMPTY(s), ((seq >> 2) & 1u) ^ 1u);
+                for (int t = 0; t < ly.taps; ++t) {
+                    if (lane == 0) {
+                        mbar_wait(BAR_W_EMPTY(s), ph ^ 1u);
                         TL(0u, k, 0, 16 + t);
                         mbar_arrive_expect_tx(BAR_W_FULL(s), (uint32_t)ly.stage_bytes);
                         bulk_g2s(sbase + TC_OFF_W + s * TC_STAGE_BYTES,
                                  reinterpret_cast<const uint8_t *>(ly.w) + (size_t)t * ly.stage_bytes, (uint32_t)ly.stage_bytes,
                                  BAR_W_FULL(s));
                     }
+                    if (++s == TC_STAGES) { s = 0; ph ^= 1u; }
+                    if (k == p.in_layer && t == p.in_tap && next < p.total_tiles) {
+                        __syncwarp();
+                        issue_input(next, it + 1);
+                    }
                 }
             }
-            __syncwarp();
         }
         if (lane == 0) TL_FLUSH(0u);
     } else if (warp <= 2) {
         // =================================== MMA issuers =================================================
-        // Two issuing warps, one per 128-row block of the tile (warp 1 -> block 0, warp 2 -> block 1).  The tensor pipe's
-        // queue is shallow, so a single issuing thread exposes its own barrier waits and descriptor arithmetic; two
-        // independent streams (different accumulators) hide each other's issue gaps and the lagging stream's MMAs cover
-        // the leading stream's epilogue wait.  The weight ring bounds the lag to TC_STAGES taps.
+        // Two issuing warps, one per 128-row block of the tile (warp 1 -> block 0, warp 2 -> block 1); each block's MMAs are
+        // issued by one thread in a fixed order, so the accumulation order - hence the result - is deterministic.  The two
+        // streams (different accumulators) hide each other's issue gaps, and one block's MMAs cover the other block's
+        // epilogue; the weight ring bounds the lag between the blocks to TC_STAGES taps.
         // Each warp runs warp-uniform control flow (descriptors stay in uniform registers); one elected lane issues.
         // Descriptor low word = (addr >> 4) | (LBO >> 4) << 16; the high word (SBO = 128 B, version 1) is constant.
         constexpr uint32_t kDescHi = (128u >> 4) | (1u << 14);
         constexpr uint32_t kALoBase = (uint32_t)(TC_SLAB >> 4) << 16;            // A: LBO = one slab
         const int b = warp - 1;
-        uint32_t seq0 = 0, lseq = 0;
+        const uint32_t role = 1u + (uint32_t)b;
+        const bool tl_on = (lane == 0);
+        const uint32_t d_tmem = tmem0 + (uint32_t)b * 128u;
+        int s = 0;
+        uint32_t ph = 0, lseq = 0;
         int it = 0;
         for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
-            if (b == 0 && lane == 0) TL(1u, 0, 0, 1);
+            if (tl_on) TL(role, 0, b, 1);
             mbar_wait(BAR_IN_FULL, (uint32_t)(it & 1));
             tc_fence_after_sync();
-            if (b == 0 && lane == 0) TL(1u, 0, 0, 2);
+            if (tl_on) TL(role, 0, b, 2);
             for (int k = 0; k < n_layers; ++k, ++lseq) {
                 const TcLayer &ly = p.layer[k];
                 const int taps = ly.taps;
@@ -240,21 +256,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                 const uint32_t w_rows = (uint32_t)ly.w_rows;                    // K-chunk stride of a weight stage / 16
                 const uint32_t w_hi_off = (uint32_t)ly.lo_row;
                 const uint32_t lo_col = (uint32_t)ly.lo_col;
-                const uint32_t set = (uint32_t)b + 2u * (lseq & 1u);
-                const uint32_t d_tmem = tmem0 + set * 128u;
-                if (lane == 0) TL(1u + b, k, b, 3);
-                mbar_wait(BAR_ACC_EMPTY(set), ((lseq >> 1) & 1u) ^ 1u);
+                if (tl_on) TL(role, k, b, 3);
+                mbar_wait(BAR_ACC_EMPTY(b), (lseq & 1u) ^ 1u);
                 if (k > 0) {
                     mbar_wait(BAR_ACT(k - 1, 0), (uint32_t)(it & 1));
                     if (b == 1) mbar_wait(BAR_ACT(k - 1, 1), (uint32_t)(it & 1));
                 }
                 tc_fence_after_sync();
                 for (int t = 0; t < taps; ++t) {
-                    const uint32_t seq = seq0 + t;
-                    const uint32_t s = seq & 3u;
-                    mbar_wait(BAR_W_FULL(s), (seq >> 2) & 1u);
+                    mbar_wait(BAR_W_FULL(s), ph);
                     tc_fence_after_sync();
-                    if (lane == 0) TL(1u + b, k, b, 16 + t);
+                    if (tl_on) TL(role, k, b, 16 + t);
                     if (elect_one()) {
                         const uint32_t a_lo = a_base + (uint32_t)t;
                         const uint32_t w_lo = ((sbase + TC_OFF_W + s * TC_STAGE_BYTES) >> 4) | (w_rows << 16);
@@ -268,21 +280,24 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                             umma_f16(d_tmem + lo_col, da_lo, db_hi, idesc_b, 1u);
                         }
                         umma_commit(BAR_W_EMPTY(s));                             // this stream is done with the stage
-                        if (t == taps - 1) umma_commit(BAR_ACC_FULL(set));
+                        if (t == taps - 1) umma_commit(BAR_ACC_FULL(b));
                     }
                     __syncwarp();
+                    if (++s == TC_STAGES) { s = 0; ph ^= 1u; }
                 }
-                seq0 += taps;
             }
         }
-        if (lane == 0) TL_FLUSH(1u + b);
+        if (tl_on) TL_FLUSH(role);
     } else {
         // =================================== epilogue ====================================================
         // 8 warps: warp quadrant (warp & 3) selects the 32 TMEM lanes, group (0/1) the 32-channel half of the block.
+        // The blocks are processed one after the other, which staggers their layer pipelines by one epilogue: while block
+        // 0's epilogue runs, block 1's MMAs keep the tensor pipe and the shared-memory ports busy, and vice versa.
         const int quad = warp & 3;
         const int egrp = (warp - 3) >> 2;
         const int trow = 32 * quad + lane;                       // TMEM lane = row within the 128-block
         const uint32_t lane_addr = (uint32_t)(32 * quad) << 16;
+        const bool tl_on = (warp == 3) && (lane == 0);
         uint32_t lseq = 0;
         int it = 0;
         for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
@@ -297,14 +312,25 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                 uint8_t *outbuf = smem + ((k & 1) ? TC_OFF_P : TC_OFF_Q);
                 const float *bias = s_bias + 64 * k;
                 for (int b = 0; b < 2; ++b) {
-                    const uint32_t set = (uint32_t)b + 2u * (lseq & 1u);
                     const int r = p.b_row[k] + 128 * b + trow;
                     const int l = l_org + r;
                     const bool inside = (l >= 0) && (l < p.L);
-                    mbar_wait(BAR_ACC_FULL(set), (lseq >> 1) & 1u);
+                    // long skip (res1 = x0 planes in global memory): issue the loads before waiting for the accumulator so
+                    // that their latency hides behind the block's MMAs (the producer has pulled the rows into L2)
+                    uint4 xs_h[4], xs_l[4];
+                    if (type == TC_LONGSKIP) {
+                        const uint4 *x0 = reinterpret_cast<const uint4 *>(p.x0) + (size_t)n * 16 * p.L;
+#pragma unroll
+                        for (int h = 0; h < 4; ++h) {
+                            xs_h[h] = inside ? __ldg(x0 + (size_t)(4 * egrp + h) * p.L + l) : make_uint4(0, 0, 0, 0);
+                            xs_l[h] = inside ? __ldg(x0 + (size_t)(8 + 4 * egrp + h) * p.L + l) : make_uint4(0, 0, 0, 0);
+                        }
+                    }
+                    mbar_wait(BAR_ACC_FULL(b), lseq & 1u);
                     tc_fence_after_sync();
-                    if (warp == 3 && lane == 0) TL(3u, k, b, 1);
-                    const uint32_t d_tmem = tmem0 + set * 128u + lane_addr;
+                    if (tl_on) TL(3u, k, b, 1);
+                    const uint32_t d_tmem = tmem0 + (uint32_t)b * 128u + lane_addr;
+                    const uint32_t stash = tmem0 + 256u + 64u * (uint32_t)b + 32u * (uint32_t)egrp + lane_addr;
                     if (type == TC_LAST) {
                         // conv_last + SampleShuffle1D: mask[n][4 l + u] = D0[u] + 2^-11 D1[u] + bias[u]   (group 0 only)
                         uint32_t d[16];
@@ -314,7 +340,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                         }
                         tc_fence_before_sync();
                         __syncwarp();
-                        if (lane == 0) mbar_arrive(BAR_ACC_EMPTY(set));
+                        if (lane == 0) mbar_arrive(BAR_ACC_EMPTY(b));
                         if (egrp == 0 && l >= l0 && l < l_end) {
                             float4 o;
                             o.x = (__uint_as_float(d[0]) + TC_LO_INV * __uint_as_float(d[8])) + bias[0];
@@ -323,81 +349,108 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                             o.w = (__uint_as_float(d[3]) + TC_LO_INV * __uint_as_float(d[11])) + bias[3];
                             reinterpret_cast<float4 *>(p.out_mask)[(size_t)n * p.L + l] = o;
                         }
-                        continue;
-                    }
-                    const bool store_global = last_in_seg && (l >= l0) && (l < l_end);
-                    // this group's 32 channels: columns [32 egrp, +32) of D0 and of D1 (at +64)
-                    uint32_t d0[32], d1[32];
-                    tmem_ld16(d_tmem + 32 * egrp, *reinterpret_cast<uint32_t(*)[16]>(&d0[0]));
-                    tmem_ld16(d_tmem + 32 * egrp + 16, *reinterpret_cast<uint32_t(*)[16]>(&d0[16]));
-                    tmem_ld16(d_tmem + 64 + 32 * egrp, *reinterpret_cast<uint32_t(*)[16]>(&d1[0]));
-                    tmem_ld16(d_tmem + 64 + 32 * egrp + 16, *reinterpret_cast<uint32_t(*)[16]>(&d1[16]));
-                    tmem_ld_wait();
-                    tc_fence_before_sync();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(BAR_ACC_EMPTY(set));              // accumulator read: hand it back
-#pragma unroll
-                    for (int h = 0; h < 4; ++h) {                                  // 4 chunks of 8 channels
-                        const int c8 = 4 * egrp + h;
-                        float v[8];
-#pragma unroll
-                        for (int i = 0; i < 8; ++i)
-                            v[i] = (__uint_as_float(d0[8 * h + i]) + TC_LO_INV * __uint_as_float(d1[8 * h + i])) + bias[8 * c8 + i];
-                        if (type == TC_LEAKY) {
-#pragma unroll
-                            for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], kLeakySlope * v[i]);
-                        } else {
-                            // residual: short skip = value stored at this row of the output buffer (x two layers back);
-                            // long skip (res1) = x0 planes in global memory
-                            uint4 rh, rl;
-                            if (type == TC_RES) {
-                                rh = *reinterpret_cast<const uint4 *>(outbuf + c8 * TC_SLAB + r * 16);
-                                rl = *reinterpret_cast<const uint4 *>(outbuf + TC_PLANE + c8 * TC_SLAB + r * 16);
-                            } else if (inside) {
-                                const uint4 *x0 = reinterpret_cast<const uint4 *>(p.x0) + (size_t)n * 16 * p.L;
-                                rh = __ldg(x0 + (size_t)c8 * p.L + l);
-                                rl = __ldg(x0 + (size_t)(8 + c8) * p.L + l);
-                            } else {
-                                rh = make_uint4(0, 0, 0, 0);
-                                rl = rh;
-                            }
-                            float fh[8], fl[8];
-                            unpack8(rh, fh);
-                            unpack8(rl, fl);
-#pragma unroll
-                            for (int i = 0; i < 8; ++i) v[i] += fh[i] + TC_LO_INV * fl[i];
-                        }
-                        if (!inside) {
-#pragma unroll
-                            for (int i = 0; i < 8; ++i) v[i] = 0.0f;               // per-layer zero padding outside the row
-                        }
-                        uint4 uh, ul;
-                        split_pair(v[0], v[1], uh.x, ul.x);
-                        split_pair(v[2], v[3], uh.y, ul.y);
-                        split_pair(v[4], v[5], uh.z, ul.z);
-                        split_pair(v[6], v[7], uh.w, ul.w);
-                        if (!last_in_seg) {
-                            *reinterpret_cast<uint4 *>(outbuf + c8 * TC_SLAB + r * 16) = uh;
-                            *reinterpret_cast<uint4 *>(outbuf + TC_PLANE + c8 * TC_SLAB + r * 16) = ul;
-                        } else if (store_global) {
-                            uint4 *dst = reinterpret_cast<uint4 *>(p.out_planes) + (size_t)n * 16 * p.L;
-                            dst[(size_t)c8 * p.L + l] = uh;
-                            dst[(size_t)(8 + c8) * p.L + l] = ul;
-                        }
-                    }
-                    if (!last_in_seg) {
-                        fence_proxy_async_smem();
+                    } else {
+                        const bool store_global = last_in_seg && (l >= l0) && (l < l_end);
+                        const bool from_stash = (type == TC_RES) && last_in_seg && (p.stash != 0);
+                        // this group's 32 channels: columns [32 egrp, +32) of D0 and of D1 (at +64)
+                        uint32_t d0[32], d1[32];
+                        tmem_ld16(d_tmem + 32 * egrp, *reinterpret_cast<uint32_t(*)[16]>(&d0[0]));
+                        tmem_ld16(d_tmem + 32 * egrp + 16, *reinterpret_cast<uint32_t(*)[16]>(&d0[16]));
+                        tmem_ld16(d_tmem + 64 + 32 * egrp, *reinterpret_cast<uint32_t(*)[16]>(&d1[0]));
+                        tmem_ld16(d_tmem + 64 + 32 * egrp + 16, *reinterpret_cast<uint32_t(*)[16]>(&d1[16]));
+                        tmem_ld_wait();
+                        tc_fence_before_sync();
                         __syncwarp();
-                        if (lane == 0) mbar_arrive(BAR_ACT(k, b));
+                        if (lane == 0) mbar_arrive(BAR_ACC_EMPTY(b));              // accumulator read: hand it back
+#pragma unroll
+                        for (int h = 0; h < 4; ++h) {                                  // 4 chunks of 8 channels
+                            const int c8 = 4 * egrp + h;
+                            float v[8];
+#pragma unroll
+                            for (int i = 0; i < 8; ++i)
+                                v[i] = (__uint_as_float(d0[8 * h + i]) + TC_LO_INV * __uint_as_float(d1[8 * h + i])) + bias[8 * c8 + i];
+                            if (type == TC_LEAKY) {
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], kLeakySlope * v[i]);
+                            } else if (from_stash) {
+                                // short skip of the segment's last layer: fp32 copy parked in TMEM by the previous layer's epilogue
+                                uint32_t rs[8];
+                                tmem_ld8(stash + 8 * h, rs);
+                                tmem_ld_wait();
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) v[i] += __uint_as_float(rs[i]);
+                            } else {
+                                // residual: short skip = value stored at this row of the output buffer (x two layers back);
+                                // long skip (res1) = the x0 vectors loaded above
+                                uint4 rh, rl;
+                                if (type == TC_RES) {
+                                    rh = *reinterpret_cast<const uint4 *>(outbuf + c8 * TC_SLAB + r * 16);
+                                    rl = *reinterpret_cast<const uint4 *>(outbuf + TC_PLANE + c8 * TC_SLAB + r * 16);
+                                } else {
+                                    rh = xs_h[h];
+                                    rl = xs_l[h];
+                                }
+                                float fh[8], fl[8];
+                                unpack8(rh, fh);
+                                unpack8(rl, fl);
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) v[i] += fh[i] + TC_LO_INV * fl[i];
+                            }
+                            if (!inside) {
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) v[i] = 0.0f;               // per-layer zero padding outside the row
+                            }
+                            uint4 uh, ul;
+                            split_pair(v[0], v[1], uh.x, ul.x);
+                            split_pair(v[2], v[3], uh.y, ul.y);
+                            split_pair(v[4], v[5], uh.z, ul.z);
+                            split_pair(v[6], v[7], uh.w, ul.w);
+                            if (!last_in_seg) {
+                                *reinterpret_cast<uint4 *>(outbuf + c8 * TC_SLAB + r * 16) = uh;
+                                *reinterpret_cast<uint4 *>(outbuf + TC_PLANE + c8 * TC_SLAB + r * 16) = ul;
+                            } else if (store_global) {
+                                uint4 *dst = reinterpret_cast<uint4 *>(p.out_planes) + (size_t)n * 16 * p.L;
+                                dst[(size_t)c8 * p.L + l] = uh;
+                                dst[(size_t)(8 + c8) * p.L + l] = ul;
+                            }
+                        }
+                        if (!last_in_seg) {
+                            fence_proxy_async_smem();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(BAR_ACT(k, b));
+                        }
+                        if (p.stash != 0 && k == n_layers - 2) {
+                            // park the last layer's short skip (rows of buffer P, the output of layer k - 1) as fp32 in spare
+                            // TMEM columns, so that P can take the next tile's input while the last layer still runs
+                            const int rr = p.b_row[n_layers - 1] + 128 * b + trow;
+                            const uint8_t *pb = smem + TC_OFF_P + rr * 16;
+#pragma unroll
+                            for (int h2 = 0; h2 < 2; ++h2) {
+                                uint32_t rs[16];
+#pragma unroll
+                                for (int h = 0; h < 2; ++h) {
+                                    const int c8 = 4 * egrp + 2 * h2 + h;
+                                    float fh[8], fl[8];
+                                    unpack8(*reinterpret_cast<const uint4 *>(pb + c8 * TC_SLAB), fh);
+                                    unpack8(*reinterpret_cast<const uint4 *>(pb + TC_PLANE + c8 * TC_SLAB), fl);
+#pragma unroll
+                                    for (int i = 0; i < 8; ++i) rs[8 * h + i] = __float_as_uint(fh[i] + TC_LO_INV * fl[i]);
+                                }
+                                tmem_st16(stash + 16 * h2, rs);
+                            }
+                            tmem_st_wait();
+                        }
                     }
-                    if (warp == 3 && lane == 0) TL(3u, k, b, 3);
+                    if (tl_on) TL(3u, k, b, 3);
+                }
+                if (k == p.free_layer) {
+                    // every read of buffer P for this tile is done (this warp's share)
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(BAR_P_FREE);
                 }
             }
-            // every read of this tile's buffers by this warp is done
-            __syncwarp();
-            if (lane == 0) mbar_arrive(BAR_TILE_FREE);
         }
-        if (warp == 3 && lane == 0) TL_FLUSH(3u);
+        if (tl_on) TL_FLUSH(3u);
     }
 
     // ---- teardown --------------------------------------------------------------------------------------
@@ -541,6 +594,17 @@ int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void
     p.N = N; p.L = L;
     p.in = in; p.x0 = x0; p.out_planes = out_planes; p.out_mask = out_mask;
     p.timeline = g_timeline; p.timeline_cap = g_timeline_cap;
+    // Buffer P (input tile; operand of even layers, output / short-skip source of odd layers) is last touched by layer
+    // count-2 when the count is even, provided the last layer's short skip is parked in TMEM (stash); else by the last layer.
+    const bool even = (count % 2) == 0;
+    p.stash = (even && layers[count - 1].type == TC_RES) ? 1 : 0;
+    p.free_layer = even ? count - 2 : count - 1;
+    // the producer requests the next tile's input after this tap of the last layer (the ring holds that many taps of the
+    // last layer while the epilogue of free_layer is still running, so waiting for P there delays no weights)
+    p.in_layer = count - 1;
+    p.in_tap = (even && layers[count - 1].taps > TC_STAGES - 1) ? TC_STAGES - 2 : layers[count - 1].taps - 1;
+    for (int k = 0; k < count; ++k)
+        STOF_REQUIRE(layers[k].taps >= 1, STOF_E_INVALID, "chain_tc: layer without taps");
     const bool ends_last = layers[count - 1].type == TC_LAST;
     STOF_REQUIRE(ends_last ? out_mask != nullptr : out_planes != nullptr, STOF_E_INVALID, "chain_tc: missing output buffer");
     const int grid = (int)(total < kSMs ? total : kSMs);

@@ -40,6 +40,9 @@ struct TcParams {
     int r_in;                   // input rows staged per tile
     int l_shift;                // position of smem row 0 relative to the tile's first output position
     int t_out;                  // valid output positions per tile
+    int free_layer;             // layer after whose epilogue the input buffer P is no longer touched by the tile
+    int stash;                  // 1: the last layer's short skip is parked in TMEM by the epilogue of layer n_layers-2
+    int in_layer, in_tap;       // the producer requests the next tile's input after issuing this weight tap
     int tiles_per_row, total_tiles;
     int N, L;
     const void *in;             // split planes [N][2][8][L][8] fp16
