@@ -161,6 +161,63 @@ int stof_debug_set_timeline(void *dev_buf, int capacity_events);
 /* Counter of kernels launched by this library since load (bench.py's gpu_launches). */
 uint64_t stof_launch_count(void);
 
+/* ------------------------------------------------------------------------------------------------
+ * Operators either side of the path (SURVEY.md 8f "next" rows and 8a rows a9-a13)
+ * ------------------------------------------------------------------------------------------------ */
+
+/* Replaces toa_rmse (utils/metrics.py:9-41), the consumer of the ToF table with `etol` (main.py:347).
+ *   gt_dev (N, G) fp32, es_dev (N, E) fp32: zeros / NaN / inf are "no echo" and dropped (:6,19-20)
+ *   tol compares with the SQUARED distance (:27-33)
+ *   out_dev (N, 7) fp32: rmse, precision, recall, jaccard [percent], tp, fp, fn; rows without a valid gt or
+ *   estimate give 0, NaN, NaN, NaN, 0, 0, 0 exactly like the reference's 0/0 divisions                  */
+int stof_toa_rmse(const float *gt_dev, int G, const float *es_dev, int E, int N, float tol, float *out_dev, void *stream);
+
+/* Replaces coords2mask (utils/mask2samples.py:139-148): mask = 0; mask[n, max(s,0)] = 1; mask[n, 0] = 0.
+ *   samples_dev (N, G) int64 (negative entries are clamped to 0 IN PLACE like the reference; entries >= M raise in
+ *   torch's scatter_ and are ignored here), mask_dev (N, M) fp32                                        */
+int stof_coords2mask(int64_t *samples_dev, int N, int G, int M, float *mask_dev, void *stream);
+
+/* Replaces the training / validation loss of main.py:228-232 in one pass over the mask:
+ *   true  = coords2mask(gt_true);  blur = conv1d(true, gauss(k, sigma), pad k/2);  blur *= amplitude / max(blur)
+ *   loss  = mean((pred - blur)^2) + lambda * mean(|pred|)
+ *   gauss_dev (k) fp32 taps (utils/gaussian.py:4-7), k odd <= 31
+ *   blur_max_io_dev (1) fp32: global max of the un-normalised blur.  mode 0: computed here (single GPU, main.py:230);
+ *       mode 1: only compute it (first phase of the sharded loss: MAX-all-reduce it, then call with mode 2);
+ *       mode 2: use the value already in blur_max_io_dev
+ *   loss_dev (1) fp64: the loss over these N rows (mean over N*M elements); grad_dev (N, M) fp32 or NULL: d loss / d pred
+ *   scratch_dev: at least stof_loss_scratch_bytes(N, M) bytes                                              */
+size_t stof_loss_scratch_bytes(int N, int M);
+int stof_mask_loss(const float *pred_dev, const int64_t *samples_dev, int N, int G, int M, const float *gauss_dev, int k,
+                   float amplitude, float lambda, int mode, float *blur_max_io_dev, double *loss_dev, float *grad_dev,
+                   void *scratch_dev, void *stream);
+
+/* Replaces find_threshold (utils/threshold.py:6-28; sklearn.metrics.roc_curve on batch element 0, main.py:330):
+ * clamp negatives (or min-max normalise over the WHOLE batch when norm_opt), ROC of row 0 with drop_intermediate,
+ * threshold at the arg-max of sqrt(tpr * (1 - fpr)).
+ *   pred_dev, true_dev (N, M) fp32; th_out_dev (1) fp64 (+inf when row 0 has no positive, as sklearn's first point)
+ *   scratch_dev: at least stof_threshold_scratch_bytes(N, M) bytes                                       */
+size_t stof_threshold_scratch_bytes(int N, int M);
+int stof_find_threshold(const float *pred_dev, const float *true_dev, int N, int M, int norm_opt, double *th_out_dev,
+                        void *scratch_dev, void *stream);
+
+/* Replaces the dataset-side rf_scale_factor interpolation (datasets/chirp_dataset.py:10-17 upscale_1d and :79-91 iq2rf):
+ * linear interpolation of each row from n to floor(n * rf) samples on np.linspace(0, n/fs, ., endpoint=True) grids,
+ * optionally modulated onto the carrier: out = Re((I + jQ)(t) * exp(2j pi fc t)).  Computed in fp64 like scipy, stored fp32.
+ *   in_re_dev (N, n) fp32 (envelope / I), in_im_dev (N, n) fp32 or NULL (Q); out_dev (N, floor(n * rf)) fp32
+ *   fc = 0 and in_im_dev = NULL gives upscale_1d                                                          */
+int stof_rf_upscale(const float *in_re_dev, const float *in_im_dev, int N, int n, double rf, double fs, double fc,
+                    float *out_dev, void *stream);
+
+/* Replaces AttentionBlock.forward (utils/attention_block.py:13-25; dead code in the reference, parity unpinned):
+ *   q, k, v = x Wq^T + bq, ...;  out = dropout(softmax(q k^T / sqrt(H)), p) v
+ *   x_dev (B, S, D) fp32; w*_dev (H, D), b*_dev (H) fp32 (nn.Linear layout); out_dev (B, S, H)
+ *   dropout_p in [0, 1): 0 disables it (the reference hard-codes 0.5, also in eval); seed drives a counter-based RNG
+ *   scratch_dev: at least stof_attention_scratch_bytes(B, S, H) bytes                                     */
+size_t stof_attention_scratch_bytes(int B, int S, int H);
+int stof_attention_block(const float *x_dev, int B, int S, int D, int H, const float *wq_dev, const float *bq_dev,
+                         const float *wk_dev, const float *bk_dev, const float *wv_dev, const float *bv_dev,
+                         float dropout_p, uint64_t seed, float *out_dev, void *scratch_dev, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -180,3 +180,52 @@ def sample_shuffle(x, r):
     out = np.empty((B, Cs // r, W * r), dtype=np.float32)
     lib().stof_oracle_sample_shuffle(_p(x), B, Cs, W, int(r), _p(out))
     return out
+
+
+def mask_loss(pred, samples, gauss, amp=20.0, lam=1e-2, want_grad=True):
+    """main.py:228-232 -> (loss, grad (N,M) or None, blur_max)."""
+    pred = _f32(pred)
+    n, m = pred.shape[0], pred.shape[-1]
+    pred2 = pred.reshape(n, m)
+    s2 = np.ascontiguousarray(samples, dtype=np.int64).reshape(n, -1)
+    g = _f32(gauss).reshape(-1)
+    grad = np.empty((n, m), dtype=np.float32) if want_grad else None
+    mx = C.c_float(0)
+    f = lib().stof_oracle_mask_loss
+    f.restype = C.c_double
+    loss = f(_p(pred2), _p(s2), n, s2.shape[1], m, _p(g), g.size, C.c_float(amp), C.c_float(lam),
+             _p(grad) if want_grad else None, C.byref(mx))
+    return float(loss), grad, float(mx.value)
+
+
+def find_threshold(pred, truth, norm_opt=False):
+    """utils/threshold.py:6-28 (sklearn roc_curve restated)."""
+    pred = _f32(pred); truth = _f32(truth)
+    n = pred.shape[0]
+    p2 = pred.reshape(n, -1); t2 = truth.reshape(n, -1)
+    f = lib().stof_oracle_find_threshold
+    f.restype = C.c_double
+    return float(f(_p(p2), _p(t2), n, p2.shape[1], int(bool(norm_opt))))
+
+
+def rf_upscale(re, im, rf, fs=1.0, fc=0.0):
+    """datasets/chirp_dataset.py:10-17,79-91."""
+    re = _f32(re)
+    re2 = re.reshape(-1, re.shape[-1])
+    im2 = _f32(im).reshape(re2.shape) if im is not None else None
+    n = re2.shape[1]
+    out = np.empty((re2.shape[0], int(n * rf)), dtype=np.float32)
+    lib().stof_oracle_rf_upscale(_p(re2), _p(im2) if im2 is not None else None, re2.shape[0], n, C.c_double(rf),
+                                 C.c_double(fs), C.c_double(fc), _p(out))
+    return out
+
+
+def attention(x, wq, bq, wk, bk, wv, bv):
+    """utils/attention_block.py:13-25, dropout disabled."""
+    x = _f32(x)
+    b, s, d = x.shape
+    ws = [_f32(a) for a in (wq, bq, wk, bk, wv, bv)]
+    h = ws[0].shape[0]
+    out = np.empty((b, s, h), dtype=np.float32)
+    lib().stof_oracle_attention(_p(x), b, s, d, h, *[_p(a) for a in ws], _p(out))
+    return out

@@ -344,3 +344,184 @@ void stof_oracle_toa_rmse(const float *gt, int G, const float *es, int E, int N,
         o[4] = tp; o[5] = fp; o[6] = fn;
     }
 }
+
+/* ------------------------------------------------------------------ loss (training / validation step)
+ * main.py:228-232 with utils/gaussian.py:4-7 and utils/mask2samples.py:139-148:
+ *   true = coords2mask(gt);  blur = conv1d(true, gauss, padding k/2);  blur /= blur.max();  blur *= amp
+ *   loss = mean((pred - blur)^2) + lambda * mean(|pred|)
+ * Dense restatement (mask and blur are materialised, unlike the CUDA kernel).  grad (N,M) may be NULL:
+ * d loss / d pred = (2 (pred - blur) + lambda sign(pred)) / (N M).  Returns the loss; *blur_max_out = blur.max().     */
+double stof_oracle_mask_loss(const float *pred, const int64_t *samples, int N, int G, int M, const float *gauss, int k,
+                             float amp, float lambda, float *grad, float *blur_max_out)
+{
+    const size_t tot = (size_t)N * M;
+    float *mask = (float *)malloc(sizeof(float) * tot);
+    float *blur = (float *)malloc(sizeof(float) * tot);
+    stof_oracle_coords2mask(samples, N, G, M, mask);
+    const int h = k / 2;
+    float mx = -INFINITY;
+    for (int n = 0; n < N; ++n)
+        for (int m = 0; m < M; ++m) {
+            float a = 0.0f;
+            for (int t = 0; t < k; ++t) {                   /* cross-correlation, zero padding */
+                const int q = m + t - h;
+                if (q >= 0 && q < M) a += gauss[t] * mask[(size_t)n * M + q];
+            }
+            blur[(size_t)n * M + m] = a;
+            if (a > mx) mx = a;
+        }
+    if (blur_max_out) *blur_max_out = mx;
+    double se = 0.0, sa = 0.0;
+    const float inv = (float)(1.0 / ((double)N * (double)M));
+    for (size_t i = 0; i < tot; ++i) {
+        const float b = (blur[i] / mx) * amp;
+        const float d = pred[i] - b;
+        se += (double)d * (double)d;
+        sa += fabs((double)pred[i]);
+        if (grad) {
+            const float sg = pred[i] > 0.0f ? 1.0f : (pred[i] < 0.0f ? -1.0f : 0.0f);
+            grad[i] = 2.0f * d * inv + lambda * sg * inv;
+        }
+    }
+    free(mask); free(blur);
+    return se / (double)tot + (double)lambda * (sa / (double)tot);
+}
+
+/* ------------------------------------------------------------------ find_threshold
+ * utils/threshold.py:6-28.  The ROC itself is scikit-learn's (third-party dependency, unpinned in requirements.txt;
+ * restated from scikit-learn 1.9 sklearn/metrics/_ranking.py roc_curve + confusion_matrix_at_thresholds): stable sort
+ * by descending score, cumulative tp at the last index of each distinct score, fps = 1 + idx - tps, drop_intermediate
+ * (second differences of fps and tps both zero), prepend (0,0) at threshold +inf, fpr/tpr = NaN when a class is empty;
+ * then threshold.py:24-26: first arg-max of sqrt(tpr (1 - fpr)) with numpy's NaN-is-max rule.                       */
+typedef struct { float s; int y; } roc_item;
+static int roc_cmp(const void *a, const void *b)
+{
+    const float x = ((const roc_item *)a)->s, y = ((const roc_item *)b)->s;
+    return (x < y) - (x > y);                               /* descending */
+}
+double stof_oracle_find_threshold(const float *pred, const float *truth, int N, int M, int norm_opt)
+{
+    const size_t tot = (size_t)N * M;
+    float tmax = -INFINITY, pmin = INFINITY, pmax = -INFINITY;
+    for (size_t i = 0; i < tot; ++i) {
+        if (truth[i] > tmax) tmax = truth[i];
+        if (pred[i] < pmin) pmin = pred[i];
+        if (pred[i] > pmax) pmax = pred[i];
+    }
+    const float pos = (tmax != 0.0f) ? tmax : 1.0f;         /* :18 */
+    roc_item *it = (roc_item *)malloc(sizeof(roc_item) * (size_t)M);
+    for (int i = 0; i < M; ++i) {
+        float s = pred[i];
+        if (norm_opt) { s = s - pmin; s = s / (pmax - pmin); }     /* :12-13 (max of the shifted tensor = pmax - pmin) */
+        else if (s < 0.0f) s = 0.0f;                               /* :15 */
+        it[i].s = s;
+        it[i].y = (truth[i] == pos);
+    }
+    qsort(it, (size_t)M, sizeof(roc_item), roc_cmp);
+    double *fps = (double *)malloc(sizeof(double) * (size_t)(M + 1));
+    double *tps = (double *)malloc(sizeof(double) * (size_t)(M + 1));
+    double *thr = (double *)malloc(sizeof(double) * (size_t)(M + 1));
+    int np_ = 0;
+    double c = 0.0;
+    for (int i = 0; i < M; ++i) {
+        c += it[i].y;
+        if (i == M - 1 || it[i].s != it[i + 1].s) { tps[np_] = c; fps[np_] = 1.0 + i - c; thr[np_] = it[i].s; ++np_; }
+    }
+    double *f2 = (double *)malloc(sizeof(double) * (size_t)(M + 2));
+    double *t2 = (double *)malloc(sizeof(double) * (size_t)(M + 2));
+    double *h2 = (double *)malloc(sizeof(double) * (size_t)(M + 2));
+    /* drop_intermediate decides on the uncompacted neighbours, then the (0, 0) point is prepended */
+    int n2 = 0;
+    f2[n2] = 0.0; t2[n2] = 0.0; h2[n2] = INFINITY; ++n2;     /* prepended (0, 0) point */
+    for (int p = 0; p < np_; ++p) {
+        int keep = 1;
+        if (np_ > 2 && p > 0 && p < np_ - 1)
+            keep = (fps[p + 1] - 2 * fps[p] + fps[p - 1] != 0.0) || (tps[p + 1] - 2 * tps[p] + tps[p - 1] != 0.0);
+        if (keep) { f2[n2] = fps[p]; t2[n2] = tps[p]; h2[n2] = thr[p]; ++n2; }
+    }
+    const double P = t2[n2 - 1], Nn = f2[n2 - 1];
+    double best = -1.0, best_th = INFINITY;
+    int have_nan = 0;
+    for (int p = 0; p < n2 && !have_nan; ++p) {
+        const double tpr = (P <= 0.0) ? NAN : t2[p] / P;
+        const double fpr = (Nn <= 0.0) ? NAN : f2[p] / Nn;
+        const double g = sqrt(tpr * (1.0 - fpr));
+        if (g != g) { best_th = h2[p]; have_nan = 1; break; }     /* np.argmax: the first NaN wins */
+        if (g > best) { best = g; best_th = h2[p]; }
+    }
+    free(it); free(fps); free(tps); free(thr); free(f2); free(t2); free(h2);
+    return best_th;
+}
+
+/* ------------------------------------------------------------------ rf_scale_factor pre-interpolation
+ * datasets/chirp_dataset.py:10-17 (upscale_1d) and :79-91 (iq2rf).  The interpolation is scipy.interpolate.interp1d
+ * (kind='linear'; third-party, unpinned; restated from scipy 1.x _interpolate.py _call_linear): idx =
+ * searchsorted(x, t) clipped to [1, n-1]; y = slope * (t - x_lo) + y_lo.  Grids are np.linspace(0, n/fs, num,
+ * endpoint=True) = arange(num) * step with the last sample set to the stop value.  in_im may be NULL (upscale_1d).     */
+void stof_oracle_rf_upscale(const float *in_re, const float *in_im, int N, int n, double rf, double fs, double fc, float *out)
+{
+    const int m = (int)((double)n * rf);
+    const double T = (double)n / fs;
+    const double dx = T / (double)(n - 1), dt = (m > 1) ? T / (double)(m - 1) : 0.0;
+    for (int r = 0; r < N; ++r)
+        for (int i = 0; i < m; ++i) {
+            const double t = (i == m - 1 && m > 1) ? T : (double)i * dt;
+            int idx = 0;                                       /* searchsorted(x, t, side='left'), linear scan */
+            while (idx < n && ((idx == n - 1) ? T : (double)idx * dx) < t) ++idx;
+            if (idx < 1) idx = 1;
+            if (idx > n - 1) idx = n - 1;
+            const double x_lo = (double)(idx - 1) * dx, x_hi = (idx == n - 1) ? T : (double)idx * dx;
+            const double a = in_re[(size_t)r * n + idx - 1], b = in_re[(size_t)r * n + idx];
+            const double yr = (b - a) / (x_hi - x_lo) * (t - x_lo) + a;
+            double v = yr;
+            if (in_im || fc != 0.0) {
+                double yi = 0.0;
+                if (in_im) {
+                    const double c = in_im[(size_t)r * n + idx - 1], d = in_im[(size_t)r * n + idx];
+                    yi = (d - c) / (x_hi - x_lo) * (t - x_lo) + c;
+                }
+                const double ph = ((2.0 * M_PI) * fc) * t;     /* exp(2j*np.pi*fc*t), :88 */
+                v = yr * cos(ph) - yi * sin(ph);
+            }
+            out[(size_t)r * m + i] = (float)v;
+        }
+}
+
+/* ------------------------------------------------------------------ AttentionBlock (parity UNPINNED)
+ * utils/attention_block.py:13-25 with dropout disabled: out = softmax(q k^T / sqrt(H)) v, q/k/v = x W^T + b.
+ * The shipped class raises NameError (F is never imported) and no checkpoint has its weights.                     */
+void stof_oracle_attention(const float *x, int B, int S, int D, int H, const float *wq, const float *bq, const float *wk,
+                           const float *bk, const float *wv, const float *bv, float *out)
+{
+    double *q = (double *)malloc(sizeof(double) * (size_t)S * H * 3), *k = q + (size_t)S * H, *v = k + (size_t)S * H;
+    double *p = (double *)malloc(sizeof(double) * (size_t)S);
+    for (int b = 0; b < B; ++b) {
+        const float *xb = x + (size_t)b * S * D;
+        for (int s = 0; s < S; ++s)
+            for (int h = 0; h < H; ++h) {
+                double aq = bq[h], ak = bk[h], av = bv[h];
+                for (int d = 0; d < D; ++d) {
+                    const double xv = xb[(size_t)s * D + d];
+                    aq += xv * wq[(size_t)h * D + d]; ak += xv * wk[(size_t)h * D + d]; av += xv * wv[(size_t)h * D + d];
+                }
+                q[(size_t)s * H + h] = aq; k[(size_t)s * H + h] = ak; v[(size_t)s * H + h] = av;
+            }
+        const double sc = 1.0 / sqrt((double)H);
+        for (int s = 0; s < S; ++s) {
+            double mx = -INFINITY, sum = 0.0;
+            for (int j = 0; j < S; ++j) {
+                double a = 0.0;
+                for (int h = 0; h < H; ++h) a += q[(size_t)s * H + h] * k[(size_t)j * H + h];
+                p[j] = a * sc;
+                if (p[j] > mx) mx = p[j];
+            }
+            for (int j = 0; j < S; ++j) { p[j] = exp(p[j] - mx); sum += p[j]; }
+            for (int h = 0; h < H; ++h) {
+                double a = 0.0;
+                for (int j = 0; j < S; ++j) a += p[j] * v[(size_t)j * H + h];
+                out[((size_t)b * S + s) * H + h] = (float)(a / sum);
+            }
+        }
+    }
+    free(q); free(p);
+}

@@ -10,6 +10,12 @@ from .models.espcn_1d import ESPCN_1D                          # noqa: F401
 from .utils.sample_shuffle import SampleShuffle1D              # noqa: F401
 from .utils.mask2samples import (mask2coords, get_maxima_positions, nms_1d, thresholding,  # noqa: F401
                                  coords2mask)
+from .utils.metrics import toa_rmse                             # noqa: F401
+from .utils.threshold import find_threshold                     # noqa: F401
+from .utils.attention_block import AttentionBlock               # noqa: F401
+from .utils.gaussian import gaussian_kernel                     # noqa: F401
+from .datasets.chirp_dataset import upscale_1d, iq2rf           # noqa: F401
+from .loss import mask_loss                                     # noqa: F401
 from .checkpoint import load_checkpoint, load_config, build_model  # noqa: F401
 
 __version__ = "0.1"

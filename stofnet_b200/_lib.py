@@ -38,7 +38,7 @@ if not os.path.exists(LIB_PATH):
 
 lib = C.CDLL(LIB_PATH)
 
-_vp, _i, _f, _sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
+_vp, _i, _f, _sz, _d = C.c_void_p, C.c_int, C.c_float, C.c_size_t, C.c_double
 _SIGS = {
     "stof_version": (C.c_char_p, []),
     "stof_last_error": (C.c_char_p, []),
@@ -59,6 +59,16 @@ _SIGS = {
     "stof_debug_set_timeline": (_i, [_vp, _i]),
     "stof_profile_enable": (_i, [_vp, _i]),
     "stof_profile_collect": (_i, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
+    # operators either side of the path
+    "stof_toa_rmse": (_i, [_vp, _i, _vp, _i, _i, _f, _vp, _vp]),
+    "stof_coords2mask": (_i, [_vp, _i, _i, _i, _vp, _vp]),
+    "stof_loss_scratch_bytes": (_sz, [_i, _i]),
+    "stof_mask_loss": (_i, [_vp, _vp, _i, _i, _i, _vp, _i, _f, _f, _i, _vp, _vp, _vp, _vp, _vp]),
+    "stof_threshold_scratch_bytes": (_sz, [_i, _i]),
+    "stof_find_threshold": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
+    "stof_rf_upscale": (_i, [_vp, _vp, _i, _i, _d, _d, _d, _vp, _vp]),
+    "stof_attention_scratch_bytes": (_sz, [_i, _i, _i]),
+    "stof_attention_block": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _f, C.c_uint64, _vp, _vp, _vp]),
 }
 for _name, (_res, _args) in _SIGS.items():
     _fn = getattr(lib, _name)

@@ -137,11 +137,19 @@ def get_amplitudes(frames, samples):
 
 
 def coords2mask(samples, ref):
-    """One-hot ground-truth mask for the loss (reference :139-148): scatter ones at the (clamped)
-    sample indices, then clear column 0 (placeholder for absent echoes).  Loss-side helper, off the
-    inference path; plain tensor indexing on the caller's device."""
-    empty_mask = torch.zeros_like(ref)
-    samples[samples < 0] = 0
-    empty_mask.scatter_(2, samples, 1)
-    empty_mask[..., :1] = 0
-    return empty_mask
+    """One-hot ground-truth mask for the loss (reference :139-148): ones at the (clamped, in place like the
+    reference) sample indices, column 0 cleared (placeholder for absent echoes).  One memset + one scatter
+    kernel (stof_coords2mask).  samples (N, 1, G) int64, ref (N, 1, M)."""
+    require_cuda(ref, "ref")
+    require_cuda(samples, "samples")
+    if samples.dtype != torch.int64:
+        raise RuntimeError("stofnet_b200: coords2mask expects int64 sample indices (scatter_ index), got %s" % samples.dtype)
+    n, m = ref.shape[0], ref.shape[-1]
+    work = samples if samples.is_contiguous() else samples.contiguous()
+    g = work.numel() // n
+    mask = torch.empty(ref.shape, dtype=torch.float32, device=ref.device)
+    with torch.cuda.device(ref.device):
+        check(lib.stof_coords2mask(work.data_ptr(), n, g, m, mask.data_ptr(), stream_ptr(ref.device)))
+    if work is not samples:
+        samples.copy_(work)
+    return mask if ref.dtype == torch.float32 else mask.to(ref.dtype)

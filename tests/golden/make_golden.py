@@ -18,6 +18,8 @@ kernels (torch 2.11.0, oneDNN, fp32; fp64 re-run stored beside it as the tie-bre
   peaks_cases.npz      hand-made stage-4 edge cases -> reference indices / coords
   espcn_<ckpt>.npz     ESPCN_1D forward masks
   metrics_cases.npz    toa_rmse / coords2mask / find_threshold known answers
+  aux_cases.npz        loss + gradient (main.py:228-232 through the reference's ops and autograd),
+                       find_threshold, upscale_1d / iq2rf, AttentionBlock (dropout off)
 
 Nothing here is imported by the product; tests/ read the .npz files only.
 """
@@ -215,8 +217,112 @@ def gen_metrics_cases():
     np.savez_compressed(os.path.join(HERE, "metrics_cases.npz"), **out)
 
 
+def gen_aux_cases():
+    """loss (main.py:228-232), find_threshold, rf pre-interpolation, AttentionBlock -> aux_cases.npz"""
+    import types
+    import torch.nn.functional as F
+    from utils.gaussian import gaussian_kernel
+    rng = np.random.default_rng(33)
+    out = {}
+    # ---- loss + d loss / d pred through the reference's own ops and autograd
+    gk = torch.tensor(gaussian_kernel(size=7, sigma=1), dtype=torch.float32).unsqueeze(0).unsqueeze(0)
+    out["gauss7"] = gk.numpy().reshape(-1)
+    loss_cases = {
+        "a": (rng.normal(size=(3, 1, 400)).astype(np.float32), [[37, 120, 0, 0], [5, 8, 399, 250], [-4, 0, 0, 0]], 1e-2),
+        "b": (rng.normal(scale=3, size=(2, 1, 9000)).astype(np.float32), [[100, 100, 103], [8999, 1, 4500]], 1.0),
+        "c": (np.zeros((2, 1, 64), dtype=np.float32), [[10], [20]], 1e-2),
+    }
+    for name, (pred, gt, lam) in loss_cases.items():
+        mp = torch.from_numpy(pred.copy()).requires_grad_(True)
+        gt_true = torch.tensor(gt, dtype=torch.long).unsqueeze(1)
+        mt = coords2mask(gt_true.clone(), mp.detach())
+        blur = F.conv1d(mt, gk, padding=3)
+        blur /= blur.max()
+        blur *= 20
+        loss = torch.nn.MSELoss()(mp.squeeze(1), blur.squeeze(1).float()) + \
+            torch.nn.L1Loss()(mp.squeeze(1), torch.zeros_like(mp.squeeze(1))) * lam
+        loss.backward()
+        out["loss_%s_pred" % name] = pred
+        out["loss_%s_gt" % name] = gt_true.numpy()
+        out["loss_%s_lambda" % name] = np.float64(lam)
+        out["loss_%s_value" % name] = np.float64(loss.item())
+        out["loss_%s_grad" % name] = mp.grad.numpy()
+        out["loss_%s_blur" % name] = blur.numpy()
+    out["loss_names"] = np.array(sorted(loss_cases))
+    # ---- find_threshold (utils/threshold.py:6-28)
+    ft = {}
+    pred = rng.normal(size=(2, 1, 10240)).astype(np.float32)
+    true = np.zeros((2, 1, 10240), dtype=np.float32); true[0, 0, [100, 5000, 9999]] = 1; pred[0, 0, [100, 5000]] += 4
+    ft["long"] = (pred, true)
+    pred = (np.round(rng.normal(size=(1, 1, 700)) * 2) / 2).astype(np.float32)
+    true = np.zeros((1, 1, 700), dtype=np.float32); true[0, 0, ::50] = 1
+    ft["ties"] = (pred, true)
+    ft["nopos"] = (rng.normal(size=(2, 1, 300)).astype(np.float32), np.zeros((2, 1, 300), dtype=np.float32))
+    pred = rng.normal(size=(1, 1, 5000)).astype(np.float32)
+    true = np.zeros((1, 1, 5000), dtype=np.float32); true[0, 0, 77] = 20.0; pred[0, 0, 77] = 9
+    ft["amp20"] = (pred, true)
+    pred = np.abs(rng.normal(size=(1, 1, 4096))).astype(np.float32)
+    true = (rng.uniform(size=(1, 1, 4096)) < 0.3).astype(np.float32); pred += true
+    ft["dense"] = (pred, true)
+    import warnings
+    for name, (pred, true) in ft.items():
+        out["ft_%s_pred" % name] = pred
+        out["ft_%s_true" % name] = true
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            out["ft_%s_th" % name] = np.float64(find_threshold(torch.from_numpy(pred), torch.from_numpy(true), 20))
+            out["ft_%s_th_norm" % name] = np.float64(find_threshold(torch.from_numpy(pred), torch.from_numpy(true), 20, norm_opt=True))
+    out["ft_names"] = np.array(sorted(ft))
+    # ---- rf_scale_factor pre-interpolation: import datasets/chirp_dataset.py unmodified; natsort / omegaconf are not
+    # installed here and are only used by the file loader, so empty stand-in modules satisfy its import lines
+    for modname, attr in (("natsort", "natsorted"), ("omegaconf", "OmegaConf")):
+        if modname not in sys.modules:
+            mod = types.ModuleType(modname)
+            setattr(mod, attr, None)
+            sys.modules[modname] = mod
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("ref_chirp_dataset", os.path.join(REF, "datasets", "chirp_dataset.py"))
+    cd = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(cd)                      # the reference file, loaded by path (no package __init__ there)
+    upscale_1d, ChirpDataset = cd.upscale_1d, cd.ChirpDataset
+    env = np.abs(rng.normal(size=(3, 257))).astype(np.float32)
+    iq = (rng.normal(size=(3, 200)) + 1j * rng.normal(size=(3, 200))).astype(np.complex64)
+    out["up_env"] = env
+    out["up_iq_re"] = iq.real.copy(); out["up_iq_im"] = iq.imag.copy()
+    for rf in (10, 20, 2.5):
+        out["up_env_rf%s" % th_key(rf)] = np.stack([upscale_1d(e.astype(np.float64), rf) for e in env]).astype(np.float32)
+    fs, fc = 20e6, 5e6
+    out["up_fs"] = np.float64(fs); out["up_fc"] = np.float64(fc)
+    for rf in (10, 20):
+        out["up_iq_rf%s" % th_key(rf)] = np.stack([ChirpDataset.iq2rf(z.astype(np.complex128), fc=fc, fs=fs, rescale_factor=rf)
+                                                   for z in iq]).astype(np.float32)
+    # ---- AttentionBlock (utils/attention_block.py; dead code: F is never imported -> inject it, dropout forced to 0)
+    import utils.attention_block as ab
+
+    class _F:
+        @staticmethod
+        def scaled_dot_product_attention(q, k, v, dropout_p=0.0):
+            return F.scaled_dot_product_attention(q, k, v, dropout_p=0.0)
+    ab.F = _F
+    torch.manual_seed(5)
+    blk = ab.AttentionBlock(48, 40).eval()
+    x = torch.randn(2, 70, 48)
+    with torch.no_grad():
+        y = blk(x)
+    out["att_x"] = x.numpy(); out["att_y"] = y.numpy()
+    for nm in ("query", "key", "value"):
+        out["att_%s_w" % nm] = getattr(blk, nm).weight.detach().numpy()
+        out["att_%s_b" % nm] = getattr(blk, nm).bias.detach().numpy()
+    np.savez_compressed(os.path.join(HERE, "aux_cases.npz"), **out)
+    print("aux cases done")
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "aux":
+        gen_aux_cases()
+        sys.exit(0)
     gen_forward()
     gen_peaks_cases()
     gen_metrics_cases()
+    gen_aux_cases()
     print("done")
