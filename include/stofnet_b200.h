@@ -218,6 +218,43 @@ int stof_attention_block(const float *x_dev, int B, int S, int D, int H, const f
                          const float *wk_dev, const float *bk_dev, const float *wv_dev, const float *bv_dev,
                          float dropout_p, uint64_t seed, float *out_dev, void *scratch_dev, void *stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Training step (main.py:217-248): forward that keeps the activations, backward of the whole stack, fused AdamW.
+ * fp32 CUDA-core kernels; gradients are deterministic (fixed reduction order, no float atomics).
+ * ------------------------------------------------------------------------------------------------ */
+
+/* Device-side gradient buffers, one per parameter tensor, fp32 in PyTorch's (Cout, Cin, K) / (Cout) layout - i.e. what
+ * `param.grad` holds after loss.backward() (main.py:247).  The caller typically carves them out of ONE flat buffer so that the
+ * data-parallel gradient all-reduce is a single collective.  Pointers are device memory.                                */
+typedef struct stof_grads {
+    float *conv1_w, *conv1_b;
+    float *mid_w[STOF_MAX_MID_CONVS];
+    float *mid_b[STOF_MAX_MID_CONVS];
+    float *last_w, *last_b;
+    float *contract_w, *contract_b;     /* NULL when the model has no semi-global block */
+    float *expand_w, *expand_b;
+} stof_grads;
+
+/* Bytes of the activation / scratch workspace one training step of N rows of length L needs (forward + backward). */
+int stof_train_workspace_bytes(const stof_model *m, int N, int L, size_t *bytes);
+
+/* `masks_pred = model(frame)` in training mode (main.py:221): same result as stof_forward's fp32 path, and every layer's
+ * activations (plus the max-pool arg-max of the semi-global block) stay in ws_dev for stof_backward.                    */
+int stof_forward_train(stof_model *m, const float *x_dev, int N, int L, float *mask_dev, void *ws_dev, size_t ws_bytes,
+                       void *stream);
+
+/* `loss.backward()` (main.py:247) for the StofNet stack: g_mask_dev (N, r*L) = d loss / d masks_pred -> every parameter's
+ * gradient (overwritten, not accumulated: the reference calls optimizer.zero_grad() before every backward, main.py:246).
+ * Must follow stof_forward_train on the same x_dev / ws_dev with unchanged weights.                                      */
+int stof_backward(stof_model *m, const float *x_dev, const float *g_mask_dev, int N, int L, void *ws_dev, size_t ws_bytes,
+                  const stof_grads *grads, void *stream);
+
+/* torch.optim.AdamW step (main.py:179,248; amsgrad off, maximize off) on flat fp32 buffers of n elements:
+ *   p *= 1 - lr * wd;  m = b1 m + (1 - b1) g;  v = b2 v + (1 - b2) g^2;
+ *   p -= lr / (1 - b1^step) * m / (sqrt(v) / sqrt(1 - b2^step) + eps)            step counts from 1                    */
+int stof_adamw_step(float *params_dev, const float *grads_dev, float *exp_avg_dev, float *exp_avg_sq_dev, size_t n, int step,
+                    float lr, float beta1, float beta2, float eps, float weight_decay, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

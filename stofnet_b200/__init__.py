@@ -16,6 +16,7 @@ from .utils.attention_block import AttentionBlock               # noqa: F401
 from .utils.gaussian import gaussian_kernel                     # noqa: F401
 from .datasets.chirp_dataset import upscale_1d, iq2rf           # noqa: F401
 from .loss import mask_loss                                     # noqa: F401
+from .train import Trainer, cosine_lr, average_gradients          # noqa: F401
 from .checkpoint import load_checkpoint, load_config, build_model  # noqa: F401
 
 __version__ = "0.1"

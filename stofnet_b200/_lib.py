@@ -31,6 +31,16 @@ class Weights(C.Structure):
     ]
 
 
+class Grads(C.Structure):
+    _fields_ = [
+        ("conv1_w", C.c_void_p), ("conv1_b", C.c_void_p),
+        ("mid_w", C.c_void_p * MAX_MID), ("mid_b", C.c_void_p * MAX_MID),
+        ("last_w", C.c_void_p), ("last_b", C.c_void_p),
+        ("contract_w", C.c_void_p), ("contract_b", C.c_void_p),
+        ("expand_w", C.c_void_p), ("expand_b", C.c_void_p),
+    ]
+
+
 if not os.path.exists(LIB_PATH):
     raise ImportError(
         "stofnet_b200: %s not found - build it with `python -c 'import __graft_entry__ as g; g.build()'` "
@@ -67,6 +77,10 @@ _SIGS = {
     "stof_threshold_scratch_bytes": (_sz, [_i, _i]),
     "stof_find_threshold": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "stof_rf_upscale": (_i, [_vp, _vp, _i, _i, _d, _d, _d, _vp, _vp]),
+    "stof_train_workspace_bytes": (_i, [_vp, _i, _i, C.POINTER(_sz)]),
+    "stof_forward_train": (_i, [_vp, _vp, _i, _i, _vp, _vp, _sz, _vp]),
+    "stof_backward": (_i, [_vp, _vp, _vp, _i, _i, _vp, _sz, C.POINTER(Grads), _vp]),
+    "stof_adamw_step": (_i, [_vp, _vp, _vp, _vp, _sz, _i, _f, _f, _f, _f, _f, _vp]),
     "stof_attention_scratch_bytes": (_sz, [_i, _i, _i]),
     "stof_attention_block": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _f, C.c_uint64, _vp, _vp, _vp]),
 }

@@ -107,7 +107,7 @@ __device__ __forceinline__ void dc_compute(const float *xs, const float *ws, flo
     }
 }
 
-// EPI: 0 = LeakyReLU, 1 = + residual (no activation), 2 = tanh (ESPCN conv2 is handled elsewhere)
+// EPI: 0 = LeakyReLU, 1 = + residual (no activation), 2 = plain (bias only; the dgrad convs of train.cu)
 template <int K, int EPI>
 __global__ void __launch_bounds__(DC_THREADS, 1)
 conv_mid_simt_kernel(const float *__restrict__ in, const float *res, float *out,   // res may alias out (in-place skip add)
@@ -167,11 +167,12 @@ template <int K>
 __global__ void __launch_bounds__(DC_THREADS, 1)
 contract_pool_simt_kernel(const float *__restrict__ in, float *__restrict__ pooled /*[N][512][P]*/,
                           const float *__restrict__ w /*[8][64][K][64]*/, const float *__restrict__ b /*[512]*/,
-                          int N, int L, int P, int tiles_per_row) {
+                          int N, int L, int P, int tiles_per_row, int *__restrict__ argmax /*[N][512][P] or NULL*/) {
     extern __shared__ __align__(16) float dc_smem[];
     float *xs = dc_smem;
     float *ws = dc_smem + 64 * DC_PITCH;          // [64][K][64] of the current cout tile
     float *pm = ws + 64 * K * 64;                 // [64 co][32 lanes]
+    int *pi = reinterpret_cast<int *>(pm + 64 * 32);   // [64 co][32 lanes] position of the lane's maximum (training only)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int total = N * tiles_per_row;
     for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
@@ -189,18 +190,28 @@ contract_pool_simt_kernel(const float *__restrict__ in, float *__restrict__ pool
             for (int c = 0; c < 8; ++c) {
                 const float bc = __ldg(b + ct * 64 + 8 * warp + c);
                 float m = leaky(acc[c][0] + bc);
+                int mj = 0;
 #pragma unroll
-                for (int j = 1; j < 8; ++j) m = fmaxf(m, leaky(acc[c][j] + bc));
+                for (int j = 1; j < 8; ++j) {
+                    const float v = leaky(acc[c][j] + bc);
+                    if (v > m) { m = v; mj = j; }             // first maximum wins, like torch's max_pool1d
+                }
                 pm[(8 * warp + c) * 32 + lane] = m;
+                if (argmax != nullptr) pi[(8 * warp + c) * 32 + lane] = l0 + 8 * lane + mj;
             }
             __syncthreads();
             if (threadIdx.x < 192) {
                 const int co = threadIdx.x & 63, wdw = threadIdx.x >> 6;
                 if (p0 + wdw < P) {
                     float m = pm[co * 32 + 10 * wdw];
+                    int mi = 0;
 #pragma unroll
-                    for (int i = 1; i < 10; ++i) m = fmaxf(m, pm[co * 32 + 10 * wdw + i]);
+                    for (int i = 1; i < 10; ++i) {
+                        const float v = pm[co * 32 + 10 * wdw + i];
+                        if (v > m) { m = v; mi = i; }
+                    }
                     pooled[((size_t)n * 512 + ct * 64 + co) * P + p0 + wdw] = m;
+                    if (argmax != nullptr) argmax[((size_t)n * 512 + ct * 64 + co) * P + p0 + wdw] = pi[co * 32 + 10 * wdw + mi];
                 }
             }
         }
@@ -468,21 +479,23 @@ int launch_conv_mid_simt(const float *in, const float *res, float *out, const fl
     if (!attr) {
         STOF_CUDA(cudaFuncSetAttribute(conv_mid_simt_kernel<7, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         STOF_CUDA(cudaFuncSetAttribute(conv_mid_simt_kernel<7, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        STOF_CUDA(cudaFuncSetAttribute(conv_mid_simt_kernel<7, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr = true;
     }
     const int tpr = (L + 255) / 256;
     const long long total = (long long)N * tpr;
     const int grid = (int)(total < kSMs ? total : kSMs);
     if (epi == 0) conv_mid_simt_kernel<7, 0><<<grid, DC_THREADS, smem, st>>>(in, res, out, w, b, N, L, tpr);
-    else conv_mid_simt_kernel<7, 1><<<grid, DC_THREADS, smem, st>>>(in, res, out, w, b, N, L, tpr);
+    else if (epi == 1) conv_mid_simt_kernel<7, 1><<<grid, DC_THREADS, smem, st>>>(in, res, out, w, b, N, L, tpr);
+    else conv_mid_simt_kernel<7, 2><<<grid, DC_THREADS, smem, st>>>(in, res, out, w, b, N, L, tpr);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }
 
 int launch_contract_pool_simt(const float *in, float *pooled, const float *w, const float *b, int N, int L, int P,
-                              cudaStream_t st) {
+                              cudaStream_t st, int *argmax) {
     static bool attr = false;
-    const size_t smem = mid_smem(5) + sizeof(float) * 64 * 32;
+    const size_t smem = mid_smem(5) + sizeof(float) * 64 * 32 * 2;
     if (!attr) {
         STOF_CUDA(cudaFuncSetAttribute(contract_pool_simt_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr = true;
@@ -490,7 +503,7 @@ int launch_contract_pool_simt(const float *in, float *pooled, const float *w, co
     const int tpr = (P + 2) / 3;
     const long long total = (long long)N * tpr;
     const int grid = (int)(total < kSMs ? total : kSMs);
-    contract_pool_simt_kernel<5><<<grid, DC_THREADS, smem, st>>>(in, pooled, w, b, N, L, P, tpr);
+    contract_pool_simt_kernel<5><<<grid, DC_THREADS, smem, st>>>(in, pooled, w, b, N, L, P, tpr, argmax);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }

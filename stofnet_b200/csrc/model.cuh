@@ -1,0 +1,56 @@
+// Internal definition of the opaque stof_model handle (shared by stof_api.cu and train.cu).
+#pragma once
+#include <vector>
+
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace stof {
+
+// Device-resident weights in the layouts the kernels read (all fp32):
+//   first : [K][64]            w[t][co]        = W[co][0][t]
+//   mid   : [64][K][64]        w[ci][t][co]    = W[co][ci][t]          (conv2..conv12, contract tiles)
+//   expand: [512][5][64]       w[ci][t][co]
+//   last  : [CIN][3][4]        w[ci][t][u]     = W[u][ci][t]
+struct DevConv {
+    float *w = nullptr;
+    float *b = nullptr;
+};
+
+}  // namespace stof
+
+struct stof_model {
+    int device = 0;
+    int kind = STOF_KIND_STOFNET;
+    int F = 64, r = 4, n_mid = 0;
+    int k_first = 9, k_mid = 7, k_last = 3;
+    int sgb_scale = 1, sgb_feat = 0, sgb_k = 0;
+    stof::DevConv first, last, contract, expand;
+    stof::DevConv mid[STOF_MAX_MID_CONVS];
+    // tensor-core path (conv_tc.cu): packed fp16 hi/lo taps of conv2..conv{nb-1} + conv_last, one allocation
+    int path = STOF_PATH_TC;
+    int seg_len = 4;                                  // layers fused per chain launch
+    void *tc_w = nullptr;
+    void *tc_contract_w = nullptr;                    // contract conv: [4 slices][5 taps][8 c8][W_hi 128 | W_lo 128][8] fp16
+    stof::TcLayer tc_layer[STOF_MAX_MID_CONVS + 1];   // spec list: mid convs then conv_last
+    int n_tc = 0;
+    // training step (train.cu): dgrad weights of the mid convs [co][K-1-t][ci] (a conv with channels swapped and taps
+    // flipped), a zero bias vector, and PyTorch-layout copies of conv_last / contract / expand for the backward kernels
+    float *bw_mid[STOF_MAX_MID_CONVS] = {};
+    float *zero_bias = nullptr;                       // 512 zeros
+    float *raw_last_w = nullptr;                      // (4, 64, 3)
+    float *raw_contract_w = nullptr;                  // (512, 64, 5)
+    float *raw_expand_w = nullptr;                    // (64, 512, 5)
+    // scratch of stof_infer_host (grow-only)
+    static constexpr int kPipe = 2;
+    cudaStream_t streams[kPipe] = {nullptr, nullptr};
+    void *scratch[kPipe] = {nullptr, nullptr};
+    size_t scratch_bytes[kPipe] = {0, 0};
+    int64_t *h_stats = nullptr;   // pinned, kPipe * 2
+    // optional per-kernel-class CUDA-event timing (stof_profile_*): pairs recorded on the launch stream
+    bool profiling = false;
+    std::vector<cudaEvent_t> ev_pool;                 // start/stop pairs
+    std::vector<int> ev_class;                        // class of pair i
+    size_t ev_used = 0;
+};
+

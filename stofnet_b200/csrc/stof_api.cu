@@ -27,45 +27,9 @@ int cuda_fail(cudaError_t e, const char *what, const char *file, int line) {
     return STOF_E_CUDA;
 }
 
-// Device-resident weights in the layouts the kernels read (all fp32):
-//   first : [K][64]            w[t][co]        = W[co][0][t]
-//   mid   : [64][K][64]        w[ci][t][co]    = W[co][ci][t]          (conv2..conv12, contract tiles)
-//   expand: [512][5][64]       w[ci][t][co]
-//   last  : [CIN][3][4]        w[ci][t][u]     = W[u][ci][t]
-struct DevConv {
-    float *w = nullptr;
-    float *b = nullptr;
-};
-
 }  // namespace stof
 
-struct stof_model {
-    int device = 0;
-    int kind = STOF_KIND_STOFNET;
-    int F = 64, r = 4, n_mid = 0;
-    int k_first = 9, k_mid = 7, k_last = 3;
-    int sgb_scale = 1, sgb_feat = 0, sgb_k = 0;
-    stof::DevConv first, last, contract, expand;
-    stof::DevConv mid[STOF_MAX_MID_CONVS];
-    // tensor-core path (conv_tc.cu): packed fp16 hi/lo taps of conv2..conv{nb-1} + conv_last, one allocation
-    int path = STOF_PATH_TC;
-    int seg_len = 4;                                  // layers fused per chain launch
-    void *tc_w = nullptr;
-    void *tc_contract_w = nullptr;                    // contract conv: [4 slices][5 taps][8 c8][W_hi 128 | W_lo 128][8] fp16
-    stof::TcLayer tc_layer[STOF_MAX_MID_CONVS + 1];   // spec list: mid convs then conv_last
-    int n_tc = 0;
-    // scratch of stof_infer_host (grow-only)
-    static constexpr int kPipe = 2;
-    cudaStream_t streams[kPipe] = {nullptr, nullptr};
-    void *scratch[kPipe] = {nullptr, nullptr};
-    size_t scratch_bytes[kPipe] = {0, 0};
-    int64_t *h_stats = nullptr;   // pinned, kPipe * 2
-    // optional per-kernel-class CUDA-event timing (stof_profile_*): pairs recorded on the launch stream
-    bool profiling = false;
-    std::vector<cudaEvent_t> ev_pool;                 // start/stop pairs
-    std::vector<int> ev_class;                        // class of pair i
-    size_t ev_used = 0;
-};
+#include "model.cuh"
 
 namespace stof {
 
@@ -141,6 +105,36 @@ static int upload_tc(stof_model *m, const stof_weights *w) {
     return STOF_OK;
 }
 
+static int upload_raw(float **dst, const float *src, size_t n) {
+    if (!*dst) STOF_CUDA(cudaMalloc(dst, n * sizeof(float)));
+    STOF_CUDA(cudaMemcpy(*dst, src, n * sizeof(float), cudaMemcpyHostToDevice));
+    return STOF_OK;
+}
+
+// weights in the layouts the backward kernels read (train.cu)
+static int upload_train(stof_model *m, const stof_weights *w) {
+    int rc;
+    if (!m->zero_bias) {
+        STOF_CUDA(cudaMalloc(&m->zero_bias, 512 * sizeof(float)));
+        STOF_CUDA(cudaMemset(m->zero_bias, 0, 512 * sizeof(float)));
+    }
+    std::vector<float> t((size_t)64 * 7 * 64);
+    for (int j = 0; j < w->n_mid; ++j) {
+        // dX[ci][l] = sum_co sum_t W[co][ci][t] dY[co][l - t + 3] = sum_co sum_t' W[co][ci][6 - t'] dY[co][l + t' - 3]:
+        // the forward kernel's [in][tap][out] layout with in = co, out = ci, tap flipped
+        for (int co = 0; co < 64; ++co)
+            for (int ci = 0; ci < 64; ++ci)
+                for (int tp = 0; tp < 7; ++tp) t[((size_t)co * 7 + tp) * 64 + ci] = w->mid_w[j][((size_t)co * 64 + ci) * 7 + (6 - tp)];
+        if ((rc = upload_raw(&m->bw_mid[j], t.data(), t.size()))) return rc;
+    }
+    if ((rc = upload_raw(&m->raw_last_w, w->last_w, (size_t)4 * 64 * 3))) return rc;
+    if (w->contract_w) {
+        if ((rc = upload_raw(&m->raw_contract_w, w->contract_w, (size_t)512 * 64 * 5))) return rc;
+        if ((rc = upload_raw(&m->raw_expand_w, w->expand_w, (size_t)64 * 512 * 5))) return rc;
+    }
+    return STOF_OK;
+}
+
 static int validate(const stof_weights *w) {
     STOF_REQUIRE(w != nullptr, STOF_E_INVALID, "weights: NULL");
     STOF_REQUIRE(w->conv1_w && w->conv1_b && w->last_w && w->last_b, STOF_E_INVALID, "weights: missing conv1/conv_last");
@@ -187,6 +181,7 @@ static int set_weights(stof_model *m, const stof_weights *w) {
         if ((rc = upload(m->mid[i], repack_cikco(w->mid_w[i], 64, 64, 7), w->mid_b[i], 64))) return rc;
     if ((rc = upload(m->last, repack_cikco(w->last_w, 4, 64, 3), w->last_b, 4))) return rc;
     if ((rc = upload_tc(m, w))) return rc;
+    if ((rc = upload_train(m, w))) return rc;
     if (w->contract_w) {
         m->sgb_scale = w->sgb_scale; m->sgb_feat = w->sgb_feat; m->sgb_k = w->sgb_k;
         // 8 cout tiles of 64, each [ci][t][co]
@@ -416,6 +411,11 @@ extern "C" void stof_model_destroy(stof_model *m) {
         if (m->scratch[i]) cudaFree(m->scratch[i]);
         if (m->streams[i]) cudaStreamDestroy(m->streams[i]);
     }
+    for (int i = 0; i < STOF_MAX_MID_CONVS; ++i) if (m->bw_mid[i]) cudaFree(m->bw_mid[i]);
+    if (m->zero_bias) cudaFree(m->zero_bias);
+    if (m->raw_last_w) cudaFree(m->raw_last_w);
+    if (m->raw_contract_w) cudaFree(m->raw_contract_w);
+    if (m->raw_expand_w) cudaFree(m->raw_expand_w);
     if (m->tc_w) cudaFree(m->tc_w);
     if (m->tc_contract_w) cudaFree(m->tc_contract_w);
     if (m->h_stats) cudaFreeHost(m->h_stats);

@@ -1,0 +1,646 @@
+// Training step of the StofNet stack (reference main.py:217-248; models/stofnet.py:42-117): a forward pass that keeps every
+// layer's activations, the backward pass (what torch autograd derives from the reference's forward), and a fused AdamW.
+//
+// All fp32 on CUDA cores, activations in the C4L4 layout of conv_simt.cu.  Data gradients of the 64->64 k7 convs reuse the
+// forward conv kernel with channel-swapped, tap-flipped weights (a transposed conv with 'same' padding is a conv); weight
+// gradients are register-tiled outer-product reductions over positions with per-CTA partial sums that a second kernel adds
+// in a fixed order, so gradients are bit-reproducible run to run (no float atomics).
+//
+//   forward  (saved)   x0r = relu(conv1 x);  pooled, argmax = maxpool80(lrelu(contract x0r));  E = lrelu(expand pooled);
+//                      x0 = x0r + up80(E);  a2 = lrelu(c2 x0);  a3 = x0 + c3 a2;  ...  a12 = x0 + c12 a11;  y = c_last a12
+//   backward           g_y = g_mask (the shuffle is a relabelling);  conv_last, conv12..conv2 (pairs: skip + lrelu'),
+//                      semi-global block (window sum, expand, arg-max scatter through the pool, contract), conv1
+#include <math.h>
+
+#include "model.cuh"
+
+namespace stof {
+
+// ------------------------------------------------------------------------------------------------ workspace plan
+struct TrainPlan {
+    int P;
+    bool sgb;
+    size_t act;                    // floats of one (N, 64, L) tensor
+    size_t off_x0r, off_x0, off_a[STOF_MAX_MID_CONVS], off_g[3];     // float offsets
+    size_t off_pooled, off_argmax, off_e, off_ge, off_gpool;
+    size_t off_partial;            // float offset of the partial-sum scratch
+    size_t partial_floats;
+    size_t total_bytes;
+};
+
+constexpr int WG_MAX_PARTS = kSMs;                 // persistent wgrad CTAs
+constexpr size_t WG_MID_LEN = 64 * 64 * 7 + 64;    // dW + db of one mid conv
+
+static size_t a64(size_t floats) { return (floats + 63) & ~(size_t)63; }
+
+static int make_train_plan(const stof_model *m, int N, int L, TrainPlan *p) {
+    STOF_REQUIRE(m != nullptr && m->kind == STOF_KIND_STOFNET, STOF_E_INVALID, "training: needs a StofNet model");
+    STOF_REQUIRE(N > 0 && L > 0, STOF_E_INVALID, "training: N=%d L=%d must be positive", N, L);
+    p->sgb = m->sgb_scale != 1;
+    if (p->sgb) {
+        STOF_REQUIRE(L >= m->sgb_scale, STOF_E_LENGTH, "training: L=%d shorter than the semi-global pooling window %d", L, m->sgb_scale);
+        STOF_REQUIRE(((L % m->sgb_scale) & 1) == 0, STOF_E_LENGTH_ODD, "training: (L mod %d) = %d is odd", m->sgb_scale, L % m->sgb_scale);
+    }
+    p->P = p->sgb ? L / m->sgb_scale : 0;
+    p->act = a64((size_t)N * 64 * L);
+    size_t o = 0;
+    p->off_x0r = o; o += p->act;
+    if (p->sgb) { p->off_x0 = o; o += p->act; } else p->off_x0 = p->off_x0r;
+    for (int j = 0; j < m->n_mid; ++j) { p->off_a[j] = o; o += p->act; }
+    for (int i = 0; i < 3; ++i) { p->off_g[i] = o; o += p->act; }
+    const size_t np = a64((size_t)N * 512 * p->P), ne = a64((size_t)N * 64 * p->P);
+    p->off_pooled = o; o += p->sgb ? np : 0;
+    p->off_argmax = o; o += p->sgb ? np : 0;
+    p->off_gpool = o; o += p->sgb ? np : 0;
+    p->off_e = o; o += p->sgb ? ne : 0;
+    p->off_ge = o; o += p->sgb ? ne : 0;
+    // partial sums: the largest user is the contract wgrad (one partial per row chunk is avoided: it reduces in-kernel),
+    // then mid wgrad (WG_MAX_PARTS x WG_MID_LEN)
+    p->partial_floats = a64((size_t)WG_MAX_PARTS * WG_MID_LEN);
+    p->off_partial = o; o += p->partial_floats;
+    p->total_bytes = o * sizeof(float);
+    return STOF_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ elementwise helpers
+// g[i] *= lrelu'(a[i])   (a = LeakyReLU output: same sign as its input; derivative at 0 is the negative slope, as in ATen)
+__global__ void __launch_bounds__(256)
+lrelu_bwd_kernel(float4 *__restrict__ g, const float4 *__restrict__ a, size_t n4) {
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (size_t)gridDim.x * 256) {
+        float4 gv = g[i];
+        const float4 av = __ldg(a + i);
+        gv.x *= av.x > 0.f ? 1.f : kLeakySlope; gv.y *= av.y > 0.f ? 1.f : kLeakySlope;
+        gv.z *= av.z > 0.f ? 1.f : kLeakySlope; gv.w *= av.w > 0.f ? 1.f : kLeakySlope;
+        g[i] = gv;
+    }
+}
+// g[i] = (a[i] > 0) ? g[i] : 0     (ReLU backward)
+__global__ void __launch_bounds__(256)
+relu_bwd_kernel(float4 *__restrict__ g, const float4 *__restrict__ a, size_t n4) {
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (size_t)gridDim.x * 256) {
+        float4 gv = g[i];
+        const float4 av = __ldg(a + i);
+        gv.x = av.x > 0.f ? gv.x : 0.f; gv.y = av.y > 0.f ? gv.y : 0.f;
+        gv.z = av.z > 0.f ? gv.z : 0.f; gv.w = av.w > 0.f ? gv.w : 0.f;
+        g[i] = gv;
+    }
+}
+// d[i] += s[i]
+__global__ void __launch_bounds__(256)
+add_kernel(float4 *__restrict__ d, const float4 *__restrict__ s, size_t n4) {
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (size_t)gridDim.x * 256) {
+        float4 dv = d[i];
+        const float4 sv = __ldg(s + i);
+        dv.x += sv.x; dv.y += sv.y; dv.z += sv.z; dv.w += sv.w;
+        d[i] = dv;
+    }
+}
+static int ew_grid(size_t n4) { size_t g = (n4 + 255) / 256; return (int)(g < (size_t)kSMs * 8 ? g : (size_t)kSMs * 8); }
+
+// out[j] = sum_p partial[p][j]   (fixed order)
+__global__ void __launch_bounds__(256)
+reduce_parts_kernel(const float *__restrict__ partial, int parts, size_t len, float *__restrict__ out_w, size_t len_w,
+                    float *__restrict__ out_b) {
+    const size_t j = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (j >= len) return;
+    float s = 0.0f;
+    for (int p = 0; p < parts; ++p) s += partial[(size_t)p * len + j];
+    if (j < len_w) out_w[j] = s; else out_b[j - len_w] = s;
+}
+
+// ------------------------------------------------------------------------------------------------ conv_last backward
+// y[n][u][l] = b[u] + sum_ci sum_t W[u][ci][t] a[n][ci][l + t - 1];  mask[n][4l + u] = y[n][u][l]  => g_y[n][l][u] = g_mask[n][4l+u]
+// dgrad: g_a[n][ci][l] = sum_u sum_t W[u][ci][t] g_y[n][u][l - t + 1]     (C4L4 output)
+__global__ void __launch_bounds__(256)
+last_dgrad_kernel(const float4 *__restrict__ gy /*[N][L] (4 u)*/, const float *__restrict__ w /*(4,64,3)*/, int N, int L,
+                  float4 *__restrict__ ga /*C4L4*/) {
+    __shared__ float ws[4 * 64 * 3];
+    for (int i = threadIdx.x; i < 768; i += 256) ws[i] = __ldg(w + i);
+    __syncthreads();
+    const int n = blockIdx.y;
+    const int l = blockIdx.x * 256 + threadIdx.x;
+    if (l >= L) return;
+    float4 g[3];                                   // g_y at l + 1, l, l - 1  (t = 0, 1, 2)
+#pragma unroll
+    for (int t = 0; t < 3; ++t) {
+        const int q = l - t + 1;
+        g[t] = (q >= 0 && q < L) ? __ldg(gy + (size_t)n * L + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    for (int c4 = 0; c4 < 16; ++c4) {
+        float o[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int ci = 4 * c4 + i;
+            float a = 0.0f;
+#pragma unroll
+            for (int t = 0; t < 3; ++t) {
+                a = fmaf(ws[(0 * 64 + ci) * 3 + t], g[t].x, a);
+                a = fmaf(ws[(1 * 64 + ci) * 3 + t], g[t].y, a);
+                a = fmaf(ws[(2 * 64 + ci) * 3 + t], g[t].z, a);
+                a = fmaf(ws[(3 * 64 + ci) * 3 + t], g[t].w, a);
+            }
+            o[i] = a;
+        }
+        ga[((size_t)n * 16 + c4) * L + l] = make_float4(o[0], o[1], o[2], o[3]);
+    }
+}
+
+// wgrad: dW[u][ci][t] = sum_{n,l} g_y[n][u][l] a[n][ci][l + t - 1];  db[u] = sum g_y.   One CTA per (row, 1024-position chunk):
+// thread = (ci, t) (192 threads) keeps 4 accumulators (u); partial [768 + 4] per CTA.
+constexpr int LW_CHUNK = 1024;
+constexpr int LW_MAX_CTAS = 4 * kSMs;
+__global__ void __launch_bounds__(192)
+last_wgrad_kernel(const float4 *__restrict__ gy, const float *__restrict__ a /*C4L4*/, int N, int L, int chunks,
+                  float *__restrict__ partial /*[gridDim.x][772]*/) {
+    const int ci = threadIdx.x / 3, t = threadIdx.x - 3 * ci;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f}, bs[4] = {0.f, 0.f, 0.f, 0.f};
+    const int total = N * chunks;
+    for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
+        const int n = tile / chunks, l0 = (tile - n * chunks) * LW_CHUNK;
+        const float *ar = a + ((size_t)n * 16 + (ci >> 2)) * L * 4 + (ci & 3);
+        const int l1 = min(L, l0 + LW_CHUNK);
+        for (int l = l0; l < l1; ++l) {
+            const float4 g = __ldg(gy + (size_t)n * L + l);
+            const int q = l + t - 1;
+            const float av = (q >= 0 && q < L) ? __ldg(ar + (size_t)q * 4) : 0.0f;
+            acc[0] = fmaf(g.x, av, acc[0]); acc[1] = fmaf(g.y, av, acc[1]);
+            acc[2] = fmaf(g.z, av, acc[2]); acc[3] = fmaf(g.w, av, acc[3]);
+            if (threadIdx.x == 0) { bs[0] += g.x; bs[1] += g.y; bs[2] += g.z; bs[3] += g.w; }
+        }
+    }
+    float *o = partial + (size_t)blockIdx.x * 772;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) o[(u * 64 + ci) * 3 + t] = acc[u];
+    if (threadIdx.x == 0) { o[768] = bs[0]; o[769] = bs[1]; o[770] = bs[2]; o[771] = bs[3]; }
+}
+
+// ------------------------------------------------------------------------------------------------ mid conv wgrad
+// dW[co][ci][t] = sum_{n,l} G[n][co][l] A[n][ci][l + t - 3],  db[co] = sum G[n][co][l]        (64 x 64 x 7 + 64 outputs)
+// Persistent CTAs; a tile = 128 positions of one row staged in shared memory (G: 16 x 128 float4, A: 16 x 134 float4 with the
+// conv's zero padding).  Thread (cog, cig) owns 4 co x 4 ci x 7 taps = 112 accumulators; per position it reads one float4 of G
+// and one new float4 of A (the 7-tap window slides through registers).  Each CTA writes one partial [64][64][7] (+ bias).
+constexpr int WG_TL = 128;
+constexpr int WG_AP = 135;          // float4 pitch of an A slab (>= WG_TL + 6, odd multiple keeps 8 consecutive slabs conflict-free)
+constexpr int WG_GP = 129;
+
+__global__ void __launch_bounds__(256, 1)
+mid_wgrad_kernel(const float4 *__restrict__ G /*C4L4*/, const float4 *__restrict__ A /*C4L4*/, int N, int L, int tiles_per_row,
+                 float *__restrict__ partial /*[gridDim.x][WG_MID_LEN]*/) {
+    extern __shared__ __align__(16) float4 wg_smem[];
+    float4 *Gs = wg_smem;                     // [16][WG_GP]
+    float4 *As = wg_smem + 16 * WG_GP;        // [16][WG_AP]
+    const int cog = threadIdx.x >> 4, cig = threadIdx.x & 15;
+    float acc[7][4][4];
+#pragma unroll
+    for (int t = 0; t < 7; ++t)
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[t][i][j] = 0.0f;
+    float bsum[4] = {0.f, 0.f, 0.f, 0.f};
+    const int total = N * tiles_per_row;
+    for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
+        const int n = tile / tiles_per_row, l0 = (tile - n * tiles_per_row) * WG_TL;
+        __syncthreads();
+        for (int idx = threadIdx.x; idx < 16 * WG_TL; idx += 256) {
+            const int c4 = idx / WG_TL, j = idx - c4 * WG_TL;
+            const int l = l0 + j;
+            Gs[c4 * WG_GP + j] = (l < L) ? __ldg(G + ((size_t)n * 16 + c4) * L + l) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        for (int idx = threadIdx.x; idx < 16 * (WG_TL + 6); idx += 256) {
+            const int c4 = idx / (WG_TL + 6), j = idx - c4 * (WG_TL + 6);
+            const int l = l0 + j - 3;
+            As[c4 * WG_AP + j] = (l >= 0 && l < L) ? __ldg(A + ((size_t)n * 16 + c4) * L + l) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        __syncthreads();
+        const float4 *gp = Gs + cog * WG_GP;
+        const float4 *ap = As + cig * WG_AP;
+        float4 win[7];                       // A at positions j .. j + 6  (tap t reads win[t])
+#pragma unroll
+        for (int t = 0; t < 6; ++t) win[t + 1] = ap[t];
+#pragma unroll 2
+        for (int j = 0; j < WG_TL; ++j) {
+#pragma unroll
+            for (int t = 0; t < 6; ++t) win[t] = win[t + 1];
+            win[6] = ap[j + 6];
+            const float4 g = gp[j];
+            const float gv[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+            for (int t = 0; t < 7; ++t) {
+                const float av[4] = {win[t].x, win[t].y, win[t].z, win[t].w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int jj = 0; jj < 4; ++jj) acc[t][i][jj] = fmaf(gv[i], av[jj], acc[t][i][jj]);
+            }
+            if (cig == 0) { bsum[0] += g.x; bsum[1] += g.y; bsum[2] += g.z; bsum[3] += g.w; }
+        }
+    }
+    float *o = partial + (size_t)blockIdx.x * WG_MID_LEN;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj)
+#pragma unroll
+            for (int t = 0; t < 7; ++t) o[((size_t)(4 * cog + i) * 64 + 4 * cig + jj) * 7 + t] = acc[t][i][jj];
+    if (cig == 0) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) o[64 * 64 * 7 + 4 * cog + i] = bsum[i];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ semi-global block backward
+// x0 = x0r + pad(up80(E)):  g_E[n][c][p] = sum_{l = off + 80 p}^{+79} g_x0[n][c][l]      (one warp per (n, c4, p))
+__global__ void __launch_bounds__(256)
+window_sum_kernel(const float4 *__restrict__ gx0 /*C4L4*/, int N, int L, int P, int scale, int off, float *__restrict__ ge /*[N][64][P]*/) {
+    const long long wid = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (wid >= (long long)N * 16 * P) return;
+    const int p = (int)(wid % P);
+    const int c4 = (int)((wid / P) % 16);
+    const int n = (int)(wid / ((long long)P * 16));
+    const float4 *src = gx0 + ((size_t)n * 16 + c4) * L + off + (size_t)p * scale;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int j = lane; j < scale; j += 32) {
+        const float4 v = __ldg(src + j);
+        s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+        s.x += __shfl_xor_sync(0xffffffffu, s.x, o); s.y += __shfl_xor_sync(0xffffffffu, s.y, o);
+        s.z += __shfl_xor_sync(0xffffffffu, s.z, o); s.w += __shfl_xor_sync(0xffffffffu, s.w, o);
+    }
+    if (lane == 0) {
+        float *d = ge + ((size_t)n * 64 + 4 * c4) * P + p;
+        d[0] = s.x; d[P] = s.y; d[2 * (size_t)P] = s.z; d[3 * (size_t)P] = s.w;
+    }
+}
+
+// plain elementwise lrelu' on NCL tensors (E, pooled): g *= a > 0 ? 1 : slope
+__global__ void __launch_bounds__(256)
+lrelu_bwd1_kernel(float *__restrict__ g, const float *__restrict__ a, size_t n) {
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (size_t)gridDim.x * 256)
+        g[i] *= (__ldg(a + i) > 0.f) ? 1.f : kLeakySlope;
+}
+
+// expand conv (512 -> 64, k5, pad 2 on the pooled axis):  e_pre[n][co][p] = b + sum_ci sum_t We[co][ci][t] pooled[n][ci][p+t-2]
+// wgrad: dWe[co][ci][t] = sum_{n,p} g[n][co][p] pooled[n][ci][p + t - 2];  one CTA per ci, thread = (co, t), fixed (n, p) order
+__global__ void __launch_bounds__(320)
+expand_wgrad_kernel(const float *__restrict__ g /*[N][64][P]*/, const float *__restrict__ pooled /*[N][512][P]*/, int N, int P,
+                    float *__restrict__ dW /*(64,512,5)*/) {
+    const int ci = blockIdx.x;
+    const int co = threadIdx.x / 5, t = threadIdx.x - 5 * co;
+    float acc = 0.0f;
+    for (int n = 0; n < N; ++n) {
+        const float *gr = g + ((size_t)n * 64 + co) * P;
+        const float *pr = pooled + ((size_t)n * 512 + ci) * P;
+        for (int p = 0; p < P; ++p) {
+            const int q = p + t - 2;
+            if (q >= 0 && q < P) acc = fmaf(__ldg(gr + p), __ldg(pr + q), acc);
+        }
+    }
+    dW[((size_t)co * 512 + ci) * 5 + t] = acc;
+}
+// db[c] = sum_{n,p} g[n][c][p]     (NCL tensor with C channels; one CTA per channel, fixed-order tree)
+__global__ void __launch_bounds__(256)
+bias_grad_ncl_kernel(const float *__restrict__ g, int N, int Cn, int P, float *__restrict__ db) {
+    __shared__ float red[256];
+    const int c = blockIdx.x;
+    float s = 0.0f;
+    for (long long i = threadIdx.x; i < (long long)N * P; i += 256) {
+        const int n = (int)(i / P), p = (int)(i - (long long)n * P);
+        s += __ldg(g + ((size_t)n * Cn + c) * P + p);
+    }
+    red[threadIdx.x] = s;
+    __syncthreads();
+    for (int k = 128; k; k >>= 1) { if ((int)threadIdx.x < k) red[threadIdx.x] += red[threadIdx.x + k]; __syncthreads(); }
+    if (threadIdx.x == 0) db[c] = red[0];
+}
+// dgrad: g_pooled[n][ci][p] = sum_co sum_t We[co][ci][t] g[n][co][p - t + 2];  then through LeakyReLU of the pooled value
+__global__ void __launch_bounds__(256)
+expand_dgrad_kernel(const float *__restrict__ g /*[N][64][P]*/, const float *__restrict__ We /*(64,512,5)*/,
+                    const float *__restrict__ pooled, int N, int P, float *__restrict__ gpool /*[N][512][P]*/) {
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (i >= (long long)N * 512 * P) return;
+    const int p = (int)(i % P);
+    const int ci = (int)((i / P) % 512);
+    const int n = (int)(i / ((long long)P * 512));
+    float acc = 0.0f;
+    for (int co = 0; co < 64; ++co) {
+        const float *gr = g + ((size_t)n * 64 + co) * P;
+        const float *wr = We + ((size_t)co * 512 + ci) * 5;
+#pragma unroll
+        for (int t = 0; t < 5; ++t) {
+            const int q = p - t + 2;
+            if (q >= 0 && q < P) acc = fmaf(__ldg(wr + t), __ldg(gr + q), acc);
+        }
+    }
+    // pooled = lrelu(max + bias): the max-pool routes the gradient to the arg-max position, scaled by lrelu'
+    gpool[i] = acc * ((__ldg(pooled + i) > 0.f) ? 1.f : kLeakySlope);
+}
+
+// contract conv (64 -> 512, k5, pad 2) behind the max-pool: the gradient of c[n][co][.] is gpool[n][co][p] at l* = argmax only.
+// wgrad: dWc[co][ci][t] = sum_{n,p} gpool[n][co][p] x0r[n][ci][l* + t - 2];  dbc[co] = sum gpool.  One CTA per co.
+__global__ void __launch_bounds__(320)
+contract_wgrad_kernel(const float *__restrict__ gpool, const int *__restrict__ argmax, const float *__restrict__ x0r /*C4L4*/,
+                      int N, int L, int P, float *__restrict__ dW /*(512,64,5)*/, float *__restrict__ db /*(512)*/) {
+    const int co = blockIdx.x;
+    const int ci = threadIdx.x / 5, t = threadIdx.x - 5 * ci;
+    float acc = 0.0f, bs = 0.0f;
+    for (int n = 0; n < N; ++n) {
+        const float *xr = x0r + ((size_t)n * 16 + (ci >> 2)) * L * 4 + (ci & 3);
+        const size_t base = ((size_t)n * 512 + co) * P;
+        for (int p = 0; p < P; ++p) {
+            const float gv = __ldg(gpool + base + p);
+            const int q = __ldg(argmax + base + p) + t - 2;
+            if (q >= 0 && q < L) acc = fmaf(gv, __ldg(xr + (size_t)q * 4), acc);
+            bs += gv;
+        }
+    }
+    dW[((size_t)co * 64 + ci) * 5 + t] = acc;
+    if (threadIdx.x == 0) db[co] = bs;
+}
+// dgrad (gather form, deterministic): g_x0r[n][ci][l] += sum over (co, p) with |l - l*| <= 2 of Wc[co][ci][l - l* + 2] gpool.
+// One CTA per (row, 80-position tile); it scans the (co, p) entries of the pooling windows that can reach the tile
+// (p in [tile-1, tile+1]); thread = (ci, quarter of the tile) owns its outputs exclusively (shared accumulators, no races).
+constexpr int CD_T = 80;
+__global__ void __launch_bounds__(256)
+contract_dgrad_kernel(const float *__restrict__ gpool, const int *__restrict__ argmax, const float *__restrict__ Wc /*(512,64,5)*/,
+                      int N, int L, int P, int tiles, float *__restrict__ gx /*C4L4, accumulated into*/) {
+    __shared__ float accs[64][CD_T + 1];
+    __shared__ int e_l[3 * 512];
+    __shared__ float e_g[3 * 512];
+    const int n = blockIdx.x / tiles, tile = blockIdx.x - n * tiles;
+    const int l0 = tile * CD_T;
+    for (int i = threadIdx.x; i < 64 * (CD_T + 1); i += 256) (&accs[0][0])[i] = 0.0f;
+    for (int i = threadIdx.x; i < 3 * 512; i += 256) {
+        const int w = tile - 1 + i / 512, co = i & 511;
+        int l = -1000000; float g = 0.0f;
+        if (w >= 0 && w < P) { l = __ldg(argmax + ((size_t)n * 512 + co) * P + w); g = __ldg(gpool + ((size_t)n * 512 + co) * P + w); }
+        e_l[i] = l; e_g[i] = g;
+    }
+    __syncthreads();
+    const int ci = threadIdx.x >> 2, qt = threadIdx.x & 3;
+    const int lo = l0 + 20 * qt, hi = lo + 20;                 // this thread's positions [lo, hi)
+    for (int i = 0; i < 3 * 512; ++i) {
+        const int ls = e_l[i];
+        if (ls + 2 < lo || ls - 2 >= hi) continue;
+        const float g = e_g[i];
+        const float *wr = Wc + ((size_t)(i & 511) * 64 + ci) * 5;
+#pragma unroll
+        for (int t = 0; t < 5; ++t) {
+            const int l = ls + t - 2;                          // c[l*] reads x0r[l* + t - 2]
+            if (l >= lo && l < hi) accs[ci][l - l0] += __ldg(wr + t) * g;
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 16 * CD_T; i += 256) {
+        const int c4 = i / CD_T, j = i - c4 * CD_T;
+        const int l = l0 + j;
+        if (l >= L) continue;
+        float4 *d = reinterpret_cast<float4 *>(gx) + ((size_t)n * 16 + c4) * L + l;
+        float4 v = *d;
+        v.x += accs[4 * c4][j]; v.y += accs[4 * c4 + 1][j]; v.z += accs[4 * c4 + 2][j]; v.w += accs[4 * c4 + 3][j];
+        *d = v;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ conv1 backward
+// x0r = relu(conv1 x), g already masked by relu':  dW1[c][t] = sum_{n,l} g[n][c][l] x[n][l + t - 4];  db1[c] = sum g.
+// Persistent CTAs over (row, 1024-position) tiles; thread = (c4, lane16): 4 channels x 9 taps + 4 bias accumulators over the
+// positions l = lane16 mod 16; block tree over the 16 lanes; one partial [64*9 + 64] per CTA.
+constexpr int C1_CHUNK = 1024;
+constexpr int C1_LEN = 64 * 9 + 64;
+__global__ void __launch_bounds__(256)
+first_wgrad_kernel(const float4 *__restrict__ g /*C4L4*/, const float *__restrict__ x, int N, int L, int chunks,
+                   float *__restrict__ partial /*[gridDim.x][C1_LEN]*/) {
+    __shared__ float red[16][16][40];
+    const int c4 = threadIdx.x >> 4, ln = threadIdx.x & 15;
+    float acc[4][9], bs[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { bs[i] = 0.f;
+#pragma unroll
+        for (int t = 0; t < 9; ++t) acc[i][t] = 0.f; }
+    const int total = N * chunks;
+    for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
+        const int n = tile / chunks, l0 = (tile - n * chunks) * C1_CHUNK;
+        const int l1 = min(L, l0 + C1_CHUNK);
+        const float *xr = x + (size_t)n * L;
+        for (int l = l0 + ln; l < l1; l += 16) {
+            const float4 gv = __ldg(g + ((size_t)n * 16 + c4) * L + l);
+            const float ga[4] = {gv.x, gv.y, gv.z, gv.w};
+#pragma unroll
+            for (int t = 0; t < 9; ++t) {
+                const int q = l + t - 4;
+                const float xv = (q >= 0 && q < L) ? __ldg(xr + q) : 0.0f;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) acc[i][t] = fmaf(ga[i], xv, acc[i][t]);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) bs[i] += ga[i];
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+#pragma unroll
+        for (int t = 0; t < 9; ++t) red[c4][ln][i * 9 + t] = acc[i][t];
+        red[c4][ln][36 + i] = bs[i];
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < 16 * 40; idx += 256) {
+        const int cc = idx / 40, k = idx - cc * 40;
+        float s = 0.0f;
+        for (int j = 0; j < 16; ++j) s += red[cc][j][k];
+        float *o = partial + (size_t)blockIdx.x * C1_LEN;
+        if (k < 36) o[(4 * cc + k / 9) * 9 + (k % 9)] = s;          // (64, 1, 9) layout
+        else o[64 * 9 + 4 * cc + (k - 36)] = s;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ AdamW
+__global__ void __launch_bounds__(256)
+adamw_kernel(float *__restrict__ p, const float *__restrict__ g, float *__restrict__ m, float *__restrict__ v, size_t n,
+             float lr, float b1, float b2, float eps, float wd, float bc1, float bc2_sqrt) {
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (size_t)gridDim.x * 256) {
+        const float gi = g[i];
+        float pi = p[i] * (1.0f - lr * wd);                       // decoupled weight decay
+        const float mi = m[i] + (1.0f - b1) * (gi - m[i]);        // torch: exp_avg.lerp_(grad, 1 - beta1)
+        const float vi = b2 * v[i] + (1.0f - b2) * gi * gi;
+        m[i] = mi; v[i] = vi;
+        const float denom = sqrtf(vi) / bc2_sqrt + eps;
+        pi -= (lr / bc1) * (mi / denom);
+        p[i] = pi;
+    }
+}
+
+}  // namespace stof
+
+using namespace stof;
+
+extern "C" int stof_train_workspace_bytes(const stof_model *m, int N, int L, size_t *bytes) {
+    STOF_REQUIRE(bytes != nullptr, STOF_E_INVALID, "stof_train_workspace_bytes: bytes is NULL");
+    TrainPlan pl;
+    int rc = make_train_plan(m, N, L, &pl);
+    if (rc) return rc;
+    *bytes = pl.total_bytes;
+    return STOF_OK;
+}
+
+extern "C" int stof_forward_train(stof_model *m, const float *x, int N, int L, float *mask, void *ws_dev, size_t ws_bytes,
+                                  void *stream) {
+    TrainPlan pl;
+    int rc = make_train_plan(m, N, L, &pl);
+    if (rc) return rc;
+    STOF_REQUIRE(x && mask && ws_dev, STOF_E_INVALID, "stof_forward_train: NULL buffer");
+    STOF_REQUIRE(ws_bytes >= pl.total_bytes, STOF_E_WORKSPACE, "stof_forward_train: workspace %zu < %zu bytes", ws_bytes, pl.total_bytes);
+    STOF_REQUIRE((reinterpret_cast<uintptr_t>(ws_dev) & 255) == 0 && (reinterpret_cast<uintptr_t>(mask) & 15) == 0, STOF_E_INVALID,
+                 "stof_forward_train: workspace must be 256-byte and mask 16-byte aligned");
+    cudaStream_t st = (cudaStream_t)stream;
+    float *ws = reinterpret_cast<float *>(ws_dev);
+    float *x0r = ws + pl.off_x0r, *x0 = ws + pl.off_x0;
+    // models/stofnet.py:45
+    if ((rc = launch_conv_first(x, N, L, m->first.w, m->first.b, x0r, 9, 0, st))) return rc;
+    if (pl.sgb) {
+        // :98-117
+        float *pooled = ws + pl.off_pooled, *e = ws + pl.off_e;
+        int *argmax = reinterpret_cast<int *>(ws + pl.off_argmax);
+        if ((rc = launch_contract_pool_simt(x0r, pooled, m->contract.w, m->contract.b, N, L, pl.P, st, argmax))) return rc;
+        if ((rc = launch_expand(pooled, e, m->expand.w, m->expand.b, N, pl.P, st))) return rc;
+        STOF_CUDA(cudaMemcpyAsync(x0, x0r, (size_t)N * 64 * L * sizeof(float), cudaMemcpyDeviceToDevice, st));
+        if ((rc = launch_sgb_add(x0, e, N, L, pl.P, m->sgb_scale, (L - pl.P * m->sgb_scale) / 2, st))) return rc;
+    }
+    // :51-62  conv index i = j + 2
+    const float *cur = x0;
+    for (int j = 0; j < m->n_mid; ++j) {
+        float *out = ws + pl.off_a[j];
+        const bool longskip = (j == m->n_mid - 1), res = (j & 1) && !longskip;
+        if (longskip) rc = launch_conv_mid_simt(cur, x0, out, m->mid[j].w, m->mid[j].b, N, L, 1, st);
+        else if (res) rc = launch_conv_mid_simt(cur, (j >= 2) ? ws + pl.off_a[j - 2] : x0, out, m->mid[j].w, m->mid[j].b, N, L, 1, st);
+        else rc = launch_conv_mid_simt(cur, nullptr, out, m->mid[j].w, m->mid[j].b, N, L, 0, st);
+        if (rc) return rc;
+        cur = out;
+    }
+    // :65
+    return launch_conv_last(cur, mask, m->last.w, m->last.b, N, L, 64, 0, st);
+}
+
+static int mid_wgrad(const float *G, const float *A, int N, int L, float *partial, float *dW, float *db, cudaStream_t st) {
+    const int tpr = (L + WG_TL - 1) / WG_TL;
+    const long long total = (long long)N * tpr;
+    const int grid = (int)(total < WG_MAX_PARTS ? total : WG_MAX_PARTS);
+    constexpr int smem = 16 * (WG_GP + WG_AP) * sizeof(float4);
+    static bool attr = false;
+    if (!attr) {
+        STOF_CUDA(cudaFuncSetAttribute(mid_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr = true;
+    }
+    mid_wgrad_kernel<<<grid, 256, smem, st>>>(reinterpret_cast<const float4 *>(G), reinterpret_cast<const float4 *>(A), N, L, tpr, partial);
+    STOF_LAUNCH_CHECK();
+    reduce_parts_kernel<<<(unsigned)((WG_MID_LEN + 255) / 256), 256, 0, st>>>(partial, grid, WG_MID_LEN, dW, 64 * 64 * 7, db);
+    STOF_LAUNCH_CHECK();
+    return STOF_OK;
+}
+
+extern "C" int stof_backward(stof_model *m, const float *x, const float *g_mask, int N, int L, void *ws_dev, size_t ws_bytes,
+                             const stof_grads *gr, void *stream) {
+    TrainPlan pl;
+    int rc = make_train_plan(m, N, L, &pl);
+    if (rc) return rc;
+    STOF_REQUIRE(x && g_mask && ws_dev && gr, STOF_E_INVALID, "stof_backward: NULL buffer");
+    STOF_REQUIRE(ws_bytes >= pl.total_bytes, STOF_E_WORKSPACE, "stof_backward: workspace %zu < %zu bytes", ws_bytes, pl.total_bytes);
+    STOF_REQUIRE(gr->conv1_w && gr->conv1_b && gr->last_w && gr->last_b, STOF_E_INVALID, "stof_backward: missing gradient buffer");
+    for (int j = 0; j < m->n_mid; ++j) STOF_REQUIRE(gr->mid_w[j] && gr->mid_b[j], STOF_E_INVALID, "stof_backward: conv%d gradient buffer missing", j + 2);
+    if (pl.sgb) STOF_REQUIRE(gr->contract_w && gr->contract_b && gr->expand_w && gr->expand_b, STOF_E_INVALID, "stof_backward: semi-global block gradient buffers missing");
+    STOF_REQUIRE((reinterpret_cast<uintptr_t>(g_mask) & 15) == 0, STOF_E_INVALID, "stof_backward: g_mask must be 16-byte aligned");
+    cudaStream_t st = (cudaStream_t)stream;
+    float *ws = reinterpret_cast<float *>(ws_dev);
+    float *x0r = ws + pl.off_x0r, *x0 = ws + pl.off_x0;
+    float *X = ws + pl.off_g[0], *S = ws + pl.off_g[1], *T = ws + pl.off_g[2];
+    float *partial = ws + pl.off_partial;
+    const size_t n4 = (size_t)N * 16 * L;
+    const float4 *gy = reinterpret_cast<const float4 *>(g_mask);
+    auto act = [&](int j) -> const float * { return j < 0 ? x0 : ws + pl.off_a[j]; };     // output of mid conv j (x0 for j = -1)
+    const int nm = m->n_mid;
+
+    // ---- conv_last: g_a12 -> X
+    {
+        dim3 grid((L + 255) / 256, N);
+        STOF_REQUIRE(N <= 65535, STOF_E_INVALID, "stof_backward: at most 65535 rows per call");
+        last_dgrad_kernel<<<grid, 256, 0, st>>>(gy, m->raw_last_w, N, L, reinterpret_cast<float4 *>(X));
+        STOF_LAUNCH_CHECK();
+        const int chunks = (L + LW_CHUNK - 1) / LW_CHUNK;
+        const long long total = (long long)N * chunks;
+        const int g2 = (int)(total < LW_MAX_CTAS ? total : LW_MAX_CTAS);
+        last_wgrad_kernel<<<g2, 192, 0, st>>>(gy, act(nm - 1), N, L, chunks, partial);
+        STOF_LAUNCH_CHECK();
+        reduce_parts_kernel<<<4, 256, 0, st>>>(partial, g2, 772, gr->last_w, 768, gr->last_b);
+        STOF_LAUNCH_CHECK();
+    }
+    // ---- conv{nb-1} (long skip): a = x0 + conv(a_prev): g_conv = X;  S = dgrad(X)
+    if ((rc = mid_wgrad(X, act(nm - 2), N, L, partial, gr->mid_w[nm - 1], gr->mid_b[nm - 1], st))) return rc;
+    if ((rc = launch_conv_mid_simt(X, nullptr, S, m->bw_mid[nm - 1], m->zero_bias, N, L, 2, st))) return rc;
+    // ---- pairs (RES j, LEAKY j - 1), j = nm-2, nm-4, ..., 1:   S = g wrt a_j
+    for (int j = nm - 2; j >= 1; j -= 2) {
+        // a_j = a_{j-2} + conv_j(a_{j-1}):  wgrad with input a_{j-1};  T = dgrad_j(S);  skip keeps S
+        if ((rc = mid_wgrad(S, act(j - 1), N, L, partial, gr->mid_w[j], gr->mid_b[j], st))) return rc;
+        if ((rc = launch_conv_mid_simt(S, nullptr, T, m->bw_mid[j], m->zero_bias, N, L, 2, st))) return rc;
+        // a_{j-1} = lrelu(conv_{j-1}(a_{j-2})):  T *= lrelu'(a_{j-1});  wgrad with input a_{j-2};  S += dgrad_{j-1}(T)
+        lrelu_bwd_kernel<<<ew_grid(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(T), reinterpret_cast<const float4 *>(act(j - 1)), n4);
+        STOF_LAUNCH_CHECK();
+        if ((rc = mid_wgrad(T, act(j - 2), N, L, partial, gr->mid_w[j - 1], gr->mid_b[j - 1], st))) return rc;
+        if ((rc = launch_conv_mid_simt(T, S, S, m->bw_mid[j - 1], m->zero_bias, N, L, 1, st))) return rc;
+    }
+    // ---- S = g wrt x0 through the chain; add the long skip
+    add_kernel<<<ew_grid(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(S), reinterpret_cast<const float4 *>(X), n4);
+    STOF_LAUNCH_CHECK();
+    // ---- semi-global block: x0 = x0r + pad(up(E))
+    if (pl.sgb) {
+        float *pooled = ws + pl.off_pooled, *e = ws + pl.off_e, *ge = ws + pl.off_ge, *gpool = ws + pl.off_gpool;
+        const int *argmax = reinterpret_cast<const int *>(ws + pl.off_argmax);
+        const int P = pl.P, off = (L - P * m->sgb_scale) / 2;
+        const long long warps = (long long)N * 16 * P;
+        window_sum_kernel<<<(unsigned)((warps + 7) / 8), 256, 0, st>>>(reinterpret_cast<const float4 *>(S), N, L, P, m->sgb_scale, off, ge);
+        STOF_LAUNCH_CHECK();
+        const size_t ne = (size_t)N * 64 * P;
+        lrelu_bwd1_kernel<<<ew_grid(ne), 256, 0, st>>>(ge, e, ne);
+        STOF_LAUNCH_CHECK();
+        expand_wgrad_kernel<<<512, 320, 0, st>>>(ge, pooled, N, P, gr->expand_w);
+        STOF_LAUNCH_CHECK();
+        bias_grad_ncl_kernel<<<64, 256, 0, st>>>(ge, N, 64, P, gr->expand_b);
+        STOF_LAUNCH_CHECK();
+        const long long np = (long long)N * 512 * P;
+        expand_dgrad_kernel<<<(unsigned)((np + 255) / 256), 256, 0, st>>>(ge, m->raw_expand_w, pooled, N, P, gpool);
+        STOF_LAUNCH_CHECK();
+        contract_wgrad_kernel<<<512, 320, 0, st>>>(gpool, argmax, x0r, N, L, P, gr->contract_w, gr->contract_b);
+        STOF_LAUNCH_CHECK();
+        const int tiles = (L + CD_T - 1) / CD_T;
+        STOF_REQUIRE((long long)N * tiles < (1ll << 31), STOF_E_INVALID, "stof_backward: batch too large");
+        contract_dgrad_kernel<<<(unsigned)(N * tiles), 256, 0, st>>>(gpool, argmax, m->raw_contract_w, N, L, P, tiles, S);
+        STOF_LAUNCH_CHECK();
+    }
+    // ---- conv1: x0r = relu(conv1 x)
+    relu_bwd_kernel<<<ew_grid(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(S), reinterpret_cast<const float4 *>(x0r), n4);
+    STOF_LAUNCH_CHECK();
+    {
+        const int chunks = (L + C1_CHUNK - 1) / C1_CHUNK;
+        const long long total = (long long)N * chunks;
+        const int g1 = (int)(total < 4 * kSMs ? total : 4 * kSMs);
+        first_wgrad_kernel<<<g1, 256, 0, st>>>(reinterpret_cast<const float4 *>(S), x, N, L, chunks, partial);
+        STOF_LAUNCH_CHECK();
+        reduce_parts_kernel<<<(C1_LEN + 255) / 256, 256, 0, st>>>(partial, g1, C1_LEN, gr->conv1_w, 64 * 9, gr->conv1_b);
+        STOF_LAUNCH_CHECK();
+    }
+    return STOF_OK;
+}
+
+extern "C" int stof_adamw_step(float *params_dev, const float *grads_dev, float *exp_avg_dev, float *exp_avg_sq_dev, size_t n,
+                               int step, float lr, float beta1, float beta2, float eps, float weight_decay, void *stream) {
+    STOF_REQUIRE(params_dev && grads_dev && exp_avg_dev && exp_avg_sq_dev && n > 0 && step >= 1, STOF_E_INVALID,
+                 "stof_adamw_step: bad arguments (n=%zu step=%d)", n, step);
+    const double bc1 = 1.0 - pow((double)beta1, (double)step);
+    const double bc2 = 1.0 - pow((double)beta2, (double)step);
+    adamw_kernel<<<ew_grid(n), 256, 0, (cudaStream_t)stream>>>(params_dev, grads_dev, exp_avg_dev, exp_avg_sq_dev, n, lr, beta1, beta2, eps,
+                                                              weight_decay, (float)bc1, (float)sqrt(bc2));
+    STOF_LAUNCH_CHECK();
+    return STOF_OK;
+}

@@ -161,6 +161,62 @@ class Engine:
                                    self.ws.numel(), self.chunk_rows, stream_ptr(dev)))
         return out
 
+    # -- training step -------------------------------------------------------------------
+    def forward_train(self, module, x):
+        """Forward that keeps the activations in a workspace for backward(); returns (mask, x_contig, workspace)."""
+        require_cuda(x, "input")
+        if x.dim() != 3 or x.shape[1] != 1:
+            raise RuntimeError("stofnet_b200: expected input of shape (N, 1, L), got %s" % (tuple(x.shape),))
+        dev = x.device
+        self.sync(module, dev)
+        x = x.detach().to(torch.float32).contiguous()
+        N, _, L = x.shape
+        with torch.cuda.device(dev):
+            need = C.c_size_t()
+            check(lib.stof_train_workspace_bytes(self.handle, N, L, C.byref(need)))
+            ws = torch.empty(need.value, dtype=torch.uint8, device=dev)
+            out = torch.empty((N, 1, module.upsample_factor * L), dtype=torch.float32, device=dev)
+            check(lib.stof_forward_train(self.handle, x.data_ptr(), N, L, out.data_ptr(), ws.data_ptr(), ws.numel(),
+                                         stream_ptr(dev)))
+        return out, x, ws
+
+    def backward(self, module, x, g_mask, ws, names):
+        """d loss / d masks_pred -> one flat fp32 gradient buffer; returns (flat, [view per name in `names`])."""
+        dev = x.device
+        N, _, L = x.shape
+        g_mask = g_mask.detach().to(torch.float32).contiguous()
+        params = dict(module.named_parameters())
+        sizes = [params[k].numel() for k in names]
+        pad = [(-s) % 4 for s in sizes]                     # keep every view 16-byte aligned
+        flat = torch.zeros((sum(sizes) + sum(pad),), dtype=torch.float32, device=dev)
+        views, G, o = [], _lib.Grads(), 0
+        for k, s, p in zip(names, sizes, pad):
+            v = flat[o:o + s].view(params[k].shape)
+            views.append(v)
+            o += s + p
+            self._set_grad_ptr(G, k, v.data_ptr())
+        with torch.cuda.device(dev):
+            check(lib.stof_backward(self.handle, x.data_ptr(), g_mask.data_ptr(), N, L, ws.data_ptr(), ws.numel(),
+                                    C.byref(G), stream_ptr(dev)))
+        return flat, views
+
+    @staticmethod
+    def _set_grad_ptr(G, key, ptr):
+        stem, kind = key.rsplit(".", 1)
+        sfx = "_w" if kind == "weight" else "_b"
+        if stem == "conv1":
+            setattr(G, "conv1" + sfx, ptr)
+        elif stem == "conv_last":
+            setattr(G, "last" + sfx, ptr)
+        elif stem == "semi_global_block.contract_conv":
+            setattr(G, "contract" + sfx, ptr)
+        elif stem == "semi_global_block.expand_conv":
+            setattr(G, "expand" + sfx, ptr)
+        elif stem.startswith("conv") and stem[4:].isdigit():
+            getattr(G, "mid" + sfx)[int(stem[4:]) - 2] = ptr
+        else:
+            raise KeyError("stofnet_b200: no gradient kernel for parameter %r" % key)
+
     def infer_host(self, module, x_host, window_size, threshold, cap=64, want_mask=False, device=None):
         """End-to-end eval step on HOST tensors (pinned recommended): H2D + forward + peaks + D2H."""
         dev = device if device is not None else next(module.parameters()).device

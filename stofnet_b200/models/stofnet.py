@@ -40,6 +40,23 @@ class SemiGlobalBlock(nn.Module):
                                   "it is not available as a standalone operator yet")
 
 
+class _StofNetFunction(torch.autograd.Function):
+    """masks_pred = model(frame) with a backward: stof_forward_train keeps the activations, stof_backward turns
+    d loss / d masks_pred into every parameter's gradient (main.py:221,247)."""
+
+    @staticmethod
+    def forward(ctx, module, names, x, *params):
+        mask, xc, ws = module._engine.forward_train(module, x)
+        ctx.module, ctx.names, ctx.xc, ctx.ws = module, names, xc, ws
+        return mask
+
+    @staticmethod
+    def backward(ctx, g_mask):
+        _, views = ctx.module._engine.backward(ctx.module, ctx.xc, g_mask, ctx.ws, ctx.names)
+        ctx.ws = None
+        return (None, None, None) + tuple(views)
+
+
 class StofNet(nn.Module):
 
     def __init__(self, upsample_factor=4, num_features=64, num_blocks=13, kernel_sizes=[9, 7, 3], in_channels=1,
@@ -65,9 +82,13 @@ class StofNet(nn.Module):
         self._engine = Engine(_lib.KIND_STOFNET)
 
     def forward(self, x):
-        if torch.is_grad_enabled() and self.training and any(p.requires_grad for p in self.parameters()):
-            raise NotImplementedError("stofnet_b200: the training-step kernels (backward + AdamW) are not built "
-                                      "yet; call under torch.no_grad() / model.eval() for inference")
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            # training step (main.py:221,247): fp32 forward that keeps the activations + hand-written backward
+            named = [(k, p) for k, p in self.named_parameters()]
+            if not all(p.requires_grad for _, p in named):
+                raise NotImplementedError("stofnet_b200: the backward kernels compute every parameter's gradient; "
+                                          "freezing a subset is not supported")
+            return _StofNetFunction.apply(self, tuple(k for k, _ in named), x, *[p for _, p in named])
         return self._engine.forward(self, x)
 
     def infer_host(self, x_host, window_size=20, threshold=None, cap=64, want_mask=False):

@@ -18,6 +18,8 @@ kernels (torch 2.11.0, oneDNN, fp32; fp64 re-run stored beside it as the tie-bre
   peaks_cases.npz      hand-made stage-4 edge cases -> reference indices / coords
   espcn_<ckpt>.npz     ESPCN_1D forward masks
   metrics_cases.npz    toa_rmse / coords2mask / find_threshold known answers
+  train_<ckpt>.npz     three training steps (model -> loss -> autograd -> AdamW, main.py:217-248): gradients
+                       of every parameter after the first backward, losses and parameters after each step
   aux_cases.npz        loss + gradient (main.py:228-232 through the reference's ops and autograd),
                        find_threshold, upscale_1d / iq2rf, AttentionBlock (dropout off)
 
@@ -317,7 +319,54 @@ def gen_aux_cases():
     print("aux cases done")
 
 
+def gen_train_cases():
+    """Training step of main.py:217-248 run with the reference model, torch autograd and torch.optim.AdamW:
+    gradients of every parameter after the first backward, and losses / parameters over three steps."""
+    import torch.nn.functional as F
+    from utils.gaussian import gaussian_kernel
+    gk = torch.tensor(gaussian_kernel(size=7, sigma=1), dtype=torch.float32).unsqueeze(0).unsqueeze(0)
+    for name, L, lam in (("different-armadillo", 338, 1e-2), ("clean-serenity", 320, 1.0)):
+        sd = load_sd(name)
+        has_sgb = any(k.startswith("semi_global_block") for k in sd)
+        torch.manual_seed(1)
+        model = StofNet(upsample_factor=4, semi_global_scale=80 if has_sgb else 1)
+        model.load_state_dict(sd)
+        model.train()
+        opt = torch.optim.AdamW(model.parameters(), lr=5e-4, weight_decay=1e-8)
+        N = 3
+        x = torch.from_numpy(synth_waveforms(N, L, seed=77, rf=10)).unsqueeze(1)
+        gt = torch.tensor([[[4 * 100 + 1, 4 * 200, 0]], [[4 * 50, 0, 0]], [[4 * 300 + 2, 4 * 310, 4 * 20]]], dtype=torch.long)
+        out = {"x": x.squeeze(1).numpy(), "gt": gt.numpy(), "lambda": np.float64(lam), "L": np.int64(L)}
+        losses = []
+        for step in range(3):
+            masks_pred = model(x)
+            mt = coords2mask(gt.clone(), masks_pred)
+            blur = F.conv1d(mt, gk, padding=3)
+            blur /= blur.max()
+            blur *= 20
+            loss = torch.nn.MSELoss()(masks_pred.squeeze(1), blur.squeeze(1).float()) + \
+                torch.nn.L1Loss()(masks_pred.squeeze(1), torch.zeros_like(masks_pred.squeeze(1))) * lam
+            opt.zero_grad()
+            loss.backward()
+            if step == 0:
+                out["mask0"] = masks_pred.detach().squeeze(1).numpy()
+                for k, p in model.named_parameters():
+                    out["grad0/" + k] = p.grad.detach().numpy().copy()
+            opt.step()
+            losses.append(loss.item())
+            if step == 2:
+                for k, p in model.named_parameters():
+                    out["param3/" + k] = p.detach().numpy().copy()
+        out["losses"] = np.array(losses, dtype=np.float64)
+        out["names"] = np.array([k for k, _ in model.named_parameters()])
+        np.savez_compressed(os.path.join(HERE, "train_%s.npz" % name), **out)
+        print("train case", name, losses)
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "train":
+        gen_train_cases()
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "aux":
         gen_aux_cases()
         sys.exit(0)
@@ -325,4 +374,5 @@ if __name__ == "__main__":
     gen_peaks_cases()
     gen_metrics_cases()
     gen_aux_cases()
+    gen_train_cases()
     print("done")

@@ -102,3 +102,77 @@ def test_single_process_path():
     assert out.shape == (2, 2) and torch.equal(out, t[:, :2])
     z = gather_tof_table(torch.zeros((2, 4)), 0, 2)
     assert z.shape == (2, 1, 1)
+
+
+# ---- training-step exchange (stofnet_b200/train.py): flat gradient bucket all-reduce + global blur max -------------
+def _loss_and_grads(sd, x, gt, blur_max_value, lam=1e-2):
+    """Stand-in for the per-rank CUDA compute: the oracle's torch port + torch autograd on CPU (main.py:228-232 with
+    the target normalised by a GIVEN batch-wide maximum)."""
+    import torch.nn.functional as F
+    from oracle import torch_port
+    from stofnet_b200.utils.gaussian import gaussian_kernel
+    params = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    pred = torch_port.stofnet_forward(params, x)
+    mask = torch.zeros_like(pred)
+    mask.scatter_(2, gt.clamp(min=0), 1)
+    mask[..., :1] = 0
+    gk = torch.tensor(gaussian_kernel(7, 1.0), dtype=torch.float32).view(1, 1, -1)
+    blur = F.conv1d(mask, gk, padding=3)
+    local_max = blur.max()
+    mx = local_max if blur_max_value is None else blur_max_value
+    blur = blur / mx * 20
+    loss = F.mse_loss(pred, blur) + lam * pred.abs().mean()
+    loss.backward()
+    flat = torch.cat([params[k].grad.reshape(-1) for k in sd])
+    return loss.detach(), flat, local_max.detach()
+
+
+def _train_inputs():
+    from stofnet_b200.synth import synth_waveforms
+    sd = {k: torch.from_numpy(v) for k, v in load_npz("weights_clean-serenity.npz").items()}
+    x = torch.from_numpy(synth_waveforms(4, 160, seed=9, rf=10)).unsqueeze(1)
+    # rank 1's rows hold two adjacent echoes (blur max > single tap): the batch-wide maximum lives on one shard only
+    gt = torch.tensor([[[100, 0]], [[300, 0]], [[200, 201]], [[50, 400]]], dtype=torch.long)
+    return sd, x, gt
+
+
+def _train_worker(rank, world, port, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from stofnet_b200.train import average_gradients, global_blur_max
+        sd, x, gt = _train_inputs()
+        lo, hi = shard_rows(x.shape[0], world, rank)
+        _, _, local_max = _loss_and_grads(sd, x[lo:hi], gt[lo:hi], None)
+        mx = global_blur_max(local_max.reshape(1).clone())
+        loss, flat, _ = _loss_and_grads(sd, x[lo:hi], gt[lo:hi], mx[0])
+        average_gradients(flat)
+        dist.all_reduce(loss)
+        np.save(os.path.join(out_dir, "grads_%d.npy" % rank), flat.numpy())
+        np.save(os.path.join(out_dir, "loss_%d.npy" % rank), (loss / world).numpy())
+    finally:
+        dist.destroy_process_group()
+
+
+def test_data_parallel_gradients_match_undivided_batch(tmp_path):
+    world = 2
+    mp.spawn(_train_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    sd, x, gt = _train_inputs()
+    loss, flat, _ = _loss_and_grads(sd, x, gt, None)
+    g0 = np.load(os.path.join(str(tmp_path), "grads_0.npy"))
+    g1 = np.load(os.path.join(str(tmp_path), "grads_1.npy"))
+    assert np.array_equal(g0, g1)                                   # every rank ends with the same bucket
+    assert np.abs(g0 - flat.numpy()).max() <= 1e-5 * np.abs(flat.numpy()).max()
+    assert abs(float(np.load(os.path.join(str(tmp_path), "loss_0.npy"))) - float(loss)) <= 1e-5 * abs(float(loss))
+
+
+def test_cosine_lr_matches_torch_scheduler():
+    from stofnet_b200.train import cosine_lr
+    p = torch.nn.Parameter(torch.zeros(1))
+    opt = torch.optim.AdamW([p], lr=5e-4)
+    sch = torch.optim.lr_scheduler.CosineAnnealingLR(opt, 80)
+    for e in range(10):
+        assert abs(opt.param_groups[0]["lr"] - cosine_lr(5e-4, e, 80)) < 1e-12
+        opt.step()
+        sch.step()
