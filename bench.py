@@ -174,6 +174,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--precision", default="fp32", choices=["fp32", "fp16"],
+                    help="fp32 (default, the headline: index-exact) or fp16 (one-pass reduced-precision mode, stated tolerance)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -196,6 +198,7 @@ def main():
 
     sd = load_sd()
     model = sb.build_model(sd, dev)
+    model.set_precision(args.precision)
     eng = model._engine
     base = make_inputs(256, 3008 + rank)
     batches_host = [expand_batch(base, ROWS, s).pin_memory() for s in (0, 7, 13)]

@@ -143,6 +143,10 @@ int stof_profile_collect(stof_model *m, double *ms_by_class, int64_t *launches_b
  * layers_per_launch > 0 sets how many conv layers one fused chain launch covers (1..6, default 4).     */
 #define STOF_PATH_SIMT 0
 #define STOF_PATH_TC   1
+/*   STOF_PATH_TC_FP16  same kernels, ONE tensor-core pass on fp16-rounded operands (fp32 accumulation): a third of the MMAs and
+ *                   half of the activation traffic.  Not index-exact: it is the "stated tolerance" mode of the reduced-precision
+ *                   path (a TF32-like 11-bit significand; see DESIGN.md for the measured detection agreement).  Opt-in only. */
+#define STOF_PATH_TC_FP16 2
 int stof_model_set_path(stof_model *m, int path, int layers_per_launch);
 
 /* One fused chain launch on caller-provided activations (test hook for single layers / segments):

@@ -11,7 +11,7 @@ LIB_PATH = os.path.join(_HERE, "libstofnet_b200.so")
 
 MAX_MID = 16
 KIND_STOFNET, KIND_ESPCN = 0, 1
-PATH_SIMT, PATH_TC = 0, 1
+PATH_SIMT, PATH_TC, PATH_TC_FP16 = 0, 1, 2
 
 E_INVALID, E_LENGTH, E_LENGTH_ODD, E_WORKSPACE, E_CUDA, E_NCCL, E_UNSUPPORTED = -1, -2, -3, -4, -5, -6, -7
 

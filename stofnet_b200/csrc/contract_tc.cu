@@ -120,6 +120,7 @@ struct ContractParams {
     float *pooled;           // (N, 512, P)
     int N, L, P;
     int tiles_per_row, total_tiles;
+    int fast;                // 1: one-pass fp16 mode (X_hi W_hi only)
 };
 
 __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const ContractParams p) {
@@ -190,8 +191,12 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
                             const uint64_t da_hi = make_desc(a_lo0 + t + 2 * ks * rows, kDescHi);
                             const uint64_t da_lo = make_desc(a_lo0 + t + (8 + 2 * ks) * rows, kDescHi);
                             const uint64_t db = make_desc(w_lo0 + t * (CT_TAP_BYTES >> 4) + 2 * ks * 256, kDescHi);
-                            umma_f16(d_tmem, da_hi, db, kIdescA, (t > 0 || ks > 0) ? 1u : 0u);
-                            umma_f16(d_tmem + 128, da_lo, db, kIdescB, 1u);
+                            if (p.fast) {
+                                umma_f16(d_tmem, da_hi, db, kIdescB, (t > 0 || ks > 0) ? 1u : 0u);      // N = 128: W_hi rows only
+                            } else {
+                                umma_f16(d_tmem, da_hi, db, kIdescA, (t > 0 || ks > 0) ? 1u : 0u);
+                                umma_f16(d_tmem + 128, da_lo, db, kIdescB, 1u);
+                            }
                         }
                     }
                     umma_commit(BAR_A_EMPTY(b));
@@ -249,7 +254,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
                         ct_split_pair(v[4], v[5], uh.z, ul.z);
                         ct_split_pair(v[6], v[7], uh.w, ul.w);
                         *reinterpret_cast<uint4 *>(abuf + (c8 * rows + row) * 16) = uh;
-                        *reinterpret_cast<uint4 *>(abuf + ((8 + c8) * rows + row) * 16) = ul;
+                        if (!p.fast) *reinterpret_cast<uint4 *>(abuf + ((8 + c8) * rows + row) * 16) = ul;
                     }
                 }
                 fence_proxy_async_smem();
@@ -283,8 +288,13 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
                     uint32_t d0[32], d1[32];
                     tmem_ld16(d_tmem + 32 * c32, *reinterpret_cast<uint32_t(*)[16]>(&d0[0]));
                     tmem_ld16(d_tmem + 32 * c32 + 16, *reinterpret_cast<uint32_t(*)[16]>(&d0[16]));
-                    tmem_ld16(d_tmem + 128 + 32 * c32, *reinterpret_cast<uint32_t(*)[16]>(&d1[0]));
-                    tmem_ld16(d_tmem + 128 + 32 * c32 + 16, *reinterpret_cast<uint32_t(*)[16]>(&d1[16]));
+                    if (!p.fast) {
+                        tmem_ld16(d_tmem + 128 + 32 * c32, *reinterpret_cast<uint32_t(*)[16]>(&d1[0]));
+                        tmem_ld16(d_tmem + 128 + 32 * c32 + 16, *reinterpret_cast<uint32_t(*)[16]>(&d1[16]));
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) d1[i] = 0u;
+                    }
                     tmem_ld_wait();
                     if (c32 == 1) {
                         tc_fence_before_sync();
@@ -335,7 +345,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
 }
 
 int launch_contract_pool_tc(const float *x, const void *w, const float *bias, const float *w1, const float *b1, float *pooled,
-                            int N, int L, int P, cudaStream_t st) {
+                            int N, int L, int P, cudaStream_t st, int fast) {
     static bool attr = false;
     if (!attr) {
         STOF_CUDA(cudaFuncSetAttribute(contract_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM_BYTES));
@@ -343,7 +353,7 @@ int launch_contract_pool_tc(const float *x, const void *w, const float *bias, co
     }
     ContractParams p;
     p.x = x; p.w = w; p.bias = bias; p.w1 = w1; p.b1 = b1; p.pooled = pooled;
-    p.N = N; p.L = L; p.P = P;
+    p.N = N; p.L = L; p.P = P; p.fast = fast;
     p.tiles_per_row = (P + 2) / 3;
     const long long total = (long long)N * p.tiles_per_row;
     STOF_REQUIRE(total < (1ll << 31), STOF_E_INVALID, "contract_tc: too many tiles");

@@ -42,8 +42,9 @@ constexpr int TC_R = 280;                              // smem rows per (plane, 
 constexpr int TC_SLAB = TC_R * 16;                     // bytes of one (plane, c8) slab
 constexpr int TC_PLANE = 8 * TC_SLAB;                  // one fp16 plane (hi or lo): 64 channels
 constexpr int TC_BUF = 2 * TC_PLANE;                   // hi + lo
-constexpr int TC_STAGES = 5;
+constexpr int TC_STAGES = 5;                          // weight ring of the fp32-faithful mode: 5 x 16 KB taps
 constexpr int TC_STAGE_BYTES = 16384;                  // one k7 tap: [8 c8][128 n][8] fp16
+constexpr int TC_MAX_STAGES = 10;                     // one-pass fp16 mode: 10 x 8 KB (W_hi only) in the same 80 KB
 constexpr float TC_LO_SCALE = 2048.0f;                 // 2^11
 constexpr float TC_LO_INV = 1.0f / 2048.0f;
 
@@ -54,7 +55,7 @@ constexpr int TC_OFF_W = 2 * TC_BUF;
 constexpr int TC_OFF_BIAS = TC_OFF_W + TC_STAGES * TC_STAGE_BYTES;          // [TC_MAX_LAYERS][64] fp32
 constexpr int TC_OFF_BAR = TC_OFF_BIAS + TC_MAX_LAYERS * 64 * 4;
 // barriers (8 B each): w_full[STAGES] w_empty[STAGES] acc_full[2] acc_empty[2] act_ready[TC_MAX_LAYERS][2] in_full p_free
-constexpr int TC_NBAR = 2 * TC_STAGES + 4 + 2 * TC_MAX_LAYERS + 2;
+constexpr int TC_NBAR = 2 * TC_MAX_STAGES + 4 + 2 * TC_MAX_LAYERS + 2;
 constexpr int TC_OFF_TMEM = TC_OFF_BAR + TC_NBAR * 8;
 constexpr int TC_SMEM_BYTES = TC_OFF_TMEM + 16;
 
@@ -111,6 +112,7 @@ __device__ __forceinline__ void tl_event(unsigned long long *tl, int cap, uint32
 #define TL(role, k, b, what) tl_event(p.timeline, p.timeline_cap, (role), ((role) << 24) | ((uint32_t)(k) << 16) | ((uint32_t)(b) << 8) | (what), tl_cnt)
 #define TL_FLUSH(role) do { if (p.timeline != nullptr && blockIdx.x == 0) p.timeline[(role)] = (unsigned long long)tl_cnt; } while (0)
 
+template <bool FAST>
 __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     const uint32_t sbase = smem_u32(smem);
@@ -118,11 +120,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
     int tl_cnt = 0;
     const uint32_t bar0 = sbase + TC_OFF_BAR;
     auto BAR_W_FULL = [&](int s) { return bar0 + 8 * s; };
-    auto BAR_W_EMPTY = [&](int s) { return bar0 + 8 * (TC_STAGES + s); };
-    auto BAR_ACC_FULL = [&](int b) { return bar0 + 8 * (2 * TC_STAGES + b); };
-    auto BAR_ACC_EMPTY = [&](int b) { return bar0 + 8 * (2 * TC_STAGES + 2 + b); };
-    auto BAR_ACT = [&](int k, int b) { return bar0 + 8 * (2 * TC_STAGES + 4 + 2 * k + b); };
-    const uint32_t BAR_IN_FULL = bar0 + 8 * (2 * TC_STAGES + 4 + 2 * TC_MAX_LAYERS);
+    auto BAR_W_EMPTY = [&](int s) { return bar0 + 8 * (TC_MAX_STAGES + s); };
+    auto BAR_ACC_FULL = [&](int b) { return bar0 + 8 * (2 * TC_MAX_STAGES + b); };
+    auto BAR_ACC_EMPTY = [&](int b) { return bar0 + 8 * (2 * TC_MAX_STAGES + 2 + b); };
+    auto BAR_ACT = [&](int k, int b) { return bar0 + 8 * (2 * TC_MAX_STAGES + 4 + 2 * k + b); };
+    const uint32_t BAR_IN_FULL = bar0 + 8 * (2 * TC_MAX_STAGES + 4 + 2 * TC_MAX_LAYERS);
+    constexpr int n_stages = FAST ? TC_MAX_STAGES : TC_STAGES;          // weight ring depth / stage stride
+    constexpr uint32_t stage_stride = FAST ? TC_STAGE_BYTES / 2 : TC_STAGE_BYTES;
     const uint32_t BAR_P_FREE = BAR_IN_FULL + 8;
     float *s_bias = reinterpret_cast<float *>(smem + TC_OFF_BIAS);
     volatile uint32_t *s_tmem = reinterpret_cast<volatile uint32_t *>(smem + TC_OFF_TMEM);
@@ -133,7 +137,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
         s_bias[i] = (c < p.layer[k].n_out) ? __ldg(p.layer[k].bias + c) : 0.0f;
     }
     if (threadIdx.x == 0) {
-        for (int s = 0; s < TC_STAGES; ++s) {
+        for (int s = 0; s < TC_MAX_STAGES; ++s) {
             mbar_init(BAR_W_FULL(s), 1);
             mbar_init(BAR_W_EMPTY(s), 2);                 // one issuing warp per block consumes a tap
         }
@@ -169,9 +173,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
             if (j > 0) mbar_wait(BAR_P_FREE, (uint32_t)(j - 1) & 1u);
             if (lane == 0) TL(0u, 0, 0, 1);
             const int r_lo = max(0, -l_org), r_hi = min(r_in, p.L - l_org);
+            const int nslab = FAST ? 8 : 16;               // one-pass fp16 mode: hi plane only
             // rows outside the waveform are the conv's zero padding (only tiles at the ends of a row have any)
             if (r_lo > 0 || r_hi < r_in) {
-                for (int slab = 0; slab < 16; ++slab) {
+                for (int slab = 0; slab < nslab; ++slab) {
                     uint8_t *sl = smem + TC_OFF_P + slab * TC_SLAB;
                     for (int r = lane; r < r_lo; r += 32) *reinterpret_cast<uint4 *>(sl + r * 16) = make_uint4(0, 0, 0, 0);
                     for (int r = r_hi + lane; r < r_in; r += 32) *reinterpret_cast<uint4 *>(sl + r * 16) = make_uint4(0, 0, 0, 0);
@@ -181,9 +186,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
             __syncwarp();
             if (lane == 0) {
                 const uint32_t bytes = (uint32_t)(r_hi - r_lo) * 16u;
-                mbar_arrive_expect_tx(BAR_IN_FULL, bytes * 16u);
+                mbar_arrive_expect_tx(BAR_IN_FULL, bytes * (uint32_t)nslab);
                 const __half *src = reinterpret_cast<const __half *>(p.in) + (size_t)n * 16 * p.L * 8;
-                for (int slab = 0; slab < 16; ++slab)
+                for (int slab = 0; slab < nslab; ++slab)
                     bulk_g2s(sbase + TC_OFF_P + slab * TC_SLAB + r_lo * 16, src + ((size_t)slab * p.L + l_org + r_lo) * 8, bytes,
                              BAR_IN_FULL);
             }
@@ -203,19 +208,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                     const int l0 = (tile - n * p.tiles_per_row) * p.t_out;
                     const int a0 = max(0, l0 - 16), a1 = min(p.L, l0 + p.t_out + 16);
                     const __half *src = reinterpret_cast<const __half *>(p.x0) + (size_t)n * 16 * p.L * 8;
-                    for (int slab = 0; slab < 16; ++slab)
+                    for (int slab = 0; slab < (FAST ? 8 : 16); ++slab)
                         bulk_prefetch_l2(src + ((size_t)slab * p.L + a0) * 8, (uint32_t)(a1 - a0) * 16u);
                 }
                 for (int t = 0; t < ly.taps; ++t) {
                     if (lane == 0) {
                         mbar_wait(BAR_W_EMPTY(s), ph ^ 1u);
-                        TL(0u, k, 0, 16 + t);
-                        mbar_arrive_expect_tx(BAR_W_FULL(s), (uint32_t)ly.stage_bytes);
-                        bulk_g2s(sbase + TC_OFF_W + s * TC_STAGE_BYTES,
-                                 reinterpret_cast<const uint8_t *>(ly.w) + (size_t)t * ly.stage_bytes, (uint32_t)ly.stage_bytes,
-                                 BAR_W_FULL(s));
+                        const uint32_t sbytes = (uint32_t)(FAST ? ly.stage_bytes_fast : ly.stage_bytes);
+                        mbar_arrive_expect_tx(BAR_W_FULL(s), sbytes);
+                        bulk_g2s(sbase + TC_OFF_W + s * stage_stride,
+                                 reinterpret_cast<const uint8_t *>(FAST ? ly.w_fast : ly.w) + (size_t)t * sbytes, sbytes, BAR_W_FULL(s));
                     }
-                    if (++s == TC_STAGES) { s = 0; ph ^= 1u; }
+                    if (++s == n_stages) { s = 0; ph ^= 1u; }
                     if (k == p.in_layer && t == p.in_tap && next < p.total_tiles) {
                         __syncwarp();
                         issue_input(next, it + 1);
@@ -251,9 +255,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                 const int taps = ly.taps;
                 const uint32_t a_base = (((sbase + ((k & 1) ? TC_OFF_Q : TC_OFF_P)) >> 4) | kALoBase) +
                                         (uint32_t)(p.b_row[k] - ly.pad + 128 * b);
-                const uint32_t idesc_a = umma_idesc_f16(128, ly.n_stack);
+                const uint32_t idesc_a = umma_idesc_f16(128, FAST ? ly.n_fast : ly.n_stack);
+                const bool fast = FAST;
                 const uint32_t idesc_b = umma_idesc_f16(128, ly.n_lo);
-                const uint32_t w_rows = (uint32_t)ly.w_rows;                    // K-chunk stride of a weight stage / 16
+                const uint32_t w_rows = (uint32_t)(FAST ? ly.w_rows_fast : ly.w_rows);   // K-chunk stride of a weight stage / 16
                 const uint32_t w_hi_off = (uint32_t)ly.lo_row;
                 const uint32_t lo_col = (uint32_t)ly.lo_col;
                 if (tl_on) TL(role, k, b, 3);
@@ -266,10 +271,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                 for (int t = 0; t < taps; ++t) {
                     mbar_wait(BAR_W_FULL(s), ph);
                     tc_fence_after_sync();
-                    if (tl_on) TL(role, k, b, 16 + t);
                     if (elect_one()) {
                         const uint32_t a_lo = a_base + (uint32_t)t;
-                        const uint32_t w_lo = ((sbase + TC_OFF_W + s * TC_STAGE_BYTES) >> 4) | (w_rows << 16);
+                        const uint32_t w_lo = ((sbase + TC_OFF_W + s * stage_stride) >> 4) | (w_rows << 16);
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks) {
                             const uint64_t da_hi = make_desc(a_lo + 2 * ks * TC_R, kDescHi);
@@ -277,14 +281,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                             const uint64_t db_all = make_desc(w_lo + 2 * ks * w_rows, kDescHi);
                             const uint64_t db_hi = make_desc(w_lo + 2 * ks * w_rows + w_hi_off, kDescHi);
                             umma_f16(d_tmem, da_hi, db_all, idesc_a, (t > 0 || ks > 0) ? 1u : 0u);
-                            umma_f16(d_tmem + lo_col, da_lo, db_hi, idesc_b, 1u);
+                            if (!fast) umma_f16(d_tmem + lo_col, da_lo, db_hi, idesc_b, 1u);
                         }
                         umma_commit(BAR_W_EMPTY(s));                             // this stream is done with the stage
                         if (t == taps - 1) umma_commit(BAR_ACC_FULL(b));
                     }
                     __syncwarp();
-                    if (++s == TC_STAGES) { s = 0; ph ^= 1u; }
+                    if (++s == n_stages) { s = 0; ph ^= 1u; }
                 }
+                if (tl_on) TL(role, k, b, 4);
             }
         }
         if (tl_on) TL_FLUSH(role);
@@ -323,7 +328,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
 #pragma unroll
                         for (int h = 0; h < 4; ++h) {
                             xs_h[h] = inside ? __ldg(x0 + (size_t)(4 * egrp + h) * p.L + l) : make_uint4(0, 0, 0, 0);
-                            xs_l[h] = inside ? __ldg(x0 + (size_t)(8 + 4 * egrp + h) * p.L + l) : make_uint4(0, 0, 0, 0);
+                            xs_l[h] = (inside && !FAST) ? __ldg(x0 + (size_t)(8 + 4 * egrp + h) * p.L + l) : make_uint4(0, 0, 0, 0);
                         }
                     }
                     mbar_wait(BAR_ACC_FULL(b), lseq & 1u);
@@ -343,10 +348,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                         if (lane == 0) mbar_arrive(BAR_ACC_EMPTY(b));
                         if (egrp == 0 && l >= l0 && l < l_end) {
                             float4 o;
-                            o.x = (__uint_as_float(d[0]) + TC_LO_INV * __uint_as_float(d[8])) + bias[0];
-                            o.y = (__uint_as_float(d[1]) + TC_LO_INV * __uint_as_float(d[9])) + bias[1];
-                            o.z = (__uint_as_float(d[2]) + TC_LO_INV * __uint_as_float(d[10])) + bias[2];
-                            o.w = (__uint_as_float(d[3]) + TC_LO_INV * __uint_as_float(d[11])) + bias[3];
+                            const float li = FAST ? 0.0f : TC_LO_INV;      // one-pass mode: columns 8..11 hold X_hi W_lo only
+                            o.x = (__uint_as_float(d[0]) + li * __uint_as_float(d[8])) + bias[0];
+                            o.y = (__uint_as_float(d[1]) + li * __uint_as_float(d[9])) + bias[1];
+                            o.z = (__uint_as_float(d[2]) + li * __uint_as_float(d[10])) + bias[2];
+                            o.w = (__uint_as_float(d[3]) + li * __uint_as_float(d[11])) + bias[3];
                             reinterpret_cast<float4 *>(p.out_mask)[(size_t)n * p.L + l] = o;
                         }
                     } else {
@@ -356,8 +362,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                         uint32_t d0[32], d1[32];
                         tmem_ld16(d_tmem + 32 * egrp, *reinterpret_cast<uint32_t(*)[16]>(&d0[0]));
                         tmem_ld16(d_tmem + 32 * egrp + 16, *reinterpret_cast<uint32_t(*)[16]>(&d0[16]));
-                        tmem_ld16(d_tmem + 64 + 32 * egrp, *reinterpret_cast<uint32_t(*)[16]>(&d1[0]));
-                        tmem_ld16(d_tmem + 64 + 32 * egrp + 16, *reinterpret_cast<uint32_t(*)[16]>(&d1[16]));
+                        const bool fast = FAST;
+                        if (!fast) {
+                            tmem_ld16(d_tmem + 64 + 32 * egrp, *reinterpret_cast<uint32_t(*)[16]>(&d1[0]));
+                            tmem_ld16(d_tmem + 64 + 32 * egrp + 16, *reinterpret_cast<uint32_t(*)[16]>(&d1[16]));
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) d1[i] = 0u;
+                        }
                         tmem_ld_wait();
                         tc_fence_before_sync();
                         __syncwarp();
@@ -385,7 +397,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                                 uint4 rh, rl;
                                 if (type == TC_RES) {
                                     rh = *reinterpret_cast<const uint4 *>(outbuf + c8 * TC_SLAB + r * 16);
-                                    rl = *reinterpret_cast<const uint4 *>(outbuf + TC_PLANE + c8 * TC_SLAB + r * 16);
+                                    rl = fast ? make_uint4(0, 0, 0, 0) : *reinterpret_cast<const uint4 *>(outbuf + TC_PLANE + c8 * TC_SLAB + r * 16);
                                 } else {
                                     rh = xs_h[h];
                                     rl = xs_l[h];
@@ -407,11 +419,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                             split_pair(v[6], v[7], uh.w, ul.w);
                             if (!last_in_seg) {
                                 *reinterpret_cast<uint4 *>(outbuf + c8 * TC_SLAB + r * 16) = uh;
-                                *reinterpret_cast<uint4 *>(outbuf + TC_PLANE + c8 * TC_SLAB + r * 16) = ul;
+                                if (!fast) *reinterpret_cast<uint4 *>(outbuf + TC_PLANE + c8 * TC_SLAB + r * 16) = ul;
                             } else if (store_global) {
                                 uint4 *dst = reinterpret_cast<uint4 *>(p.out_planes) + (size_t)n * 16 * p.L;
                                 dst[(size_t)c8 * p.L + l] = uh;
-                                dst[(size_t)(8 + c8) * p.L + l] = ul;
+                                if (!fast) dst[(size_t)(8 + c8) * p.L + l] = ul;
                             }
                         }
                         if (!last_in_seg) {
@@ -432,7 +444,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                                     const int c8 = 4 * egrp + 2 * h2 + h;
                                     float fh[8], fl[8];
                                     unpack8(*reinterpret_cast<const uint4 *>(pb + c8 * TC_SLAB), fh);
-                                    unpack8(*reinterpret_cast<const uint4 *>(pb + TC_PLANE + c8 * TC_SLAB), fl);
+                                    unpack8(FAST ? make_uint4(0, 0, 0, 0) : *reinterpret_cast<const uint4 *>(pb + TC_PLANE + c8 * TC_SLAB), fl);
 #pragma unroll
                                     for (int i = 0; i < 8; ++i) rs[8 * h + i] = __float_as_uint(fh[i] + TC_LO_INV * fl[i]);
                                 }
@@ -469,7 +481,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 x0_split_kernel(const float *__restrict__ x, const float *__restrict__ e, int N, int L, int P, int scale, int off,
-                const float *__restrict__ w /*[9][64]*/, const float *__restrict__ b, uint4 *__restrict__ planes) {
+                const float *__restrict__ w /*[9][64]*/, const float *__restrict__ b, uint4 *__restrict__ planes, int fast) {
     __shared__ float4 ws[9 * 16];
     __shared__ float4 bs[16];
     for (int i = threadIdx.x; i < 9 * 16; i += 256) ws[i] = reinterpret_cast<const float4 *>(w)[i];
@@ -515,7 +527,7 @@ x0_split_kernel(const float *__restrict__ x, const float *__restrict__ e, int N,
         uh.x = pack_half2(hi[0], hi[1]); uh.y = pack_half2(hi[2], hi[3]); uh.z = pack_half2(hi[4], hi[5]); uh.w = pack_half2(hi[6], hi[7]);
         ul.x = pack_half2(lo[0], lo[1]); ul.y = pack_half2(lo[2], lo[3]); ul.z = pack_half2(lo[4], lo[5]); ul.w = pack_half2(lo[6], lo[7]);
         dst[(size_t)c8 * L] = uh;
-        dst[(size_t)(8 + c8) * L] = ul;
+        if (!fast) dst[(size_t)(8 + c8) * L] = ul;
     }
 }
 
@@ -558,11 +570,12 @@ static int g_timeline_cap = 0;
 void set_chain_timeline(void *dev_buf, int cap) { g_timeline = reinterpret_cast<unsigned long long *>(dev_buf); g_timeline_cap = cap; }
 
 int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void *x0, void *out_planes, float *out_mask,
-                    int N, int L, cudaStream_t st) {
+                    int N, int L, cudaStream_t st, int fast) {
     STOF_REQUIRE(count >= 1 && count <= TC_MAX_LAYERS, STOF_E_INVALID, "chain_tc: %d layers per segment (max %d)", count, TC_MAX_LAYERS);
     static bool attr = false;
     if (!attr) {
-        STOF_CUDA(cudaFuncSetAttribute(chain_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+        STOF_CUDA(cudaFuncSetAttribute(chain_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+        STOF_CUDA(cudaFuncSetAttribute(chain_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
         attr = true;
     }
     TcParams p;
@@ -591,7 +604,9 @@ int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void
     const long long total = (long long)N * p.tiles_per_row;
     STOF_REQUIRE(total < (1ll << 31), STOF_E_INVALID, "chain_tc: too many tiles");
     p.total_tiles = (int)total;
-    p.N = N; p.L = L;
+    p.N = N; p.L = L; p.fast = fast;
+    p.n_stages = fast ? TC_MAX_STAGES : TC_STAGES;
+    p.stage_stride = fast ? TC_STAGE_BYTES / 2 : TC_STAGE_BYTES;
     p.in = in; p.x0 = x0; p.out_planes = out_planes; p.out_mask = out_mask;
     p.timeline = g_timeline; p.timeline_cap = g_timeline_cap;
     // Buffer P (input tile; operand of even layers, output / short-skip source of odd layers) is last touched by layer
@@ -602,21 +617,24 @@ int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void
     // the producer requests the next tile's input after this tap of the last layer (the ring holds that many taps of the
     // last layer while the epilogue of free_layer is still running, so waiting for P there delays no weights)
     p.in_layer = count - 1;
-    p.in_tap = (even && layers[count - 1].taps > TC_STAGES - 1) ? TC_STAGES - 2 : layers[count - 1].taps - 1;
+    // exact mode: the producer asks for the next tile's input after tap STAGES-2 of the last layer (tuned on the timeline);
+    // one-pass mode (deep ring): after the tile's last tap
+    p.in_tap = (!fast && even && layers[count - 1].taps > TC_STAGES - 1) ? TC_STAGES - 2 : layers[count - 1].taps - 1;
     for (int k = 0; k < count; ++k)
         STOF_REQUIRE(layers[k].taps >= 1, STOF_E_INVALID, "chain_tc: layer without taps");
     const bool ends_last = layers[count - 1].type == TC_LAST;
     STOF_REQUIRE(ends_last ? out_mask != nullptr : out_planes != nullptr, STOF_E_INVALID, "chain_tc: missing output buffer");
     const int grid = (int)(total < kSMs ? total : kSMs);
-    chain_tc_kernel<<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(p);
+    if (fast) chain_tc_kernel<true><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(p);
+    else chain_tc_kernel<false><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(p);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }
 
 int launch_x0_split(const float *x, const float *e, int N, int L, int P, int scale, int off, const float *w, const float *b,
-                    void *planes, cudaStream_t st) {
+                    void *planes, cudaStream_t st, int fast) {
     dim3 grid((L + 255) / 256, N);
-    x0_split_kernel<<<grid, 256, 0, st>>>(x, e, N, L, P, scale, off, w, b, reinterpret_cast<uint4 *>(planes));
+    x0_split_kernel<<<grid, 256, 0, st>>>(x, e, N, L, P, scale, off, w, b, reinterpret_cast<uint4 *>(planes), fast);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }

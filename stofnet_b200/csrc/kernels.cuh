@@ -31,6 +31,9 @@ struct TcLayer {
     int n_stack, n_lo;    // N of the stacked [W_hi; W_lo] MMA and of the X_lo * W_hi MMA
     int lo_row, lo_col;   // first weight row of the W_hi block used by the second MMA; its first accumulator column
     int w_rows;           // rows per c8 chunk of a tap
+    int n_fast;           // N of the single X_hi * W_hi MMA of the one-pass fp16 mode (64, or 16 for conv_last)
+    const void *w_fast;   // one-pass mode: W_hi-only taps [tap][c8][w_rows_fast][8]
+    int stage_bytes_fast, w_rows_fast;
 };
 
 struct TcParams {
@@ -45,6 +48,8 @@ struct TcParams {
     int in_layer, in_tap;       // the producer requests the next tile's input after issuing this weight tap
     int tiles_per_row, total_tiles;
     int N, L;
+    int n_stages, stage_stride; // weight ring depth / bytes between stages
+    int fast;                   // 1: one-pass fp16 mode (hi planes only, one MMA per k-step); 0: fp32-faithful hi/lo split
     const void *in;             // split planes [N][2][8][L][8] fp16
     const void *x0;             // split planes of the long-skip tensor (TC_LONGSKIP), or NULL
     void *out_planes;           // segment output (split planes) unless the segment ends with TC_LAST
@@ -56,13 +61,13 @@ void set_chain_timeline(void *dev_buf, int cap);
 
 // layers[first .. first+count) of the spec list; returns STOF_E_* on error
 int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void *x0, void *out_planes, float *out_mask,
-                    int N, int L, cudaStream_t st);
+                    int N, int L, cudaStream_t st, int fast = 0);
 // x (N, L) fp32 -> split planes of x0 = act(conv_first(x)) [+ nearest-upsampled E, centred]  (models/stofnet.py:45,96-115)
 int launch_x0_split(const float *x, const float *e, int N, int L, int P, int scale, int off, const float *w, const float *b,
-                    void *planes, cudaStream_t st);
+                    void *planes, cudaStream_t st, int fast = 0);
 // contract_tc.cu: pooled = maxpool80(LeakyReLU(contract_conv(relu(conv1 x)))) on tcgen05, conv1 recomputed per tile
 int launch_contract_pool_tc(const float *x, const void *w, const float *bias, const float *w1, const float *b1, float *pooled,
-                            int N, int L, int P, cudaStream_t st);
+                            int N, int L, int P, cudaStream_t st, int fast = 0);
 // fp32 C4L4 activations <-> split planes (debug / hand-over between the SIMT and tensor paths)
 int launch_c4l4_to_planes(const float *act, void *planes, int N, int L, cudaStream_t st);
 int launch_planes_to_c4l4(const void *planes, float *act, int N, int L, cudaStream_t st);

@@ -86,6 +86,24 @@ static int upload_tc(stof_model *m, const stof_weights *w) {
             }
     if (!m->tc_w) STOF_CUDA(cudaMalloc(&m->tc_w, buf.size() * sizeof(__half)));
     STOF_CUDA(cudaMemcpy(m->tc_w, buf.data(), buf.size() * sizeof(__half), cudaMemcpyHostToDevice));
+    // one-pass fp16 mode: W_hi only, [tap][c8][64][8] (8 KB per k7 tap); conv_last keeps its 16-row tap (rows 0-3 = W_hi)
+    const size_t mid_tap_f = 8 * 64 * 8, last_tap_f = 8 * 16 * 8;
+    std::vector<__half> bf((size_t)n_mid * 7 * mid_tap_f + 3 * last_tap_f, __float2half_rn(0.0f));
+    for (int j = 0; j < n_mid; ++j)
+        for (int t = 0; t < 7; ++t) {
+            __half *tap = bf.data() + ((size_t)j * 7 + t) * mid_tap_f;
+            for (int co = 0; co < 64; ++co)
+                for (int ci = 0; ci < 64; ++ci)
+                    tap[((size_t)(ci >> 3) * 64 + co) * 8 + (ci & 7)] = __float2half_rn(w->mid_w[j][((size_t)co * 64 + ci) * 7 + t]);
+        }
+    for (int t = 0; t < 3; ++t)
+        for (int u = 0; u < 4; ++u)
+            for (int ci = 0; ci < 64; ++ci)
+                bf[(size_t)n_mid * 7 * mid_tap_f + (size_t)t * last_tap_f + ((size_t)(ci >> 3) * 16 + u) * 8 + (ci & 7)] =
+                    __float2half_rn(w->last_w[((size_t)u * 64 + ci) * 3 + t]);
+    if (!m->tc_w_fast) STOF_CUDA(cudaMalloc(&m->tc_w_fast, bf.size() * sizeof(__half)));
+    STOF_CUDA(cudaMemcpy(m->tc_w_fast, bf.data(), bf.size() * sizeof(__half), cudaMemcpyHostToDevice));
+    const __half *fbase = reinterpret_cast<const __half *>(m->tc_w_fast);
     const __half *base = reinterpret_cast<const __half *>(m->tc_w);
     for (int j = 0; j < n_mid; ++j) {
         TcLayer &l = m->tc_layer[j];
@@ -94,13 +112,15 @@ static int upload_tc(stof_model *m, const stof_weights *w) {
         l.taps = 7; l.pad = 3;
         // models/stofnet.py:51-62: conv index i = j + 2; even i -> LeakyReLU, odd i -> res + conv, last -> res1 + conv
         l.type = (j == n_mid - 1) ? TC_LONGSKIP : ((j & 1) ? TC_RES : TC_LEAKY);
-        l.stage_bytes = 16384; l.n_out = 64; l.n_stack = 128; l.n_lo = 64; l.lo_row = 0; l.lo_col = 64; l.w_rows = 128;
+        l.stage_bytes = 16384; l.n_out = 64; l.n_stack = 128; l.n_lo = 64; l.lo_row = 0; l.lo_col = 64; l.w_rows = 128; l.n_fast = 64;
+        l.w_fast = fbase + (size_t)j * 7 * mid_tap_f; l.stage_bytes_fast = 8192; l.w_rows_fast = 64;
     }
     TcLayer &l = m->tc_layer[n_mid];
     l.w = base + (size_t)n_mid * 7 * mid_tap;
     l.bias = m->last.b;
     l.taps = 3; l.pad = 1; l.type = TC_LAST;
-    l.stage_bytes = 4096; l.n_out = 4; l.n_stack = 16; l.n_lo = 16; l.lo_row = 16; l.lo_col = 8; l.w_rows = 32;
+    l.stage_bytes = 4096; l.n_out = 4; l.n_stack = 16; l.n_lo = 16; l.lo_row = 16; l.lo_col = 8; l.w_rows = 32; l.n_fast = 16;
+    l.w_fast = fbase + (size_t)n_mid * 7 * mid_tap_f; l.stage_bytes_fast = 2048; l.w_rows_fast = 16;
     m->n_tc = n_mid + 1;
     return STOF_OK;
 }
@@ -285,17 +305,18 @@ static int forward_chunk_tc(stof_model *m, const float *x, int n, int L, float *
                             float *pooled, float *e, const Plan &pl, cudaStream_t st) {
     int rc;
     const bool sgb = m->sgb_scale != 1;
+    const int fast = (m->path == STOF_PATH_TC_FP16) ? 1 : 0;
     int off = 0;
     if (sgb) {
         // models/stofnet.py:45,98-107: E = LeakyReLU(expand(maxpool80(LeakyReLU(contract(relu(conv1 x))))))
         { ProfScope p(m, STOF_PROF_CONTRACT, st);
-          if ((rc = launch_contract_pool_tc(x, m->tc_contract_w, m->contract.b, m->first.w, m->first.b, pooled, n, L, pl.P, st))) return rc; }
+          if ((rc = launch_contract_pool_tc(x, m->tc_contract_w, m->contract.b, m->first.w, m->first.b, pooled, n, L, pl.P, st, fast))) return rc; }
         { ProfScope p(m, STOF_PROF_EXPAND, st); if ((rc = launch_expand(pooled, e, m->expand.w, m->expand.b, n, pl.P, st))) return rc; }
         off = (L - pl.P * m->sgb_scale) / 2;
     }
     // x0 = relu(conv1 x) + upsample(E) as split planes (:45,108-115); also the long skip res1 (:51,62)
     { ProfScope p(m, STOF_PROF_SGB_ADD, st);
-      if ((rc = launch_x0_split(x, sgb ? e : nullptr, n, L, pl.P, m->sgb_scale, off, m->first.w, m->first.b, B1, st))) return rc; }
+      if ((rc = launch_x0_split(x, sgb ? e : nullptr, n, L, pl.P, m->sgb_scale, off, m->first.w, m->first.b, B1, st, fast))) return rc; }
     const void *cur = B1;
     void *pp[2] = {B2, B0};
     int which = 0;
@@ -306,7 +327,7 @@ static int forward_chunk_tc(stof_model *m, const float *x, int n, int L, float *
         if (j + cnt < m->n_tc && m->tc_layer[j + cnt].type == TC_RES) cnt = (cnt > 1) ? cnt - 1 : cnt + 1;
         const bool ends = (j + cnt == m->n_tc);
         ProfScope p(m, ends ? STOF_PROF_LAST : STOF_PROF_MID, st);
-        if ((rc = launch_chain_tc(m->tc_layer + j, cnt, cur, B1, ends ? nullptr : pp[which], ends ? mask : nullptr, n, L, st))) return rc;
+        if ((rc = launch_chain_tc(m->tc_layer + j, cnt, cur, B1, ends ? nullptr : pp[which], ends ? mask : nullptr, n, L, st, fast))) return rc;
         cur = pp[which];
         which ^= 1;
         j += cnt;
@@ -329,7 +350,7 @@ static int forward_chunk(stof_model *m, const float *x, int n, int L, float *mas
         ProfScope p(m, STOF_PROF_LAST, st);
         return launch_conv_last(B1, mask, m->last.w, m->last.b, n, L, 32, 1, st);
     }
-    if (m->path == STOF_PATH_TC) return forward_chunk_tc(m, x, n, L, mask, B0, B1, B2, pooled, e, pl, st);
+    if (m->path != STOF_PATH_SIMT) return forward_chunk_tc(m, x, n, L, mask, B0, B1, B2, pooled, e, pl, st);
     // models/stofnet.py:45
     { ProfScope p(m, STOF_PROF_FIRST, st); if ((rc = launch_conv_first(x, n, L, m->first.w, m->first.b, B0, 9, 0, st))) return rc; }
     // :48 semi-global block
@@ -417,6 +438,7 @@ extern "C" void stof_model_destroy(stof_model *m) {
     if (m->raw_contract_w) cudaFree(m->raw_contract_w);
     if (m->raw_expand_w) cudaFree(m->raw_expand_w);
     if (m->tc_w) cudaFree(m->tc_w);
+    if (m->tc_w_fast) cudaFree(m->tc_w_fast);
     if (m->tc_contract_w) cudaFree(m->tc_contract_w);
     if (m->h_stats) cudaFreeHost(m->h_stats);
     for (cudaEvent_t e : m->ev_pool) cudaEventDestroy(e);
@@ -540,7 +562,8 @@ extern "C" int stof_profile_collect(stof_model *m, double *ms_by_class, int64_t 
 
 extern "C" int stof_model_set_path(stof_model *m, int path, int layers_per_launch) {
     STOF_REQUIRE(m != nullptr, STOF_E_INVALID, "stof_model_set_path: model is NULL");
-    STOF_REQUIRE(path == STOF_PATH_SIMT || path == STOF_PATH_TC, STOF_E_INVALID, "stof_model_set_path: path %d", path);
+    STOF_REQUIRE(path == STOF_PATH_SIMT || path == STOF_PATH_TC || path == STOF_PATH_TC_FP16, STOF_E_INVALID,
+                 "stof_model_set_path: path %d", path);
     STOF_REQUIRE(path == STOF_PATH_SIMT || m->kind == STOF_KIND_STOFNET, STOF_E_UNSUPPORTED,
                  "stof_model_set_path: the tensor-core path covers StofNet only");
     if (layers_per_launch > 0) {
@@ -560,7 +583,8 @@ extern "C" int stof_chain_segment(stof_model *m, int first, int count, const voi
     STOF_REQUIRE(in_planes_dev && out_dev && N > 0 && L > 0, STOF_E_INVALID, "stof_chain_segment: bad arguments");
     const bool ends = m->tc_layer[first + count - 1].type == stof::TC_LAST;
     return stof::launch_chain_tc(m->tc_layer + first, count, in_planes_dev, x0_planes_dev, ends ? nullptr : out_dev,
-                                 ends ? reinterpret_cast<float *>(out_dev) : nullptr, N, L, (cudaStream_t)stream);
+                                 ends ? reinterpret_cast<float *>(out_dev) : nullptr, N, L, (cudaStream_t)stream,
+                                 m->path == STOF_PATH_TC_FP16 ? 1 : 0);
 }
 
 extern "C" int stof_debug_set_timeline(void *dev_buf, int capacity_events) {

@@ -91,6 +91,17 @@ class StofNet(nn.Module):
             return _StofNetFunction.apply(self, tuple(k for k, _ in named), x, *[p for _, p in named])
         return self._engine.forward(self, x)
 
+    def set_precision(self, precision="fp32"):
+        """Arithmetic of the conv stack (inference): "fp32" (default) = fp32-faithful hi/lo split on the tensor cores,
+        index-exact against the reference; "fp16" = ONE tensor-core pass on fp16-rounded operands with fp32 accumulation
+        (about a third of the tensor work; detections agree with the exact mode only to the tolerance stated in
+        DESIGN.md); "simt" = plain fp32 FFMA kernels (cross-check path)."""
+        path = {"fp32": _lib.PATH_TC, "fp16": _lib.PATH_TC_FP16, "simt": _lib.PATH_SIMT}.get(precision)
+        if path is None:
+            raise ValueError("stofnet_b200: precision must be 'fp32', 'fp16' or 'simt', got %r" % (precision,))
+        self._engine.set_path(path)
+        return self
+
     def infer_host(self, x_host, window_size=20, threshold=None, cap=64, want_mask=False):
         """Eval step of main.py:307-320 on host tensors in one C-ABI call (stof_infer_host)."""
         return self._engine.infer_host(self, x_host, window_size, threshold, cap, want_mask)

@@ -133,3 +133,25 @@ def test_forward_tc_matches_simt(sb, dev, golden, name, seg):
     torch.cuda.synchronize()
     err = (a - b).abs().max().item() / a.abs().max().item()
     assert err <= REL_TOL, (name, seg, err)
+
+
+def test_fp16_one_pass_mode_tolerance(sb, dev, golden):
+    """STOF_PATH_TC_FP16: one tensor-core pass on fp16-rounded operands.  Not index-exact by design; stated tolerance
+    (DESIGN.md): mask error <= 2e-2 of the mask range (rms <= 5e-4), >= 97 % of the exact mode's detections reproduced
+    at the identical mask sample, and the exact mode is restored by set_precision('fp32')."""
+    from stofnet_b200.synth import synth_waveforms
+    for name, rf, th in (("different-armadillo", 10, 0.5), ("graceful-snow", 20, 0.015)):
+        sd = {k: torch.from_numpy(v) for k, v in golden("weights_%s.npz" % name).items()}
+        model = sb.build_model(sd, dev)
+        x = torch.from_numpy(synth_waveforms(96, 256 * rf, seed=5, rf=rf)).unsqueeze(1).to(dev)
+        with torch.no_grad():
+            ref = model(x)
+            fast = model.set_precision("fp16")(x)
+            back = model.set_precision("fp32")(x)
+        assert torch.equal(ref, back)
+        rng_ = float(ref.abs().max())
+        assert float((fast - ref).abs().max()) <= 2e-2 * rng_
+        assert float((fast - ref).pow(2).mean().sqrt()) <= 5e-4 * rng_
+        a = set(map(tuple, sb.get_maxima_positions(ref, 20, th).cpu().numpy()))
+        b = set(map(tuple, sb.get_maxima_positions(fast, 20, th).cpu().numpy()))
+        assert len(a & b) >= 0.97 * len(a) and len(a & b) >= 0.97 * len(b), (name, len(a), len(b), len(a & b))
