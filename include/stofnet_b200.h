@@ -35,11 +35,12 @@ extern "C" {
 #define STOF_E_NCCL       -6   /* reserved: collective error */
 #define STOF_E_UNSUPPORTED -7  /* architecture of the checkpoint not supported by the kernels */
 
-#define STOF_MAX_MID_CONVS 16
+#define STOF_MAX_MID_CONVS 24
 
 /* Model kinds */
 #define STOF_KIND_STOFNET 0    /* models/stofnet.py  */
 #define STOF_KIND_ESPCN   1    /* models/espcn_1d.py */
+#define STOF_KIND_EDSR    2    /* models/edsr_1d.py  */
 
 /* Host-side description of a checkpoint: fp32 tensors in PyTorch's (Cout, Cin, K) layout exactly
  * as stored in the reference's .pth state_dict (main.py:174-177).  Pointers are host memory and
@@ -59,7 +60,10 @@ typedef struct stof_weights {
     int k_first, k_mid, k_last;                     /* 9, 7, 3 */
     int sgb_scale, sgb_feat, sgb_k;                 /* 80, 512, 5 ; sgb_scale = 1 when no semi-global block (:27) */
     /* ESPCN_1D (models/espcn_1d.py:12-14): conv1 (64,1,5) -> conv1_w/b, conv2 (32,64,3) -> mid_w[0]/mid_b[0],
-     * conv3 (r,32,3) -> last_w/b */
+     * conv3 (r,32,3) -> last_w/b
+     * EDSR_1D (models/edsr_1d.py:22-30): conv_input (64,1,3) -> conv1_w/b; residual_blocks[i].conv1 / .conv2 (64,64,3) ->
+     * mid_w[2i] / mid_w[2i+1]; conv_mid -> mid_w[2*num_blocks]; conv_output (1,16,3) -> last_w/b; n_mid = 2*num_blocks+1,
+     * k_first = k_mid = k_last = 3 */
 } stof_weights;
 
 typedef struct stof_model stof_model;   /* opaque: device-resident repacked weights */

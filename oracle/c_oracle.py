@@ -113,6 +113,26 @@ def conv1d(x, w, b, pad, acc64=True):
     return y
 
 
+def edsr_forward(sd, x, acc64=True):
+    """EDSR_1D.forward (models/edsr_1d.py:14-19,32-45) composed from the C conv1d / shuffle primitives, row by row."""
+    x = _f32(x)
+    k = {n: _f32(v) for n, v in sd.items()}
+    nb = 1 + max(int(n.split(".")[1]) for n in k if n.startswith("residual_blocks."))
+    r = k["conv_input.weight"].shape[0] // k["conv_output.weight"].shape[1]
+    rows = []
+    for row in x:
+        out = np.maximum(conv1d(row[None, :], k["conv_input.weight"], k["conv_input.bias"], 1, acc64), 0)
+        residual = out
+        for i in range(nb):
+            p = "residual_blocks.%d." % i
+            t = np.maximum(conv1d(out, k[p + "conv1.weight"], k[p + "conv1.bias"], 1, acc64), 0)
+            out = conv1d(t, k[p + "conv2.weight"], k[p + "conv2.bias"], 1, acc64) + out
+        out = conv1d(out, k["conv_mid.weight"], k["conv_mid.bias"], 1, acc64) + residual
+        s = sample_shuffle(out[None], r)[0]
+        rows.append(conv1d(s, k["conv_output.weight"], k["conv_output.bias"], 1, acc64)[0])
+    return np.stack(rows)
+
+
 def _th(threshold):
     none = (threshold is None) or (not threshold)     # "if threshold:" (mask2samples.py:16)
     return int(none), C.c_float(0.0 if none else float(threshold))

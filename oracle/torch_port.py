@@ -68,6 +68,21 @@ def espcn_forward(sd, x):
     return torch.sigmoid(sample_shuffle(F.conv1d(x, sd["conv3.weight"], sd["conv3.bias"], padding=1), r))
 
 
+def edsr_forward(sd, x):
+    """models/edsr_1d.py:14-19,32-45."""
+    out = F.relu(F.conv1d(x, sd["conv_input.weight"], sd["conv_input.bias"], padding=1))
+    residual = out
+    nb = 1 + max(int(k.split(".")[1]) for k in sd if k.startswith("residual_blocks."))
+    for i in range(nb):
+        p = "residual_blocks.%d." % i
+        t = F.relu(F.conv1d(out, sd[p + "conv1.weight"], sd[p + "conv1.bias"], padding=1))
+        out = F.conv1d(t, sd[p + "conv2.weight"], sd[p + "conv2.bias"], padding=1) + out
+    out = F.conv1d(out, sd["conv_mid.weight"], sd["conv_mid.bias"], padding=1) + residual
+    r = sd["conv_input.weight"].shape[0] // sd["conv_output.weight"].shape[1]
+    out = sample_shuffle(out, r)
+    return F.conv1d(out, sd["conv_output.weight"], sd["conv_output.bias"], padding=1)
+
+
 def get_maxima_positions(scores, window_size, threshold=None):
     """utils/mask2samples.py:5-34."""
     s = scores.clone().detach()

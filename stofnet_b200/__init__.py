@@ -7,6 +7,7 @@ CUDA kernels reached through the C ABI of ``libstofnet_b200.so`` (include/stofne
 """
 from .models.stofnet import StofNet, SemiGlobalBlock          # noqa: F401
 from .models.espcn_1d import ESPCN_1D                          # noqa: F401
+from .models.edsr_1d import EDSR_1D                            # noqa: F401
 from .utils.sample_shuffle import SampleShuffle1D              # noqa: F401
 from .utils.mask2samples import (mask2coords, get_maxima_positions, nms_1d, thresholding,  # noqa: F401
                                  coords2mask)

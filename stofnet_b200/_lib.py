@@ -9,8 +9,8 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libstofnet_b200.so")
 
-MAX_MID = 16
-KIND_STOFNET, KIND_ESPCN = 0, 1
+MAX_MID = 24
+KIND_STOFNET, KIND_ESPCN, KIND_EDSR = 0, 1, 2
 PATH_SIMT, PATH_TC, PATH_TC_FP16 = 0, 1, 2
 
 E_INVALID, E_LENGTH, E_LENGTH_ODD, E_WORKSPACE, E_CUDA, E_NCCL, E_UNSUPPORTED = -1, -2, -3, -4, -5, -6, -7

@@ -38,6 +38,7 @@ def build_model(sd, device=None):
     """state_dict -> (model in eval mode with the weights loaded strictly)."""
     from .models.stofnet import StofNet
     from .models.espcn_1d import ESPCN_1D
+    from .models.edsr_1d import EDSR_1D
     keys = set(sd)
     if "conv_last.weight" in keys:
         nb = 2 + sum(1 for k in keys if re.fullmatch(r"conv\d+\.weight", k) and k != "conv1.weight")
@@ -51,6 +52,11 @@ def build_model(sd, device=None):
                         semi_global_scale=scale)
     elif {"conv1.weight", "conv2.weight", "conv3.weight"} <= keys and len(keys) == 6:
         model = ESPCN_1D(sd["conv3.weight"].shape[0])
+    elif "conv_input.weight" in keys and "conv_output.weight" in keys:
+        nb = 1 + max(int(k.split(".")[1]) for k in keys if k.startswith("residual_blocks."))
+        f = sd["conv_input.weight"].shape[0]
+        model = EDSR_1D(num_channels=sd["conv_input.weight"].shape[1], num_features=f, num_blocks=nb,
+                        upscale_factor=f // sd["conv_output.weight"].shape[1])
     else:
         raise ValueError("Model not recognized")          # main.py:167
     model.load_state_dict(sd, strict=True)

@@ -384,6 +384,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                             if (type == TC_LEAKY) {
 #pragma unroll
                                 for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], kLeakySlope * v[i]);
+                            } else if (type == TC_RELU) {
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.0f);
                             } else if (from_stash) {
                                 // short skip of the segment's last layer: fp32 copy parked in TMEM by the previous layer's epilogue
                                 uint32_t rs[8];
@@ -477,24 +480,25 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
 // ------------------------------------------------------------------------------------------------
 // x0 = act(conv_first(x)) [+ E upsampled x scale, centred, zero outside]  ->  split planes.
 // conv1 (1 -> 64, k9) has K = 9: CUDA-core FMAs, HBM-bound (4 B in, 256 B out per position).
-// (models/stofnet.py:23,45 and :96,108-115)
+// (models/stofnet.py:23,45 and :96,108-115; K = 3 without E is EDSR_1D's relu(conv_input(x)), models/edsr_1d.py:33)
 // ------------------------------------------------------------------------------------------------
+template <int K>
 __global__ void __launch_bounds__(256)
 x0_split_kernel(const float *__restrict__ x, const float *__restrict__ e, int N, int L, int P, int scale, int off,
-                const float *__restrict__ w /*[9][64]*/, const float *__restrict__ b, uint4 *__restrict__ planes, int fast) {
-    __shared__ float4 ws[9 * 16];
+                const float *__restrict__ w /*[K][64]*/, const float *__restrict__ b, uint4 *__restrict__ planes, int fast) {
+    __shared__ float4 ws[K * 16];
     __shared__ float4 bs[16];
-    for (int i = threadIdx.x; i < 9 * 16; i += 256) ws[i] = reinterpret_cast<const float4 *>(w)[i];
+    for (int i = threadIdx.x; i < K * 16; i += 256) ws[i] = reinterpret_cast<const float4 *>(w)[i];
     if (threadIdx.x < 16) bs[threadIdx.x] = reinterpret_cast<const float4 *>(b)[threadIdx.x];
     __syncthreads();
     const int n = blockIdx.y;
     const int l = blockIdx.x * 256 + threadIdx.x;
     if (l >= L) return;
     const float *xr = x + (size_t)n * L;
-    float xv[9];
+    float xv[K];
 #pragma unroll
-    for (int t = 0; t < 9; ++t) {
-        const int g = l + t - 4;
+    for (int t = 0; t < K; ++t) {
+        const int g = l + t - K / 2;
         xv[t] = (g >= 0 && g < L) ? __ldg(xr + g) : 0.0f;
     }
     const int j = l - off;
@@ -508,7 +512,7 @@ x0_split_kernel(const float *__restrict__ x, const float *__restrict__ e, int N,
         for (int h = 0; h < 2; ++h) {
             float4 a = bs[2 * c8 + h];
 #pragma unroll
-            for (int t = 0; t < 9; ++t) {
+            for (int t = 0; t < K; ++t) {
                 const float4 wv = ws[t * 16 + 2 * c8 + h];
                 a.x = fmaf(wv.x, xv[t], a.x); a.y = fmaf(wv.y, xv[t], a.y);
                 a.z = fmaf(wv.z, xv[t], a.z); a.w = fmaf(wv.w, xv[t], a.w);
@@ -632,9 +636,11 @@ int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void
 }
 
 int launch_x0_split(const float *x, const float *e, int N, int L, int P, int scale, int off, const float *w, const float *b,
-                    void *planes, cudaStream_t st, int fast) {
+                    void *planes, cudaStream_t st, int fast, int K) {
     dim3 grid((L + 255) / 256, N);
-    x0_split_kernel<<<grid, 256, 0, st>>>(x, e, N, L, P, scale, off, w, b, reinterpret_cast<uint4 *>(planes), fast);
+    STOF_REQUIRE(K == 9 || K == 3, STOF_E_UNSUPPORTED, "x0_split: first conv kernel size %d (built for 9 and 3)", K);
+    if (K == 9) x0_split_kernel<9><<<grid, 256, 0, st>>>(x, e, N, L, P, scale, off, w, b, reinterpret_cast<uint4 *>(planes), fast);
+    else x0_split_kernel<3><<<grid, 256, 0, st>>>(x, e, N, L, P, scale, off, w, b, reinterpret_cast<uint4 *>(planes), fast);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }

@@ -20,7 +20,7 @@ int launch_espcn_conv2(const float *in, float *out, const float *w, const float 
 
 // conv_tc.cu (tcgen05 / TMEM path) ---------------------------------------------------------------
 constexpr int TC_MAX_LAYERS = 6;
-enum TcLayerType { TC_LEAKY = 0, TC_RES = 1, TC_LONGSKIP = 2, TC_LAST = 3 };
+enum TcLayerType { TC_LEAKY = 0, TC_RES = 1, TC_LONGSKIP = 2, TC_LAST = 3, TC_RELU = 4 };
 
 struct TcLayer {
     const void *w;        // packed fp16 taps: [tap][c8][w_rows][8]
@@ -64,7 +64,7 @@ int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void
                     int N, int L, cudaStream_t st, int fast = 0);
 // x (N, L) fp32 -> split planes of x0 = act(conv_first(x)) [+ nearest-upsampled E, centred]  (models/stofnet.py:45,96-115)
 int launch_x0_split(const float *x, const float *e, int N, int L, int P, int scale, int off, const float *w, const float *b,
-                    void *planes, cudaStream_t st, int fast = 0);
+                    void *planes, cudaStream_t st, int fast = 0, int K = 9);
 // contract_tc.cu: pooled = maxpool80(LeakyReLU(contract_conv(relu(conv1 x)))) on tcgen05, conv1 recomputed per tile
 int launch_contract_pool_tc(const float *x, const void *w, const float *bias, const float *w1, const float *b1, float *pooled,
                             int N, int L, int P, cudaStream_t st, int fast = 0);

@@ -58,27 +58,44 @@ static void split_w(float w, __half &hi, __half &lo) {
     lo = __float2half_rn((w - __half2float(hi)) * 2048.0f);
 }
 
-static int upload_tc(stof_model *m, const stof_weights *w) {
+// EDSR_1D's tail (models/edsr_1d.py:43-44): SampleShuffle1D(4) of the 64-channel tensor Y, then conv_output (16 -> 1, k3,
+// pad 1) on the 4x longer signal S[c][4 w + u] = Y[16 u + c][w].  Output sample 4 l + u reads S at 4 l + u + t - 1
+// (t = 0..2), i.e. Y channel 16 ((u + t - 1) mod 4) + c at position l + floor((u + t - 1) / 4): a (4, 64, 3) conv on Y
+// followed by the same shuffle store as StofNet's conv_last - which is what the chain kernel's TC_LAST layer computes.
+static std::vector<float> edsr_tail_weights(const float *wo /*(1,16,3)*/) {
+    std::vector<float> e((size_t)4 * 64 * 3, 0.0f);
+    for (int u = 0; u < 4; ++u)
+        for (int t = 0; t < 3; ++t) {
+            const int q = u + t - 1;
+            const int dw = (q < 0) ? -1 : (q > 3 ? 1 : 0), up = (q + 4) % 4;
+            for (int c = 0; c < 16; ++c) e[((size_t)u * 64 + 16 * up + c) * 3 + (dw + 1)] = wo[c * 3 + t];
+        }
+    return e;
+}
+
+static int upload_tc(stof_model *m, const stof_weights *w, const float *last_w /*(4,64,3)*/) {
     const int n_mid = w->n_mid;
+    const int KM = w->k_mid;                                             // taps of the 64 -> 64 convs (7, or 3 for EDSR_1D)
+    const bool edsr = w->kind == STOF_KIND_EDSR;
     const size_t mid_tap = 8 * 128 * 8, last_tap = 8 * 32 * 8;          // halves per tap
-    std::vector<__half> buf((size_t)n_mid * 7 * mid_tap + 3 * last_tap, __float2half_rn(0.0f));
+    std::vector<__half> buf((size_t)n_mid * KM * mid_tap + 3 * last_tap, __float2half_rn(0.0f));
     for (int j = 0; j < n_mid; ++j)
-        for (int t = 0; t < 7; ++t) {
-            __half *tap = buf.data() + ((size_t)j * 7 + t) * mid_tap;
+        for (int t = 0; t < KM; ++t) {
+            __half *tap = buf.data() + ((size_t)j * KM + t) * mid_tap;
             for (int co = 0; co < 64; ++co)
                 for (int ci = 0; ci < 64; ++ci) {
                     __half hi, lo;
-                    split_w(w->mid_w[j][((size_t)co * 64 + ci) * 7 + t], hi, lo);
+                    split_w(w->mid_w[j][((size_t)co * 64 + ci) * KM + t], hi, lo);
                     tap[((size_t)(ci >> 3) * 128 + co) * 8 + (ci & 7)] = hi;
                     tap[((size_t)(ci >> 3) * 128 + 64 + co) * 8 + (ci & 7)] = lo;
                 }
         }
-    __half *lastp = buf.data() + (size_t)n_mid * 7 * mid_tap;
+    __half *lastp = buf.data() + (size_t)n_mid * KM * mid_tap;
     for (int t = 0; t < 3; ++t)
         for (int u = 0; u < 4; ++u)
             for (int ci = 0; ci < 64; ++ci) {
                 __half hi, lo;
-                split_w(w->last_w[((size_t)u * 64 + ci) * 3 + t], hi, lo);
+                split_w(last_w[((size_t)u * 64 + ci) * 3 + t], hi, lo);
                 __half *tap = lastp + (size_t)t * last_tap;
                 tap[((size_t)(ci >> 3) * 32 + u) * 8 + (ci & 7)] = hi;          // rows 0-3   : W_hi   (first MMA, D0)
                 tap[((size_t)(ci >> 3) * 32 + 8 + u) * 8 + (ci & 7)] = lo;      // rows 8-11  : W_lo   (first MMA, D1)
@@ -88,39 +105,40 @@ static int upload_tc(stof_model *m, const stof_weights *w) {
     STOF_CUDA(cudaMemcpy(m->tc_w, buf.data(), buf.size() * sizeof(__half), cudaMemcpyHostToDevice));
     // one-pass fp16 mode: W_hi only, [tap][c8][64][8] (8 KB per k7 tap); conv_last keeps its 16-row tap (rows 0-3 = W_hi)
     const size_t mid_tap_f = 8 * 64 * 8, last_tap_f = 8 * 16 * 8;
-    std::vector<__half> bf((size_t)n_mid * 7 * mid_tap_f + 3 * last_tap_f, __float2half_rn(0.0f));
+    std::vector<__half> bf((size_t)n_mid * KM * mid_tap_f + 3 * last_tap_f, __float2half_rn(0.0f));
     for (int j = 0; j < n_mid; ++j)
-        for (int t = 0; t < 7; ++t) {
-            __half *tap = bf.data() + ((size_t)j * 7 + t) * mid_tap_f;
+        for (int t = 0; t < KM; ++t) {
+            __half *tap = bf.data() + ((size_t)j * KM + t) * mid_tap_f;
             for (int co = 0; co < 64; ++co)
                 for (int ci = 0; ci < 64; ++ci)
-                    tap[((size_t)(ci >> 3) * 64 + co) * 8 + (ci & 7)] = __float2half_rn(w->mid_w[j][((size_t)co * 64 + ci) * 7 + t]);
+                    tap[((size_t)(ci >> 3) * 64 + co) * 8 + (ci & 7)] = __float2half_rn(w->mid_w[j][((size_t)co * 64 + ci) * KM + t]);
         }
     for (int t = 0; t < 3; ++t)
         for (int u = 0; u < 4; ++u)
             for (int ci = 0; ci < 64; ++ci)
-                bf[(size_t)n_mid * 7 * mid_tap_f + (size_t)t * last_tap_f + ((size_t)(ci >> 3) * 16 + u) * 8 + (ci & 7)] =
-                    __float2half_rn(w->last_w[((size_t)u * 64 + ci) * 3 + t]);
+                bf[(size_t)n_mid * KM * mid_tap_f + (size_t)t * last_tap_f + ((size_t)(ci >> 3) * 16 + u) * 8 + (ci & 7)] =
+                    __float2half_rn(last_w[((size_t)u * 64 + ci) * 3 + t]);
     if (!m->tc_w_fast) STOF_CUDA(cudaMalloc(&m->tc_w_fast, bf.size() * sizeof(__half)));
     STOF_CUDA(cudaMemcpy(m->tc_w_fast, bf.data(), bf.size() * sizeof(__half), cudaMemcpyHostToDevice));
     const __half *fbase = reinterpret_cast<const __half *>(m->tc_w_fast);
     const __half *base = reinterpret_cast<const __half *>(m->tc_w);
     for (int j = 0; j < n_mid; ++j) {
         TcLayer &l = m->tc_layer[j];
-        l.w = base + (size_t)j * 7 * mid_tap;
+        l.w = base + (size_t)j * KM * mid_tap;
         l.bias = m->mid[j].b;
-        l.taps = 7; l.pad = 3;
+        l.taps = KM; l.pad = KM / 2;
         // models/stofnet.py:51-62: conv index i = j + 2; even i -> LeakyReLU, odd i -> res + conv, last -> res1 + conv
-        l.type = (j == n_mid - 1) ? TC_LONGSKIP : ((j & 1) ? TC_RES : TC_LEAKY);
+        // models/edsr_1d.py:14-19,36-40: blocks of relu(conv1) -> conv2 + block input; conv_mid + first activation
+        l.type = (j == n_mid - 1) ? TC_LONGSKIP : ((j & 1) ? TC_RES : (edsr ? TC_RELU : TC_LEAKY));
         l.stage_bytes = 16384; l.n_out = 64; l.n_stack = 128; l.n_lo = 64; l.lo_row = 0; l.lo_col = 64; l.w_rows = 128; l.n_fast = 64;
-        l.w_fast = fbase + (size_t)j * 7 * mid_tap_f; l.stage_bytes_fast = 8192; l.w_rows_fast = 64;
+        l.w_fast = fbase + (size_t)j * KM * mid_tap_f; l.stage_bytes_fast = 8192; l.w_rows_fast = 64;
     }
     TcLayer &l = m->tc_layer[n_mid];
-    l.w = base + (size_t)n_mid * 7 * mid_tap;
+    l.w = base + (size_t)n_mid * KM * mid_tap;
     l.bias = m->last.b;
     l.taps = 3; l.pad = 1; l.type = TC_LAST;
     l.stage_bytes = 4096; l.n_out = 4; l.n_stack = 16; l.n_lo = 16; l.lo_row = 16; l.lo_col = 8; l.w_rows = 32; l.n_fast = 16;
-    l.w_fast = fbase + (size_t)n_mid * 7 * mid_tap_f; l.stage_bytes_fast = 2048; l.w_rows_fast = 16;
+    l.w_fast = fbase + (size_t)n_mid * KM * mid_tap_f; l.stage_bytes_fast = 2048; l.w_rows_fast = 16;
     m->n_tc = n_mid + 1;
     return STOF_OK;
 }
@@ -175,6 +193,14 @@ static int validate(const stof_weights *w) {
     } else if (w->kind == STOF_KIND_ESPCN) {
         STOF_REQUIRE(w->upsample_factor == 4 && w->mid_w[0] && w->mid_b[0], STOF_E_UNSUPPORTED,
                      "ESPCN_1D kernels are built for upscale_factor=4");
+    } else if (w->kind == STOF_KIND_EDSR) {
+        STOF_REQUIRE(w->num_features == 64 && w->upsample_factor == 4 && w->k_first == 3 && w->k_mid == 3 && w->k_last == 3,
+                     STOF_E_UNSUPPORTED, "EDSR_1D kernels are built for 64 features, upscale_factor=4, k=3 (got F=%d r=%d k=%d,%d,%d)",
+                     w->num_features, w->upsample_factor, w->k_first, w->k_mid, w->k_last);
+        STOF_REQUIRE(w->n_mid >= 3 && w->n_mid <= STOF_MAX_MID_CONVS && (w->n_mid % 2) == 1, STOF_E_UNSUPPORTED,
+                     "EDSR_1D: n_mid=%d (2*num_blocks+1) must be odd and in [3,%d]", w->n_mid, STOF_MAX_MID_CONVS);
+        for (int i = 0; i < w->n_mid; ++i)
+            STOF_REQUIRE(w->mid_w[i] && w->mid_b[i], STOF_E_INVALID, "weights: EDSR conv %d missing", i);
     } else {
         STOF_REQUIRE(false, STOF_E_INVALID, "weights: unknown kind %d", w->kind);
     }
@@ -196,11 +222,24 @@ static int set_weights(stof_model *m, const stof_weights *w) {
     }
     m->F = w->num_features; m->n_mid = w->n_mid;
     m->k_first = w->k_first; m->k_mid = w->k_mid; m->k_last = w->k_last;
+    if (w->kind == STOF_KIND_EDSR) {
+        // models/edsr_1d.py:22-45 on the tensor-core chain: conv_input -> x0 kernel (K = 3), the 2*num_blocks + 1 k3 convs ->
+        // chain layers, shuffle + conv_output -> an equivalent (4, 64, 3) conv_last (edsr_tail_weights)
+        m->sgb_scale = 1; m->sgb_feat = 0; m->sgb_k = 0;
+        m->seg_len = 6;                                   // k3 layers: 6 per launch fit the smem tile
+        if ((rc = upload(m->first, repack_cikco(w->conv1_w, 64, 1, 3), w->conv1_b, 64))) return rc;
+        for (int i = 0; i < w->n_mid; ++i)
+            if ((rc = upload(m->mid[i], repack_cikco(w->mid_w[i], 64, 64, 3), w->mid_b[i], 64))) return rc;
+        const std::vector<float> tail = edsr_tail_weights(w->last_w);
+        const float b4[4] = {w->last_b[0], w->last_b[0], w->last_b[0], w->last_b[0]};
+        if ((rc = upload(m->last, repack_cikco(tail.data(), 4, 64, 3), b4, 4))) return rc;
+        return upload_tc(m, w, tail.data());
+    }
     if ((rc = upload(m->first, repack_cikco(w->conv1_w, 64, 1, 9), w->conv1_b, 64))) return rc;
     for (int i = 0; i < w->n_mid; ++i)
         if ((rc = upload(m->mid[i], repack_cikco(w->mid_w[i], 64, 64, 7), w->mid_b[i], 64))) return rc;
     if ((rc = upload(m->last, repack_cikco(w->last_w, 4, 64, 3), w->last_b, 4))) return rc;
-    if ((rc = upload_tc(m, w))) return rc;
+    if ((rc = upload_tc(m, w, w->last_w))) return rc;
     if ((rc = upload_train(m, w))) return rc;
     if (w->contract_w) {
         m->sgb_scale = w->sgb_scale; m->sgb_feat = w->sgb_feat; m->sgb_k = w->sgb_k;
@@ -316,7 +355,7 @@ static int forward_chunk_tc(stof_model *m, const float *x, int n, int L, float *
     }
     // x0 = relu(conv1 x) + upsample(E) as split planes (:45,108-115); also the long skip res1 (:51,62)
     { ProfScope p(m, STOF_PROF_SGB_ADD, st);
-      if ((rc = launch_x0_split(x, sgb ? e : nullptr, n, L, pl.P, m->sgb_scale, off, m->first.w, m->first.b, B1, st, fast))) return rc; }
+      if ((rc = launch_x0_split(x, sgb ? e : nullptr, n, L, pl.P, m->sgb_scale, off, m->first.w, m->first.b, B1, st, fast, m->k_first))) return rc; }
     const void *cur = B1;
     void *pp[2] = {B2, B0};
     int which = 0;
@@ -350,7 +389,7 @@ static int forward_chunk(stof_model *m, const float *x, int n, int L, float *mas
         ProfScope p(m, STOF_PROF_LAST, st);
         return launch_conv_last(B1, mask, m->last.w, m->last.b, n, L, 32, 1, st);
     }
-    if (m->path != STOF_PATH_SIMT) return forward_chunk_tc(m, x, n, L, mask, B0, B1, B2, pooled, e, pl, st);
+    if (m->path != STOF_PATH_SIMT || m->kind == STOF_KIND_EDSR) return forward_chunk_tc(m, x, n, L, mask, B0, B1, B2, pooled, e, pl, st);
     // models/stofnet.py:45
     { ProfScope p(m, STOF_PROF_FIRST, st); if ((rc = launch_conv_first(x, n, L, m->first.w, m->first.b, B0, 9, 0, st))) return rc; }
     // :48 semi-global block
@@ -564,8 +603,8 @@ extern "C" int stof_model_set_path(stof_model *m, int path, int layers_per_launc
     STOF_REQUIRE(m != nullptr, STOF_E_INVALID, "stof_model_set_path: model is NULL");
     STOF_REQUIRE(path == STOF_PATH_SIMT || path == STOF_PATH_TC || path == STOF_PATH_TC_FP16, STOF_E_INVALID,
                  "stof_model_set_path: path %d", path);
-    STOF_REQUIRE(path == STOF_PATH_SIMT || m->kind == STOF_KIND_STOFNET, STOF_E_UNSUPPORTED,
-                 "stof_model_set_path: the tensor-core path covers StofNet only");
+    STOF_REQUIRE(path == STOF_PATH_SIMT ? m->kind != STOF_KIND_EDSR : m->kind != STOF_KIND_ESPCN, STOF_E_UNSUPPORTED,
+                 "stof_model_set_path: ESPCN_1D runs on the fp32 FFMA path only, EDSR_1D on the tensor-core path only");
     if (layers_per_launch > 0) {
         STOF_REQUIRE(layers_per_launch <= stof::TC_MAX_LAYERS, STOF_E_INVALID, "stof_model_set_path: at most %d layers per launch",
                      stof::TC_MAX_LAYERS);
@@ -577,7 +616,7 @@ extern "C" int stof_model_set_path(stof_model *m, int path, int layers_per_launc
 
 extern "C" int stof_chain_segment(stof_model *m, int first, int count, const void *in_planes_dev, const void *x0_planes_dev,
                                   void *out_dev, int N, int L, void *stream) {
-    STOF_REQUIRE(m != nullptr && m->kind == STOF_KIND_STOFNET, STOF_E_INVALID, "stof_chain_segment: needs a StofNet model");
+    STOF_REQUIRE(m != nullptr && m->kind != STOF_KIND_ESPCN, STOF_E_INVALID, "stof_chain_segment: needs a StofNet or EDSR_1D model");
     STOF_REQUIRE(first >= 0 && count >= 1 && first + count <= m->n_tc, STOF_E_INVALID,
                  "stof_chain_segment: layers [%d, %d) of %d", first, first + count, m->n_tc);
     STOF_REQUIRE(in_planes_dev && out_dev && N > 0 && L > 0, STOF_E_INVALID, "stof_chain_segment: bad arguments");

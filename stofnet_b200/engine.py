@@ -56,6 +56,26 @@ class Engine:
         W = _lib.Weights()
         keep = {k: _np32(v) for k, v in sd.items()}
         W.kind = self.kind
+        if self.kind == _lib.KIND_EDSR:
+            # models/edsr_1d.py:22-30
+            nb = 1 + max(int(k.split(".")[1]) for k in keep if k.startswith("residual_blocks."))
+            if 2 * nb + 1 > _lib.MAX_MID:
+                raise ValueError("stofnet_b200: EDSR_1D with %d residual blocks (at most %d)" % (nb, (_lib.MAX_MID - 1) // 2))
+            W.conv1_w, W.conv1_b = _ptr(keep["conv_input.weight"]), _ptr(keep["conv_input.bias"])
+            for i in range(nb):
+                for j, c in enumerate(("conv1", "conv2")):
+                    W.mid_w[2 * i + j] = _ptr(keep["residual_blocks.%d.%s.weight" % (i, c)])
+                    W.mid_b[2 * i + j] = _ptr(keep["residual_blocks.%d.%s.bias" % (i, c)])
+            W.mid_w[2 * nb], W.mid_b[2 * nb] = _ptr(keep["conv_mid.weight"]), _ptr(keep["conv_mid.bias"])
+            W.n_mid = 2 * nb + 1
+            W.last_w, W.last_b = _ptr(keep["conv_output.weight"]), _ptr(keep["conv_output.bias"])
+            W.num_features = keep["conv_input.weight"].shape[0]
+            W.upsample_factor = W.num_features // keep["conv_output.weight"].shape[1]
+            W.k_first = keep["conv_input.weight"].shape[2]
+            W.k_mid = keep["conv_mid.weight"].shape[2]
+            W.k_last = keep["conv_output.weight"].shape[2]
+            W.sgb_scale = 1
+            return W, keep
         W.conv1_w, W.conv1_b = _ptr(keep["conv1.weight"]), _ptr(keep["conv1.bias"])
         if self.kind == _lib.KIND_ESPCN:
             W.n_mid = 1

@@ -11,6 +11,7 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 STOF_CKPTS = ["different-armadillo", "clean-serenity", "graceful-snow", "breezy-violet"]
 ESPCN_CKPTS = ["vital-puddle", "wobbly-sponge"]
+EDSR_CKPTS = ["proud-cherry", "snowy-dragon"]
 
 
 def pytest_configure(config):

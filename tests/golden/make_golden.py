@@ -17,6 +17,7 @@ kernels (torch 2.11.0, oneDNN, fp32; fp64 re-run stored beside it as the tie-bre
                        {None, checkpoint th, 0.5}
   peaks_cases.npz      hand-made stage-4 edge cases -> reference indices / coords
   espcn_<ckpt>.npz     ESPCN_1D forward masks
+  edsr_<ckpt>.npz      EDSR_1D forward masks, fp32 + fp64
   metrics_cases.npz    toa_rmse / coords2mask / find_threshold known answers
   train_<ckpt>.npz     three training steps (model -> loss -> autograd -> AdamW, main.py:217-248): gradients
                        of every parameter after the first backward, losses and parameters after each step
@@ -43,6 +44,7 @@ from stofnet_b200.synth import synth_waveforms  # our generator (inputs only)
 
 from models.stofnet import StofNet  # noqa: E402  (reference)
 from models.espcn_1d import ESPCN_1D  # noqa: E402
+from models.edsr_1d import EDSR_1D  # noqa: E402
 from utils.mask2samples import mask2coords, get_maxima_positions, coords2mask, nms_1d  # noqa: E402
 from utils.metrics import toa_rmse  # noqa: E402
 from utils.threshold import find_threshold  # noqa: E402
@@ -59,6 +61,7 @@ STOF = {
     "breezy-violet": (20, 2.3),
 }
 ESPCN = {"vital-puddle": (10, None), "wobbly-sponge": (20, 0.2)}
+EDSR = {"proud-cherry": (10, None), "snowy-dragon": (20, 1.5)}
 
 
 def ckpt_path(prefix):
@@ -129,6 +132,34 @@ def gen_forward():
             for t in sorted({None, th, 0.5}, key=lambda v: (v is not None, v or 0)):
                 peaks_dict(p, m, t, out)
         np.savez_compressed(os.path.join(HERE, "espcn_%s.npz" % name), **out)
+
+
+def gen_edsr():
+    """edsr_<ckpt>.npz: EDSR_1D forward masks (fp32 + fp64) and stage-4 outputs."""
+    for name, (rf, th) in EDSR.items():
+        sd = load_sd(name)
+        np.savez(os.path.join(HERE, "weights_%s.npz" % name), **{k: v.numpy() for k, v in sd.items()})
+        model = EDSR_1D().eval()
+        print(name, model.load_state_dict(sd))
+        model64 = EDSR_1D().double().eval()
+        model64.load_state_dict({k: v.double() for k, v in sd.items()})
+        out = {"rf": np.int64(rf), "th": np.float64(np.nan if th is None else th)}
+        cases = [(3, 160, 11), (2, 256 * rf, 3008), (1, 37, 2), (2, 601, 5)]
+        out["cases"] = np.array(cases, dtype=np.int64)
+        for ci, (N, L, seed) in enumerate(cases):
+            x = torch.from_numpy(synth_waveforms(N, L, seed=seed, rf=rf)).unsqueeze(1)
+            with torch.no_grad():
+                m = model(x)
+                m64 = model64(x.double())
+            p = "c%d" % ci
+            out[p + "_x"] = x.squeeze(1).numpy()
+            out[p + "_mask"] = m.squeeze(1).numpy()
+            out[p + "_mask64"] = m64.squeeze(1).numpy()
+            for t in sorted({None, th, 0.5}, key=lambda v: (v is not None, v or 0)):
+                peaks_dict(p, m, t, out)
+            print("  case", ci, N, L, "mask range", float(m.min()), float(m.max()),
+                  "max|fp32-fp64|", float((m.double() - m64).abs().max()))
+        np.savez_compressed(os.path.join(HERE, "edsr_%s.npz" % name), **out)
 
 
 def gen_peaks_cases():
@@ -367,10 +398,14 @@ if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "train":
         gen_train_cases()
         sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "edsr":
+        gen_edsr()
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "aux":
         gen_aux_cases()
         sys.exit(0)
     gen_forward()
+    gen_edsr()
     gen_peaks_cases()
     gen_metrics_cases()
     gen_aux_cases()

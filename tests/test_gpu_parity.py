@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 import torch
 
-from conftest import STOF_CKPTS, ESPCN_CKPTS, th_key, th_list
+from conftest import STOF_CKPTS, ESPCN_CKPTS, EDSR_CKPTS, th_key, th_list
 
 pytestmark = pytest.mark.gpu
 
@@ -107,6 +107,36 @@ def test_espcn_forward_golden(sb, dev, golden, name):
             m = model(x)
         ref = g["c%d_mask" % ci]
         assert np.abs(m.squeeze(1).cpu().numpy() - ref).max() <= 2e-5     # sigmoid output in (0, 1)
+
+
+@pytest.mark.parametrize("name", EDSR_CKPTS)
+def test_edsr_forward_golden(sb, dev, golden, name):
+    """EDSR_1D on the tensor-core chain (k3 layers, ReLU epilogue, shuffle + conv_output folded into conv_last) against the
+    reference's masks; indices / ToF tables bit-exact, masks within fp32 accumulation noise of the fp64 re-run."""
+    g = golden("edsr_%s.npz" % name)
+    model = _model(sb, golden, name, dev)
+    assert isinstance(model, sb.EDSR_1D)
+    for ci, (N, L, seed) in enumerate(g["cases"]):
+        x = torch.from_numpy(g["c%d_x" % ci]).unsqueeze(1).to(dev)
+        with torch.no_grad():
+            m = model(x)
+        assert m.shape == (N, 1, 4 * L)
+        ref, ref64 = g["c%d_mask" % ci], g["c%d_mask64" % ci]
+        got = m.squeeze(1).cpu().numpy()
+        scale = np.abs(ref64).max()
+        assert np.abs(got - ref64).max() <= 2e-5 * scale, (name, ci, np.abs(got - ref64).max() / scale)
+        assert np.abs(got - ref).max() <= 2e-5 * scale
+        for th in th_list(g):
+            co = sb.mask2coords(m, 20, th, upsample_factor=4).cpu().numpy()
+            gc = g["c%d_coords_%s" % (ci, th_key(th))]
+            assert co.shape == gc.shape and np.array_equal(co, gc), (name, ci, th)
+    # opt-in one-pass mode: stated tolerance (11-bit significand operands, fp32 accumulation)
+    model.set_precision("fp16")
+    x = torch.from_numpy(g["c1_x"]).unsqueeze(1).to(dev)
+    with torch.no_grad():
+        mf = model(x).squeeze(1).cpu().numpy()
+    assert np.abs(mf - g["c1_mask64"]).max() <= 2e-2 * np.abs(g["c1_mask64"]).max()
+    model.set_precision("fp32")
 
 
 def test_bad_lengths_raise_like_reference(sb, dev, golden):

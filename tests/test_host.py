@@ -67,6 +67,15 @@ def test_espcn_checkpoint_detected(golden):
         sb.build_model({"foo.weight": torch.zeros(1)})
 
 
+def test_edsr_checkpoint_detected(golden):
+    sd = {k: torch.from_numpy(v) for k, v in golden("weights_proud-cherry.npz").items()}
+    model = sb.build_model(sd)
+    assert isinstance(model, sb.EDSR_1D) and model.upsample_factor == 4 and len(model.residual_blocks) == 8
+    assert set(model.state_dict()) == set(sd)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        model(torch.zeros(1, 1, 160))
+
+
 def test_no_cpu_fallback(golden):
     sd = {k: torch.from_numpy(v) for k, v in golden("weights_clean-serenity.npz").items()}
     model = sb.build_model(sd)
