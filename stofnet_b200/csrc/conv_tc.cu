@@ -112,6 +112,40 @@ __device__ __forceinline__ void tl_event(unsigned long long *tl, int cap, uint32
 #define TL(role, k, b, what) tl_event(p.timeline, p.timeline_cap, (role), ((role) << 24) | ((uint32_t)(k) << 16) | ((uint32_t)(b) << 8) | (what), tl_cnt)
 #define TL_FLUSH(role) do { if (p.timeline != nullptr && blockIdx.x == 0) p.timeline[(role)] = (unsigned long long)tl_cnt; } while (0)
 
+// All taps of one layer for one 128-row block, issued by a single thread.  Layer kinds (upload_tc in stof_api.cu):
+//   64 -> 64 conv : taps [c8][W_hi 64 | W_lo 64][8] (one-pass mode: [c8][W_hi 64][8]); D0 = columns 0-63, D1 = 64-127
+//   conv_last     : taps [c8][32 rows][8]: rows 0-3 W_hi, 8-11 W_lo, 16-19 W_hi (one-pass: [c8][16][8]); D0 = 0-3, D1 = 8-11
+// Descriptor low word = (addr >> 4) | (LBO >> 4) << 16; the high word (SBO = 128 B, version 1) is constant.
+template <bool FAST, bool LAST>
+__device__ __forceinline__ void issue_layer_taps(uint32_t a_base, uint32_t w_base, uint32_t d_tmem, int taps, int s, uint32_t ph,
+                                                 uint32_t bar_w_full0, uint32_t bar_w_empty0, uint32_t bar_acc_full) {
+    constexpr uint32_t kDescHi = (128u >> 4) | (1u << 14);
+    constexpr uint32_t W_ROWS = LAST ? (FAST ? 16u : 32u) : (FAST ? 64u : 128u);    // K-chunk stride of a weight stage / 16
+    constexpr uint32_t LO_ROW = LAST ? 16u : 0u;                                     // W_hi rows of the X_lo product
+    constexpr uint32_t LO_COL = LAST ? 8u : 64u;                                     // its accumulator columns
+    constexpr uint32_t STRIDE16 = (uint32_t)(FAST ? TC_STAGE_BYTES / 2 : TC_STAGE_BYTES) >> 4;
+    constexpr int NST = FAST ? TC_MAX_STAGES : TC_STAGES;
+    constexpr uint32_t idesc_a = umma_idesc_f16(128, LAST ? 16 : (FAST ? 64 : 128));
+    constexpr uint32_t idesc_b = umma_idesc_f16(128, LAST ? 16 : 64);
+    for (int t = 0; t < taps; ++t) {
+        mbar_wait(bar_w_full0 + 8u * (uint32_t)s, ph);
+        tc_fence_after_sync();
+        const uint32_t a_lo = a_base + (uint32_t)t;
+        const uint32_t w_lo = (w_base + (uint32_t)s * STRIDE16) | (W_ROWS << 16);
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {
+            umma_f16(d_tmem, make_desc(a_lo + 2 * ks * TC_R, kDescHi), make_desc(w_lo + 2 * ks * W_ROWS, kDescHi), idesc_a,
+                     (t > 0 || ks > 0) ? 1u : 0u);
+            if (!FAST)
+                umma_f16(d_tmem + LO_COL, make_desc(a_lo + (8 + 2 * ks) * TC_R, kDescHi),
+                         make_desc(w_lo + 2 * ks * W_ROWS + LO_ROW, kDescHi), idesc_b, 1u);
+        }
+        umma_commit(bar_w_empty0 + 8u * (uint32_t)s);                            // this stream is done with the stage
+        if (++s == NST) { s = 0; ph ^= 1u; }
+    }
+    umma_commit(bar_acc_full);
+}
+
 template <bool FAST>
 __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -236,7 +270,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
         // epilogue; the weight ring bounds the lag between the blocks to TC_STAGES taps.
         // Each warp runs warp-uniform control flow (descriptors stay in uniform registers); one elected lane issues.
         // Descriptor low word = (addr >> 4) | (LBO >> 4) << 16; the high word (SBO = 128 B, version 1) is constant.
-        constexpr uint32_t kDescHi = (128u >> 4) | (1u << 14);
         constexpr uint32_t kALoBase = (uint32_t)(TC_SLAB >> 4) << 16;            // A: LBO = one slab
         const int b = warp - 1;
         const uint32_t role = 1u + (uint32_t)b;
@@ -255,12 +288,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                 const int taps = ly.taps;
                 const uint32_t a_base = (((sbase + ((k & 1) ? TC_OFF_Q : TC_OFF_P)) >> 4) | kALoBase) +
                                         (uint32_t)(p.b_row[k] - ly.pad + 128 * b);
-                const uint32_t idesc_a = umma_idesc_f16(128, FAST ? ly.n_fast : ly.n_stack);
-                const bool fast = FAST;
-                const uint32_t idesc_b = umma_idesc_f16(128, ly.n_lo);
-                const uint32_t w_rows = (uint32_t)(FAST ? ly.w_rows_fast : ly.w_rows);   // K-chunk stride of a weight stage / 16
-                const uint32_t w_hi_off = (uint32_t)ly.lo_row;
-                const uint32_t lo_col = (uint32_t)ly.lo_col;
                 if (tl_on) TL(role, k, b, 3);
                 mbar_wait(BAR_ACC_EMPTY(b), (lseq & 1u) ^ 1u);
                 if (k > 0) {
@@ -268,27 +295,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                     if (b == 1) mbar_wait(BAR_ACT(k - 1, 1), (uint32_t)(it & 1));
                 }
                 tc_fence_after_sync();
-                for (int t = 0; t < taps; ++t) {
-                    mbar_wait(BAR_W_FULL(s), ph);
-                    tc_fence_after_sync();
-                    if (elect_one()) {
-                        const uint32_t a_lo = a_base + (uint32_t)t;
-                        const uint32_t w_lo = ((sbase + TC_OFF_W + s * stage_stride) >> 4) | (w_rows << 16);
-#pragma unroll
-                        for (int ks = 0; ks < 4; ++ks) {
-                            const uint64_t da_hi = make_desc(a_lo + 2 * ks * TC_R, kDescHi);
-                            const uint64_t da_lo = make_desc(a_lo + (8 + 2 * ks) * TC_R, kDescHi);
-                            const uint64_t db_all = make_desc(w_lo + 2 * ks * w_rows, kDescHi);
-                            const uint64_t db_hi = make_desc(w_lo + 2 * ks * w_rows + w_hi_off, kDescHi);
-                            umma_f16(d_tmem, da_hi, db_all, idesc_a, (t > 0 || ks > 0) ? 1u : 0u);
-                            if (!fast) umma_f16(d_tmem + lo_col, da_lo, db_hi, idesc_b, 1u);
-                        }
-                        umma_commit(BAR_W_EMPTY(s));                             // this stream is done with the stage
-                        if (t == taps - 1) umma_commit(BAR_ACC_FULL(b));
-                    }
-                    __syncwarp();
-                    if (++s == n_stages) { s = 0; ph ^= 1u; }
+                // the layer's taps are issued by ONE elected lane in a single region (it also polls the weight ring), with every
+                // per-layer quantity a compile-time constant of the layer kind: per tap only the A row shift and the ring stage change
+                if (elect_one()) {
+                    const uint32_t w_base = (sbase + TC_OFF_W) >> 4;
+                    if (ly.type == TC_LAST)
+                        issue_layer_taps<FAST, true>(a_base, w_base, d_tmem, taps, s, ph, BAR_W_FULL(0), BAR_W_EMPTY(0), BAR_ACC_FULL(b));
+                    else
+                        issue_layer_taps<FAST, false>(a_base, w_base, d_tmem, taps, s, ph, BAR_W_FULL(0), BAR_W_EMPTY(0), BAR_ACC_FULL(b));
                 }
+                __syncwarp();
+                s += taps;
+                while (s >= n_stages) { s -= n_stages; ph ^= 1u; }
                 if (tl_on) TL(role, k, b, 4);
             }
         }
@@ -303,6 +321,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
         const int trow = 32 * quad + lane;                       // TMEM lane = row within the 128-block
         const uint32_t lane_addr = (uint32_t)(32 * quad) << 16;
         const bool tl_on = (warp == 3) && (lane == 0);
+        const bool free_early = (p.stash == 0);     // free_layer has an even index: it reads P as operand only
         uint32_t lseq = 0;
         int it = 0;
         for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
@@ -334,6 +353,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                     mbar_wait(BAR_ACC_FULL(b), lseq & 1u);
                     tc_fence_after_sync();
                     if (tl_on) TL(3u, k, b, 1);
+                    if (free_early && b == 1 && k == p.free_layer) {
+                        // both blocks' MMAs of the last layer that reads buffer P have completed, and this layer's epilogue does
+                        // not touch P (its output goes to Q / global, no TMEM stash): hand P to the producer before the epilogue
+                        // math, so the next tile's input load overlaps it
+                        if (lane == 0) mbar_arrive(BAR_P_FREE);
+                    }
                     const uint32_t d_tmem = tmem0 + (uint32_t)b * 128u + lane_addr;
                     const uint32_t stash = tmem0 + 256u + 64u * (uint32_t)b + 32u * (uint32_t)egrp + lane_addr;
                     if (type == TC_LAST) {
@@ -458,7 +483,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                     }
                     if (tl_on) TL(3u, k, b, 3);
                 }
-                if (k == p.free_layer) {
+                if (k == p.free_layer && !free_early) {
                     // every read of buffer P for this tile is done (this warp's share)
                     __syncwarp();
                     if (lane == 0) mbar_arrive(BAR_P_FREE);
