@@ -175,6 +175,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--layers-per-launch", type=int, default=0, help="conv layers fused per chain launch (0 = library default)")
     ap.add_argument("--precision", default="fp32", choices=["fp32", "fp16"],
                     help="fp32 (default, the headline: index-exact) or fp16 (one-pass reduced-precision mode, stated tolerance)")
     args = ap.parse_args()
@@ -201,6 +202,8 @@ def main():
     model = sb.build_model(sd, dev)
     model.set_precision(args.precision)
     eng = model._engine
+    if args.layers_per_launch:
+        eng.set_path(eng.path, args.layers_per_launch)          # tuning knob: conv layers fused per chain launch
     base = make_inputs(256, 3008 + rank)
     batches_host = [expand_batch(base, ROWS, s).pin_memory() for s in (0, 7, 13)]
     batches_dev = [b.to(dev).unsqueeze(1).contiguous() for b in batches_host]

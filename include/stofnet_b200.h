@@ -161,6 +161,11 @@ int stof_model_set_path(stof_model *m, int path, int layers_per_launch);
 int stof_chain_segment(stof_model *m, int first, int count, const void *in_planes_dev, const void *x0_planes_dev,
                        void *out_dev, int N, int L, void *stream);
 
+/* The expanding half of the semi-global block alone (test hook): E = LeakyReLU(expand_conv(pooled)), models/stofnet.py:94-95,
+ * 104-105.  pooled_dev (N, 512, P) fp32 -> e_dev (N, 64, P) fp32.  path: STOF_PATH_TC = tcgen05 kernel (what stof_forward
+ * runs), STOF_PATH_SIMT = fp32 FFMA kernel (what the training forward runs).                                  */
+int stof_sgb_expand(stof_model *m, const float *pooled_dev, int N, int P, float *e_dev, int path, void *stream);
+
 /* Debug: chain launches issued after this call make four warps of CTA 0 (producer, the two MMA issuers, one epilogue
  * warp) append (code, clock64) event pairs to dev_buf (uint64[4 + 2*capacity]: [role] = event count of that role, then
  * four regions of capacity/4 pairs; must be zeroed by the caller).  NULL switches it off.                  */

@@ -67,6 +67,7 @@ _SIGS = {
     "stof_model_set_path": (_i, [_vp, _i, _i]),
     "stof_chain_segment": (_i, [_vp, _i, _i, _vp, _vp, _vp, _i, _i, _vp]),
     "stof_debug_set_timeline": (_i, [_vp, _i]),
+    "stof_sgb_expand": (_i, [_vp, _vp, _i, _i, _vp, _i, _vp]),
     "stof_profile_enable": (_i, [_vp, _i]),
     "stof_profile_collect": (_i, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     # operators either side of the path

@@ -68,6 +68,8 @@ int launch_x0_split(const float *x, const float *e, int N, int L, int P, int sca
 // contract_tc.cu: pooled = maxpool80(LeakyReLU(contract_conv(relu(conv1 x)))) on tcgen05, conv1 recomputed per tile
 int launch_contract_pool_tc(const float *x, const void *w, const float *bias, const float *w1, const float *b1, float *pooled,
                             int N, int L, int P, cudaStream_t st, int fast = 0);
+// expand_tc.cu: E = LeakyReLU(expand_conv(pooled)) on tcgen05 (fp32 in / out, operands split on the fly)
+int launch_expand_tc(const float *pooled, float *e, const void *w_packed, const float *bias, int N, int P, cudaStream_t st);
 // fp32 C4L4 activations <-> split planes (debug / hand-over between the SIMT and tensor paths)
 int launch_c4l4_to_planes(const float *act, void *planes, int N, int L, cudaStream_t st);
 int launch_planes_to_c4l4(const void *planes, float *act, int N, int L, cudaStream_t st);

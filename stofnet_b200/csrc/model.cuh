@@ -32,6 +32,7 @@ struct stof_model {
     int seg_len = 4;                                  // layers fused per chain launch
     void *tc_w = nullptr;
     void *tc_w_fast = nullptr;                        // W_hi-only taps of the one-pass fp16 mode
+    void *tc_expand_w = nullptr;                      // expand conv: [8 groups][5 taps][8 c8][W_hi 64 | W_lo 64][8] fp16
     void *tc_contract_w = nullptr;                    // contract conv: [4 slices][5 taps][8 c8][W_hi 128 | W_lo 128][8] fp16
     stof::TcLayer tc_layer[STOF_MAX_MID_CONVS + 1];   // spec list: mid convs then conv_last
     int n_tc = 0;

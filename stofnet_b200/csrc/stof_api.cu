@@ -267,6 +267,23 @@ static int set_weights(stof_model *m, const stof_weights *w) {
             if (!m->tc_contract_w) STOF_CUDA(cudaMalloc(&m->tc_contract_w, buf.size() * sizeof(__half)));
             STOF_CUDA(cudaMemcpy(m->tc_contract_w, buf.data(), buf.size() * sizeof(__half), cudaMemcpyHostToDevice));
         }
+        {
+            // expand conv (64, 512, 5) -> [group g][tap t][c8][W_hi 64 | W_lo 64][8]: input channel 64 g + 8 c8 + (ci & 7)
+            std::vector<__half> buf((size_t)8 * 5 * 8 * 128 * 8);
+            for (int g = 0; g < 8; ++g)
+                for (int t = 0; t < 5; ++t) {
+                    __half *tap = buf.data() + ((size_t)g * 5 + t) * 8 * 128 * 8;
+                    for (int co = 0; co < 64; ++co)
+                        for (int ci = 0; ci < 64; ++ci) {
+                            __half hi, lo;
+                            split_w(w->expand_w[((size_t)co * 512 + 64 * g + ci) * 5 + t], hi, lo);
+                            tap[((size_t)(ci >> 3) * 128 + co) * 8 + (ci & 7)] = hi;
+                            tap[((size_t)(ci >> 3) * 128 + 64 + co) * 8 + (ci & 7)] = lo;
+                        }
+                }
+            if (!m->tc_expand_w) STOF_CUDA(cudaMalloc(&m->tc_expand_w, buf.size() * sizeof(__half)));
+            STOF_CUDA(cudaMemcpy(m->tc_expand_w, buf.data(), buf.size() * sizeof(__half), cudaMemcpyHostToDevice));
+        }
     } else {
         m->sgb_scale = 1; m->sgb_feat = 0; m->sgb_k = 0;
     }
@@ -350,7 +367,7 @@ static int forward_chunk_tc(stof_model *m, const float *x, int n, int L, float *
         // models/stofnet.py:45,98-107: E = LeakyReLU(expand(maxpool80(LeakyReLU(contract(relu(conv1 x))))))
         { ProfScope p(m, STOF_PROF_CONTRACT, st);
           if ((rc = launch_contract_pool_tc(x, m->tc_contract_w, m->contract.b, m->first.w, m->first.b, pooled, n, L, pl.P, st, fast))) return rc; }
-        { ProfScope p(m, STOF_PROF_EXPAND, st); if ((rc = launch_expand(pooled, e, m->expand.w, m->expand.b, n, pl.P, st))) return rc; }
+        { ProfScope p(m, STOF_PROF_EXPAND, st); if ((rc = launch_expand_tc(pooled, e, m->tc_expand_w, m->expand.b, n, pl.P, st))) return rc; }
         off = (L - pl.P * m->sgb_scale) / 2;
     }
     // x0 = relu(conv1 x) + upsample(E) as split planes (:45,108-115); also the long skip res1 (:51,62)
@@ -479,6 +496,7 @@ extern "C" void stof_model_destroy(stof_model *m) {
     if (m->tc_w) cudaFree(m->tc_w);
     if (m->tc_w_fast) cudaFree(m->tc_w_fast);
     if (m->tc_contract_w) cudaFree(m->tc_contract_w);
+    if (m->tc_expand_w) cudaFree(m->tc_expand_w);
     if (m->h_stats) cudaFreeHost(m->h_stats);
     for (cudaEvent_t e : m->ev_pool) cudaEventDestroy(e);
     delete m;
@@ -624,6 +642,15 @@ extern "C" int stof_chain_segment(stof_model *m, int first, int count, const voi
     return stof::launch_chain_tc(m->tc_layer + first, count, in_planes_dev, x0_planes_dev, ends ? nullptr : out_dev,
                                  ends ? reinterpret_cast<float *>(out_dev) : nullptr, N, L, (cudaStream_t)stream,
                                  m->path == STOF_PATH_TC_FP16 ? 1 : 0);
+}
+
+extern "C" int stof_sgb_expand(stof_model *m, const float *pooled_dev, int N, int P, float *e_dev, int path, void *stream) {
+    STOF_REQUIRE(m != nullptr && m->kind == STOF_KIND_STOFNET && m->sgb_scale != 1, STOF_E_INVALID,
+                 "stof_sgb_expand: needs a StofNet model with a semi-global block");
+    STOF_REQUIRE(pooled_dev && e_dev && N > 0 && P > 0, STOF_E_INVALID, "stof_sgb_expand: bad arguments");
+    STOF_CUDA(cudaSetDevice(m->device));
+    if (path == STOF_PATH_SIMT) return stof::launch_expand(pooled_dev, e_dev, m->expand.w, m->expand.b, N, P, (cudaStream_t)stream);
+    return stof::launch_expand_tc(pooled_dev, e_dev, m->tc_expand_w, m->expand.b, N, P, (cudaStream_t)stream);
 }
 
 extern "C" int stof_debug_set_timeline(void *dev_buf, int capacity_events) {
