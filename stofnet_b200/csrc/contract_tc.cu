@@ -12,12 +12,18 @@
 // per tile by eight loader warps straight into the UMMA operand layout, so the kernel reads 4 B and writes 6.4 B per
 // position and moves no weights after start-up.
 //
-// fp32 accuracy on fp16 tensor cores as in conv_tc.cu: v = hi + 2^-11 lo;  per K-step
-//     [D0 | D1] (+)= X_hi [W_hi ; W_lo]^T   (N = 256),      D1 += X_lo W_hi^T   (N = 128),      result D0 + 2^-11 D1.
+// Orientation: the WEIGHTS are the MMA's A operand (M = the slice's 128 output channels = TMEM lanes) and the positions are
+// its N dimension (TMEM columns), so that max-pooling over positions is a running maximum over the columns a thread reads
+// from its own lane - no cross-lane reduction, no shared-memory atomics (the positions-on-lanes form spent more issue slots
+// on its butterfly transpose-max than the tensor pipe needed for the MMAs: the epilogue warps paced the kernel).
+//
+// fp32 accuracy on fp16 tensor cores as in conv_tc.cu: v = hi + 2^-11 lo;  per K-step three M = 128 MMAs
+//     D0 (+)= W_hi X_hi^T,      D1 (+)= W_lo X_hi^T,      D1 += W_hi X_lo^T,      result D0 + 2^-11 D1.
+// A tile of 240 positions is two accumulator halves: positions [0, 128) (N = 128) and [128, 240) (N = 112); pooling window 1
+// (positions 80..159) straddles them and is carried in a register.
 //
 // Roles: warp 0 = weight loader (bulk copies, once), warp 1 = MMA issuer + TMEM owner, warps 2-9 = conv1 loaders
-// (one thread per row and 32-channel half), warps 10-17 = pooling epilogue (warp & 3 = TMEM lane quadrant,
-// (warp - 10) >> 2 = 64-channel half).
+// (one thread per row and 32-channel half), warps 10-13 = pooling epilogue (warp & 3 = TMEM lane quadrant = 32 channels).
 #include <cuda_fp16.h>
 #include <limits.h>
 
@@ -29,7 +35,7 @@ namespace stof {
 
 using namespace ptx;
 
-constexpr int CT_THREADS = 576;                       // 2 + 8 loader + 8 epilogue warps
+constexpr int CT_THREADS = 448;                       // 2 + 8 loader + 4 epilogue warps
 constexpr int CT_TILE = 240;                         // positions per tile = 3 pooling windows of 80
 constexpr int CT_WINDOW = 80;
 constexpr int CT_ROWS0 = 132;                        // operand rows of block 0: positions [-2, 130) of the tile
@@ -38,7 +44,7 @@ constexpr int CT_TAP_BYTES = 8 * 256 * 16;           // one tap of one 128-chann
 constexpr int CT_OFF_W = 0;
 constexpr int CT_OFF_A0 = 5 * CT_TAP_BYTES;                      // 163,840
 constexpr int CT_OFF_A1 = CT_OFF_A0 + 16 * CT_ROWS0 * 16;        // + 33,792
-constexpr int CT_OFF_POOL = CT_OFF_A1 + 16 * CT_ROWS1 * 16;      // + 29,696 ; block 1's MMAs over-read 256 B into here (unused rows)
+constexpr int CT_OFF_POOL = CT_OFF_A1 + 16 * CT_ROWS1 * 16;      // + 29,696 ; 1.5 KB spare (guard behind the operand buffers)
 constexpr int CT_OFF_W1 = CT_OFF_POOL + 3 * 128 * 4;             // conv1 weights [9][64] + bias [64] fp32
 constexpr int CT_OFF_BAR = CT_OFF_W1 + (9 * 64 + 64) * 4;
 constexpr int CT_NBAR = 9;                                       // w_full, a_full[2], a_empty[2], acc_full[2], acc_empty[2]
@@ -54,63 +60,10 @@ __device__ __forceinline__ uint32_t ct_cvt_sat_half2(float a, float b) {
 __device__ __forceinline__ void ct_split_pair(float v0, float v1, uint32_t &hi, uint32_t &lo) {
     hi = ct_cvt_sat_half2(v0, v1);
     const float2 h = __half22float2(*reinterpret_cast<const __half2 *>(&hi));
-    lo = ct_cvt_sat_half2((v0 - h.x) * 2048.0f, (v1 - h.y) * 2048.0f);
+    // (v - h) * 2^11 with packed fp32 ops; both steps are exact, so this equals the scalar form bit for bit
+    const float2 d = __fmul2_rn(__ffma2_rn(h, make_float2(-1.0f, -1.0f), make_float2(v0, v1)), make_float2(2048.0f, 2048.0f));
+    lo = ct_cvt_sat_half2(d.x, d.y);
 }
-// order-preserving float <-> int32 map (so the pooling can use integer warp reductions and atomics)
-__device__ __forceinline__ int float_key(float v) {
-    const int b = __float_as_int(v);
-    return b ^ ((b >> 31) & 0x7fffffff);
-}
-__device__ __forceinline__ float key_float(int k) { return __int_as_float(k ^ ((k >> 31) & 0x7fffffff)); }
-
-// Warp "transpose-reduce": every lane holds 32 column values of its own row; afterwards lane j holds the maximum over the
-// rows (lanes) of its segment for column j (FULL: one 32-lane segment; otherwise two 16-lane segments and lane j holds
-// columns 2 * (j & 15) + {0, 1} in v[0], v[1]).  log-step butterfly: 31 (30) shuffles instead of 32 warp reductions.
-template <bool FULL>
-__device__ __forceinline__ void transpose_max(float (&v)[32], int lane) {
-    if (FULL) {
-        const bool up = lane & 16;
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            const float send = up ? v[i] : v[i + 16], keep = up ? v[i + 16] : v[i];
-            v[i] = fmaxf(keep, __shfl_xor_sync(0xffffffffu, send, 16));
-        }
-    }
-    constexpr int N0 = FULL ? 16 : 32;
-    {
-        const bool up = lane & 8;
-#pragma unroll
-        for (int i = 0; i < N0 / 2; ++i) {
-            const float send = up ? v[i] : v[i + N0 / 2], keep = up ? v[i + N0 / 2] : v[i];
-            v[i] = fmaxf(keep, __shfl_xor_sync(0xffffffffu, send, 8));
-        }
-    }
-    {
-        const bool up = lane & 4;
-#pragma unroll
-        for (int i = 0; i < N0 / 4; ++i) {
-            const float send = up ? v[i] : v[i + N0 / 4], keep = up ? v[i + N0 / 4] : v[i];
-            v[i] = fmaxf(keep, __shfl_xor_sync(0xffffffffu, send, 4));
-        }
-    }
-    {
-        const bool up = lane & 2;
-#pragma unroll
-        for (int i = 0; i < N0 / 8; ++i) {
-            const float send = up ? v[i] : v[i + N0 / 8], keep = up ? v[i + N0 / 8] : v[i];
-            v[i] = fmaxf(keep, __shfl_xor_sync(0xffffffffu, send, 2));
-        }
-    }
-    {
-        const bool up = lane & 1;
-#pragma unroll
-        for (int i = 0; i < N0 / 16; ++i) {
-            const float send = up ? v[i] : v[i + N0 / 16], keep = up ? v[i + N0 / 16] : v[i];
-            v[i] = fmaxf(keep, __shfl_xor_sync(0xffffffffu, send, 1));
-        }
-    }
-}
-
 struct ContractParams {
     const float *x;          // (N, L) fp32
     const void *w;           // [4 slices][5 taps][8 c8][256][8] fp16
@@ -133,7 +86,6 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
     auto BAR_A_EMPTY = [&](int b) { return bar0 + 8 * (3 + b); };
     auto BAR_ACC_FULL = [&](int b) { return bar0 + 8 * (5 + b); };
     auto BAR_ACC_EMPTY = [&](int b) { return bar0 + 8 * (7 + b); };
-    int *s_pool = reinterpret_cast<int *>(smem + CT_OFF_POOL);            // [3 windows][128 channels] keys
     float *s_w1 = reinterpret_cast<float *>(smem + CT_OFF_W1);            // [9][64] then bias [64]
     volatile uint32_t *s_tmem = reinterpret_cast<volatile uint32_t *>(smem + CT_OFF_TMEM);
 
@@ -143,14 +95,13 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
 
     for (int i = threadIdx.x; i < 9 * 64; i += CT_THREADS) s_w1[i] = __ldg(p.w1 + i);
     for (int i = threadIdx.x; i < 64; i += CT_THREADS) s_w1[9 * 64 + i] = __ldg(p.b1 + i);
-    for (int i = threadIdx.x; i < 3 * 128; i += CT_THREADS) s_pool[i] = INT_MIN;
     if (threadIdx.x == 0) {
         mbar_init(BAR_W_FULL, 1);
         for (int b = 0; b < 2; ++b) {
             mbar_init(BAR_A_FULL(b), 8);
             mbar_init(BAR_A_EMPTY(b), 1);
             mbar_init(BAR_ACC_FULL(b), 1);
-            mbar_init(BAR_ACC_EMPTY(b), 8);
+            mbar_init(BAR_ACC_EMPTY(b), 4);
         }
         fence_mbar_init();
     }
@@ -170,16 +121,16 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
     } else if (warp == 1) {
         // =================================== MMA issuer ==================================================
         constexpr uint32_t kDescHi = (128u >> 4) | (1u << 14);                  // SBO = 128 B, descriptor version 1
-        constexpr uint32_t kIdescA = umma_idesc_f16(128, 256), kIdescB = umma_idesc_f16(128, 128);
-        const uint32_t w_lo0 = ((sbase + CT_OFF_W) >> 4) | (256u << 16);        // LBO = 256 rows * 16 B
+        const uint32_t w_lo0 = ((sbase + CT_OFF_W) >> 4) | (256u << 16);        // weights (A): LBO = 256 rows * 16 B; W_hi rows 0-127, W_lo 128-255
         mbar_wait(BAR_W_FULL, 0);
         int it = 0;
         for (int tile = worker; tile < p.total_tiles; tile += workers, ++it) {
 #pragma unroll 1
             for (int b = 0; b < 2; ++b) {
                 const uint32_t rows = b ? CT_ROWS1 : CT_ROWS0;
-                const uint32_t a_lo0 = ((sbase + (b ? CT_OFF_A1 : CT_OFF_A0)) >> 4) | (rows << 16);
-                const uint32_t d_tmem = tmem0 + 256u * b;
+                const uint32_t idesc = b ? umma_idesc_f16(128, 112) : umma_idesc_f16(128, 128);   // N = positions of this half
+                const uint32_t x_lo0 = ((sbase + (b ? CT_OFF_A1 : CT_OFF_A0)) >> 4) | (rows << 16);
+                const uint32_t d0 = tmem0 + 256u * b, d1 = d0 + 128u;
                 mbar_wait(BAR_A_FULL(b), (uint32_t)(it & 1));
                 mbar_wait(BAR_ACC_EMPTY(b), (uint32_t)(it & 1) ^ 1u);
                 tc_fence_after_sync();
@@ -188,14 +139,15 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
                     for (int t = 0; t < 5; ++t) {
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks) {
-                            const uint64_t da_hi = make_desc(a_lo0 + t + 2 * ks * rows, kDescHi);
-                            const uint64_t da_lo = make_desc(a_lo0 + t + (8 + 2 * ks) * rows, kDescHi);
-                            const uint64_t db = make_desc(w_lo0 + t * (CT_TAP_BYTES >> 4) + 2 * ks * 256, kDescHi);
-                            if (p.fast) {
-                                umma_f16(d_tmem, da_hi, db, kIdescB, (t > 0 || ks > 0) ? 1u : 0u);      // N = 128: W_hi rows only
-                            } else {
-                                umma_f16(d_tmem, da_hi, db, kIdescA, (t > 0 || ks > 0) ? 1u : 0u);
-                                umma_f16(d_tmem + 128, da_lo, db, kIdescB, 1u);
+                            const uint64_t dx_hi = make_desc(x_lo0 + t + 2 * ks * rows, kDescHi);
+                            const uint64_t dx_lo = make_desc(x_lo0 + t + (8 + 2 * ks) * rows, kDescHi);
+                            const uint64_t dw_hi = make_desc(w_lo0 + t * (CT_TAP_BYTES >> 4) + 2 * ks * 256, kDescHi);
+                            const uint64_t dw_lo = make_desc(w_lo0 + t * (CT_TAP_BYTES >> 4) + 2 * ks * 256 + 128, kDescHi);
+                            const uint32_t acc = (t > 0 || ks > 0) ? 1u : 0u;
+                            umma_f16(d0, dw_hi, dx_hi, idesc, acc);
+                            if (!p.fast) {
+                                umma_f16(d1, dw_lo, dx_hi, idesc, acc);
+                                umma_f16(d1, dw_hi, dx_lo, idesc, 1u);
                             }
                         }
                     }
@@ -208,9 +160,26 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
     } else if (warp < 10) {
         // =================================== conv1 loaders ===============================================
         // x0[l][c] = relu(b1[c] + sum_t w1[c][t] x[l + t - 4]) for 0 <= l < L, 0 outside (the contract conv's zero padding).
-        // Work item = (row, 32-channel half); 256 threads.
-        const int tid = threadIdx.x - 64;               // 0..255
-        const float4 *w4 = reinterpret_cast<const float4 *>(s_w1);
+        // Warp w owns the 8-channel chunk c8 = w and keeps its 72 conv1 weights + 8 biases in registers for the whole launch;
+        // lane = row within a group of 32 (conflict-free 16-byte operand stores).  A block's waveform samples are fetched once
+        // per lane up front (6 coalesced loads issued before the buffer wait: one memory latency per block, overlapped with
+        // the MMAs still reading the buffer) and the 9-tap windows are assembled with warp shuffles; the FMAs are packed
+        // (fma.rn.f32x2, bit-identical to fmaf).  No shared-memory reads at all in this role.
+        const int c8 = warp - 2;                        // 0..7
+        float2 wr[9][4], br[4];
+        {
+            const float4 *w4 = reinterpret_cast<const float4 *>(s_w1) + 2 * c8;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const float4 bq = w4[9 * 16 + h];
+                br[2 * h] = make_float2(bq.x, bq.y); br[2 * h + 1] = make_float2(bq.z, bq.w);
+#pragma unroll
+                for (int t = 0; t < 9; ++t) {
+                    const float4 wv = w4[t * 16 + h];
+                    wr[t][2 * h] = make_float2(wv.x, wv.y); wr[t][2 * h + 1] = make_float2(wv.z, wv.w);
+                }
+            }
+        }
         int it = 0;
         for (int tile = worker; tile < p.total_tiles; tile += workers, ++it) {
             const int n = tile / p.tiles_per_row;
@@ -219,42 +188,44 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
 #pragma unroll 1
             for (int b = 0; b < 2; ++b) {
                 const int rows = b ? CT_ROWS1 : CT_ROWS0;
-                uint8_t *abuf = smem + (b ? CT_OFF_A1 : CT_OFF_A0);
+                uint8_t *abuf = smem + (b ? CT_OFF_A1 : CT_OFF_A0) + (size_t)c8 * rows * 16;
+                const int l_base = l_tile + 128 * b - 2;                 // position of operand row 0
+                float xg[6];                                             // xg[k] = x[l_base - 4 + 32 k + lane], 0 outside the row
+#pragma unroll
+                for (int k = 0; k < 6; ++k) {
+                    const int g = l_base - 4 + 32 * k + lane;
+                    xg[k] = (g >= 0 && g < p.L) ? __ldg(xr + g) : 0.0f;
+                }
                 mbar_wait(BAR_A_EMPTY(b), (uint32_t)(it & 1) ^ 1u);
-                for (int item = tid; item < 2 * rows; item += 256) {
-                    const int half = item >= rows ? 1 : 0;
-                    const int row = item - half * rows;
-                    const int l = l_tile + 128 * b - 2 + row;
+#pragma unroll
+                for (int k = 0; k < 5; ++k) {
+                    const int row = 32 * k + lane;
+                    const int l = l_base + row;
                     const bool inside = (l >= 0) && (l < p.L);
-                    float xv[9];
+                    float2 acc[4] = {br[0], br[1], br[2], br[3]};
 #pragma unroll
                     for (int t = 0; t < 9; ++t) {
-                        const int g = l + t - 4;
-                        xv[t] = (inside && g >= 0 && g < p.L) ? __ldg(xr + g) : 0.0f;
+                        const float lo = __shfl_sync(0xffffffffu, xg[k], (lane + t) & 31);
+                        const float hi = __shfl_sync(0xffffffffu, xg[k + 1], (lane + t) & 31);
+                        const float xv = (lane + t < 32) ? lo : hi;
+                        const float2 xx = make_float2(xv, xv);
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) acc[q] = __ffma2_rn(wr[t][q], xx, acc[q]);
                     }
-#pragma unroll 2
-                    for (int j = 0; j < 4; ++j) {
-                        const int c8 = 4 * half + j;
+                    if (row < rows) {
                         float v[8];
 #pragma unroll
-                        for (int h = 0; h < 2; ++h) {
-                            float4 a = w4[9 * 16 + 2 * c8 + h];
-#pragma unroll
-                            for (int t = 0; t < 9; ++t) {
-                                const float4 wv = w4[t * 16 + 2 * c8 + h];
-                                a.x = fmaf(wv.x, xv[t], a.x); a.y = fmaf(wv.y, xv[t], a.y);
-                                a.z = fmaf(wv.z, xv[t], a.z); a.w = fmaf(wv.w, xv[t], a.w);
-                            }
-                            v[4 * h + 0] = inside ? fmaxf(a.x, 0.f) : 0.f; v[4 * h + 1] = inside ? fmaxf(a.y, 0.f) : 0.f;
-                            v[4 * h + 2] = inside ? fmaxf(a.z, 0.f) : 0.f; v[4 * h + 3] = inside ? fmaxf(a.w, 0.f) : 0.f;
+                        for (int q = 0; q < 4; ++q) {
+                            v[2 * q] = inside ? fmaxf(acc[q].x, 0.f) : 0.f;
+                            v[2 * q + 1] = inside ? fmaxf(acc[q].y, 0.f) : 0.f;
                         }
                         uint4 uh, ul;
                         ct_split_pair(v[0], v[1], uh.x, ul.x);
                         ct_split_pair(v[2], v[3], uh.y, ul.y);
                         ct_split_pair(v[4], v[5], uh.z, ul.z);
                         ct_split_pair(v[6], v[7], uh.w, ul.w);
-                        *reinterpret_cast<uint4 *>(abuf + (c8 * rows + row) * 16) = uh;
-                        if (!p.fast) *reinterpret_cast<uint4 *>(abuf + ((8 + c8) * rows + row) * 16) = ul;
+                        *reinterpret_cast<uint4 *>(abuf + row * 16) = uh;
+                        if (!p.fast) *reinterpret_cast<uint4 *>(abuf + (size_t)8 * rows * 16 + row * 16) = ul;
                     }
                 }
                 fence_proxy_async_smem();
@@ -264,75 +235,59 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
         }
     } else {
         // =================================== pooling epilogue ============================================
+        // thread = output channel (TMEM lane) of the slice; a tile's three pooling windows are running maxima over the columns
         const int quad = warp & 3;
-        const int grp = (warp - 10) >> 2;                // channel half: co [64 grp, +64) of the slice
-        const int etid = threadIdx.x - 320;              // 0..255
+        const int co = slice * 128 + 32 * quad + lane;
         const uint32_t lane_addr = (uint32_t)(32 * quad) << 16;
+        const float bias = __ldg(p.bias + co);
+        const float li = p.fast ? 0.0f : (1.0f / 2048.0f);
         int it = 0;
         for (int tile = worker; tile < p.total_tiles; tile += workers, ++it) {
             const int n = tile / p.tiles_per_row;
             const int ti = tile - n * p.tiles_per_row;
             const int p0 = 3 * ti;                        // first pooling window of the tile
-#pragma unroll 1
+            float m[3] = {-INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
             for (int b = 0; b < 2; ++b) {
-                const int row = 128 * b + 32 * quad + lane;             // row within the tile
-                const int win = row / CT_WINDOW;                        // 0..3 (3 = beyond the tile)
-                const bool valid = (row < CT_TILE) && (p0 + win < p.P);
-                // the only warp whose rows belong to two pooling windows of the tile: rows 64..95 (split at lane 16)
-                const bool split = (b == 0) && (quad == 2);
                 mbar_wait(BAR_ACC_FULL(b), (uint32_t)(it & 1));
                 tc_fence_after_sync();
-                const uint32_t d_tmem = tmem0 + 256u * b + lane_addr + 64u * grp;
-#pragma unroll 1
-                for (int c32 = 0; c32 < 2; ++c32) {
+                const uint32_t d_tmem = tmem0 + 256u * b + lane_addr;
+                const int nch = (b == 0) ? 8 : 7;         // 16-column chunks: positions [0, 128) and [128, 240)
+#pragma unroll
+                for (int c = 0; c < 8; c += 2) {
                     uint32_t d0[32], d1[32];
-                    tmem_ld16(d_tmem + 32 * c32, *reinterpret_cast<uint32_t(*)[16]>(&d0[0]));
-                    tmem_ld16(d_tmem + 32 * c32 + 16, *reinterpret_cast<uint32_t(*)[16]>(&d0[16]));
+                    const bool two = (c + 1 < nch);
+                    tmem_ld16(d_tmem + 16 * c, *reinterpret_cast<uint32_t(*)[16]>(&d0[0]));
+                    if (two) tmem_ld16(d_tmem + 16 * c + 16, *reinterpret_cast<uint32_t(*)[16]>(&d0[16]));
                     if (!p.fast) {
-                        tmem_ld16(d_tmem + 128 + 32 * c32, *reinterpret_cast<uint32_t(*)[16]>(&d1[0]));
-                        tmem_ld16(d_tmem + 128 + 32 * c32 + 16, *reinterpret_cast<uint32_t(*)[16]>(&d1[16]));
+                        tmem_ld16(d_tmem + 128 + 16 * c, *reinterpret_cast<uint32_t(*)[16]>(&d1[0]));
+                        if (two) tmem_ld16(d_tmem + 128 + 16 * c + 16, *reinterpret_cast<uint32_t(*)[16]>(&d1[16]));
                     } else {
 #pragma unroll
                         for (int i = 0; i < 32; ++i) d1[i] = 0u;
                     }
                     tmem_ld_wait();
-                    if (c32 == 1) {
-                        tc_fence_before_sync();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(BAR_ACC_EMPTY(b));
-                    }
-                    float v[32];
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        const float t = __uint_as_float(d0[i]) + (1.0f / 2048.0f) * __uint_as_float(d1[i]);
-                        v[i] = valid ? t : -INFINITY;
-                    }
-                    const int co0 = 64 * grp + 32 * c32;
-                    if (!split) {
-                        transpose_max<true>(v, lane);                   // lane j: max over the warp's rows of column j
-                        const int w = (128 * b + 32 * quad) / CT_WINDOW;
-                        if (v[0] != -INFINITY) atomicMax(&s_pool[w * 128 + co0 + lane], float_key(v[0]));
-                    } else {
-                        transpose_max<false>(v, lane);                  // lane j: columns 2 (j & 15) + {0, 1} of its 16-row half
-                        const int w = lane >> 4;                        // rows 64..79 -> window 0, rows 80..95 -> window 1
-                        const int c = 2 * (lane & 15);
-                        if (v[0] != -INFINITY) atomicMax(&s_pool[w * 128 + co0 + c], float_key(v[0]));
-                        if (v[1] != -INFINITY) atomicMax(&s_pool[w * 128 + co0 + c + 1], float_key(v[1]));
+                    for (int h = 0; h < 2; ++h) {
+                        if (h == 0 || two) {
+                            const int w = (128 * b + 16 * (c + h)) / CT_WINDOW;  // compile-time: window of this 16-column chunk
+                            float mm = m[w];
+#pragma unroll
+                            for (int i = 0; i < 16; ++i)
+                                mm = fmaxf(mm, fmaf(li, __uint_as_float(d1[16 * h + i]), __uint_as_float(d0[16 * h + i])));
+                            m[w] = mm;
+                        }
                     }
                 }
+                tc_fence_before_sync();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(BAR_ACC_EMPTY(b));
             }
-            // all 8 epilogue warps have folded both blocks: publish bias + LeakyReLU of the window maxima, reset the pool
-            asm volatile("bar.sync 1, 256;" ::: "memory");
-            for (int idx = etid; idx < 3 * 128; idx += 256) {
-                const int w = idx >> 7, co = idx & 127;
-                const int key = s_pool[idx];
-                s_pool[idx] = INT_MIN;
-                if (p0 + w < p.P) {
-                    const float v = key_float(key) + __ldg(p.bias + slice * 128 + co);
-                    p.pooled[((size_t)n * 512 + slice * 128 + co) * p.P + p0 + w] = leaky(v);
-                }
-            }
-            asm volatile("bar.sync 1, 256;" ::: "memory");
+            // bias and LeakyReLU are monotone: applied once per pooled value (models/stofnet.py:89-91)
+            float *dst = p.pooled + ((size_t)n * 512 + co) * p.P + p0;
+#pragma unroll
+            for (int w = 0; w < 3; ++w)
+                if (p0 + w < p.P) dst[w] = leaky(m[w] + bias);
         }
     }
 
