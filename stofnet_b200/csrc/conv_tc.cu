@@ -535,15 +535,18 @@ x0_split_kernel(const float *__restrict__ x, const float *__restrict__ e, int N,
         float v[8];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-            float4 a = bs[2 * c8 + h];
+            // packed fp32 FMAs (fma.rn.f32x2, bit-identical to fmaf): half the FMA-pipe instructions of this FMA-bound loop
+            const float4 bq = bs[2 * c8 + h];
+            float2 a01 = make_float2(bq.x, bq.y), a23 = make_float2(bq.z, bq.w);
 #pragma unroll
             for (int t = 0; t < K; ++t) {
                 const float4 wv = ws[t * 16 + 2 * c8 + h];
-                a.x = fmaf(wv.x, xv[t], a.x); a.y = fmaf(wv.y, xv[t], a.y);
-                a.z = fmaf(wv.z, xv[t], a.z); a.w = fmaf(wv.w, xv[t], a.w);
+                const float2 xx = make_float2(xv[t], xv[t]);
+                a01 = __ffma2_rn(make_float2(wv.x, wv.y), xx, a01);
+                a23 = __ffma2_rn(make_float2(wv.z, wv.w), xx, a23);
             }
-            v[4 * h + 0] = fmaxf(a.x, 0.f); v[4 * h + 1] = fmaxf(a.y, 0.f);
-            v[4 * h + 2] = fmaxf(a.z, 0.f); v[4 * h + 3] = fmaxf(a.w, 0.f);
+            v[4 * h + 0] = fmaxf(a01.x, 0.f); v[4 * h + 1] = fmaxf(a01.y, 0.f);
+            v[4 * h + 2] = fmaxf(a23.x, 0.f); v[4 * h + 3] = fmaxf(a23.y, 0.f);
         }
         if (has_e) {
 #pragma unroll

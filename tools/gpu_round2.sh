@@ -2,7 +2,7 @@
 # usage: tools/gpu_round2.sh <tag> [bench steps] -- GPU tests + smoke + bench (exact, fp16) + ncu launch list + ncu full set of the hot kernels
 tag=${1:-run}; steps=${2:-5}
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/${tag}_pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/${tag}_pytest_gpu.log
+timeout 600 python -m pytest tests -m gpu -x -q > gpurun_out/${tag}_pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/${tag}_pytest_gpu.log
 tail -3 gpurun_out/${tag}_pytest_gpu.log
 timeout 300 python __graft_entry__.py smoke > gpurun_out/${tag}_smoke.log 2>&1; echo "smoke rc=$?"
 timeout 600 python bench.py --steps $steps --warmup 3 > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench rc=$?"

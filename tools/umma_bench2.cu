@@ -111,6 +111,14 @@ __global__ void __launch_bounds__(416, 1) bench(Cfg c, long long *out, const uin
                             umma_f16(tmem + 128 * b, make_desc((((sb) >> 4) | kALo) + (uint32_t)(128 * b) + (uint32_t)(2 * ks) * R, kHi), B(ks, 0), ia, 1u);
                             umma_f16(tmem + 128 * b + 64, make_desc((((sb) >> 4) | kALo) + (uint32_t)(128 * b) + (uint32_t)(8 + 2 * ks) * R, kHi), B(ks, 0), ib, 1u);
                         }
+                    } else if (v == 9) {     // term split: BOTH warps work on block 0 - warp 0 issues the hi products, warp 1 the lo ones (own columns)
+                        if (b == 0) {
+#pragma unroll
+                            for (int ks = 0; ks < 4; ++ks) umma_f16(tmem, A(0, 0, ks), B(ks, 0), ia, 1u);
+                        } else {
+#pragma unroll
+                            for (int ks = 0; ks < 4; ++ks) umma_f16(tmem + 128, A(0, 1, ks), B(ks, 0), ib, 1u);
+                        }
                     } else if (v == 8) {     // N192 single MMA (hi x [Whi;Wlo;Whi-ish]) - operand-traffic probe
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks) umma_f16(tmem + 256 * b, A(b, 0, ks), B(ks, 0), i192, 1u);
@@ -211,13 +219,13 @@ int main() {
     const char *names[] = {"v0 today: hi N128 + lo N64 overlapping cols, 2 warps", "v1 lo in own columns, 2 warps",
                            "v2 4x hi then 4x lo, own columns, 2 warps", "v3 lo reuses hi descriptor (A reuse probe)",
                            "v4 hi only (N128)", "v5 lo only (N64)", "v6 hi only, 2 accumulators alternating", "v7 today without tap shift",
-                           "v8 N192 single MMA", "", "v10 one issuer: a0 l0 a1 l1", "v11 one issuer: a0 a1 l0 l1 (own cols)",
+                           "v8 N192 single MMA", "v9 term split: 2 warps on ONE block (hi / lo)", "v10 one issuer: a0 l0 a1 l1", "v11 one issuer: a0 a1 l0 l1 (own cols)",
                            "v12 one issuer: a0 a1 l0 l1 (overlapping cols)", "", "", "", "", "", "", "",
                            "v20 contract: one issuer, per 'tap' = one block of 5x4x(N256+N128)", "v21 contract hi only: 5x4xN256"};
     uint8_t *gsrc;
     cudaMalloc(&gsrc, 77 * STAGE);
     cudaMemset(gsrc, 0x3c, 77 * STAGE);
-    for (int vv : {0, 30, 31, 32, 34, 35}) {
+    for (int vv : {0, 30, 9, 31, 32, 34, 35}) {
         const int v = vv % 100 % 30, solo = (vv % 100) >= 30, spin = (vv / 100) % 10, data = (vv / 1000) % 10, reps = 256, tma = vv / 100000;
         Cfg c{vv % 100, reps, data, tma, spin};
         long long h[3] = {0, 0, 0};
