@@ -44,22 +44,70 @@ __device__ __forceinline__ int pk_phys(int q) { return q + (q >> 2); }
 
 // Stage row[cs-12 .. cs+4096+12) into shared memory; outside [0,M) reads as -inf
 // (max_pool1d's implicit padding, utils/mask2samples.py:8).
-template <bool ALIGNED>
-__device__ __forceinline__ void pk_fill(float4 *sm, const float *__restrict__ row, int M, int cs) {
+// Unaligned rows: a global -> register load and a register -> shared store, so that the NEXT chunk's loads are in flight
+// while the current chunk is processed.
+constexpr int PK_PRE = (PK_Q4 + PK_THREADS - 1) / PK_THREADS;     // float4 per thread per chunk (5)
+__device__ __forceinline__ void pk_load(float4 (&pre)[PK_PRE], const float *__restrict__ row, int M, int cs) {
     const float ninf = -INFINITY;
-    for (int q = threadIdx.x; q < PK_Q4; q += PK_THREADS) {
+#pragma unroll
+    for (int k = 0; k < PK_PRE; ++k) {
+        const int q = threadIdx.x + k * PK_THREADS;
         const int g = cs - 4 * PK_HALO4 + 4 * q;
-        float4 v;
-        if (ALIGNED && g >= 0 && g + 3 < M) {
-            v = __ldg(reinterpret_cast<const float4 *>(row + g));
-        } else {
+        float4 v = make_float4(ninf, ninf, ninf, ninf);
+        if (q < PK_Q4) {
             v.x = (g + 0 >= 0 && g + 0 < M) ? __ldg(row + g + 0) : ninf;
             v.y = (g + 1 >= 0 && g + 1 < M) ? __ldg(row + g + 1) : ninf;
             v.z = (g + 2 >= 0 && g + 2 < M) ? __ldg(row + g + 2) : ninf;
             v.w = (g + 3 >= 0 && g + 3 < M) ? __ldg(row + g + 3) : ninf;
         }
-        sm[pk_phys(q)] = v;
+        pre[k] = v;
     }
+}
+__device__ __forceinline__ void pk_store(float4 *sm, const float4 (&pre)[PK_PRE]) {
+#pragma unroll
+    for (int k = 0; k < PK_PRE; ++k) {
+        const int q = threadIdx.x + k * PK_THREADS;
+        if (q < PK_Q4) sm[pk_phys(q)] = pre[k];
+    }
+}
+// Aligned rows: the chunk goes global -> shared with 16-byte cp.async into the other of two chunk buffers (no registers held
+// across the chunk's work, so four CTAs per SM each keep a whole 16 KB chunk in flight); float4 slots that straddle the row
+// ends are filled with plain loads.
+__device__ __forceinline__ void pk_fill_async(float4 *sm, const float *__restrict__ row, int M, int cs) {
+    const float ninf = -INFINITY;
+    if (cs >= 4 * PK_HALO4 && cs + PK_CHUNK + 4 * PK_HALO4 <= M) {
+        // interior chunk: every slot lies inside the row, no per-slot bounds checks
+        const float *src = row + cs - 4 * PK_HALO4;
+#pragma unroll
+        for (int k = 0; k < PK_Q4 / PK_THREADS; ++k) {
+            const int q = threadIdx.x + k * PK_THREADS;
+            const uint32_t d = (uint32_t)__cvta_generic_to_shared(sm + pk_phys(q));
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src + 4 * q) : "memory");
+        }
+        if (threadIdx.x < PK_Q4 % PK_THREADS) {
+            const int q = threadIdx.x + (PK_Q4 / PK_THREADS) * PK_THREADS;
+            const uint32_t d = (uint32_t)__cvta_generic_to_shared(sm + pk_phys(q));
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src + 4 * q) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        return;
+    }
+    for (int q = threadIdx.x; q < PK_Q4; q += PK_THREADS) {
+        const int g = cs - 4 * PK_HALO4 + 4 * q;
+        float4 *dst = sm + pk_phys(q);
+        if (g >= 0 && g + 3 < M) {
+            const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst);
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(row + g) : "memory");
+        } else {
+            float4 v;
+            v.x = (g + 0 >= 0 && g + 0 < M) ? __ldg(row + g + 0) : ninf;
+            v.y = (g + 1 >= 0 && g + 1 < M) ? __ldg(row + g + 1) : ninf;
+            v.z = (g + 2 >= 0 && g + 2 < M) ? __ldg(row + g + 2) : ninf;
+            v.w = (g + 3 >= 0 && g + 3 < M) ? __ldg(row + g + 3) : ninf;
+            *dst = v;
+        }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
 }
 
 // sup[j] = (x == window21max ? 1 : 0) * x for the 16 samples owned by this thread
@@ -142,10 +190,21 @@ peaks_kernel(const float *__restrict__ scores, int N, int M, int h, int th_is_no
         const bool measuring = th_is_none && pass == 0;
         float mx = -INFINITY;
         int nan = 0;
+        float4 pre[PK_PRE];
+        float4 *buf = pk_sm4;                            // WIN21 && ALIGNED: two chunk buffers, the next one filling by cp.async
+        if (WIN21 && ALIGNED) pk_fill_async(pk_sm4, row, M, 0);
+        else if (WIN21) pk_load(pre, row, M, 0);
         for (int cs = 0; cs < M; cs += PK_CHUNK) {
+            if (WIN21 && ALIGNED) {
+                asm volatile("cp.async.wait_all;" ::: "memory");
+                __syncthreads();                         // chunk cs visible to all; everyone is done with the other buffer
+                buf = pk_sm4 + ((cs / PK_CHUNK) & 1) * PK_SMEM4;
+                if (cs + PK_CHUNK < M) pk_fill_async(pk_sm4 + (((cs / PK_CHUNK) + 1) & 1) * PK_SMEM4, row, M, cs + PK_CHUNK);
+            } else {
             __syncthreads();
             if (WIN21) {
-                pk_fill<ALIGNED>(pk_sm4, row, M, cs);
+                pk_store(pk_sm4, pre);
+                if (cs + PK_CHUNK < M) pk_load(pre, row, M, cs + PK_CHUNK);      // prefetch behind this chunk's work
             } else {
                 for (int i = threadIdx.x; i < PK_CHUNK + 2 * h; i += PK_THREADS) {
                     const int g = cs - h + i;
@@ -153,10 +212,30 @@ peaks_kernel(const float *__restrict__ scores, int N, int M, int h, int th_is_no
                 }
             }
             __syncthreads();
+            }
             float x[PK_E], sup[PK_E];
             const int p0 = cs + PK_E * threadIdx.x;
             if (WIN21) {
-                pk_nms21(pk_sm4, x, sup);
+                // Pre-filter (extraction passes only): a sample can survive only if !(x < limit) - limit = th, or the row max of
+                // the suppressed scores in the row-max mode - or if x = -inf (0 * -inf = NaN counts as non-zero, like the
+                // reference); NaN fails `x < limit` and is covered.  A warp none of whose 512 samples qualifies skips the
+                // window-max arithmetic, which otherwise (not the 4 M bytes per row) paces this kernel on mask-like data.
+                bool need = (nms_out != nullptr) || measuring || (th_is_none && rownan);
+                if (!need) {
+                    const float limit = th_is_none ? rowmax : th;
+#pragma unroll
+                    for (int m = 0; m < 4; ++m) {
+                        const float4 t = buf[pk_phys(4 * threadIdx.x + 3 + m)];
+                        need = need || !(t.x < limit) || !(t.y < limit) || !(t.z < limit) || !(t.w < limit) ||
+                               t.x == -INFINITY || t.y == -INFINITY || t.z == -INFINITY || t.w == -INFINITY;
+                    }
+                }
+                if (__any_sync(0xffffffffu, need)) {
+                    pk_nms21(buf, x, sup);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < PK_E; ++j) sup[j] = 0.0f;          // nothing here can be kept: same flags as the full path
+                }
             } else {
 #pragma unroll 1
                 for (int j = 0; j < PK_E; ++j) sup[j] = pk_nms_generic(sm, halo + PK_E * threadIdx.x + j, h);
@@ -287,7 +366,7 @@ static int launch_peaks(const float *scores, int N, int M, int window, int th_is
     const float rf = (float)upsample_factor;
     unsigned long long *st64 = reinterpret_cast<unsigned long long *>(stats);
     if (h == 10) {
-        const size_t smem = sizeof(float4) * PK_SMEM4;
+        const size_t smem = sizeof(float4) * PK_SMEM4 * (aligned ? 2 : 1);     // aligned rows: two chunk buffers (cp.async)
         if (aligned)
             peaks_kernel<true, true><<<N, PK_THREADS, smem, st>>>(scores, N, M, h, th_is_none, th, rf, coords, pos, cap, counts, st64, nms_out);
         else
