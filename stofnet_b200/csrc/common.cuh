@@ -34,6 +34,23 @@ inline void count_launch(unsigned long long n = 1) { g_launches.fetch_add(n, std
         if (!(cond)) { ::stof::set_error(__VA_ARGS__); return (code); }         \
     } while (0)
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is per device: done once per (kernel, device) - a process may hold one
+// model handle per GPU
+struct SmemAttrOnce {
+    std::atomic<unsigned long long> done{0};
+};
+template <typename K>
+inline int ensure_dyn_smem(K kernel, int bytes, SmemAttrOnce &once) {
+    int dev = 0;
+    STOF_CUDA(cudaGetDevice(&dev));
+    const unsigned long long bit = 1ull << (dev & 63);
+    if (!(once.done.load(std::memory_order_acquire) & bit)) {
+        STOF_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        once.done.fetch_or(bit, std::memory_order_release);
+    }
+    return STOF_OK;
+}
+
 constexpr int kSMs = 148;           // B200: 2 dies x 74 SMs
 constexpr float kLeakySlope = 0.01f;  // nn.LeakyReLU() / F.leaky_relu default (models/stofnet.py:56,89,95)
 

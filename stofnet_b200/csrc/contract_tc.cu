@@ -301,11 +301,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
 
 int launch_contract_pool_tc(const float *x, const void *w, const float *bias, const float *w1, const float *b1, float *pooled,
                             int N, int L, int P, cudaStream_t st, int fast) {
-    static bool attr = false;
-    if (!attr) {
-        STOF_CUDA(cudaFuncSetAttribute(contract_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM_BYTES));
-        attr = true;
-    }
+    static SmemAttrOnce attr;
+    { const int rc = ensure_dyn_smem(contract_tc_kernel, CT_SMEM_BYTES, attr); if (rc) return rc; }
     ContractParams p;
     p.x = x; p.w = w; p.bias = bias; p.w1 = w1; p.b1 = b1; p.pooled = pooled;
     p.N = N; p.L = L; p.P = P; p.fast = fast;

@@ -474,13 +474,13 @@ int launch_conv_first(const float *x, int N, int L, const float *w, const float 
 
 int launch_conv_mid_simt(const float *in, const float *res, float *out, const float *w, const float *b, int N, int L,
                          int epi, cudaStream_t st) {
-    static bool attr = false;
+    static SmemAttrOnce attr0, attr1, attr2;
     const size_t smem = mid_smem(7);
-    if (!attr) {
-        STOF_CUDA(cudaFuncSetAttribute(conv_mid_simt_kernel<7, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        STOF_CUDA(cudaFuncSetAttribute(conv_mid_simt_kernel<7, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        STOF_CUDA(cudaFuncSetAttribute(conv_mid_simt_kernel<7, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr = true;
+    {
+        int rc = ensure_dyn_smem(conv_mid_simt_kernel<7, 0>, (int)smem, attr0);
+        if (!rc) rc = ensure_dyn_smem(conv_mid_simt_kernel<7, 1>, (int)smem, attr1);
+        if (!rc) rc = ensure_dyn_smem(conv_mid_simt_kernel<7, 2>, (int)smem, attr2);
+        if (rc) return rc;
     }
     const int tpr = (L + 255) / 256;
     const long long total = (long long)N * tpr;
@@ -494,12 +494,9 @@ int launch_conv_mid_simt(const float *in, const float *res, float *out, const fl
 
 int launch_contract_pool_simt(const float *in, float *pooled, const float *w, const float *b, int N, int L, int P,
                               cudaStream_t st, int *argmax) {
-    static bool attr = false;
+    static SmemAttrOnce attr;
     const size_t smem = mid_smem(5) + sizeof(float) * 64 * 32 * 2;
-    if (!attr) {
-        STOF_CUDA(cudaFuncSetAttribute(contract_pool_simt_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr = true;
-    }
+    { const int rc = ensure_dyn_smem(contract_pool_simt_kernel<5>, (int)smem, attr); if (rc) return rc; }
     const int tpr = (P + 2) / 3;
     const long long total = (long long)N * tpr;
     const int grid = (int)(total < kSMs ? total : kSMs);

@@ -604,12 +604,9 @@ void set_chain_timeline(void *dev_buf, int cap) { g_timeline = reinterpret_cast<
 int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void *x0, void *out_planes, float *out_mask,
                     int N, int L, cudaStream_t st, int fast) {
     STOF_REQUIRE(count >= 1 && count <= TC_MAX_LAYERS, STOF_E_INVALID, "chain_tc: %d layers per segment (max %d)", count, TC_MAX_LAYERS);
-    static bool attr = false;
-    if (!attr) {
-        STOF_CUDA(cudaFuncSetAttribute(chain_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-        STOF_CUDA(cudaFuncSetAttribute(chain_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-        attr = true;
-    }
+    static SmemAttrOnce attr_exact, attr_fast;
+    { const int rc = fast ? ensure_dyn_smem(chain_tc_kernel<true>, TC_SMEM_BYTES, attr_fast)
+                          : ensure_dyn_smem(chain_tc_kernel<false>, TC_SMEM_BYTES, attr_exact); if (rc) return rc; }
     TcParams p;
     memset(&p, 0, sizeof(p));
     int S = 0, Sp = 0;

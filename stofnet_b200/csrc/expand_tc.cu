@@ -233,11 +233,8 @@ __global__ void __launch_bounds__(XT_THREADS, 1) expand_tc_kernel(const ExpandPa
 }
 
 int launch_expand_tc(const float *pooled, float *e, const void *w_packed, const float *bias, int N, int P, cudaStream_t st) {
-    static bool attr = false;
-    if (!attr) {
-        STOF_CUDA(cudaFuncSetAttribute(expand_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, XT_SMEM_BYTES));
-        attr = true;
-    }
+    static SmemAttrOnce attr;
+    { const int rc = ensure_dyn_smem(expand_tc_kernel, XT_SMEM_BYTES, attr); if (rc) return rc; }
     ExpandParams p;
     p.pooled = pooled; p.e = e; p.w = w_packed; p.bias = bias; p.N = N; p.P = P;
     p.slots = (long long)N * (P + 4);

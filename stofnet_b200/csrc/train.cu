@@ -529,11 +529,8 @@ static int mid_wgrad(const float *G, const float *A, int N, int L, float *partia
     const long long total = (long long)N * tpr;
     const int grid = (int)(total < WG_MAX_PARTS ? total : WG_MAX_PARTS);
     constexpr int smem = 16 * (WG_GP + WG_AP) * sizeof(float4);
-    static bool attr = false;
-    if (!attr) {
-        STOF_CUDA(cudaFuncSetAttribute(mid_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        attr = true;
-    }
+    static SmemAttrOnce attr;
+    { const int rc = ensure_dyn_smem(mid_wgrad_kernel, (int)smem, attr); if (rc) return rc; }
     mid_wgrad_kernel<<<grid, 256, smem, st>>>(reinterpret_cast<const float4 *>(G), reinterpret_cast<const float4 *>(A), N, L, tpr, partial);
     STOF_LAUNCH_CHECK();
     reduce_parts_kernel<<<(unsigned)((WG_MID_LEN + 255) / 256), 256, 0, st>>>(partial, grid, WG_MID_LEN, dW, 64 * 64 * 7, db);
