@@ -185,6 +185,14 @@ uint64_t stof_launch_count(void);
  *   estimate give 0, NaN, NaN, NaN, 0, 0, 0 exactly like the reference's 0/0 divisions                  */
 int stof_toa_rmse(const float *gt_dev, int G, const float *es_dev, int E, int N, float tol, float *out_dev, void *stream);
 
+/* Replaces the `echo_max` branch of mask2coords (utils/mask2samples.py:103-111) with reduce_echoes (:117-132) and
+ * get_amplitudes (:135-136): per row keep the echo_max entries of the position table with the largest mask amplitude
+ * scores[row][round(position)] (descending, NaN first, ties in table order), re-ordered by position, / divisor.
+ *   scores_dev (N, M) fp32 (may be NULL when K <= echo_max), coords_dev (N, K) fp32 positions (undivided, zero padded,
+ *   row stride ld >= K), out_dev (N, echo_max) fp32; K <= echo_max copies the table and pads it with zeros (:107-109).  */
+int stof_reduce_echoes(const float *scores_dev, int N, int M, const float *coords_dev, int ld, int K, int echo_max,
+                       float divisor, float *out_dev, void *stream);
+
 /* Replaces coords2mask (utils/mask2samples.py:139-148): mask = 0; mask[n, max(s,0)] = 1; mask[n, 0] = 0.
  *   samples_dev (N, G) int64 (negative entries are clamped to 0 IN PLACE like the reference; entries >= M raise in
  *   torch's scatter_ and are ignored here), mask_dev (N, M) fp32                                        */

@@ -178,6 +178,28 @@ def mask2coords(scores, window, threshold=None, upsample_factor=1):
     return coords
 
 
+def mask2coords_echo_max(scores, window, threshold, upsample_factor, echo_max):
+    """mask2coords with echo_max (utils/mask2samples.py:103-111, reduce_echoes :117-132, get_amplitudes :135-136), numpy
+    on top of the C stage-4 oracle: amplitudes at the rounded (undivided) positions, stable descending sort, first echo_max,
+    stable ascending sort by position, zero padding when echo_max > K_max, division last."""
+    s = _f32(scores)
+    coords = mask2coords(s, window, threshold, 1)
+    if coords.ndim == 3:
+        return coords
+    rows = s.reshape(s.shape[0], s.shape[-1])
+    K = coords.shape[1]
+    if echo_max < K:
+        amps = np.take_along_axis(rows, np.rint(coords).astype(np.int64), axis=1)
+        key = np.where(np.isnan(amps), np.float32(np.inf), amps)                    # torch.sort: NaN is the largest value
+        nanfirst = np.isnan(amps)
+        order = np.lexsort((np.arange(K)[None, :].repeat(len(rows), 0), -key.astype(np.float64), ~nanfirst), axis=1)[:, :echo_max]
+        kept = np.take_along_axis(coords, order, axis=1)
+        coords = np.take_along_axis(kept, np.argsort(kept, axis=1, kind="stable"), axis=1)
+    elif echo_max > K:
+        coords = np.concatenate([coords, np.zeros((coords.shape[0], echo_max - K), np.float32)], axis=1)
+    return (coords / np.float32(upsample_factor)).astype(np.float32)
+
+
 def coords2mask(samples, M):
     s = np.ascontiguousarray(samples, dtype=np.int64)
     s2 = s.reshape(s.shape[0], s.shape[-1])

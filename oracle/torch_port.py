@@ -96,8 +96,18 @@ def get_maxima_positions(scores, window_size, threshold=None):
     return torch.nonzero(s.squeeze(1), as_tuple=False).long()
 
 
-def mask2coords(scores, window_size, threshold=None, upsample_factor=1):
-    """utils/mask2samples.py:81-114 (echo_max=None), including its per-row Python pack loop."""
+def reduce_echoes(pairs, echo_max):
+    """utils/mask2samples.py:117-132: (N, K, 2) [position, amplitude] -> the echo_max largest amplitudes, by position."""
+    if pairs.shape[1] > echo_max:
+        order = torch.argsort(pairs[..., 1], descending=True, dim=1, stable=True)
+        pairs = torch.gather(pairs, 1, order[..., None].expand(-1, -1, 2))[:, :echo_max]
+        order = torch.argsort(pairs[..., 0], descending=False, dim=1, stable=True)
+        pairs = torch.gather(pairs, 1, order[..., None].expand(-1, -1, 2))
+    return pairs
+
+
+def mask2coords(scores, window_size, threshold=None, upsample_factor=1, echo_max=None):
+    """utils/mask2samples.py:81-114, including its per-row Python pack loop and the echo_max branch (:103-110)."""
     idx = get_maxima_positions(scores, window_size, threshold)
     if idx.numel() == 0:
         return torch.zeros((scores.shape[0], scores.shape[1], 1))
@@ -111,6 +121,11 @@ def mask2coords(scores, window_size, threshold=None, upsample_factor=1):
     flat = flat[flat >= 0]
     coords = torch.zeros((n, kmax))
     coords.view(-1)[flat] = idx[:, 1].float()
+    if echo_max and echo_max < coords.shape[-1]:
+        amps = torch.gather(scores.squeeze(), -1, torch.round(coords).long())          # get_amplitudes :135-136
+        coords = reduce_echoes(torch.dstack([coords, amps]), echo_max)[..., 0]
+    elif echo_max and echo_max > coords.shape[-1]:
+        coords = torch.cat([coords, torch.zeros(coords.shape[0], echo_max - coords.shape[-1])], dim=-1)
     coords /= upsample_factor
     return coords
 

@@ -73,6 +73,7 @@ _SIGS = {
     # operators either side of the path
     "stof_toa_rmse": (_i, [_vp, _i, _vp, _i, _i, _f, _vp, _vp]),
     "stof_coords2mask": (_i, [_vp, _i, _i, _i, _vp, _vp]),
+    "stof_reduce_echoes": (_i, [_vp, _i, _i, _vp, _i, _i, _i, _f, _vp, _vp]),
     "stof_loss_scratch_bytes": (_sz, [_i, _i]),
     "stof_mask_loss": (_i, [_vp, _vp, _i, _i, _i, _vp, _i, _f, _f, _i, _vp, _vp, _vp, _vp, _vp]),
     "stof_threshold_scratch_bytes": (_sz, [_i, _i]),

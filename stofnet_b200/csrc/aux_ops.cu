@@ -1,6 +1,7 @@
 // Operators either side of the inference path, as hand-written kernels behind the C ABI:
 //   stof_toa_rmse        utils/metrics.py:9-41        (consumer of the ToF table, `etol`)
 //   stof_coords2mask     utils/mask2samples.py:139-148
+//   stof_reduce_echoes   utils/mask2samples.py:103-110,117-137   (`echo_max` amplitude selection of mask2coords)
 //   stof_mask_loss       main.py:228-232 + utils/gaussian.py:4-7   (loss value and d loss / d pred)
 //   stof_find_threshold  utils/threshold.py:6-28      (sklearn.metrics.roc_curve restated on the device)
 //   stof_rf_upscale      datasets/chirp_dataset.py:10-17,79-91     (rf_scale_factor pre-interpolation)
@@ -14,6 +15,56 @@
 namespace stof {
 
 __device__ __forceinline__ bool valid_sample(float v) { return v != 0.0f && isfinite(v); }   // metrics.py:6 remove_invalids
+
+// ------------------------------------------------------------------------------------------------
+// echo_max selection of mask2coords (utils/mask2samples.py:103-110, reduce_echoes :117-132, get_amplitudes :135-136):
+// amplitude of entry j = scores[row][round(position j)]; keep the echo_max largest amplitudes (descending sort, NaN first
+// like torch.sort; equal amplitudes in table order), then order the kept entries by position.  One block per row; the
+// table has at most a few hundred entries per row, so both orderings are rank counts over the row held in shared memory.
+// K <= echo_max: the table is copied and zero padded (:107-109).  Every output is divided by `divisor` (:111).
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool amp_before(float a, int ia, float b, int ib) {     // a sorts before b (descending, stable)
+    const bool an = isnan(a), bn = isnan(b);
+    if (an || bn) return (an && !bn) || (an && bn && ia < ib);
+    return a > b || (a == b && ia < ib);
+}
+
+__global__ void __launch_bounds__(128)
+reduce_echoes_kernel(const float *__restrict__ scores, int N, int M, const float *__restrict__ coords, int ld, int K, int echo_max,
+                     float divisor, float *__restrict__ out) {
+    extern __shared__ float re_sm[];
+    float *pos = re_sm, *amp = re_sm + K;
+    int *keep = reinterpret_cast<int *>(re_sm + 2 * K);
+    const int row = blockIdx.x;
+    const float *c = coords + (size_t)row * ld;
+    float *o = out + (size_t)row * echo_max;
+    if (K <= echo_max) {
+        for (int j = threadIdx.x; j < echo_max; j += blockDim.x) o[j] = (j < K) ? __ldg(c + j) / divisor : 0.0f;
+        return;
+    }
+    const float *s = scores + (size_t)row * M;
+    for (int j = threadIdx.x; j < K; j += blockDim.x) {
+        const float p = __ldg(c + j);
+        const int i = min(max((int)rintf(p), 0), M - 1);              // torch.round: half to even
+        pos[j] = p;
+        amp[j] = __ldg(s + i);
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < K; j += blockDim.x) {
+        const float a = amp[j];
+        int rank = 0;
+        for (int i = 0; i < K; ++i) rank += (i != j && amp_before(amp[i], i, a, j)) ? 1 : 0;
+        keep[j] = rank < echo_max ? 1 : 0;
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < K; j += blockDim.x) {
+        if (!keep[j]) continue;
+        const float p = pos[j];
+        int slot = 0;
+        for (int i = 0; i < K; ++i) slot += (keep[i] && (pos[i] < p || (pos[i] == p && i < j))) ? 1 : 0;
+        o[slot] = p / divisor;
+    }
+}
 
 // ------------------------------------------------------------------------------------------------
 // toa_rmse: one warp per row.  Lane i walks the ground-truth entries i, i+32, ...; every entry scans the row's estimates
@@ -215,6 +266,18 @@ extern "C" int stof_toa_rmse(const float *gt_dev, int G, const float *es_dev, in
     STOF_REQUIRE(gt_dev && es_dev && out_dev && N > 0 && G > 0 && E > 0, STOF_E_INVALID,
                  "stof_toa_rmse: bad arguments (N=%d G=%d E=%d)", N, G, E);
     toa_rmse_kernel<<<(N + 7) / 8, 256, 0, (cudaStream_t)stream>>>(gt_dev, G, es_dev, E, N, tol, out_dev);
+    STOF_LAUNCH_CHECK();
+    return STOF_OK;
+}
+
+extern "C" int stof_reduce_echoes(const float *scores_dev, int N, int M, const float *coords_dev, int ld, int K, int echo_max,
+                                  float divisor, float *out_dev, void *stream) {
+    STOF_REQUIRE(coords_dev && out_dev && N > 0 && M > 0 && K > 0 && ld >= K && echo_max > 0, STOF_E_INVALID,
+                 "stof_reduce_echoes: bad arguments (N=%d M=%d K=%d ld=%d echo_max=%d)", N, M, K, ld, echo_max);
+    STOF_REQUIRE(K <= echo_max || scores_dev, STOF_E_INVALID, "stof_reduce_echoes: scores needed to select %d of %d echoes", echo_max, K);
+    STOF_REQUIRE(K <= 4096, STOF_E_UNSUPPORTED, "stof_reduce_echoes: at most 4096 table columns (got %d)", K);
+    STOF_REQUIRE(divisor != 0.0f, STOF_E_INVALID, "stof_reduce_echoes: divisor 0");
+    reduce_echoes_kernel<<<N, 128, (size_t)K * 12, (cudaStream_t)stream>>>(scores_dev, N, M, coords_dev, ld, K, echo_max, divisor, out_dev);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }

@@ -94,33 +94,33 @@ def mask2coords(scores, window_size, threshold=None, upsample_factor=1, echo_max
     """(N, K_max) fp32 time-of-flight table: ascending positions / upsample_factor, zero padded
     (reference :81-114)."""
     rows = _as_rows(scores)
-    N = rows.shape[0]
+    N, M = rows.shape
     int_r = isinstance(upsample_factor, int) or float(upsample_factor).is_integer()
+    if echo_max:
+        # reference :103-111: the amplitude selection works on the undivided positions, the division comes last.
+        # One kernel (stof_reduce_echoes): amplitudes, keep the echo_max largest, re-order by position, zero pad, divide.
+        pos, _, _, kmax, _ = _run_peaks(rows, window_size, threshold, 1, False, _DEFAULT_CAP)
+        if kmax == 0:
+            return torch.zeros((scores.shape[0], scores.shape[1] if scores.dim() == 3 else 1, 1), device=scores.device)
+        echo_max = int(echo_max)
+        out = torch.empty((N, echo_max), dtype=torch.float32, device=rows.device)
+        with torch.cuda.device(rows.device):
+            check(lib.stof_reduce_echoes(rows.data_ptr(), N, M, pos.data_ptr(), pos.shape[1], kmax, echo_max,
+                                         float(upsample_factor), out.data_ptr(), stream_ptr(rows.device)))
+        return out
     coords, _, counts, kmax, _ = _run_peaks(rows, window_size, threshold, int(upsample_factor) if int_r else 1,
                                             False, _DEFAULT_CAP)
     if kmax == 0:
         return torch.zeros((scores.shape[0], scores.shape[1] if scores.dim() == 3 else 1, 1), device=scores.device)
     coords = coords[:, :kmax].contiguous()
-    if echo_max:
-        # reference :105-110 applies the amplitude selection BEFORE dividing by upsample_factor
-        if echo_max < coords.shape[-1]:
-            if int_r:
-                coords = coords * int(upsample_factor)
-            amplitudes = get_amplitudes(scores, coords)
-            coords = reduce_echoes(torch.dstack([coords, amplitudes]), echo_max=echo_max)[..., 0]
-            coords = coords / upsample_factor
-            return coords
-        elif echo_max > coords.shape[-1]:
-            pad = torch.zeros(coords.shape[0], echo_max - coords.shape[-1], device=coords.device, dtype=coords.dtype)
-            coords = torch.cat([coords, pad], dim=-1)
     if not int_r:
         coords /= upsample_factor
     return coords
 
 
 def reduce_echoes(samples_and_amps, echo_max=100):
-    """Keep the echo_max largest-amplitude echoes, re-sorted by time (reference :117-132; off the hot
-    path: main.py never passes echo_max)."""
+    """Keep the echo_max largest-amplitude echoes, re-sorted by time (reference :117-132).  Standalone tensor utility with
+    the reference's signature; mask2coords(echo_max=...) itself runs the fused stof_reduce_echoes kernel."""
     echo_num = samples_and_amps.shape[1]
     channel_num = samples_and_amps.shape[-1]
     echoes = samples_and_amps

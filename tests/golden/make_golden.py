@@ -19,6 +19,7 @@ kernels (torch 2.11.0, oneDNN, fp32; fp64 re-run stored beside it as the tie-bre
   espcn_<ckpt>.npz     ESPCN_1D forward masks
   edsr_<ckpt>.npz      EDSR_1D forward masks, fp32 + fp64
   metrics_cases.npz    toa_rmse / coords2mask / find_threshold known answers
+  echo_cases.npz       mask2coords(echo_max=...) : amplitude selection / zero padding (utils/mask2samples.py:103-132)
   train_<ckpt>.npz     three training steps (model -> loss -> autograd -> AdamW, main.py:217-248): gradients
                        of every parameter after the first backward, losses and parameters after each step
   aux_cases.npz        loss + gradient (main.py:228-232 through the reference's ops and autograd),
@@ -217,6 +218,43 @@ def gen_peaks_cases():
     print("peaks cases:", len(names))
 
 
+def gen_echo_cases():
+    """mask2coords with echo_max (reference utils/mask2samples.py:103-111): fewer, equal and more echoes than K_max,
+    rows of very different counts (zero pads compete with their amplitude scores[row][0]), r = 4 / 3 / 2.5."""
+    rng = np.random.default_rng(33)
+    cases, names = {}, []
+
+    def add(name, scores, th, echo_max, win=20, r=4):
+        s = torch.from_numpy(np.ascontiguousarray(scores, dtype=np.float32))
+        co = mask2coords(s.clone(), win, th, upsample_factor=r, echo_max=echo_max)
+        cases[name + "_scores"] = s.numpy()
+        cases[name + "_th"] = np.float64(np.nan if th is None else th)
+        cases[name + "_win"] = np.int64(win)
+        cases[name + "_r"] = np.float64(r)
+        cases[name + "_echo_max"] = np.int64(echo_max)
+        cases[name + "_coords"] = co.numpy().astype(np.float32)
+        names.append(name)
+
+    x = rng.normal(size=(6, 1, 2000))
+    kmax = mask2coords(torch.from_numpy(x.astype(np.float32)), 20, 1.0).shape[-1]
+    for e in (1, 5, kmax - 1, kmax, kmax + 7):
+        add("noise_e%d" % e, x, 1.0, e)
+    add("noise_r3", x, 1.0, 9, r=3)
+    add("noise_rfloat", x, 1.0, 9, r=2.5)
+    add("none_pad", x, None, 3)
+    y = np.abs(rng.normal(size=(5, 1, 1500)))
+    y[1] *= 0.05                      # a row with almost no detections: its zero pads enter the selection ...
+    y[1, 0, 0] = 9.0                  # ... and win it, because their amplitude is scores[row][0]
+    y[3, 0, 40:1400] = 0.0
+    add("ragged_e4", y, 1.2, 4)
+    add("ragged_e12", y, 1.2, 12, win=8, r=1)
+    # (equal amplitudes across the cut are left out: the reference's argsort is the unstable one, so which of two equal
+    #  echoes survives is implementation-defined there; the oracle and the kernel keep table order)
+    cases["names"] = np.array(names)
+    np.savez_compressed(os.path.join(HERE, "echo_cases.npz"), **cases)
+    print("echo cases:", len(names), "kmax", kmax)
+
+
 def gen_metrics_cases():
     rng = np.random.default_rng(21)
     out = {}
@@ -401,12 +439,16 @@ if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "edsr":
         gen_edsr()
         sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "echo":
+        gen_echo_cases()
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "aux":
         gen_aux_cases()
         sys.exit(0)
     gen_forward()
     gen_edsr()
     gen_peaks_cases()
+    gen_echo_cases()
     gen_metrics_cases()
     gen_aux_cases()
     gen_train_cases()

@@ -46,6 +46,19 @@ def test_stage4_edge_cases_bit_exact(sb, dev, golden):
         assert np.array_equal(co, g[name + "_coords"]), name
 
 
+def test_echo_max_bit_exact(sb, dev, golden):
+    """mask2coords(echo_max=...) through stof_reduce_echoes vs the reference's outputs (tests/golden/echo_cases.npz)."""
+    g = golden("echo_cases.npz")
+    for name in g["names"]:
+        s = torch.from_numpy(g[name + "_scores"]).to(dev)
+        th = float(g[name + "_th"]); th = None if np.isnan(th) else th
+        win, r, e = int(g[name + "_win"]), float(g[name + "_r"]), int(g[name + "_echo_max"])
+        r = int(r) if r.is_integer() else r
+        co = sb.mask2coords(s, win, th, upsample_factor=r, echo_max=e).cpu().numpy()
+        assert co.shape == g[name + "_coords"].shape, (name, co.shape)
+        assert np.array_equal(co, g[name + "_coords"]), name
+
+
 @pytest.mark.parametrize("name", STOF_CKPTS)
 def test_stage4_on_reference_masks(sb, dev, golden, name):
     g = golden("forward_%s.npz" % name)

@@ -121,6 +121,22 @@ def test_stage4_edge_cases(golden):
         assert np.array_equal(torch_port.mask2coords(ts, win, th, r).numpy(), g[name + "_coords"]), name
 
 
+def test_echo_max_cases(golden):
+    """mask2coords(echo_max=...) of the reference (utils/mask2samples.py:103-132) against both oracle restatements."""
+    g = golden("echo_cases.npz")
+    for name in g["names"]:
+        s = g[name + "_scores"]
+        th = float(g[name + "_th"])
+        th = None if np.isnan(th) else th
+        win, r, e = int(g[name + "_win"]), float(g[name + "_r"]), int(g[name + "_echo_max"])
+        r = int(r) if r.is_integer() else r
+        want = g[name + "_coords"]
+        got = torch_port.mask2coords(torch.from_numpy(s), win, th, r, echo_max=e).numpy()
+        assert got.shape == want.shape and np.array_equal(got, want), name
+        got = c_oracle.mask2coords_echo_max(s, win, th, r, e)
+        assert got.shape == want.shape and np.array_equal(got, want), name
+
+
 def test_bad_lengths_raise(golden):
     sd = golden("weights_different-armadillo.npz")
     for L in (79, 161, 1001):
