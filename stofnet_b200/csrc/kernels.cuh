@@ -17,6 +17,9 @@ int launch_sgb_add(float *act, const float *e, int N, int L, int P, int scale, i
 int launch_conv_last(const float *in, float *mask, const float *w, const float *b, int N, int L, int cin, int act,
                      cudaStream_t st);
 int launch_espcn_conv2(const float *in, float *out, const float *w, const float *b, int N, int L, cudaStream_t st);
+// ESPCN_1D forward in one kernel (espcn_fused.cu): x (N, L) -> mask (N, 4 L); weights in the layouts of the three kernels above
+int launch_espcn_fused(const float *x, float *mask, int N, int L, const float *w1, const float *b1, const float *w2,
+                       const float *b2, const float *w3, const float *b3, cudaStream_t st);
 
 // conv_tc.cu (tcgen05 / TMEM path) ---------------------------------------------------------------
 constexpr int TC_MAX_LAYERS = 6;

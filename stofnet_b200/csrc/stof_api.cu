@@ -400,7 +400,12 @@ static int forward_chunk(stof_model *m, const float *x, int n, int L, float *mas
     float *e = reinterpret_cast<float *>(ws + 3 * align256(pl.act * 4) + align256(pl.pooled * 4));
     int rc;
     if (m->kind == STOF_KIND_ESPCN) {
-        // models/espcn_1d.py:31-36
+        // models/espcn_1d.py:31-36: one fused kernel; layers_per_launch == 1 (stof_model_set_path) selects the three
+        // layer-by-layer kernels instead, which give bit-identical masks (kept as the cross-check of the fused kernel)
+        if (m->seg_len != 1) {
+            ProfScope p(m, STOF_PROF_MID, st);
+            return launch_espcn_fused(x, mask, n, L, m->first.w, m->first.b, m->mid[0].w, m->mid[0].b, m->last.w, m->last.b, st);
+        }
         { ProfScope p(m, STOF_PROF_FIRST, st); if ((rc = launch_conv_first(x, n, L, m->first.w, m->first.b, B0, 5, 1, st))) return rc; }
         { ProfScope p(m, STOF_PROF_MID, st); if ((rc = launch_espcn_conv2(B0, B1, m->mid[0].w, m->mid[0].b, n, L, st))) return rc; }
         ProfScope p(m, STOF_PROF_LAST, st);

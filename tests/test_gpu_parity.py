@@ -122,6 +122,25 @@ def test_espcn_forward_golden(sb, dev, golden, name):
         assert np.abs(m.squeeze(1).cpu().numpy() - ref).max() <= 2e-5     # sigmoid output in (0, 1)
 
 
+@pytest.mark.parametrize("name", ESPCN_CKPTS)
+def test_espcn_fused_matches_layer_kernels(sb, dev, golden, name):
+    """The fused ESPCN kernel (espcn_fused.cu) against the three layer-by-layer kernels: same accumulation order, so the
+    masks must be bit-identical; lengths around the 126-position tile and the row ends."""
+    model = _model(sb, golden, name, dev)
+    eng = model._engine
+    rng = np.random.default_rng(5)
+    for N, L in ((1, 1), (2, 5), (3, 125), (3, 126), (2, 127), (4, 253), (5, 1000), (37, 2560)):
+        x = torch.from_numpy(rng.normal(size=(N, 1, L)).astype(np.float32)).to(dev)
+        with torch.no_grad():
+            eng.set_path(sb._lib.PATH_SIMT, 4)          # ESPCN_1D: fp32 FFMA kernels only; != 1 -> fused kernel
+            fused = model(x).clone()
+            eng.set_path(sb._lib.PATH_SIMT, 1)          # 1 layer per launch -> conv_first / espcn_conv2 / conv_last kernels
+            layered = model(x).clone()
+            eng.set_path(sb._lib.PATH_SIMT, 4)
+        assert fused.shape == (N, 1, 4 * L)
+        assert torch.equal(fused, layered), (N, L, float((fused - layered).abs().max()))
+
+
 @pytest.mark.parametrize("name", EDSR_CKPTS)
 def test_edsr_forward_golden(sb, dev, golden, name):
     """EDSR_1D on the tensor-core chain (k3 layers, ReLU epilogue, shuffle + conv_output folded into conv_last) against the
