@@ -8,7 +8,7 @@
 //
 // Persistent CTAs (2 per SM), each looping over tiles of EF_T = 126 output positions of one row:
 //   phase A  x[l0-4, l0+130) -> h1[64][130]  (positions l0-2 .. l0+128)   one (position, 4 channels) item per thread step
-//   phase B  h1 -> h2[32][128]               (positions l0-1 .. l0+127)   thread = 2 positions x 8 channels, packed FMAs
+//   phase B  h1 -> h2[32][128]               (positions l0-1 .. l0+127)   thread = 4 positions x 8 channels, packed FMAs
 //   phase C  h2 -> mask[n][4 l .. 4 l + 3]                                 thread = (position, sub-pixel pair), 8-byte store
 // Activations outside [0, L) are the next conv's zero padding, so they are stored as exact zeros (not tanh(bias)).
 // The accumulation order of every sum is the one of the layer-by-layer kernels in conv_simt.cu (bias first, then
@@ -83,24 +83,27 @@ espcn_fused_kernel(const float *__restrict__ x, float *__restrict__ mask, int N,
         }
         __syncthreads();
 
-        // ---- phase B: conv2 + tanh (espcn_1d.py:13,33); thread = positions 2 pp, 2 pp + 1 x channels [8 og, +8) --------
-        {
-            const int og = tid >> 6, pp = tid & 63;        // og is warp-uniform: the weight loads are broadcasts
-            float2 acc[2][4];
+        // ---- phase B: conv2 + tanh (espcn_1d.py:13,33); thread = positions 4 pp .. 4 pp + 3 x channels [8 og, +8) ----------
+        // Warps 0-3 (one per scheduler), og = warp: the weight loads are warp-wide broadcasts, and a 4-position register
+        // tile gets 8 packed FMAs out of every 16-byte weight wavefront - with 2 positions the shared-memory pipe, not the
+        // FMA pipe, bounded this phase.  Warps 4-7 wait at the barrier (the SM's other CTA fills their issue slots).
+        if (tid < 128) {
+            const int og = tid >> 5, pp = tid & 31;
+            float2 acc[4][4];
 #pragma unroll
-            for (int q = 0; q < 2; ++q) {
+            for (int q = 0; q < 4; ++q) {
                 const float4 ba = s.b2[2 * og], bb = s.b2[2 * og + 1];
                 acc[q][0] = make_float2(ba.x, ba.y); acc[q][1] = make_float2(ba.z, ba.w);
                 acc[q][2] = make_float2(bb.x, bb.y); acc[q][3] = make_float2(bb.z, bb.w);
             }
-#pragma unroll 2
+#pragma unroll 1
             for (int c4 = 0; c4 < 16; ++c4) {
-                float hv[4][4];                            // [channel of the group][position 2 pp + 0..3]
+                float hv[4][6];                            // [channel of the group][position 4 pp + 0..5]
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    const float2 lo = *reinterpret_cast<const float2 *>(&s.h1[(4 * c4 + i) * EF_H1P + 2 * pp]);
-                    const float2 hi = *reinterpret_cast<const float2 *>(&s.h1[(4 * c4 + i) * EF_H1P + 2 * pp + 2]);
-                    hv[i][0] = lo.x; hv[i][1] = lo.y; hv[i][2] = hi.x; hv[i][3] = hi.y;
+                    const float4 lo = *reinterpret_cast<const float4 *>(&s.h1[(4 * c4 + i) * EF_H1P + 4 * pp]);
+                    const float2 hi = *reinterpret_cast<const float2 *>(&s.h1[(4 * c4 + i) * EF_H1P + 4 * pp + 4]);
+                    hv[i][0] = lo.x; hv[i][1] = lo.y; hv[i][2] = lo.z; hv[i][3] = lo.w; hv[i][4] = hi.x; hv[i][5] = hi.y;
                 }
 #pragma unroll
                 for (int t = 0; t < 3; ++t) {
@@ -109,7 +112,7 @@ espcn_fused_kernel(const float *__restrict__ x, float *__restrict__ mask, int N,
                         const float4 wa = s.w2[((4 * c4 + i) * 3 + t) * 8 + 2 * og];
                         const float4 wb = s.w2[((4 * c4 + i) * 3 + t) * 8 + 2 * og + 1];
 #pragma unroll
-                        for (int q = 0; q < 2; ++q) {
+                        for (int q = 0; q < 4; ++q) {
                             const float2 xx = make_float2(hv[i][q + t], hv[i][q + t]);
                             acc[q][0] = __ffma2_rn(make_float2(wa.x, wa.y), xx, acc[q][0]);
                             acc[q][1] = __ffma2_rn(make_float2(wa.z, wa.w), xx, acc[q][1]);
@@ -120,15 +123,17 @@ espcn_fused_kernel(const float *__restrict__ x, float *__restrict__ mask, int N,
                 }
             }
 #pragma unroll
-            for (int q = 0; q < 2; ++q) {
-                const int p = 2 * pp + q;
-                const int g = l0 - 1 + p;
-                const bool inside = (g >= 0) && (g < L);
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    s.h2[(8 * og + 2 * k) * EF_H2P + p] = inside ? tanhf(acc[q][k].x) : 0.0f;
-                    s.h2[(8 * og + 2 * k + 1) * EF_H2P + p] = inside ? tanhf(acc[q][k].y) : 0.0f;
-                }
+            for (int k = 0; k < 4; ++k) {
+                float4 v0, v1;                             // channel 8 og + 2 k (+1), positions 4 pp .. 4 pp + 3
+                v0.x = tanhf(acc[0][k].x); v0.y = tanhf(acc[1][k].x); v0.z = tanhf(acc[2][k].x); v0.w = tanhf(acc[3][k].x);
+                v1.x = tanhf(acc[0][k].y); v1.y = tanhf(acc[1][k].y); v1.z = tanhf(acc[2][k].y); v1.w = tanhf(acc[3][k].y);
+                const int g = l0 - 1 + 4 * pp;
+                if (g < 0 || g >= L) { v0.x = 0.0f; v1.x = 0.0f; }
+                if (g + 1 < 0 || g + 1 >= L) { v0.y = 0.0f; v1.y = 0.0f; }
+                if (g + 2 < 0 || g + 2 >= L) { v0.z = 0.0f; v1.z = 0.0f; }
+                if (g + 3 < 0 || g + 3 >= L) { v0.w = 0.0f; v1.w = 0.0f; }
+                *reinterpret_cast<float4 *>(&s.h2[(8 * og + 2 * k) * EF_H2P + 4 * pp]) = v0;
+                *reinterpret_cast<float4 *>(&s.h2[(8 * og + 2 * k + 1) * EF_H2P + 4 * pp]) = v1;
             }
         }
         __syncthreads();
