@@ -6,8 +6,9 @@
 // it) plus 96 tanh per position, so this is a CUDA-core kernel: K = 64 x 3 with N = 32 is far too thin a contraction to
 // pay for operand splitting on the tensor pipe.
 //
-// Persistent CTAs (2 per SM), each looping over tiles of EF_T = 126 output positions of one row:
-//   phase A  x[l0-4, l0+130) -> h1[64][130]  (positions l0-2 .. l0+128)   one (position, 4 channels) item per thread step
+// Persistent CTAs (3 per SM), each looping over tiles of EF_T = 126 output positions of one row:
+//   phase A  x[l0-4, l0+130) -> h1[32][130]  (positions l0-2 .. l0+128)   one (position, 4 channels) item per thread step;
+//            32 of the 64 channels at a time (A, B, A, B), conv2's accumulators live in registers across the halves
 //   phase B  h1 -> h2[32][128]               (positions l0-1 .. l0+127)   thread = 4 positions x 8 channels, packed FMAs
 //   phase C  h2 -> mask[n][4 l .. 4 l + 3]                                 thread = (position, sub-pixel pair), 8-byte store
 // Activations outside [0, L) are the next conv's zero padding, so they are stored as exact zeros (not tanh(bias)).
@@ -27,7 +28,7 @@ constexpr int EF_H2 = EF_T + 2;            // conv2 outputs per tile (128)
 constexpr int EF_H2P = 128;
 
 struct EfSmem {
-    float h1[64 * EF_H1P];
+    float h1[32 * EF_H1P];                 // one half (32 channels) of conv1's output at a time
     float h2[32 * EF_H2P];
     float4 w2[64 * 3 * 8];                 // [ci][t][32 oc]
     float4 w1[5 * 16];                     // [t][64 oc]
@@ -38,7 +39,7 @@ struct EfSmem {
     float x[EF_X + 2];
 };
 
-__global__ void __launch_bounds__(EF_THREADS, 2)
+__global__ void __launch_bounds__(EF_THREADS, 3)
 espcn_fused_kernel(const float *__restrict__ x, float *__restrict__ mask, int N, int L, const float *__restrict__ w1,
                    const float *__restrict__ b1, const float *__restrict__ w2, const float *__restrict__ b2,
                    const float *__restrict__ w3, const float *__restrict__ b3, int tiles_per_row, int total_tiles) {
@@ -63,65 +64,74 @@ espcn_fused_kernel(const float *__restrict__ x, float *__restrict__ mask, int N,
         }
         __syncthreads();
 
-        // ---- phase A: conv1 + tanh (espcn_1d.py:12,32); item = (position, group of 4 output channels) ----------------
-        for (int it = tid; it < EF_H1 * 16; it += EF_THREADS) {
-            const int c4 = it / EF_H1, p = it - c4 * EF_H1;
-            const int g = l0 - 2 + p;
-            float4 a = s.b1[c4];
+        // ---- phases A + B, in two halves of conv1's 64 output channels so that h1 needs 17 KB instead of 34 KB (3 CTAs per
+        //      SM); conv2's accumulators stay in registers across the halves, its sum order (channel ascending) is unchanged
+        const int og = (tid >> 5) & 3, pp = tid & 31;      // phase B: warps 0-3, og = warp (weight loads are broadcasts)
+        float2 acc[4][4];
 #pragma unroll
-            for (int t = 0; t < 5; ++t) {
-                const float4 wv = s.w1[t * 16 + c4];
-                const float xv = s.x[p + t];
-                a.x = fmaf(wv.x, xv, a.x); a.y = fmaf(wv.y, xv, a.y);
-                a.z = fmaf(wv.z, xv, a.z); a.w = fmaf(wv.w, xv, a.w);
-            }
-            const bool inside = (g >= 0) && (g < L);
-            s.h1[(4 * c4 + 0) * EF_H1P + p] = inside ? tanhf(a.x) : 0.0f;
-            s.h1[(4 * c4 + 1) * EF_H1P + p] = inside ? tanhf(a.y) : 0.0f;
-            s.h1[(4 * c4 + 2) * EF_H1P + p] = inside ? tanhf(a.z) : 0.0f;
-            s.h1[(4 * c4 + 3) * EF_H1P + p] = inside ? tanhf(a.w) : 0.0f;
+        for (int q = 0; q < 4; ++q) {
+            const float4 ba = s.b2[2 * og], bb = s.b2[2 * og + 1];
+            acc[q][0] = make_float2(ba.x, ba.y); acc[q][1] = make_float2(ba.z, ba.w);
+            acc[q][2] = make_float2(bb.x, bb.y); acc[q][3] = make_float2(bb.z, bb.w);
         }
-        __syncthreads();
-
-        // ---- phase B: conv2 + tanh (espcn_1d.py:13,33); thread = positions 4 pp .. 4 pp + 3 x channels [8 og, +8) ----------
-        // Warps 0-3 (one per scheduler), og = warp: the weight loads are warp-wide broadcasts, and a 4-position register
-        // tile gets 8 packed FMAs out of every 16-byte weight wavefront - with 2 positions the shared-memory pipe, not the
-        // FMA pipe, bounded this phase.  Warps 4-7 wait at the barrier (the SM's other CTA fills their issue slots).
-        if (tid < 128) {
-            const int og = tid >> 5, pp = tid & 31;
-            float2 acc[4][4];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const float4 ba = s.b2[2 * og], bb = s.b2[2 * og + 1];
-                acc[q][0] = make_float2(ba.x, ba.y); acc[q][1] = make_float2(ba.z, ba.w);
-                acc[q][2] = make_float2(bb.x, bb.y); acc[q][3] = make_float2(bb.z, bb.w);
-            }
 #pragma unroll 1
-            for (int c4 = 0; c4 < 16; ++c4) {
-                float hv[4][6];                            // [channel of the group][position 4 pp + 0..5]
+        for (int half = 0; half < 2; ++half) {
+            if (half) __syncthreads();                     // phase B of the first half is done with h1
+            // ---- phase A: conv1 + tanh (espcn_1d.py:12,32); item = (position, group of 4 output channels) -------------
+            for (int it = tid; it < EF_H1 * 8; it += EF_THREADS) {
+                const int cl = it / EF_H1, p = it - cl * EF_H1;
+                const int c4 = 8 * half + cl;
+                const int g = l0 - 2 + p;
+                float4 a = s.b1[c4];
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const float4 lo = *reinterpret_cast<const float4 *>(&s.h1[(4 * c4 + i) * EF_H1P + 4 * pp]);
-                    const float2 hi = *reinterpret_cast<const float2 *>(&s.h1[(4 * c4 + i) * EF_H1P + 4 * pp + 4]);
-                    hv[i][0] = lo.x; hv[i][1] = lo.y; hv[i][2] = lo.z; hv[i][3] = lo.w; hv[i][4] = hi.x; hv[i][5] = hi.y;
+                for (int t = 0; t < 5; ++t) {
+                    const float4 wv = s.w1[t * 16 + c4];
+                    const float xv = s.x[p + t];
+                    a.x = fmaf(wv.x, xv, a.x); a.y = fmaf(wv.y, xv, a.y);
+                    a.z = fmaf(wv.z, xv, a.z); a.w = fmaf(wv.w, xv, a.w);
                 }
-#pragma unroll
-                for (int t = 0; t < 3; ++t) {
+                const bool inside = (g >= 0) && (g < L);
+                s.h1[(4 * cl + 0) * EF_H1P + p] = inside ? tanhf(a.x) : 0.0f;
+                s.h1[(4 * cl + 1) * EF_H1P + p] = inside ? tanhf(a.y) : 0.0f;
+                s.h1[(4 * cl + 2) * EF_H1P + p] = inside ? tanhf(a.z) : 0.0f;
+                s.h1[(4 * cl + 3) * EF_H1P + p] = inside ? tanhf(a.w) : 0.0f;
+            }
+            __syncthreads();
+            // ---- phase B: conv2 (espcn_1d.py:13,33); thread = positions 4 pp .. 4 pp + 3 x channels [8 og, +8) ---------
+            // A 4-position register tile gets 8 packed FMAs out of every 16-byte weight wavefront - with 2 positions the
+            // shared-memory pipe, not the FMA pipe, bounded this phase.  Warps 4-7 go on to the barrier; the SM's other
+            // CTAs fill their issue slots.
+            if (tid < 128) {
+#pragma unroll 1
+                for (int cl = 0; cl < 8; ++cl) {
+                    const int c4 = 8 * half + cl;
+                    float hv[4][6];                        // [channel of the group][position 4 pp + 0..5]
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
-                        const float4 wa = s.w2[((4 * c4 + i) * 3 + t) * 8 + 2 * og];
-                        const float4 wb = s.w2[((4 * c4 + i) * 3 + t) * 8 + 2 * og + 1];
+                        const float4 lo = *reinterpret_cast<const float4 *>(&s.h1[(4 * cl + i) * EF_H1P + 4 * pp]);
+                        const float2 hi = *reinterpret_cast<const float2 *>(&s.h1[(4 * cl + i) * EF_H1P + 4 * pp + 4]);
+                        hv[i][0] = lo.x; hv[i][1] = lo.y; hv[i][2] = lo.z; hv[i][3] = lo.w; hv[i][4] = hi.x; hv[i][5] = hi.y;
+                    }
 #pragma unroll
-                        for (int q = 0; q < 4; ++q) {
-                            const float2 xx = make_float2(hv[i][q + t], hv[i][q + t]);
-                            acc[q][0] = __ffma2_rn(make_float2(wa.x, wa.y), xx, acc[q][0]);
-                            acc[q][1] = __ffma2_rn(make_float2(wa.z, wa.w), xx, acc[q][1]);
-                            acc[q][2] = __ffma2_rn(make_float2(wb.x, wb.y), xx, acc[q][2]);
-                            acc[q][3] = __ffma2_rn(make_float2(wb.z, wb.w), xx, acc[q][3]);
+                    for (int t = 0; t < 3; ++t) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const float4 wa = s.w2[((4 * c4 + i) * 3 + t) * 8 + 2 * og];
+                            const float4 wb = s.w2[((4 * c4 + i) * 3 + t) * 8 + 2 * og + 1];
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                const float2 xx = make_float2(hv[i][q + t], hv[i][q + t]);
+                                acc[q][0] = __ffma2_rn(make_float2(wa.x, wa.y), xx, acc[q][0]);
+                                acc[q][1] = __ffma2_rn(make_float2(wa.z, wa.w), xx, acc[q][1]);
+                                acc[q][2] = __ffma2_rn(make_float2(wb.x, wb.y), xx, acc[q][2]);
+                                acc[q][3] = __ffma2_rn(make_float2(wb.z, wb.w), xx, acc[q][3]);
+                            }
                         }
                     }
                 }
             }
+        }
+        if (tid < 128) {                                   // tanh + zero padding outside the row -> h2
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 float4 v0, v1;                             // channel 8 og + 2 k (+1), positions 4 pp .. 4 pp + 3
@@ -173,7 +183,7 @@ int launch_espcn_fused(const float *x, float *mask, int N, int L, const float *w
     const int tiles_per_row = (L + EF_T - 1) / EF_T;
     const long long total = (long long)N * tiles_per_row;
     STOF_REQUIRE(total < (1ll << 31), STOF_E_INVALID, "espcn_fused: too many tiles");
-    const int grid = (int)(total < 2 * kSMs ? total : 2 * kSMs);
+    const int grid = (int)(total < 3 * kSMs ? total : 3 * kSMs);
     espcn_fused_kernel<<<grid, EF_THREADS, sizeof(EfSmem), st>>>(x, mask, N, L, w1, b1, w2, b2, w3, b3, tiles_per_row, (int)total);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
