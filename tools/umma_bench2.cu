@@ -138,6 +138,19 @@ __global__ void __launch_bounds__(416, 1) bench(Cfg c, long long *out, const uin
                                 if (v == 20) umma_f16(tmem + 256 * blk + 128, al, db, i128, 1u);
                             }
                     }
+                    if (v >= 13 && v <= 16) {  // role swap probe: weights as A, 256 positions (both blocks) as one N = 256 B operand
+                        const uint32_t i128x256 = umma_idesc_f16(128, 256), i64x256 = umma_idesc_f16(64, 256), i64x128 = umma_idesc_f16(64, 128);
+                        const uint32_t xl = ((sb + OFF_W) >> 4) | (256u << 16);
+#pragma unroll
+                        for (int ks = 0; ks < 4; ++ks) {
+                            const uint64_t aw = make_desc((((sb) >> 4) | kALo) + (uint32_t)(2 * ks) * R, kHi);          // [W_hi; W_lo] 128 rows
+                            const uint64_t aw64 = make_desc((((sb) >> 4) | kALo) + (uint32_t)(8 + 2 * ks) * R, kHi);   // W_hi 64 rows
+                            const uint64_t bx = make_desc(xl + (t & 1) * 2048 + 2 * ks * 256, kHi);
+                            if (v == 13 || v == 15) umma_f16(tmem, aw, bx, i128x256, 1u);
+                            if (v == 14 || v == 15) umma_f16(tmem + 256, aw64, bx, i64x256, 1u);
+                            if (v == 16) umma_f16(tmem + 256, aw64, bx, i64x128, 1u);
+                        }
+                    }
                     // single-warp variants (one issuer for both blocks)
                     if (v == 10) {           // a(b0) b(b0) a(b1) b(b1) per k-step
 #pragma unroll
@@ -220,12 +233,12 @@ int main() {
                            "v2 4x hi then 4x lo, own columns, 2 warps", "v3 lo reuses hi descriptor (A reuse probe)",
                            "v4 hi only (N128)", "v5 lo only (N64)", "v6 hi only, 2 accumulators alternating", "v7 today without tap shift",
                            "v8 N192 single MMA", "v9 term split: 2 warps on ONE block (hi / lo)", "v10 one issuer: a0 l0 a1 l1", "v11 one issuer: a0 a1 l0 l1 (own cols)",
-                           "v12 one issuer: a0 a1 l0 l1 (overlapping cols)", "", "", "", "", "", "", "",
+                           "v12 one issuer: a0 a1 l0 l1 (overlapping cols)", "v13 swap: 4 x (M128 N256) per tap", "v14 swap: 4 x (M64 N256) per tap", "v15 swap: 4 x (M128 N256 + M64 N256) per tap = both blocks", "v16 swap: 4 x (M64 N128) per tap", "", "", "",
                            "v20 contract: one issuer, per 'tap' = one block of 5x4x(N256+N128)", "v21 contract hi only: 5x4xN256"};
     uint8_t *gsrc;
     cudaMalloc(&gsrc, 77 * STAGE);
     cudaMemset(gsrc, 0x3c, 77 * STAGE);
-    for (int vv : {0, 30, 9, 31, 32, 34, 35}) {
+    for (int vv : {0, 13, 14, 15, 16, 21}) {
         const int v = vv % 100 % 30, solo = (vv % 100) >= 30, spin = (vv / 100) % 10, data = (vv / 1000) % 10, reps = 256, tma = vv / 100000;
         Cfg c{vv % 100, reps, data, tma, spin};
         long long h[3] = {0, 0, 0};
