@@ -214,6 +214,7 @@ peaks_kernel(const float *__restrict__ scores, int N, int M, int h, int th_is_no
             __syncthreads();
             }
             float x[PK_E], sup[PK_E];
+            bool skip = false;                           // warp-uniform (extraction passes of the WIN21 path only)
             const int p0 = cs + PK_E * threadIdx.x;
             if (WIN21) {
                 // Pre-filter (extraction passes only): a sample can survive only if !(x < limit) - limit = th, or the row max of
@@ -230,12 +231,8 @@ peaks_kernel(const float *__restrict__ scores, int N, int M, int h, int th_is_no
                                t.x == -INFINITY || t.y == -INFINITY || t.z == -INFINITY || t.w == -INFINITY;
                     }
                 }
-                if (__any_sync(0xffffffffu, need)) {
-                    pk_nms21(buf, x, sup);
-                } else {
-#pragma unroll
-                    for (int j = 0; j < PK_E; ++j) sup[j] = 0.0f;          // nothing here can be kept: same flags as the full path
-                }
+                skip = !__any_sync(0xffffffffu, need);   // nothing in this warp's 512 samples can be kept: flags = 0 below
+                if (!skip) pk_nms21(buf, x, sup);
             } else {
 #pragma unroll 1
                 for (int j = 0; j < PK_E; ++j) sup[j] = pk_nms_generic(sm, halo + PK_E * threadIdx.x + j, h);
@@ -256,6 +253,7 @@ peaks_kernel(const float *__restrict__ scores, int N, int M, int h, int th_is_no
                 continue;
             }
             unsigned flags = 0;
+            if (!skip) {
 #pragma unroll
             for (int j = 0; j < PK_E; ++j) {
                 const float s = sup[j];
@@ -263,6 +261,7 @@ peaks_kernel(const float *__restrict__ scores, int N, int M, int h, int th_is_no
                 if (th_is_none) keep = keep && (rownan || !(s < rowmax));   // masked_fill(s < max, 0) (:21)
                 else            keep = keep && !(s < th);                    // scores[scores < th] = 0 (:17)
                 flags |= (keep ? 1u : 0u) << j;
+            }
             }
             if (__syncthreads_or(flags != 0)) {
                 const int cnt = __popc(flags);
