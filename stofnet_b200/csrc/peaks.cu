@@ -164,6 +164,18 @@ __device__ __forceinline__ RowMax block_rowmax(float mx, int nan, float *s_red) 
 }
 
 // WIN21: specialised register path for window 21 (nms_win_size 20, config.yaml:26); otherwise generic.
+// max.NaN / min over three inputs (FMNMX3 on sm_100): building blocks of the pre-filter in peaks_kernel
+__device__ __forceinline__ float pk_max3nan(float a, float b, float c) {
+    float r;
+    asm("max.NaN.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
+__device__ __forceinline__ float pk_min3(float a, float b, float c) {
+    float r;
+    asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
+
 template <bool WIN21, bool ALIGNED>
 __global__ void __launch_bounds__(PK_THREADS)
 peaks_kernel(const float *__restrict__ scores, int N, int M, int h, int th_is_none, float th,
@@ -223,13 +235,16 @@ peaks_kernel(const float *__restrict__ scores, int N, int M, int h, int th_is_no
                 // window-max arithmetic, which otherwise (not the 4 M bytes per row) paces this kernel on mask-like data.
                 bool need = (nms_out != nullptr) || measuring || (th_is_none && rownan);
                 if (!need) {
+                    // one NaN-propagating maximum and one minimum over the thread's 16 samples (3-input FMNMX3): the largest
+                    // sample decides `!(x < limit)` for all of them (a NaN anywhere makes the maximum NaN), the smallest `-inf`
                     const float limit = th_is_none ? rowmax : th;
-#pragma unroll
-                    for (int m = 0; m < 4; ++m) {
-                        const float4 t = buf[pk_phys(4 * threadIdx.x + 3 + m)];
-                        need = need || !(t.x < limit) || !(t.y < limit) || !(t.z < limit) || !(t.w < limit) ||
-                               t.x == -INFINITY || t.y == -INFINITY || t.z == -INFINITY || t.w == -INFINITY;
-                    }
+                    const float4 t0 = buf[pk_phys(4 * threadIdx.x + 3)], t1 = buf[pk_phys(4 * threadIdx.x + 4)];
+                    const float4 t2 = buf[pk_phys(4 * threadIdx.x + 5)], t3 = buf[pk_phys(4 * threadIdx.x + 6)];
+                    const float hi = pk_max3nan(pk_max3nan(pk_max3nan(t0.x, t0.y, t0.z), pk_max3nan(t0.w, t1.x, t1.y), pk_max3nan(t1.z, t1.w, t2.x)),
+                                                pk_max3nan(pk_max3nan(t2.y, t2.z, t2.w), pk_max3nan(t3.x, t3.y, t3.z), t3.w), t3.w);
+                    const float lo = pk_min3(pk_min3(pk_min3(t0.x, t0.y, t0.z), pk_min3(t0.w, t1.x, t1.y), pk_min3(t1.z, t1.w, t2.x)),
+                                             pk_min3(pk_min3(t2.y, t2.z, t2.w), pk_min3(t3.x, t3.y, t3.z), t3.w), t3.w);
+                    need = !(hi < limit) || lo == -INFINITY;
                 }
                 skip = !__any_sync(0xffffffffu, need);   // nothing in this warp's 512 samples can be kept: flags = 0 below
                 if (!skip) pk_nms21(buf, x, sup);
