@@ -198,6 +198,48 @@ peaks_kernel(const float *__restrict__ scores, int N, int M, int h, int th_is_no
     int rownan = 0;
     const int passes = th_is_none ? 2 : 1;
     int base = 0;
+    __shared__ int s_any[3];                              // "somebody keeps something" per chunk, three slots in rotation
+    if (threadIdx.x < 3) s_any[threadIdx.x] = 0;          // ordered before its first use by the first chunk's barrier
+    unsigned pflags = 0;
+    int pp0 = 0, ci = 0;
+    bool pending = false;
+    // ordered per-row compaction of one chunk's kept samples (block-uniform call: contains a barrier)
+    auto compact = [&](unsigned flags, int p0) {
+        const int cnt = __popc(flags);
+        int inc = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_warp[warp] = inc;
+        __syncthreads();
+        int off = base + inc - cnt, tot = 0;
+#pragma unroll
+        for (int w = 0; w < PK_THREADS / 32; ++w) {
+            const int t = s_warp[w];
+            if (w < warp) off += t;
+            tot += t;
+        }
+        while (flags) {
+            const int j = __ffs(flags) - 1;
+            flags &= flags - 1;
+            if (off < cap) {
+                if (coords) coords[(size_t)n * cap + off] = __fdiv_rn((float)(p0 + j), r);  // (:102,112)
+                if (pos_out) pos_out[(size_t)n * cap + off] = p0 + j;
+            }
+            ++off;
+        }
+        base += tot;
+    };
+    // after the first barrier of a chunk iteration: the previous chunk's flags are visible to everybody
+    auto deferred = [&]() {
+        if (pending) {
+            if (s_any[(ci - 1) % 3]) compact(pflags, pp0);
+            pending = false;
+        }
+        if (threadIdx.x == 0) s_any[(ci + 1) % 3] = 0;
+    };
     for (int pass = 0; pass < passes; ++pass) {
         const bool measuring = th_is_none && pass == 0;
         float mx = -INFINITY;
@@ -206,14 +248,17 @@ peaks_kernel(const float *__restrict__ scores, int N, int M, int h, int th_is_no
         float4 *buf = pk_sm4;                            // WIN21 && ALIGNED: two chunk buffers, the next one filling by cp.async
         if (WIN21 && ALIGNED) pk_fill_async(pk_sm4, row, M, 0);
         else if (WIN21) pk_load(pre, row, M, 0);
-        for (int cs = 0; cs < M; cs += PK_CHUNK) {
+        ci = 0;
+        for (int cs = 0; cs < M; cs += PK_CHUNK, ++ci) {
             if (WIN21 && ALIGNED) {
                 asm volatile("cp.async.wait_all;" ::: "memory");
                 __syncthreads();                         // chunk cs visible to all; everyone is done with the other buffer
+                deferred();
                 buf = pk_sm4 + ((cs / PK_CHUNK) & 1) * PK_SMEM4;
                 if (cs + PK_CHUNK < M) pk_fill_async(pk_sm4 + (((cs / PK_CHUNK) + 1) & 1) * PK_SMEM4, row, M, cs + PK_CHUNK);
             } else {
             __syncthreads();
+            deferred();
             if (WIN21) {
                 pk_store(pk_sm4, pre);
                 if (cs + PK_CHUNK < M) pk_load(pre, row, M, cs + PK_CHUNK);      // prefetch behind this chunk's work
@@ -278,34 +323,17 @@ peaks_kernel(const float *__restrict__ scores, int N, int M, int h, int th_is_no
                 flags |= (keep ? 1u : 0u) << j;
             }
             }
-            if (__syncthreads_or(flags != 0)) {
-                const int cnt = __popc(flags);
-                int inc = cnt;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const int t = __shfl_up_sync(0xffffffffu, inc, o);
-                    if (lane >= o) inc += t;
-                }
-                if (lane == 31) s_warp[warp] = inc;
-                __syncthreads();
-                int off = base + inc - cnt, tot = 0;
-#pragma unroll
-                for (int w = 0; w < PK_THREADS / 32; ++w) {
-                    const int t = s_warp[w];
-                    if (w < warp) off += t;
-                    tot += t;
-                }
-                while (flags) {
-                    const int j = __ffs(flags) - 1;
-                    flags &= flags - 1;
-                    if (off < cap) {
-                        if (coords) coords[(size_t)n * cap + off] = __fdiv_rn((float)(p0 + j), r);  // (:102,112)
-                        if (pos_out) pos_out[(size_t)n * cap + off] = p0 + j;
-                    }
-                    ++off;
-                }
-                base += tot;
-            }
+            // The block-wide agreement "does anybody keep anything in this chunk" costs no barrier of its own: warps that do
+            // raise a flag in shared memory, and the (rare) compaction runs after the NEXT chunk's first barrier.
+            if (__any_sync(0xffffffffu, flags != 0) && lane == 0) s_any[ci % 3] = 1;
+            pflags = flags;
+            pp0 = p0;
+            pending = true;
+        }
+        __syncthreads();
+        if (pending) {
+            if (s_any[(ci - 1) % 3]) compact(pflags, pp0);
+            pending = false;
         }
         if (measuring) {
             const RowMax rm = block_rowmax(mx, nan, s_red);
