@@ -46,6 +46,7 @@ __device__ __forceinline__ int pk_phys(int q) { return q + (q >> 2); }
 // (max_pool1d's implicit padding, utils/mask2samples.py:8).
 // Unaligned rows: a global -> register load and a register -> shared store, so that the NEXT chunk's loads are in flight
 // while the current chunk is processed.
+constexpr int PK_NBUF = 2;                     // chunk buffers of the cp.async path (3 measured slower: 4.05 vs 4.17 TB/s, fewer CTAs per SM)
 constexpr int PK_PRE = (PK_Q4 + PK_THREADS - 1) / PK_THREADS;     // float4 per thread per chunk (5)
 __device__ __forceinline__ void pk_load(float4 (&pre)[PK_PRE], const float *__restrict__ row, int M, int cs) {
     const float ninf = -INFINITY;
@@ -246,16 +247,24 @@ peaks_kernel(const float *__restrict__ scores, int N, int M, int h, int th_is_no
         int nan = 0;
         float4 pre[PK_PRE];
         float4 *buf = pk_sm4;                            // WIN21 && ALIGNED: two chunk buffers, the next one filling by cp.async
-        if (WIN21 && ALIGNED) pk_fill_async(pk_sm4, row, M, 0);
-        else if (WIN21) pk_load(pre, row, M, 0);
+        if (WIN21 && ALIGNED) {
+            // ring of PK_NBUF chunk buffers, PK_NBUF - 1 chunks in flight (one cp.async group per chunk, empty past the row end)
+#pragma unroll
+            for (int k = 0; k < PK_NBUF - 1; ++k) {
+                if (k * PK_CHUNK < M) pk_fill_async(pk_sm4 + k * PK_SMEM4, row, M, k * PK_CHUNK);
+                else asm volatile("cp.async.commit_group;" ::: "memory");
+            }
+        } else if (WIN21) pk_load(pre, row, M, 0);
         ci = 0;
         for (int cs = 0; cs < M; cs += PK_CHUNK, ++ci) {
             if (WIN21 && ALIGNED) {
-                asm volatile("cp.async.wait_all;" ::: "memory");
-                __syncthreads();                         // chunk cs visible to all; everyone is done with the other buffer
+                asm volatile("cp.async.wait_group %0;" ::"n"(PK_NBUF - 2) : "memory");
+                __syncthreads();                         // chunk cs visible to all; everyone is done with the previous chunk's buffer
                 deferred();
-                buf = pk_sm4 + ((cs / PK_CHUNK) & 1) * PK_SMEM4;
-                if (cs + PK_CHUNK < M) pk_fill_async(pk_sm4 + (((cs / PK_CHUNK) + 1) & 1) * PK_SMEM4, row, M, cs + PK_CHUNK);
+                buf = pk_sm4 + (ci % PK_NBUF) * PK_SMEM4;
+                if (cs + (PK_NBUF - 1) * PK_CHUNK < M)
+                    pk_fill_async(pk_sm4 + ((ci + PK_NBUF - 1) % PK_NBUF) * PK_SMEM4, row, M, cs + (PK_NBUF - 1) * PK_CHUNK);
+                else asm volatile("cp.async.commit_group;" ::: "memory");
             } else {
             __syncthreads();
             deferred();
@@ -408,7 +417,9 @@ static int launch_peaks(const float *scores, int N, int M, int window, int th_is
     const float rf = (float)upsample_factor;
     unsigned long long *st64 = reinterpret_cast<unsigned long long *>(stats);
     if (h == 10) {
-        const size_t smem = sizeof(float4) * PK_SMEM4 * (aligned ? 2 : 1);     // aligned rows: two chunk buffers (cp.async)
+        const size_t smem = sizeof(float4) * PK_SMEM4 * (aligned ? PK_NBUF : 1);     // aligned rows: ring of chunk buffers (cp.async)
+        static SmemAttrOnce attr;
+        if (aligned) { const int rc = ensure_dyn_smem(peaks_kernel<true, true>, smem, attr); if (rc) return rc; }
         if (aligned)
             peaks_kernel<true, true><<<N, PK_THREADS, smem, st>>>(scores, N, M, h, th_is_none, th, rf, coords, pos, cap, counts, st64, nms_out);
         else
