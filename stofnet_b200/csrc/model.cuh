@@ -36,6 +36,10 @@ struct stof_model {
     void *tc_contract_w = nullptr;                    // contract conv: [4 slices][5 taps][8 c8][W_hi 128 | W_lo 128][8] fp16
     stof::TcLayer tc_layer[STOF_MAX_MID_CONVS + 1];   // spec list: mid convs then conv_last
     int n_tc = 0;
+    // The fp16 hi/lo operand packs above are built on first use after stof_model_set_weights (an optimizer step re-uploads
+    // the weights every iteration and its fp32 training kernels never read them): host copies of the tensors they need
+    bool tc_dirty = false;
+    std::vector<float> h_mid[STOF_MAX_MID_CONVS], h_last, h_contract, h_expand;
     // training step (train.cu): dgrad weights of the mid convs [co][K-1-t][ci] (a conv with channels swapped and taps
     // flipped), a zero bias vector, and PyTorch-layout copies of conv_last / contract / expand for the backward kernels
     float *bw_mid[STOF_MAX_MID_CONVS] = {};

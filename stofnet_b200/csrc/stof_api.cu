@@ -239,8 +239,11 @@ static int set_weights(stof_model *m, const stof_weights *w) {
     for (int i = 0; i < w->n_mid; ++i)
         if ((rc = upload(m->mid[i], repack_cikco(w->mid_w[i], 64, 64, 7), w->mid_b[i], 64))) return rc;
     if ((rc = upload(m->last, repack_cikco(w->last_w, 4, 64, 3), w->last_b, 4))) return rc;
-    if ((rc = upload_tc(m, w, w->last_w))) return rc;
     if ((rc = upload_train(m, w))) return rc;
+    // tensor-core operand packs: deferred to ensure_tc() (first inference call that needs them)
+    for (int i = 0; i < w->n_mid; ++i) m->h_mid[i].assign(w->mid_w[i], w->mid_w[i] + (size_t)64 * 64 * 7);
+    m->h_last.assign(w->last_w, w->last_w + (size_t)4 * 64 * 3);
+    m->tc_dirty = true;
     if (w->contract_w) {
         m->sgb_scale = w->sgb_scale; m->sgb_feat = w->sgb_feat; m->sgb_k = w->sgb_k;
         // 8 cout tiles of 64, each [ci][t][co]
@@ -251,6 +254,29 @@ static int set_weights(stof_model *m, const stof_weights *w) {
         }
         if ((rc = upload(m->contract, cw, w->contract_b, 512))) return rc;
         if ((rc = upload(m->expand, repack_cikco(w->expand_w, 64, 512, 5), w->expand_b, 64))) return rc;
+        m->h_contract.assign(w->contract_w, w->contract_w + (size_t)512 * 64 * 5);
+        m->h_expand.assign(w->expand_w, w->expand_w + (size_t)64 * 512 * 5);
+    } else {
+        m->sgb_scale = 1; m->sgb_feat = 0; m->sgb_k = 0;
+    }
+    return STOF_OK;
+}
+
+// Builds the fp16 hi/lo operand packs of the tensor-core kernels from the host copies kept by set_weights (StofNet; the EDSR
+// packs are built eagerly).  Called by every entry point that launches a tensor-core kernel.
+static int ensure_tc(stof_model *m) {
+    if (!m->tc_dirty) return STOF_OK;
+    int rc;
+    STOF_CUDA(cudaSetDevice(m->device));
+    stof_weights v;
+    memset(&v, 0, sizeof(v));
+    v.kind = m->kind; v.n_mid = m->n_mid; v.num_features = m->F; v.upsample_factor = m->r;
+    v.k_first = m->k_first; v.k_mid = m->k_mid; v.k_last = m->k_last;
+    for (int i = 0; i < m->n_mid; ++i) v.mid_w[i] = m->h_mid[i].data();
+    v.last_w = m->h_last.data();
+    if ((rc = upload_tc(m, &v, v.last_w))) return rc;
+    if (m->sgb_scale != 1) {
+        const float *contract_w = m->h_contract.data(), *expand_w = m->h_expand.data();
         {
             std::vector<__half> buf((size_t)4 * 5 * 8 * 256 * 8);
             for (int sl = 0; sl < 4; ++sl)
@@ -259,7 +285,7 @@ static int set_weights(stof_model *m, const stof_weights *w) {
                     for (int r = 0; r < 128; ++r)
                         for (int ci = 0; ci < 64; ++ci) {
                             __half hi, lo;
-                            split_w(w->contract_w[((size_t)(sl * 128 + r) * 64 + ci) * 5 + t], hi, lo);
+                            split_w(contract_w[((size_t)(sl * 128 + r) * 64 + ci) * 5 + t], hi, lo);
                             tap[((size_t)(ci >> 3) * 256 + r) * 8 + (ci & 7)] = hi;
                             tap[((size_t)(ci >> 3) * 256 + 128 + r) * 8 + (ci & 7)] = lo;
                         }
@@ -276,7 +302,7 @@ static int set_weights(stof_model *m, const stof_weights *w) {
                     for (int co = 0; co < 64; ++co)
                         for (int ci = 0; ci < 64; ++ci) {
                             __half hi, lo;
-                            split_w(w->expand_w[((size_t)co * 512 + 64 * g + ci) * 5 + t], hi, lo);
+                            split_w(expand_w[((size_t)co * 512 + 64 * g + ci) * 5 + t], hi, lo);
                             tap[((size_t)(ci >> 3) * 128 + co) * 8 + (ci & 7)] = hi;
                             tap[((size_t)(ci >> 3) * 128 + 64 + co) * 8 + (ci & 7)] = lo;
                         }
@@ -284,9 +310,8 @@ static int set_weights(stof_model *m, const stof_weights *w) {
             if (!m->tc_expand_w) STOF_CUDA(cudaMalloc(&m->tc_expand_w, buf.size() * sizeof(__half)));
             STOF_CUDA(cudaMemcpy(m->tc_expand_w, buf.data(), buf.size() * sizeof(__half), cudaMemcpyHostToDevice));
         }
-    } else {
-        m->sgb_scale = 1; m->sgb_feat = 0; m->sgb_k = 0;
     }
+    m->tc_dirty = false;
     return STOF_OK;
 }
 
@@ -360,6 +385,7 @@ struct ProfScope {
 static int forward_chunk_tc(stof_model *m, const float *x, int n, int L, float *mask, float *B0, float *B1, float *B2,
                             float *pooled, float *e, const Plan &pl, cudaStream_t st) {
     int rc;
+    if ((rc = ensure_tc(m))) return rc;               // operand packs are built on first use after set_weights
     const bool sgb = m->sgb_scale != 1;
     const int fast = (m->path == STOF_PATH_TC_FP16) ? 1 : 0;
     int off = 0;
@@ -640,6 +666,7 @@ extern "C" int stof_model_set_path(stof_model *m, int path, int layers_per_launc
 extern "C" int stof_chain_segment(stof_model *m, int first, int count, const void *in_planes_dev, const void *x0_planes_dev,
                                   void *out_dev, int N, int L, void *stream) {
     STOF_REQUIRE(m != nullptr && m->kind != STOF_KIND_ESPCN, STOF_E_INVALID, "stof_chain_segment: needs a StofNet or EDSR_1D model");
+    { const int rc = stof::ensure_tc(m); if (rc) return rc; }
     STOF_REQUIRE(first >= 0 && count >= 1 && first + count <= m->n_tc, STOF_E_INVALID,
                  "stof_chain_segment: layers [%d, %d) of %d", first, first + count, m->n_tc);
     STOF_REQUIRE(in_planes_dev && out_dev && N > 0 && L > 0, STOF_E_INVALID, "stof_chain_segment: bad arguments");
@@ -655,6 +682,7 @@ extern "C" int stof_sgb_expand(stof_model *m, const float *pooled_dev, int N, in
     STOF_REQUIRE(pooled_dev && e_dev && N > 0 && P > 0, STOF_E_INVALID, "stof_sgb_expand: bad arguments");
     STOF_CUDA(cudaSetDevice(m->device));
     if (path == STOF_PATH_SIMT) return stof::launch_expand(pooled_dev, e_dev, m->expand.w, m->expand.b, N, P, (cudaStream_t)stream);
+    { const int rc = stof::ensure_tc(m); if (rc) return rc; }
     return stof::launch_expand_tc(pooled_dev, e_dev, m->tc_expand_w, m->expand.b, N, P, (cudaStream_t)stream);
 }
 

@@ -12,6 +12,25 @@ def _np32(t):
     return np.ascontiguousarray(t.detach().to("cpu", torch.float32).numpy())
 
 
+def _host_arrays(sd):
+    """name -> contiguous fp32 numpy array.  CUDA tensors that are views of one storage (the Trainer's flat parameter
+    buffer) come over in ONE device-to-host copy instead of one synchronising copy per tensor."""
+    out, cache = {}, {}
+    for k, v in sd.items():
+        t = v.detach()
+        if t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and t.numel() > 0:
+            st = t.untyped_storage()
+            key = (t.device.index, st.data_ptr())
+            if key not in cache:
+                whole = torch.empty(0, dtype=torch.float32, device=t.device).set_(st, 0, (st.nbytes() // 4,))
+                cache[key] = whole.cpu().numpy()
+            off = t.storage_offset()
+            out[k] = np.ascontiguousarray(cache[key][off:off + t.numel()].reshape(tuple(t.shape)))
+        else:
+            out[k] = _np32(t)
+    return out
+
+
 def _ptr(a):
     return a.ctypes.data_as(C.c_void_p)
 
@@ -54,7 +73,7 @@ class Engine:
     def _pack(self, sd):
         """sd: mapping with the reference's state_dict key names -> ctypes struct (+ keep-alive)."""
         W = _lib.Weights()
-        keep = {k: _np32(v) for k, v in sd.items()}
+        keep = _host_arrays(sd)
         W.kind = self.kind
         if self.kind == _lib.KIND_EDSR:
             # models/edsr_1d.py:22-30
