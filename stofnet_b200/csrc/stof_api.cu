@@ -568,12 +568,9 @@ extern "C" int stof_infer_host(stof_model *m, const float *x_host, int N, int L,
     if (rc) return rc;
     STOF_CUDA(cudaSetDevice(m->device));
     constexpr int kPipe = stof_model::kPipe;
-    // split into at least 2 kPipe chunks so copies overlap compute: only the first chunk's host -> device copy and the last
-    // chunk's table read-back are exposed, so smaller chunks shorten the exposed part (large batches only: a chunk keeps
-    // >= 512 rows, several persistent waves of every kernel)
+    // split into at least kPipe chunks so copies overlap compute
     int chunk = pl.chunk;
-    const int pieces = (N >= 4 * kPipe * 512) ? 2 * kPipe : kPipe;
-    if (N >= 2 * kPipe && chunk > (N + pieces - 1) / pieces) chunk = (N + pieces - 1) / pieces;
+    if (N >= 2 * kPipe && chunk > (N + kPipe - 1) / kPipe) chunk = (N + kPipe - 1) / kPipe;
     rc = stof::make_plan(m, N, L, chunk, &pl);
     if (rc) return rc;
     const size_t Mr = (size_t)L * m->r;
