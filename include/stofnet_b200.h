@@ -121,6 +121,9 @@ int stof_infer_host(stof_model *m, const float *x_host, int N, int L, int window
                     float th, float *coords_host, int cap, int32_t *counts_host, float *mask_host,
                     int *kmax_out);
 
+/* Rows per pipelined chunk of stof_infer_host (0 = automatic: balanced chunks of about 4 Mi positions, at least two). */
+int stof_model_set_host_chunk_rows(stof_model *m, int rows);
+
 /* SampleShuffle1D.forward (utils/sample_shuffle.py:10-28) as a standalone operator:
  * x (B, r*Cl, W) -> out (B, Cl, r*W), out[b,c,w*r+u] = x[b,u*Cl+c,w].                           */
 int stof_sample_shuffle(const float *x_dev, int B, int Cs, int W, int r, float *out_dev, void *stream);
@@ -238,6 +241,30 @@ size_t stof_attention_scratch_bytes(int B, int S, int H);
 int stof_attention_block(const float *x_dev, int B, int S, int D, int H, const float *wq_dev, const float *bq_dev,
                          const float *wk_dev, const float *bk_dev, const float *wv_dev, const float *bv_dev,
                          float dropout_p, uint64_t seed, float *out_dev, void *scratch_dev, void *stream);
+
+/* Standalone operators of the reference's module surface (the fused hot path does not need them; callers of the
+ * reference may).  thresholding (utils/mask2samples.py:14-23): th_is_none = 0 -> out = scores with entries < th zeroed
+ * (the reference does this in place: pass out_dev = scores_dev); th_is_none = 1 ("threshold is None or 0.0") -> entries
+ * below the row maximum zeroed, torch.max's NaN propagation kept.  scores_dev, out_dev (N, M) fp32.                      */
+int stof_thresholding(const float *scores_dev, int N, int M, int th_is_none, float th, float *out_dev, void *stream);
+
+/* get_amplitudes (utils/mask2samples.py:135-136): out[n][k] = frames[n][round_half_even(samples[n][k])].
+ *   frames_dev (N, M), samples_dev / out_dev (N, K) fp32; *oob_flag_dev (int32, zeroed by the caller) is set to 1 when an
+ *   index falls outside [0, M) (torch.gather raises there; the wrapper turns the flag into the same RuntimeError).       */
+int stof_get_amplitudes(const float *frames_dev, const float *samples_dev, int N, int M, int K, float *out_dev,
+                        int *oob_flag_dev, void *stream);
+
+/* reduce_echoes (utils/mask2samples.py:117-132) on (N, K, C) fp32 entries, column 0 = time sample, column 1 = amplitude,
+ * for echo_max < K: the echo_max entries with the largest amplitude, re-ordered by time sample -> out_dev (N, echo_max, C).
+ * Equal amplitudes keep input order (torch.argsort without stable=True leaves that order unspecified).                   */
+int stof_reduce_echoes_pairs(const float *pairs_dev, int N, int K, int C, int echo_max, float *out_dev, void *stream);
+
+/* SemiGlobalBlock.forward (models/stofnet.py:98-117) as a standalone operator on an fp32 (N, 64, L) NCL tensor:
+ * out = x + pad(upsample_nearest(LeakyReLU(expand_conv(maxpool(LeakyReLU(contract_conv(x))))))), fp32 FFMA kernels
+ * (inside stof_forward the block runs fused on the tensor cores instead).  Same length constraints as stof_forward.     */
+int stof_sgb_workspace_bytes(const stof_model *m, int N, int L, size_t *bytes);
+int stof_semi_global_block(stof_model *m, const float *x_dev, int N, int L, float *out_dev, void *ws_dev, size_t ws_bytes,
+                           void *stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Training step (main.py:217-248): forward that keeps the activations, backward of the whole stack, fused AdamW.

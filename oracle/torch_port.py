@@ -96,13 +96,28 @@ def get_maxima_positions(scores, window_size, threshold=None):
     return torch.nonzero(s.squeeze(1), as_tuple=False).long()
 
 
+def thresholding(scores, threshold=None):
+    """utils/mask2samples.py:14-23 (float threshold: in place)."""
+    if threshold:
+        scores[scores < threshold] = 0
+    else:
+        scores = scores.masked_fill(scores < torch.max(scores, dim=-1, keepdim=True)[0], 0)
+    return scores
+
+
+def get_amplitudes(frames, samples):
+    """utils/mask2samples.py:135-136."""
+    return torch.gather(frames.squeeze(), -1, torch.round(samples).long())
+
+
 def reduce_echoes(pairs, echo_max):
     """utils/mask2samples.py:117-132: (N, K, 2) [position, amplitude] -> the echo_max largest amplitudes, by position."""
     if pairs.shape[1] > echo_max:
+        c = pairs.shape[-1]
         order = torch.argsort(pairs[..., 1], descending=True, dim=1, stable=True)
-        pairs = torch.gather(pairs, 1, order[..., None].expand(-1, -1, 2))[:, :echo_max]
+        pairs = torch.gather(pairs, 1, order[..., None].expand(-1, -1, c))[:, :echo_max]
         order = torch.argsort(pairs[..., 0], descending=False, dim=1, stable=True)
-        pairs = torch.gather(pairs, 1, order[..., None].expand(-1, -1, 2))
+        pairs = torch.gather(pairs, 1, order[..., None].expand(-1, -1, c))
     return pairs
 
 

@@ -63,6 +63,7 @@ _SIGS = {
     "stof_peaks_indices": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
     "stof_nms_1d": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "stof_infer_host": (_i, [_vp, _vp, _i, _i, _i, _i, _f, _vp, _i, _vp, _vp, C.POINTER(_i)]),
+    "stof_model_set_host_chunk_rows": (_i, [_vp, _i]),
     "stof_sample_shuffle": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "stof_model_set_path": (_i, [_vp, _i, _i]),
     "stof_chain_segment": (_i, [_vp, _i, _i, _vp, _vp, _vp, _i, _i, _vp]),
@@ -83,6 +84,11 @@ _SIGS = {
     "stof_forward_train": (_i, [_vp, _vp, _i, _i, _vp, _vp, _sz, _vp]),
     "stof_backward": (_i, [_vp, _vp, _vp, _i, _i, _vp, _sz, C.POINTER(Grads), _vp]),
     "stof_adamw_step": (_i, [_vp, _vp, _vp, _vp, _sz, _i, _f, _f, _f, _f, _f, _vp]),
+    "stof_thresholding": (_i, [_vp, _i, _i, _i, _f, _vp, _vp]),
+    "stof_get_amplitudes": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
+    "stof_reduce_echoes_pairs": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
+    "stof_sgb_workspace_bytes": (_i, [_vp, _i, _i, C.POINTER(_sz)]),
+    "stof_semi_global_block": (_i, [_vp, _vp, _i, _i, _vp, _vp, _sz, _vp]),
     "stof_attention_scratch_bytes": (_sz, [_i, _i, _i]),
     "stof_attention_block": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _f, C.c_uint64, _vp, _vp, _vp]),
 }

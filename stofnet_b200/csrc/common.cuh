@@ -51,6 +51,22 @@ inline int ensure_dyn_smem(K kernel, int bytes, SmemAttrOnce &once) {
     return STOF_OK;
 }
 
+// RAII: make `dev` the calling thread's current device for the scope and restore the caller's device afterwards (a process
+// may hold models on several GPUs; the library must not leak its device into the caller's thread)
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = false;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) { cudaGetLastError(); prev = -1; }
+        if (prev == dev) { ok = true; prev = -1; return; }
+        ok = cudaSetDevice(dev) == cudaSuccess;
+        if (!ok) cudaGetLastError();
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+    DeviceGuard(const DeviceGuard &) = delete;
+    DeviceGuard &operator=(const DeviceGuard &) = delete;
+};
+
 constexpr int kSMs = 148;           // B200: 2 dies x 74 SMs
 constexpr float kLeakySlope = 0.01f;  // nn.LeakyReLU() / F.leaky_relu default (models/stofnet.py:56,89,95)
 

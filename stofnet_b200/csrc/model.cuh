@@ -53,6 +53,7 @@ struct stof_model {
     void *scratch[kPipe] = {nullptr, nullptr};
     size_t scratch_bytes[kPipe] = {0, 0};
     int64_t *h_stats = nullptr;   // pinned, kPipe * 2
+    int host_chunk_rows = 0;      // stof_model_set_host_chunk_rows: rows per pipelined chunk of stof_infer_host (0 = automatic)
     // optional per-kernel-class CUDA-event timing (stof_profile_*): pairs recorded on the launch stream
     bool profiling = false;
     std::vector<cudaEvent_t> ev_pool;                 // start/stop pairs

@@ -10,8 +10,12 @@
 // thread owns 16 consecutive samples in registers, builds the 21-wide sliding maximum from
 // three levels of 3-input max (window 3 -> 9 -> 21, 78 max-ops per 16 samples), and the
 // block compacts survivors in ascending order with warp-shuffle prefix sums.  The kernel is
-// HBM-bound: algorithmic traffic is the 4*M bytes of the row (read once with a float threshold,
-// twice - the second time from L2 - in the row-max mode) plus the tiny coords table.
+// HBM-bound: algorithmic traffic is the 4*M bytes of the row, read once, plus the tiny coords table.
+// Row-max mode (threshold None / 0.0): the maximum of the suppressed scores IS the row maximum whenever that is positive
+// (the global maximum is always a window maximum, every other suppressed score is a smaller sample or 0), so the kept set is
+// "every position equal to the row maximum" and one streaming arg-max-with-ties pass answers it without any window
+// arithmetic (pk_rowmax_fast).  Rows with NaN / -inf entries, a non-positive maximum or too many ties take the literal
+// two-pass route (nms -> row max of the suppressed scores -> selection), the second pass from L2.
 //
 // All comparisons follow the reference literally, including its NaN/inf behaviour:
 //   sup = (x == wmax ? 1 : 0) * x     (0 * inf = NaN, and NaN counts as "non-zero")
@@ -177,6 +181,93 @@ __device__ __forceinline__ float pk_min3(float a, float b, float c) {
     return r;
 }
 
+
+// ---- row-max mode, one streaming pass -----------------------------------------------------------------------------------
+// thresholding(None) keeps the entries of sup = nms(x) that are not below max(sup) (utils/mask2samples.py:19-21).  Every
+// entry of sup is x[j] (at window maxima), 0, or NaN (0 * +-inf, or a NaN sample); the global maximum of x is a window maximum.
+// Hence, for a row without NaN / -inf whose maximum is > 0: max(sup) = max(x) and the kept set = { j : x[j] == max(x) }
+// (+inf included: inf == inf is a window maximum, its neighbours give 0 * finite = 0).  Anything else -> literal route.
+constexpr int PK_FAST_TIES = 2;                // tie positions remembered per thread
+constexpr int PK_FAST_MAX = 256;               // ... and per row
+
+struct PkFastState { float mx; int ties, t0, t1, bad; };
+
+__device__ __forceinline__ void pk_fast_visit(PkFastState &s, float v, int p) {
+    s.bad |= (v != v) | (v == -INFINITY);
+    if (v > s.mx) { s.mx = v; s.ties = 0; }
+    if (v == s.mx) {
+        if (s.ties == 0) s.t0 = p; else if (s.ties == 1) s.t1 = p;
+        ++s.ties;
+    }
+}
+
+// returns the number of kept positions (written in ascending order to s_out[0 .. PK_FAST_MAX)), or -1 when the row needs
+// the literal route.  Block-uniform result; contains barriers.
+template <bool ALIGNED>
+__device__ __forceinline__ int pk_rowmax_fast(const float *__restrict__ row, int M, float *s_red, int *s_cand, int *s_out) {
+    PkFastState s;
+    s.mx = -INFINITY; s.ties = 0; s.t0 = 0; s.t1 = 0; s.bad = 0;
+    if (ALIGNED) {
+        const float4 *r4 = reinterpret_cast<const float4 *>(row);
+        const int Q = M >> 2;
+        int q = threadIdx.x;
+        for (; q + 3 * PK_THREADS < Q; q += 4 * PK_THREADS) {               // four 16-byte loads in flight per thread
+            float4 v[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) v[k] = __ldg(r4 + q + k * PK_THREADS);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int p = 4 * (q + k * PK_THREADS);
+                pk_fast_visit(s, v[k].x, p); pk_fast_visit(s, v[k].y, p + 1); pk_fast_visit(s, v[k].z, p + 2); pk_fast_visit(s, v[k].w, p + 3);
+            }
+        }
+        for (; q < Q; q += PK_THREADS) {
+            const float4 v = __ldg(r4 + q);
+            pk_fast_visit(s, v.x, 4 * q); pk_fast_visit(s, v.y, 4 * q + 1); pk_fast_visit(s, v.z, 4 * q + 2); pk_fast_visit(s, v.w, 4 * q + 3);
+        }
+    } else {
+        for (int i = threadIdx.x; i < M; i += PK_THREADS) pk_fast_visit(s, __ldg(row + i), i);
+    }
+    // block maximum, "bad" flag
+    float mx = s.mx;
+    int bad = s.bad;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        bad |= __shfl_xor_sync(0xffffffffu, bad, o);
+    }
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (threadIdx.x == 0) s_cand[0] = 0;
+    __syncthreads();
+    if (l == 0) { s_red[w] = mx; s_red[8 + w] = __int_as_float(bad); }
+    __syncthreads();
+    mx = s_red[0]; bad = __float_as_int(s_red[8]);
+#pragma unroll
+    for (int i = 1; i < PK_THREADS / 32; ++i) { mx = fmaxf(mx, s_red[i]); bad |= __float_as_int(s_red[8 + i]); }
+    // candidates of the threads that saw the maximum
+    if (s.mx == mx && s.ties > 0) {
+        if (s.ties > PK_FAST_TIES) atomicOr(&s_cand[0], 1 << 30);
+        else {
+            const int at = atomicAdd(&s_cand[0], s.ties) & ((1 << 30) - 1);
+            if (at + s.ties <= PK_FAST_MAX) {
+                s_cand[1 + at] = s.t0;
+                if (s.ties > 1) s_cand[2 + at] = s.t1;
+            }
+        }
+    }
+    __syncthreads();
+    const int tot = s_cand[0];
+    if (bad || !(mx > 0.0f) || tot > PK_FAST_MAX) return -1;            // also covers the tie-overflow bit
+    for (int j = threadIdx.x; j < tot; j += PK_THREADS) {
+        const int p = s_cand[1 + j];
+        int rank = 0;
+        for (int i = 0; i < tot; ++i) rank += (s_cand[1 + i] < p) ? 1 : 0;
+        s_out[rank] = p;
+    }
+    __syncthreads();
+    return tot;
+}
+
 template <bool WIN21, bool ALIGNED>
 __global__ void __launch_bounds__(PK_THREADS)
 peaks_kernel(const float *__restrict__ scores, int N, int M, int h, int th_is_none, float th,
@@ -241,7 +332,22 @@ peaks_kernel(const float *__restrict__ scores, int N, int M, int h, int th_is_no
         }
         if (threadIdx.x == 0) s_any[(ci + 1) % 3] = 0;
     };
-    for (int pass = 0; pass < passes; ++pass) {
+    bool fast_done = false;
+    if (th_is_none && nms_out == nullptr) {
+        __shared__ int s_cand[1 + PK_FAST_MAX], s_fout[PK_FAST_MAX];
+        const int kept = pk_rowmax_fast<ALIGNED>(row, M, s_red, s_cand, s_fout);
+        if (kept >= 0) {
+            for (int j = threadIdx.x; j < kept && j < cap; j += PK_THREADS) {
+                const int p = s_fout[j];
+                if (coords) coords[(size_t)n * cap + j] = __fdiv_rn((float)p, r);
+                if (pos_out) pos_out[(size_t)n * cap + j] = p;
+            }
+            base = kept;
+            fast_done = true;
+        }
+        __syncthreads();
+    }
+    for (int pass = 0; pass < passes && !fast_done; ++pass) {
         const bool measuring = th_is_none && pass == 0;
         float mx = -INFINITY;
         int nan = 0;

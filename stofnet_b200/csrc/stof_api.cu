@@ -207,10 +207,27 @@ static int validate(const stof_weights *w) {
     return STOF_OK;
 }
 
+static int set_weights_locked(stof_model *m, const stof_weights *w);
+
+// Weight uploads are blocking cudaMemcpy calls from pageable host vectors on the legacy default stream, while the kernels that
+// read the weights run on the caller's (possibly non-blocking) streams.  Ordering contract: every call that overwrites device
+// weights first waits for ALL work on the device (an earlier forward may still be reading the old weights) and returns only
+// when the last byte has landed (a pageable H2D copy may return before its DMA has finished).  stof_model_set_weights must
+// not be called concurrently with a forward from another thread.
 static int set_weights(stof_model *m, const stof_weights *w) {
     int rc = validate(w);
     if (rc) return rc;
-    STOF_CUDA(cudaSetDevice(m->device));
+    DeviceGuard guard(m->device);
+    STOF_REQUIRE(guard.ok, STOF_E_CUDA, "cudaSetDevice(%d) failed", m->device);
+    STOF_CUDA(cudaDeviceSynchronize());
+    rc = set_weights_locked(m, w);
+    if (rc) return rc;
+    STOF_CUDA(cudaDeviceSynchronize());
+    return STOF_OK;
+}
+
+static int set_weights_locked(stof_model *m, const stof_weights *w) {
+    int rc;
     m->kind = w->kind;
     m->r = w->upsample_factor;
     if (w->kind == STOF_KIND_ESPCN) {
@@ -267,7 +284,9 @@ static int set_weights(stof_model *m, const stof_weights *w) {
 static int ensure_tc(stof_model *m) {
     if (!m->tc_dirty) return STOF_OK;
     int rc;
-    STOF_CUDA(cudaSetDevice(m->device));
+    DeviceGuard guard(m->device);
+    STOF_REQUIRE(guard.ok, STOF_E_CUDA, "cudaSetDevice(%d) failed", m->device);
+    STOF_CUDA(cudaDeviceSynchronize());               // nothing in flight may still read the packs that are overwritten below
     stof_weights v;
     memset(&v, 0, sizeof(v));
     v.kind = m->kind; v.n_mid = m->n_mid; v.num_features = m->F; v.upsample_factor = m->r;
@@ -311,6 +330,7 @@ static int ensure_tc(stof_model *m) {
             STOF_CUDA(cudaMemcpy(m->tc_expand_w, buf.data(), buf.size() * sizeof(__half), cudaMemcpyHostToDevice));
         }
     }
+    STOF_CUDA(cudaDeviceSynchronize());               // the packs are complete before any stream's kernel can read them
     m->tc_dirty = false;
     return STOF_OK;
 }
@@ -353,6 +373,12 @@ static int make_plan(const stof_model *m, int N, int L, int chunk_rows, Plan *p)
         chunk = (int)c;
     }
     if (chunk > N) chunk = N;
+    if (chunk_rows <= 0) {
+        // balance: 4096 rows at a default of 819 are 6 chunks of 683, not 5 x 819 + a 1-row tail that runs every kernel of
+        // the chunk on a fraction of the SMs
+        const int n_chunks = (N + chunk - 1) / chunk;
+        chunk = (N + n_chunks - 1) / n_chunks;
+    }
     p->chunk = chunk;
     p->P = sgb ? L / m->sgb_scale : 0;
     p->act = (size_t)chunk * 64 * L;
@@ -476,7 +502,12 @@ static int forward_chunk(stof_model *m, const float *x, int n, int L, float *mas
 
 }  // namespace stof
 
-extern "C" const char *stof_version(void) { return "stofnet_b200 0.1 (sm_100a)"; }
+#ifndef STOF_SRC_HASH
+#define STOF_SRC_HASH "unknown"
+#endif
+// the hash of the sources this library was built from (csrc/Makefile): tests/test_host.py compares it with the tree, so a
+// stale pre-built .so cannot pass silently
+extern "C" const char *stof_version(void) { return "stofnet_b200 0.2 (sm_100a) src:" STOF_SRC_HASH; }
 extern "C" const char *stof_last_error(void) { return stof::g_err; }
 extern "C" uint64_t stof_launch_count(void) { return stof::g_launches.load(); }
 
@@ -512,7 +543,7 @@ extern "C" int stof_model_set_weights(stof_model *m, const stof_weights *w) {
 
 extern "C" void stof_model_destroy(stof_model *m) {
     if (!m) return;
-    cudaSetDevice(m->device);
+    stof::DeviceGuard guard(m->device);
     stof::free_conv(m->first); stof::free_conv(m->last); stof::free_conv(m->contract); stof::free_conv(m->expand);
     for (int i = 0; i < STOF_MAX_MID_CONVS; ++i) stof::free_conv(m->mid[i]);
     for (int i = 0; i < stof_model::kPipe; ++i) {
@@ -566,11 +597,18 @@ extern "C" int stof_infer_host(stof_model *m, const float *x_host, int N, int L,
     stof::Plan pl;
     int rc = stof::make_plan(m, N, L, 0, &pl);
     if (rc) return rc;
-    STOF_CUDA(cudaSetDevice(m->device));
+    stof::DeviceGuard guard(m->device);
+    STOF_REQUIRE(guard.ok, STOF_E_CUDA, "cudaSetDevice(%d) failed", m->device);
     constexpr int kPipe = stof_model::kPipe;
-    // split into at least kPipe chunks so copies overlap compute
+    // split into at least kPipe balanced chunks so copies overlap compute (host_chunk_rows > 0: caller's choice, test hook)
     int chunk = pl.chunk;
-    if (N >= 2 * kPipe && chunk > (N + kPipe - 1) / kPipe) chunk = (N + kPipe - 1) / kPipe;
+    if (m->host_chunk_rows > 0) {
+        chunk = m->host_chunk_rows < N ? m->host_chunk_rows : N;
+    } else {
+        int n_chunks = (N + chunk - 1) / chunk;
+        if (N >= 2 * kPipe && n_chunks < kPipe) n_chunks = kPipe;
+        chunk = (N + n_chunks - 1) / n_chunks;
+    }
     rc = stof::make_plan(m, N, L, chunk, &pl);
     if (rc) return rc;
     const size_t Mr = (size_t)L * m->r;
@@ -663,6 +701,12 @@ extern "C" int stof_model_set_path(stof_model *m, int path, int layers_per_launc
     return STOF_OK;
 }
 
+extern "C" int stof_model_set_host_chunk_rows(stof_model *m, int rows) {
+    STOF_REQUIRE(m != nullptr && rows >= 0, STOF_E_INVALID, "stof_model_set_host_chunk_rows: bad arguments");
+    m->host_chunk_rows = rows;
+    return STOF_OK;
+}
+
 extern "C" int stof_chain_segment(stof_model *m, int first, int count, const void *in_planes_dev, const void *x0_planes_dev,
                                   void *out_dev, int N, int L, void *stream) {
     STOF_REQUIRE(m != nullptr && m->kind != STOF_KIND_ESPCN, STOF_E_INVALID, "stof_chain_segment: needs a StofNet or EDSR_1D model");
@@ -680,7 +724,8 @@ extern "C" int stof_sgb_expand(stof_model *m, const float *pooled_dev, int N, in
     STOF_REQUIRE(m != nullptr && m->kind == STOF_KIND_STOFNET && m->sgb_scale != 1, STOF_E_INVALID,
                  "stof_sgb_expand: needs a StofNet model with a semi-global block");
     STOF_REQUIRE(pooled_dev && e_dev && N > 0 && P > 0, STOF_E_INVALID, "stof_sgb_expand: bad arguments");
-    STOF_CUDA(cudaSetDevice(m->device));
+    stof::DeviceGuard guard(m->device);
+    STOF_REQUIRE(guard.ok, STOF_E_CUDA, "cudaSetDevice(%d) failed", m->device);
     if (path == STOF_PATH_SIMT) return stof::launch_expand(pooled_dev, e_dev, m->expand.w, m->expand.b, N, P, (cudaStream_t)stream);
     { const int rc = stof::ensure_tc(m); if (rc) return rc; }
     return stof::launch_expand_tc(pooled_dev, e_dev, m->tc_expand_w, m->expand.b, N, P, (cudaStream_t)stream);

@@ -163,7 +163,8 @@ class Engine:
         (N, 2, 8, L, 8); returns planes, or the (N, 1, r*L) mask when the range ends with conv_last."""
         require_cuda(in_planes, "in_planes")
         dev = in_planes.device
-        self.sync(module, dev)
+        with torch.cuda.device(dev):
+            self.sync(module, dev)
         N, _, _, L, _ = in_planes.shape
         n_tc = module.num_blocks - 1
         ends = first + count == n_tc
@@ -184,12 +185,12 @@ class Engine:
         if x.dim() != 3 or x.shape[1] != 1:
             raise RuntimeError("stofnet_b200: expected input of shape (N, 1, L), got %s" % (tuple(x.shape),))
         dev = x.device
-        self.sync(module, dev)
-        self._apply_path()
         x = x.detach().to(torch.float32).contiguous()
         N, _, L = x.shape
         r = module.upsample_factor
         with torch.cuda.device(dev):
+            self.sync(module, dev)
+            self._apply_path()
             need = C.c_size_t()
             check(lib.stof_forward_workspace_bytes(self.handle, N, L, self.chunk_rows, C.byref(need)))
             if self.ws is None or self.ws.numel() < need.value or self.ws.device != dev:
@@ -207,10 +208,10 @@ class Engine:
         if x.dim() != 3 or x.shape[1] != 1:
             raise RuntimeError("stofnet_b200: expected input of shape (N, 1, L), got %s" % (tuple(x.shape),))
         dev = x.device
-        self.sync(module, dev)
         x = x.detach().to(torch.float32).contiguous()
         N, _, L = x.shape
         with torch.cuda.device(dev):
+            self.sync(module, dev)
             need = C.c_size_t()
             check(lib.stof_train_workspace_bytes(self.handle, N, L, C.byref(need)))
             ws = torch.empty(need.value, dtype=torch.uint8, device=dev)
@@ -261,23 +262,58 @@ class Engine:
         dev = device if device is not None else next(module.parameters()).device
         if dev.type != "cuda":
             raise RuntimeError("stofnet_b200: module must live on a CUDA device (no CPU path)")
-        self.sync(module, dev)
-        self._apply_path()
         x_host = x_host.detach().to(torch.float32).contiguous()
         if x_host.dim() == 3:
             x_host = x_host[:, 0, :]
         N, L = x_host.shape
         r = module.upsample_factor
         none = (threshold is None) or (not threshold)
-        while True:
-            coords = torch.empty((N, cap), dtype=torch.float32).pin_memory()
-            counts = torch.empty((N,), dtype=torch.int32).pin_memory()
-            mask = torch.empty((N, 1, r * L), dtype=torch.float32).pin_memory() if want_mask else None
-            kmax = C.c_int(0)
-            check(lib.stof_infer_host(self.handle, x_host.data_ptr(), N, L, int(window_size), int(none),
-                                      0.0 if none else float(threshold), coords.data_ptr(), cap, counts.data_ptr(),
-                                      mask.data_ptr() if want_mask else None, C.byref(kmax)))
-            if kmax.value <= cap:
-                break
-            cap = kmax.value
+        with torch.cuda.device(dev):
+            self.sync(module, dev)
+            self._apply_path()
+            while True:
+                coords = torch.empty((N, cap), dtype=torch.float32).pin_memory()
+                counts = torch.empty((N,), dtype=torch.int32).pin_memory()
+                mask = torch.empty((N, 1, r * L), dtype=torch.float32).pin_memory() if want_mask else None
+                kmax = C.c_int(0)
+                check(lib.stof_infer_host(self.handle, x_host.data_ptr(), N, L, int(window_size), int(none),
+                                          0.0 if none else float(threshold), coords.data_ptr(), cap, counts.data_ptr(),
+                                          mask.data_ptr() if want_mask else None, C.byref(kmax)))
+                if kmax.value <= cap:
+                    break
+                cap = kmax.value
         return coords, counts, kmax.value, mask
+
+    # -- standalone semi-global block -----------------------------------------------------
+    def semi_global_block(self, block, x):
+        """SemiGlobalBlock.forward on an fp32 (N, 64, L) CUDA tensor (models/stofnet.py:98-117)."""
+        require_cuda(x, "input")
+        if x.dim() != 3 or x.shape[1] != 64:
+            raise RuntimeError("stofnet_b200: SemiGlobalBlock expects (N, 64, L), got %s" % (tuple(x.shape),))
+        dev = x.device
+        x = x.detach().to(torch.float32).contiguous()
+        N, _, L = x.shape
+        with torch.cuda.device(dev):
+            # the C handle describes a whole StofNet: the block's own tensors plus zero stand-ins for the convs it never runs
+            z = lambda *shape: torch.zeros(shape, dtype=torch.float32)
+            sd = {"conv1.weight": z(64, 1, 9), "conv1.bias": z(64), "conv_last.weight": z(4, 64, 3), "conv_last.bias": z(4)}
+            for i in (2, 3, 4):
+                sd["conv%d.weight" % i], sd["conv%d.bias" % i] = z(64, 64, 7), z(64)
+            for k, v in block.state_dict(keep_vars=True).items():
+                sd["semi_global_block." + k] = v
+            key = (dev.index, tuple((k, v.data_ptr(), v._version) for k, v in block.state_dict(keep_vars=True).items()))
+            if self.handle is None or key != self.key:
+                W, keep = self._pack(sd)
+                W.sgb_scale = int(block.sample_scale)
+                self.close()
+                h = C.c_void_p()
+                check(lib.stof_model_create(C.byref(W), dev.index if dev.index is not None else 0, C.byref(h)))
+                self.handle, self.device, self.key = h, dev, key
+                del keep
+            need = C.c_size_t()
+            check(lib.stof_sgb_workspace_bytes(self.handle, N, L, C.byref(need)))
+            ws = torch.empty(need.value, dtype=torch.uint8, device=dev)
+            out = torch.empty_like(x)
+            check(lib.stof_semi_global_block(self.handle, x.data_ptr(), N, L, out.data_ptr(), ws.data_ptr(), ws.numel(),
+                                             stream_ptr(dev)))
+        return out

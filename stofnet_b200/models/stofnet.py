@@ -18,9 +18,10 @@ from ..utils.sample_shuffle import SampleShuffle1D
 
 
 class SemiGlobalBlock(nn.Module):
-    """Parameter container of the semi-global block (reference :80-96).  Its arithmetic
-    (contract conv + LeakyReLU + MaxPool(80) -> expand conv + LeakyReLU -> nearest x80 -> centred
-    pad -> skip add, :98-117) runs inside StofNet.forward's fused kernels."""
+    """Semi-global block with the reference's surface (:80-117).  Inside StofNet.forward its arithmetic (contract conv +
+    LeakyReLU + MaxPool(80) -> expand conv + LeakyReLU -> nearest x80 -> centred pad -> skip add) runs in the fused
+    tensor-core kernels; called on its own, ``forward`` runs the same stages as fp32 FFMA kernels on the caller's
+    (N, 64, L) tensor (stof_semi_global_block).  Inference only (no autograd through the standalone call)."""
 
     def __init__(self, in_channels, out_channels, sample_scale=2, kernel_size=5):
         super().__init__()
@@ -34,10 +35,16 @@ class SemiGlobalBlock(nn.Module):
                                      stride=1, padding=kernel_size // 2)
         self.expand_relu = nn.LeakyReLU()
         self.expand_upsample = nn.Upsample(scale_factor=sample_scale, mode="nearest")
+        self._engine = None
 
     def forward(self, x):
-        raise NotImplementedError("stofnet_b200: SemiGlobalBlock is fused into StofNet.forward; "
-                                  "it is not available as a standalone operator yet")
+        cw = self.contract_conv.weight
+        if tuple(cw.shape) != (512, 64, 5) or tuple(self.expand_conv.weight.shape) != (64, 512, 5) or self.sample_scale != 80:
+            raise ValueError("stofnet_b200: the semi-global block kernels are built for 64 channels, sample_scale=80, "
+                             "kernel_size=5 (got contract_conv %s, sample_scale %d)" % (tuple(cw.shape), self.sample_scale))
+        if self._engine is None:
+            self._engine = Engine(_lib.KIND_STOFNET)
+        return self._engine.semi_global_block(self, x)
 
 
 class _StofNetFunction(torch.autograd.Function):

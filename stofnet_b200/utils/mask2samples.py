@@ -66,13 +66,23 @@ def nms_1d(scores, window_size):
 
 
 def thresholding(scores, threshold=None):
-    """Reference :14-23.  Standalone convenience (inside mask2coords it is fused into the kernel);
-    elementwise on the caller's device with torch, in place for a float threshold like the reference."""
-    if threshold:
-        scores[scores < threshold] = 0
-    else:
-        max_vals = torch.max(scores, dim=-1, keepdim=True)[0]
-        scores = scores.masked_fill(scores < max_vals, 0)
+    """Reference :14-23 as one kernel (stof_thresholding).  A float threshold zeroes the entries below it IN PLACE and returns
+    the caller's tensor, like `scores[scores < threshold] = 0`; None / 0.0 returns a new tensor in which every entry below
+    its row maximum is zero (masked_fill)."""
+    require_cuda(scores, "scores")
+    if scores.dtype != torch.float32:
+        raise RuntimeError("stofnet_b200: thresholding expects float32 scores, got %s" % scores.dtype)
+    none, th = _th(threshold)
+    m = scores.shape[-1]
+    src = scores if scores.is_contiguous() else scores.contiguous()
+    out = torch.empty_like(src) if none else src
+    if src.numel():
+        with torch.cuda.device(src.device):
+            check(lib.stof_thresholding(src.data_ptr(), src.numel() // m, m, none, th, out.data_ptr(), stream_ptr(src.device)))
+    if none:
+        return out
+    if src is not scores:
+        scores.copy_(src)
     return scores
 
 
@@ -119,21 +129,35 @@ def mask2coords(scores, window_size, threshold=None, upsample_factor=1, echo_max
 
 
 def reduce_echoes(samples_and_amps, echo_max=100):
-    """Keep the echo_max largest-amplitude echoes, re-sorted by time (reference :117-132).  Standalone tensor utility with
-    the reference's signature; mask2coords(echo_max=...) itself runs the fused stof_reduce_echoes kernel."""
-    echo_num = samples_and_amps.shape[1]
-    channel_num = samples_and_amps.shape[-1]
-    echoes = samples_and_amps
-    if echo_num > echo_max:
-        idcs = torch.argsort(samples_and_amps[..., 1], descending=True, dim=1)
-        echoes = torch.gather(samples_and_amps, dim=1, index=idcs[..., None].repeat(1, 1, channel_num))[:, :echo_max]
-        idcs = torch.argsort(echoes[..., 0], descending=False, dim=1)
-        echoes = torch.gather(echoes, dim=1, index=idcs[..., None].repeat(1, 1, channel_num))
-    return echoes
+    """(N, K, C) entries [time sample, amplitude, ...] -> the echo_max entries with the largest amplitude, ordered by time
+    sample (reference :117-132).  K <= echo_max returns the input unchanged (the reference's function raises UnboundLocalError
+    there - `echoes` is only bound inside its `if` - and mask2coords never calls it that way).  One kernel
+    (stof_reduce_echoes_pairs)."""
+    require_cuda(samples_and_amps, "samples_and_amps")
+    n, k, c = samples_and_amps.shape
+    if k <= echo_max:
+        return samples_and_amps
+    src = samples_and_amps.detach().to(torch.float32).contiguous()
+    out = torch.empty((n, int(echo_max), c), dtype=torch.float32, device=src.device)
+    with torch.cuda.device(src.device):
+        check(lib.stof_reduce_echoes_pairs(src.data_ptr(), n, k, c, int(echo_max), out.data_ptr(), stream_ptr(src.device)))
+    return out
 
 
 def get_amplitudes(frames, samples):
-    return torch.gather(frames.squeeze(), -1, torch.round(samples).long())
+    """frames (N, 1, M) or (N, M), samples (N, K) float positions -> frames[n, round(samples[n, k])] (reference :135-136)."""
+    rows = _as_rows(frames)
+    require_cuda(samples, "samples")
+    smp = samples.detach().to(torch.float32).contiguous()
+    n, k = smp.shape
+    out = torch.empty((n, k), dtype=torch.float32, device=rows.device)
+    oob = torch.zeros((1,), dtype=torch.int32, device=rows.device)
+    with torch.cuda.device(rows.device):
+        check(lib.stof_get_amplitudes(rows.data_ptr(), smp.data_ptr(), n, rows.shape[1], k, out.data_ptr(), oob.data_ptr(),
+                                      stream_ptr(rows.device)))
+    if int(oob.item()):
+        raise RuntimeError("stofnet_b200: get_amplitudes: index out of range (torch.gather raises here as well)")
+    return out
 
 
 def coords2mask(samples, ref):

@@ -22,6 +22,11 @@ kernels (torch 2.11.0, oneDNN, fp32; fp64 re-run stored beside it as the tie-bre
   echo_cases.npz       mask2coords(echo_max=...) : amplitude selection / zero padding (utils/mask2samples.py:103-132)
   train_<ckpt>.npz     three training steps (model -> loss -> autograd -> AdamW, main.py:217-248): gradients
                        of every parameter after the first backward, losses and parameters after each step
+  scale_<ckpt>.npz     the SURVEY 8c golden set: N = 64 rows x seeds {3008, 0, 1} x L in {2560, 2578, 5120, 160} per StofNet
+                       checkpoint; inputs come from the host-independent generator (synth_waveforms(q15=True)) and are NOT
+                       stored - only their SHA-256, the SHA-256 of the fp32 mask, per-row mask maxima, and the index lists /
+                       ToF tables for th in {None, checkpoint th, 0.5}
+  surface_cases.npz    standalone operators: thresholding, reduce_echoes, get_amplitudes, SemiGlobalBlock.forward
   aux_cases.npz        loss + gradient (main.py:228-232 through the reference's ops and autograd),
                        find_threshold, upscale_1d / iq2rf, AttentionBlock (dropout off)
 
@@ -432,7 +437,91 @@ def gen_train_cases():
         print("train case", name, losses)
 
 
+
+def sha(a):
+    import hashlib
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def gen_scale():
+    """SURVEY 8c golden set at N = 64 x 3 seeds x 4 lengths per StofNet checkpoint (hashes + index lists, no tensors)."""
+    for name, (rf, th) in STOF.items():
+        sd = load_sd(name)
+        has_sgb = any(k.startswith("semi_global_block") for k in sd)
+        model = StofNet(upsample_factor=4, semi_global_scale=80 if has_sgb else 1).eval()
+        model.load_state_dict(sd)
+        out = {"rf": np.int64(rf), "th": np.float64(np.nan if th is None else th)}
+        cases = [(64, L, seed) for seed in (3008, 0, 1) for L in (2560, 2578, 5120, 160)]
+        out["cases"] = np.array(cases, dtype=np.int64)
+        for ci, (N, L, seed) in enumerate(cases):
+            xn = synth_waveforms(N, L, seed=seed, rf=rf, q15=True)
+            x = torch.from_numpy(xn).unsqueeze(1)
+            with torch.no_grad():
+                m = model(x)
+            p = "c%d" % ci
+            out[p + "_x_sha"] = np.array(sha(xn))
+            out[p + "_mask_sha"] = np.array(sha(m.numpy()))
+            out[p + "_rowmax"] = m.squeeze(1).max(dim=1)[0].numpy()
+            out[p + "_rowabsmax"] = m.squeeze(1).abs().max(dim=1)[0].numpy()
+            for t in sorted({None, th, 0.5}, key=lambda v: (v is not None, v or 0)):
+                peaks_dict(p, m, t, out)
+            print("  scale", name, ci, N, L, seed, "K(th=0.5) =", out[p + "_idx_0p5"].shape[0])
+        np.savez_compressed(os.path.join(HERE, "scale_%s.npz" % name), **out)
+
+
+def gen_surface_cases():
+    """Standalone operators of the reference's surface: thresholding (:14-23), reduce_echoes (:117-132), get_amplitudes
+    (:135-136) of utils/mask2samples.py and SemiGlobalBlock.forward (models/stofnet.py:98-117)."""
+    from utils.mask2samples import thresholding, reduce_echoes, get_amplitudes
+    rng = np.random.default_rng(23)
+    out = {}
+    s = rng.normal(size=(5, 1, 333)).astype(np.float32)
+    s[1, 0, 7] = np.nan
+    s[3, 0, :] = -1.25
+    for key, th in (("th_float", 0.4), ("th_none", None), ("th_zero", 0.0), ("th_neg", -0.5)):
+        t = torch.from_numpy(s.copy())
+        r = thresholding(t, th)
+        out[key + "_in"] = s
+        out[key + "_th"] = np.float64(np.nan if th is None else th)
+        out[key + "_out"] = r.numpy()
+        out[key + "_inplace"] = np.int64(r.data_ptr() == t.data_ptr())
+    # reduce_echoes: distinct amplitudes (torch.argsort's tie order is unspecified), K > echo_max and K <= echo_max
+    K = 37
+    pos = np.sort(np.stack([rng.choice(4000, size=K, replace=False) for _ in range(6)]).astype(np.float32), axis=1)   # distinct: tie order is unspecified in the reference
+    amp = rng.permutation(6 * K).reshape(6, K).astype(np.float32) / 7.0
+    pairs = np.dstack([pos, amp]).astype(np.float32)
+    out["re_in"] = pairs
+    for e in (5, 36):       # the reference raises UnboundLocalError for K <= echo_max (`echoes` is only bound inside the if, :123-130)
+        out["re_out_%d" % e] = reduce_echoes(torch.from_numpy(pairs.copy()), echo_max=e).numpy()
+    triple = np.dstack([pos, amp, rng.normal(size=(6, K)).astype(np.float32)]).astype(np.float32)
+    out["re3_in"] = triple
+    out["re3_out_9"] = reduce_echoes(torch.from_numpy(triple.copy()), echo_max=9).numpy()
+    # get_amplitudes: half-way positions round to even
+    frames = rng.normal(size=(4, 1, 500)).astype(np.float32)
+    smp = rng.uniform(0, 499, size=(4, 21)).astype(np.float32)
+    smp[:, :4] = np.array([0.5, 1.5, 2.5, 498.5], np.float32)
+    out["ga_frames"], out["ga_samples"] = frames, smp
+    out["ga_out"] = get_amplitudes(torch.from_numpy(frames), torch.from_numpy(smp)).numpy()
+    # SemiGlobalBlock.forward standalone, weights of different-armadillo, L with and without the padded branch
+    sd = load_sd("different-armadillo")
+    model = StofNet(upsample_factor=4, semi_global_scale=80).eval()
+    model.load_state_dict(sd)
+    for key, (N, L) in (("sgb_a", (2, 400)), ("sgb_b", (1, 2578)), ("sgb_c", (1, 80))):
+        # inputs on a coarse grid that float16 holds exactly (half the fixture bytes)
+        x = torch.from_numpy((rng.integers(-2048, 2049, size=(N, 64, L)) / 512.0).astype(np.float32))
+        with torch.no_grad():
+            y = model.semi_global_block(x)
+        out[key + "_x"], out[key + "_y"] = x.numpy().astype(np.float16), y.numpy()
+    np.savez_compressed(os.path.join(HERE, "surface_cases.npz"), **out)
+    print("surface cases done")
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "scale":
+        gen_scale()
+        sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "surface":
+        gen_surface_cases()
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "train":
         gen_train_cases()
         sys.exit(0)
@@ -452,4 +541,6 @@ if __name__ == "__main__":
     gen_metrics_cases()
     gen_aux_cases()
     gen_train_cases()
+    gen_scale()
+    gen_surface_cases()
     print("done")

@@ -155,3 +155,86 @@ def test_attention_block(sb, dev, golden):
     ys = torch.stack([blk(x, seed=s) for s in range(64)]).mean(0).cpu().numpy()
     assert np.abs(ys - g["att_y"]).mean() <= 0.1 * np.abs(g["att_y"]).mean() + 0.05
     assert not torch.equal(blk(x, seed=1), blk(x, seed=2)) and torch.equal(blk(x, seed=3), blk(x, seed=3))
+
+
+def test_surface_thresholding(sb, dev, golden):
+    """thresholding (utils/mask2samples.py:14-23) as stof_thresholding: bit-exact, in place for a float threshold."""
+    g = golden("surface_cases.npz")
+    for key in ("th_float", "th_none", "th_zero", "th_neg"):
+        th = float(g[key + "_th"]); th = None if np.isnan(th) else th
+        t = torch.from_numpy(g[key + "_in"].copy()).to(dev)
+        r = sb.thresholding(t, th)
+        assert np.array_equal(r.cpu().numpy(), g[key + "_out"], equal_nan=True), key
+        assert int(r.data_ptr() == t.data_ptr()) == int(g[key + "_inplace"]), key
+
+
+def test_surface_reduce_echoes_and_amplitudes(sb, dev, golden):
+    from stofnet_b200.utils.mask2samples import reduce_echoes, get_amplitudes
+    g = golden("surface_cases.npz")
+    for e in (5, 36):
+        r = reduce_echoes(torch.from_numpy(g["re_in"]).to(dev), echo_max=e)
+        assert np.array_equal(r.cpu().numpy(), g["re_out_%d" % e]), e
+    r = reduce_echoes(torch.from_numpy(g["re3_in"]).to(dev), echo_max=9)
+    assert np.array_equal(r.cpu().numpy(), g["re3_out_9"])
+    same = torch.from_numpy(g["re_in"]).to(dev)
+    assert reduce_echoes(same, echo_max=37) is same
+    a = get_amplitudes(torch.from_numpy(g["ga_frames"]).to(dev), torch.from_numpy(g["ga_samples"]).to(dev))
+    assert np.array_equal(a.cpu().numpy(), g["ga_out"])
+    with pytest.raises(RuntimeError):
+        get_amplitudes(torch.zeros(2, 1, 10, device=dev), torch.full((2, 3), 10.0, device=dev))
+
+
+def test_surface_semi_global_block_standalone(sb, dev, golden):
+    """SemiGlobalBlock.forward on its own (models/stofnet.py:98-117): fp32 FFMA kernels vs the reference's output."""
+    g = golden("surface_cases.npz")
+    sd = {k: torch.from_numpy(v) for k, v in golden("weights_different-armadillo.npz").items()}
+    model = sb.build_model(sd, dev)
+    blk = model.semi_global_block
+    for key in ("sgb_a", "sgb_b", "sgb_c"):
+        x = torch.from_numpy(g[key + "_x"].astype(np.float32)).to(dev)
+        with torch.no_grad():
+            y = blk(x)
+        ref = g[key + "_y"]
+        assert y.shape == ref.shape
+        assert np.abs(y.cpu().numpy() - ref).max() <= 2e-5 * np.abs(ref).max(), key
+    for L in (79, 161):
+        with pytest.raises(RuntimeError):
+            blk(torch.zeros(1, 64, L, device=dev))
+    # a freshly constructed block (no parent StofNet) works as well, and follows weight updates
+    fresh = sb.SemiGlobalBlock(64, 64, 80).to(dev)
+    fresh.load_state_dict(blk.state_dict())
+    x = torch.from_numpy(g["sgb_a_x"].astype(np.float32)).to(dev)
+    with torch.no_grad():
+        assert torch.equal(fresh(x), blk(x))
+        fresh.expand_conv.bias.add_(1.0)
+        assert not torch.equal(fresh(x), blk(x))
+
+
+def test_surface_sample_shuffle(sb, dev, golden):
+    """SampleShuffle1D standalone (utils/sample_shuffle.py:10-28) through stof_sample_shuffle on the reference's vectors."""
+    g = golden("metrics_cases.npz")
+    x = torch.from_numpy(g["shuffle_x"]).to(dev)
+    for r in (4, 2):
+        y = sb.SampleShuffle1D(r)(x)
+        assert np.array_equal(y.cpu().numpy(), g["shuffle_r%d" % r]), r
+
+
+def test_run_py_eval_call_sites(golden):
+    """run.py: config.yaml + key=value overrides -> checkpoint by prefix -> infer_host -> toa_rmse(tol=cfg.etol), the
+    reference's eval call sites (main.py:174-177,307-347) on a golden checkpoint."""
+    import importlib.util
+    import os
+    from conftest import ROOT, GOLDEN
+    import stofnet_b200 as sbm
+    spec = importlib.util.spec_from_file_location("run_py", os.path.join(ROOT, "run.py"))
+    run_py = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(run_py)
+    cfg = sbm.load_config(os.path.join(ROOT, "config.yaml"),
+                          ["ckpt_dir=" + GOLDEN, "model_file=weights_different-armadillo", "th=Null", "batch_size=8", "etol=4"])
+    assert cfg.th is None and cfg.rf_scale_factor == 10 and cfg.nms_win_size == 20 and cfg.upsample_factor == 4
+    out = run_py.evaluate(cfg)
+    assert out["model"] == "StofNet" and out["rows"] == 16 and out["L"] == 2560
+    assert out["tp"] + out["fn"] > 0 and 14 <= out["tp"] + out["fp"] <= 20     # th=None: one detection per row (ties / position 0 aside)
+    out2 = run_py.evaluate(sbm.load_config(os.path.join(ROOT, "config.yaml"),
+                                           ["ckpt_dir=" + GOLDEN, "model_file=weights_different-armadillo", "th=0.5", "batch_size=8"]))
+    assert out2["tp"] + out2["fp"] >= out["tp"] + out["fp"]

@@ -32,6 +32,21 @@ def test_library_exports_every_declared_symbol():
     assert b"sm_100a" in _lib.lib.stof_version()
 
 
+def test_library_is_built_from_this_tree():
+    """stof_version() embeds the SHA-256 of the sources the .so was compiled from (csrc/Makefile): a stale pre-built
+    library (the .so is git-ignored and shipped to the GPU box as built) cannot pass the suite silently."""
+    import hashlib
+    import glob
+    csrc = os.path.join(ROOT, "stofnet_b200", "csrc")
+    files = sorted(glob.glob(os.path.join(csrc, "*.cu")) + glob.glob(os.path.join(csrc, "*.cuh")), key=os.path.basename)
+    h = hashlib.sha256()
+    for f in files + [os.path.join(ROOT, "include", "stofnet_b200.h")]:
+        h.update(open(f, "rb").read())
+    want = h.hexdigest()[:16]
+    got = _lib.lib.stof_version().decode()
+    assert got.endswith("src:" + want), "libstofnet_b200.so is stale: built from %s, tree is %s - run __graft_entry__.build()" % (got, want)
+
+
 def test_library_is_sm100a_with_lineinfo():
     import subprocess
     out = subprocess.run(["cuobjdump", "-lelf", _lib.LIB_PATH], capture_output=True, text=True).stdout

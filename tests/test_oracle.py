@@ -156,3 +156,52 @@ def test_aux_ops(golden):
         ref = g["rmse_tol%s" % th_key(tol)]
         out = c_oracle.toa_rmse(g["rmse_gt"], g["rmse_es"], tol)
         assert np.allclose(out, ref, rtol=1e-5, atol=1e-6, equal_nan=True), tol
+
+
+@pytest.mark.parametrize("name", STOF_CKPTS)
+def test_scale_golden_set_port(golden, name):
+    """The N = 64 x 3 seeds golden set: the host-independent generator reproduces the inputs (SHA-256), and the
+    port reproduces the reference's index lists on a subset small enough for the CPU suite (L = 160 and one L = 2560 case)."""
+    import hashlib
+    from stofnet_b200.synth import synth_waveforms
+    g = golden("scale_%s.npz" % name)
+    sd = torch_port.to_torch_sd(golden("weights_%s.npz" % name))
+    rf = int(g["rf"])
+    assert len(g["cases"]) == 12 and all(int(c[0]) == 64 for c in g["cases"])
+    for ci, (N, L, seed) in enumerate(g["cases"]):
+        if not (L == 160 or (L == 2560 and seed == 3008)):
+            continue
+        x = synth_waveforms(int(N), int(L), seed=int(seed), rf=rf, q15=True)
+        assert hashlib.sha256(x.tobytes()).hexdigest() == str(g["c%d_x_sha" % ci])
+        with torch.no_grad():
+            m = torch_port.stofnet_forward(sd, torch.from_numpy(x).unsqueeze(1))
+        assert np.abs(m.squeeze(1).max(dim=1)[0].numpy() - g["c%d_rowmax" % ci]).max() <= 2e-5 * g["c%d_rowabsmax" % ci].max()
+        for th in th_list(g):
+            idx = torch_port.get_maxima_positions(m, 20, th).numpy()
+            ref = g["c%d_idx_%s" % (ci, th_key(th))]
+            if not np.array_equal(idx, ref):        # thread-count dependent last bits: only boundary flips are tolerated
+                from parity_util import assert_index_parity
+                assert_index_parity(sd, x, idx, ref, th, what="%s case %d" % (name, ci))
+
+
+def test_surface_ops_port(golden):
+    """thresholding / reduce_echoes / get_amplitudes / SemiGlobalBlock restatements against the reference's outputs."""
+    g = golden("surface_cases.npz")
+    for key in ("th_float", "th_none", "th_zero", "th_neg"):
+        th = float(g[key + "_th"]); th = None if np.isnan(th) else th
+        t = torch.from_numpy(g[key + "_in"].copy())
+        r = torch_port.thresholding(t, th)
+        assert np.array_equal(r.numpy(), g[key + "_out"], equal_nan=True), key
+        assert int(r.data_ptr() == t.data_ptr()) == int(g[key + "_inplace"]), key
+    for e in (5, 36):
+        r = torch_port.reduce_echoes(torch.from_numpy(g["re_in"].copy()), e)
+        assert np.array_equal(r.numpy(), g["re_out_%d" % e])
+    assert np.array_equal(torch_port.reduce_echoes(torch.from_numpy(g["re3_in"].copy()), 9).numpy(), g["re3_out_9"])
+    a = torch_port.get_amplitudes(torch.from_numpy(g["ga_frames"]), torch.from_numpy(g["ga_samples"]))
+    assert np.array_equal(a.numpy(), g["ga_out"])
+    sd = torch_port.to_torch_sd(golden("weights_different-armadillo.npz"))
+    for key in ("sgb_a", "sgb_b", "sgb_c"):
+        x = torch.from_numpy(g[key + "_x"].astype(np.float32))
+        with torch.no_grad():
+            y = torch_port.semi_global_block(sd, x)
+        assert np.abs(y.numpy() - g[key + "_y"]).max() <= 2e-5 * np.abs(g[key + "_y"]).max(), key
