@@ -17,7 +17,7 @@ in the CPU tests of the host logic (tests/test_sharded.py).
 import torch
 import torch.distributed as dist
 
-__all__ = ["shard_rows", "gather_tof_table", "infer_sharded"]
+__all__ = ["shard_rows", "gather_tof_table", "infer_sharded", "TofGatherPipeline"]
 
 
 def shard_rows(n_rows, world_size, rank):
@@ -95,3 +95,92 @@ def infer_sharded(model, frame_local, n_rows_total, window_size, threshold=None,
     table = gather_tof_table(coords, kmax, n_rows_total, group=group,
                              channels=masks.shape[1] if masks.dim() == 3 else 1)
     return masks, table
+
+
+class TofGatherPipeline:
+    """The per-step ToF gather taken off the critical path (streaming inference over many batches).
+
+    gather_tof_table() is exact but serial: MAX all-reduce -> host reads K_max -> all-gather, all on the compute stream, and
+    the all-gather moves the full cap-wide table.  In a stream of batches the table of step i is only needed once step i+1
+    is already running, so here
+      * `submit` copies the first `k_opt` columns of the local table into a slot buffer (k_opt = the previous steps' global
+        K_max, the optimistic stride; 1/2 .. 1/4 of `cap` in practice) and issues the MAX all-reduce + all-gather on a SIDE
+        stream behind an event, so the next batch's forward overlaps the exchange;
+      * `collect` (called one step later, or at the end) waits for the slot, reads the global K_max, and returns the
+        reference-shaped table; when a batch turns out to need more columns than k_opt the caller's full local table of
+        that step (kept alive by double buffering: `submit` returns the slot index) is re-gathered at the exact width - the
+        fallback costs one serial gather and raises k_opt.
+    Equal shards only (rows_local the same on every rank: what the bench and the 128 x 1000 PALA fold have).
+    CPU tensors / gloo: the same logic runs inline without streams (tests/test_sharded.py)."""
+
+    def __init__(self, rows_local, cap, device, group=None, k_init=None, slots=2):
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rows, self.cap, self.device = int(rows_local), int(cap), device
+        self.k_seen = int(k_init) if k_init else 0        # largest global K_max seen so far
+        self.k_opt = self._stride(self.k_seen) if k_init else self.cap     # first step: full width
+        self.cuda = device.type == "cuda"
+        self.stream = torch.cuda.Stream(device) if self.cuda else None
+        self.slots = slots
+        self.send = [torch.zeros((self.rows * self.cap,), dtype=torch.float32, device=device) for _ in range(slots)]
+        self.recv = [torch.zeros((self.world * self.rows * self.cap,), dtype=torch.float32, device=device) for _ in range(slots)]
+        self.kmax = [torch.zeros((1,), dtype=torch.int64, device=device) for _ in range(slots)]
+        self.done = [torch.cuda.Event() if self.cuda else None for _ in range(slots)]
+        self.k_used = [0] * slots
+        self.i = 0
+        self.fallbacks = 0
+
+    def _stride(self, k_seen):
+        """optimistic stride for the next steps: the largest K_max seen plus 1/8 headroom (at least 4 columns)"""
+        return min(self.cap, max(1, k_seen + max(4, k_seen // 8)))
+
+    def submit(self, local_coords, local_kmax):
+        """local_coords (rows, cap) fp32 as written by stof_peaks; local_kmax: 1-element int64 tensor on the device (stats[:1])
+        or an int.  Returns the slot; the caller must keep `local_coords` of this step intact until collect(slot)."""
+        slot = self.i % self.slots
+        self.i += 1
+        k = min(self.k_opt, self.cap)
+        self.k_used[slot] = k
+        send = self.send[slot][:self.rows * k].view(self.rows, k)
+        send.copy_(local_coords[:, :k])                                   # tiny; on the compute stream
+        if isinstance(local_kmax, torch.Tensor):
+            self.kmax[slot].copy_(local_kmax.reshape(-1)[:1])
+        else:
+            self.kmax[slot].fill_(int(local_kmax))
+        recv = self.recv[slot][:self.world * self.rows * k].view(self.world * self.rows, k)
+        if self.cuda:
+            ready = torch.cuda.Event()
+            ready.record(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(self.stream):
+                self.stream.wait_event(ready)
+                self._exchange(self.kmax[slot], send, recv)
+                self.done[slot].record(self.stream)
+        else:
+            self._exchange(self.kmax[slot], send, recv)
+        return slot
+
+    def _exchange(self, kmax, send, recv):
+        if self.world > 1:
+            dist.all_reduce(kmax, op=dist.ReduceOp.MAX, group=self.group)
+            dist.all_gather_into_tensor(recv, send, group=self.group)
+        else:
+            recv.copy_(send)
+
+    def collect(self, slot, local_coords=None, channels=1):
+        """Global (world * rows, K_max) table of the step submitted into `slot` (zeros((N, channels, 1)) when no rank
+        detected anything, utils/mask2samples.py:87-88).  local_coords: that step's full local table, needed only when
+        the optimistic stride was too narrow."""
+        if self.cuda:
+            self.done[slot].synchronize()
+        k, kg = self.k_used[slot], int(self.kmax[slot].item())
+        n_total = self.world * self.rows
+        if kg == 0:
+            return torch.zeros((n_total, channels, 1), dtype=torch.float32, device=self.device)
+        self.k_seen = max(self.k_seen, kg)
+        self.k_opt = self._stride(self.k_seen)
+        if kg > k:
+            if local_coords is None:
+                raise RuntimeError("TofGatherPipeline: K_max=%d exceeds the optimistic stride %d and the local table was not kept" % (kg, k))
+            self.fallbacks += 1
+            return gather_tof_table(local_coords, kg, n_total, group=self.group, channels=channels)
+        return self.recv[slot][:n_total * k].view(n_total, k)[:, :kg]

@@ -150,4 +150,4 @@ def test_c2_bench_batch_slice(sb, dev, golden):
     if not np.array_equal(idx, ref_idx):
         assert_index_parity(sd, x, idx, ref_idx, bench.TH, ref_masks32=ref, what="bench batch slice")
     co = sb.mask2coords(m, 20, bench.TH, upsample_factor=4)
-    assert co.shape[1] <= bench.CAP, "bench CAP=%d would truncate the ToF table (K_max=%d)" % (bench.CAP, co.shape[1])
+    print("bench batch: K_max = %d over %d rows (bench.py widens its table from CAP=%d when needed)" % (co.shape[1], bench.ROWS, bench.CAP))

@@ -83,6 +83,59 @@ def test_gather_matches_undivided_batch(tmp_path, world, n_rows, th, empty):
         assert np.array_equal(got, want)
 
 
+def _pipeline_worker(rank, world, port, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle import c_oracle
+        from stofnet_b200.sharded import TofGatherPipeline
+        n_rows, cap = 8, 96
+        lo, hi = shard_rows(n_rows, world, rank)
+        pipe = TofGatherPipeline(hi - lo, cap, torch.device("cpu"))
+        # a stream of batches: the stride narrows to the first batches' K_max, then a batch grows past the optimistic stride (fallback);
+        # the last batch detects nothing anywhere
+        plan = [(0.5, 1.0), (0.5, 1.0), (0.5, 1.0), (0.015, 1.0), (0.5, 0.0)]
+        pending = None
+        for step in range(len(plan) + 1):
+            if step < len(plan):
+                th, gain = plan[step]
+                masks = _masks(n_rows) * gain
+                local = c_oracle.mask2coords(masks[lo:hi], 20, th, 4)
+                tab = torch.zeros((hi - lo, cap))
+                kmax = 0
+                if local.ndim == 2:
+                    kmax = local.shape[1]
+                    tab[:, :kmax] = torch.from_numpy(np.ascontiguousarray(local))
+                slot = pipe.submit(tab, torch.tensor([kmax]))
+            if pending is not None:                     # collect the PREVIOUS step, one step late (the overlapped schedule)
+                pstep, pslot, ptab = pending
+                out = pipe.collect(pslot, ptab)
+                np.save(os.path.join(out_dir, "pipe_%d_%d.npy" % (rank, pstep)), out.numpy())
+            pending = (step, slot, tab) if step < len(plan) else None
+        np.save(os.path.join(out_dir, "pipe_fallbacks_%d.npy" % rank), np.array([pipe.fallbacks, pipe.k_opt]))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_overlapped_gather_pipeline_matches_undivided_batch(tmp_path):
+    """TofGatherPipeline (side-stream gather with the previous steps' K_max as the optimistic stride) on a world-size-2
+    gloo group: every step's table equals mask2coords on the undivided batch, including the fallback when a batch needs
+    more columns than the stride, and the (N, 1, 1) result when nothing is detected."""
+    from oracle import c_oracle
+    world, n_rows = 2, 8
+    mp.spawn(_pipeline_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    plan = [(0.5, 1.0), (0.5, 1.0), (0.5, 1.0), (0.015, 1.0), (0.5, 0.0)]
+    for step, (th, gain) in enumerate(plan):
+        want = c_oracle.mask2coords(_masks(n_rows) * gain, 20, th, 4)
+        for r in range(world):
+            got = np.load(os.path.join(str(tmp_path), "pipe_%d_%d.npy" % (r, step)))
+            assert got.shape == want.shape, (step, got.shape, want.shape)
+            assert np.array_equal(got, want), step
+    fb = np.load(os.path.join(str(tmp_path), "pipe_fallbacks_0.npy"))
+    assert fb[0] >= 1                                    # step 3 needed more columns than the narrowed stride
+
+
 def test_shard_rows_partition():
     for n in (0, 1, 7, 128000, 4096):
         for w in (1, 2, 3, 8):
