@@ -156,6 +156,12 @@ int stof_profile_collect(stof_model *m, double *ms_by_class, int64_t *launches_b
 #define STOF_PATH_TC_FP16 2
 int stof_model_set_path(stof_model *m, int path, int layers_per_launch);
 
+/* Variant of the fused chain kernel: cta_pairs = 0 (default) runs one CTA per tile; 1 runs every tile pair on a 2-CTA cluster
+ * with tcgen05 cta_group::2 MMAs (each SM reads half of the weight operand).  Same arithmetic in the same order: the masks are
+ * bit-identical (tests/test_gpu_tc.py); the pair form measured slower (cross-CTA barrier latency on the per-layer critical path,
+ * DESIGN.md).  STOF_CHAIN_PAIR=1 in the environment sets the default to 1.                                              */
+int stof_model_set_chain_kernel(stof_model *m, int cta_pairs);
+
 /* One fused chain launch on caller-provided activations (test hook for single layers / segments):
  * layers [first, first+count) of the list conv2 .. conv{nb-1}, conv_last.
  *   in_planes_dev  (N, 2, 8, L, 8) fp16: plane 0 = fp16(v), plane 1 = fp16((v - plane0) * 2^11), channel c at [c/8][l][c%8]

@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libstofnet_b200.so")
+# STOFNET_B200_LIB: development override for A/B runs of two builds on one GPU box (tools/); the default is the in-tree library
+LIB_PATH = os.environ.get("STOFNET_B200_LIB") or os.path.join(_HERE, "libstofnet_b200.so")
 
 MAX_MID = 24
 KIND_STOFNET, KIND_ESPCN, KIND_EDSR = 0, 1, 2
@@ -66,6 +67,7 @@ _SIGS = {
     "stof_model_set_host_chunk_rows": (_i, [_vp, _i]),
     "stof_sample_shuffle": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "stof_model_set_path": (_i, [_vp, _i, _i]),
+    "stof_model_set_chain_kernel": (_i, [_vp, _i]),
     "stof_chain_segment": (_i, [_vp, _i, _i, _vp, _vp, _vp, _i, _i, _vp]),
     "stof_debug_set_timeline": (_i, [_vp, _i]),
     "stof_sgb_expand": (_i, [_vp, _vp, _i, _i, _vp, _i, _vp]),

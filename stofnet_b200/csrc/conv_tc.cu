@@ -28,25 +28,11 @@
 #include <cuda_fp16.h>
 #include <string.h>
 
-#include "common.cuh"
-#include "kernels.cuh"
-#include "tc_ptx.cuh"
+#include "conv_tc_shared.cuh"
 
 namespace stof {
 
 using namespace ptx;
-
-constexpr int TC_THREADS = 352;                         // 1 producer + 2 MMA issuers + 8 epilogue warps
-constexpr int TC_EPI_WARPS = 8;
-constexpr int TC_R = 280;                              // smem rows per (plane, c8) slab
-constexpr int TC_SLAB = TC_R * 16;                     // bytes of one (plane, c8) slab
-constexpr int TC_PLANE = 8 * TC_SLAB;                  // one fp16 plane (hi or lo): 64 channels
-constexpr int TC_BUF = 2 * TC_PLANE;                   // hi + lo
-constexpr int TC_STAGES = 5;                          // weight ring of the fp32-faithful mode: 5 x 16 KB taps
-constexpr int TC_STAGE_BYTES = 16384;                  // one k7 tap: [8 c8][128 n][8] fp16
-constexpr int TC_MAX_STAGES = 10;                     // one-pass fp16 mode: 10 x 8 KB (W_hi only) in the same 80 KB
-constexpr float TC_LO_SCALE = 2048.0f;                 // 2^11
-constexpr float TC_LO_INV = 1.0f / 2048.0f;
 
 // shared memory map (dynamic, 1024-aligned base)
 constexpr int TC_OFF_P = 0;
@@ -60,41 +46,6 @@ constexpr int TC_OFF_TMEM = TC_OFF_BAR + TC_NBAR * 8;
 constexpr int TC_SMEM_BYTES = TC_OFF_TMEM + 16;
 
 static_assert(TC_SMEM_BYTES <= 232448, "chain kernel exceeds the 227 KB shared-memory limit");
-
-__device__ __forceinline__ uint32_t pack_half2(float a, float b) {
-    __half2 h = __floats2half2_rn(a, b);
-    return *reinterpret_cast<uint32_t *>(&h);
-}
-
-// two fp32 -> packed fp16x2 (round to nearest, saturated to the finite fp16 range); a in the low half
-__device__ __forceinline__ uint32_t cvt_sat_half2(float a, float b) {
-    uint32_t r;
-    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
-    return r;
-}
-// (v0, v1) -> packed hi = fp16(v), packed lo = fp16((v - hi) * 2^11)
-__device__ __forceinline__ void split_pair(float v0, float v1, uint32_t &hi, uint32_t &lo) {
-    hi = cvt_sat_half2(v0, v1);
-    const float2 h = __half22float2(*reinterpret_cast<const __half2 *>(&hi));
-    lo = cvt_sat_half2((v0 - h.x) * TC_LO_SCALE, (v1 - h.y) * TC_LO_SCALE);
-}
-
-// v -> (hi, lo) with hi = fp16(v) (saturated to the finite range), lo = fp16((v - hi) * 2^11)
-__device__ __forceinline__ void split_hi_lo(float v, float &hi, float &lo) {
-    const float c = fminf(fmaxf(v, -65504.0f), 65504.0f);
-    hi = __half2float(__float2half_rn(c));
-    lo = (c - hi) * TC_LO_SCALE;
-}
-
-__device__ __forceinline__ void unpack8(const uint4 &u, float (&f)[8]) {
-    const __half2 *h = reinterpret_cast<const __half2 *>(&u);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const float2 t = __half22float2(h[i]);
-        f[2 * i] = t.x;
-        f[2 * i + 1] = t.y;
-    }
-}
 
 // optional timeline (stof_debug_set_timeline): roles 0..3 (producer, MMA issuer 0 / 1, epilogue warp 3) of CTA 0 each append
 // (code, clock64) pairs to a private quarter of the buffer with a register counter (no atomics: the probe must not stall
@@ -513,11 +464,23 @@ x0_split_kernel(const float *__restrict__ x, const float *__restrict__ e, int N,
                 const float *__restrict__ w /*[K][64]*/, const float *__restrict__ b, uint4 *__restrict__ planes, int fast) {
     __shared__ float4 ws[K * 16];
     __shared__ float4 bs[16];
+    // E of the (at most 5) pooled positions this block's 256 samples fall into, [slot][64 channels]: one shared-memory
+    // broadcast read per 4 channels instead of 64 scalar global loads per thread
+    __shared__ float4 es[6 * 16];
+    const int n = blockIdx.y;
+    const int l0 = blockIdx.x * 256;
     for (int i = threadIdx.x; i < K * 16; i += 256) ws[i] = reinterpret_cast<const float4 *>(w)[i];
     if (threadIdx.x < 16) bs[threadIdx.x] = reinterpret_cast<const float4 *>(b)[threadIdx.x];
+    const int j0 = (l0 - off >= 0) ? (l0 - off) / scale : 0;                 // first pooled slot touched by this block
+    if (e != nullptr) {
+        for (int i = threadIdx.x; i < 6 * 64; i += 256) {
+            const int slot = i >> 6, c = i & 63;
+            const int j = j0 + slot;
+            reinterpret_cast<float *>(es)[slot * 64 + c] = (j < P) ? __ldg(e + ((size_t)n * 64 + c) * P + j) : 0.0f;
+        }
+    }
     __syncthreads();
-    const int n = blockIdx.y;
-    const int l = blockIdx.x * 256 + threadIdx.x;
+    const int l = l0 + threadIdx.x;
     if (l >= L) return;
     const float *xr = x + (size_t)n * L;
     float xv[K];
@@ -528,7 +491,7 @@ x0_split_kernel(const float *__restrict__ x, const float *__restrict__ e, int N,
     }
     const int j = l - off;
     const bool has_e = (e != nullptr) && j >= 0 && j < scale * P;
-    const float *er = has_e ? e + (size_t)n * 64 * P + j / scale : nullptr;
+    const float4 *er = es + (has_e ? (j / scale - j0) : 0) * 16;
     uint4 *dst = planes + (size_t)n * 16 * L + l;
 #pragma unroll 2
     for (int c8 = 0; c8 < 8; ++c8) {
@@ -547,17 +510,17 @@ x0_split_kernel(const float *__restrict__ x, const float *__restrict__ e, int N,
             }
             v[4 * h + 0] = fmaxf(a01.x, 0.f); v[4 * h + 1] = fmaxf(a01.y, 0.f);
             v[4 * h + 2] = fmaxf(a23.x, 0.f); v[4 * h + 3] = fmaxf(a23.y, 0.f);
+            if (has_e) {
+                const float4 ev = er[2 * c8 + h];
+                v[4 * h + 0] += ev.x; v[4 * h + 1] += ev.y; v[4 * h + 2] += ev.z; v[4 * h + 3] += ev.w;
+            }
         }
-        if (has_e) {
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] += __ldg(er + (size_t)(8 * c8 + i) * P);
-        }
-        float hi[8], lo[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) split_hi_lo(v[i], hi[i], lo[i]);
+        // (hi, lo) planes with the packed conversions of the chain kernel's epilogue (same rounding and saturation as split_hi_lo)
         uint4 uh, ul;
-        uh.x = pack_half2(hi[0], hi[1]); uh.y = pack_half2(hi[2], hi[3]); uh.z = pack_half2(hi[4], hi[5]); uh.w = pack_half2(hi[6], hi[7]);
-        ul.x = pack_half2(lo[0], lo[1]); ul.y = pack_half2(lo[2], lo[3]); ul.z = pack_half2(lo[4], lo[5]); ul.w = pack_half2(lo[6], lo[7]);
+        split_pair(v[0], v[1], uh.x, ul.x);
+        split_pair(v[2], v[3], uh.y, ul.y);
+        split_pair(v[4], v[5], uh.z, ul.z);
+        split_pair(v[6], v[7], uh.w, ul.w);
         dst[(size_t)c8 * L] = uh;
         if (!fast) dst[(size_t)(8 + c8) * L] = ul;
     }

@@ -37,6 +37,11 @@ struct TcLayer {
     int n_fast;           // N of the single X_hi * W_hi MMA of the one-pass fp16 mode (64, or 16 for conv_last)
     const void *w_fast;   // one-pass mode: W_hi-only taps [tap][c8][w_rows_fast][8]
     int stage_bytes_fast, w_rows_fast;
+    // CTA-pair kernel (conv_tc2.cu): each CTA of the pair streams its own half of every tap, [tap][c8][rows2][8];
+    // rank 0: W_hi | first half of W_hi again, rank 1: W_lo | second half of W_hi (see upload_tc)
+    const void *w2[2], *w2_fast[2];
+    int stage_bytes2, rows2, lo_row2;          // exact mode: bytes per tap and CTA, rows per c8 chunk, first row of the X_lo product's B
+    int stage_bytes2_fast, rows2_fast;
 };
 
 struct TcParams {
@@ -65,6 +70,9 @@ void set_chain_timeline(void *dev_buf, int cap);
 // layers[first .. first+count) of the spec list; returns STOF_E_* on error
 int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void *x0, void *out_planes, float *out_mask,
                     int N, int L, cudaStream_t st, int fast = 0);
+// conv_tc2.cu: the same segment on CTA pairs (2-CTA clusters, tcgen05 cta_group::2: M = 256 per MMA, each CTA reads half of B)
+int launch_chain_tc2(const TcLayer *layers, int count, const void *in, const void *x0, void *out_planes, float *out_mask,
+                     int N, int L, cudaStream_t st, int fast = 0);
 // x (N, L) fp32 -> split planes of x0 = act(conv_first(x)) [+ nearest-upsampled E, centred]  (models/stofnet.py:45,96-115)
 int launch_x0_split(const float *x, const float *e, int N, int L, int P, int scale, int off, const float *w, const float *b,
                     void *planes, cudaStream_t st, int fast = 0, int K = 9);

@@ -1,5 +1,6 @@
 // Internal definition of the opaque stof_model handle (shared by stof_api.cu and train.cu).
 #pragma once
+#include <stdlib.h>
 #include <vector>
 
 #include "common.cuh"
@@ -32,6 +33,10 @@ struct stof_model {
     int seg_len = 4;                                  // layers fused per chain launch
     void *tc_w = nullptr;
     void *tc_w_fast = nullptr;                        // W_hi-only taps of the one-pass fp16 mode
+    void *tc_w2 = nullptr, *tc_w2_fast = nullptr;     // per-rank half-taps of the CTA-pair chain kernel (conv_tc2.cu)
+    // chain kernel variant: one CTA per tile (default), or CTA pairs with cta_group::2 MMAs (STOF_CHAIN_PAIR=1 in the
+    // environment, or stof_model_set_chain_kernel; bit-identical results, measured 13-21 % slower: see DESIGN.md)
+    bool chain_pair = getenv("STOF_CHAIN_PAIR") && getenv("STOF_CHAIN_PAIR")[0] == '1';
     void *tc_expand_w = nullptr;                      // expand conv: [8 groups][5 taps][8 c8][W_hi 64 | W_lo 64][8] fp16
     void *tc_contract_w = nullptr;                    // contract conv: [4 slices][5 taps][8 c8][W_hi 128 | W_lo 128][8] fp16
     stof::TcLayer tc_layer[STOF_MAX_MID_CONVS + 1];   // spec list: mid convs then conv_last

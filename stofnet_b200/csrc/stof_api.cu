@@ -120,6 +120,45 @@ static int upload_tc(stof_model *m, const stof_weights *w, const float *last_w /
                     __float2half_rn(last_w[((size_t)u * 64 + ci) * 3 + t]);
     if (!m->tc_w_fast) STOF_CUDA(cudaMalloc(&m->tc_w_fast, bf.size() * sizeof(__half)));
     STOF_CUDA(cudaMemcpy(m->tc_w_fast, bf.data(), bf.size() * sizeof(__half), cudaMemcpyHostToDevice));
+    // CTA-pair kernel (conv_tc2.cu): per cluster rank its half of every tap.
+    //   exact, 64 -> 64: [tap][c8][96][8]   rank 0: rows 0-63 W_hi, rows 64-95 W_hi[co 0-31];  rank 1: rows 0-63 W_lo, rows 64-95 W_hi[co 32-63]
+    //   exact, conv_last: [tap][c8][16][8]  rank 0: rows 0-3 W_hi, rows 8-11 W_hi;            rank 1: rows 0-3 W_lo
+    //   one-pass, 64 -> 64: [tap][c8][32][8] rank r: W_hi[co 32 r ..];   conv_last: [tap][c8][8][8]  rank 0: rows 0-3 W_hi, rank 1: zeros
+    const size_t mid2 = 8 * 96 * 8, last2 = 8 * 16 * 8, mid2f = 8 * 32 * 8, last2f = 8 * 8 * 8;       // halves per tap and rank
+    const size_t rank2 = (size_t)n_mid * KM * mid2 + 3 * last2, rank2f = (size_t)n_mid * KM * mid2f + 3 * last2f;
+    std::vector<__half> b2(2 * rank2, __float2half_rn(0.0f)), b2f(2 * rank2f, __float2half_rn(0.0f));
+    for (int j = 0; j < n_mid; ++j)
+        for (int t = 0; t < KM; ++t)
+            for (int co = 0; co < 64; ++co)
+                for (int ci = 0; ci < 64; ++ci) {
+                    __half hi, lo;
+                    split_w(w->mid_w[j][((size_t)co * 64 + ci) * KM + t], hi, lo);
+                    const size_t c8o = (size_t)(ci >> 3), e = ci & 7;
+                    __half *t0 = b2.data() + ((size_t)j * KM + t) * mid2, *t1 = b2.data() + rank2 + ((size_t)j * KM + t) * mid2;
+                    t0[(c8o * 96 + co) * 8 + e] = hi;
+                    t1[(c8o * 96 + co) * 8 + e] = lo;
+                    if (co < 32) t0[(c8o * 96 + 64 + co) * 8 + e] = hi;
+                    else t1[(c8o * 96 + 64 + (co - 32)) * 8 + e] = hi;
+                    __half *f = b2f.data() + (size_t)(co >> 5) * rank2f + ((size_t)j * KM + t) * mid2f;
+                    f[(c8o * 32 + (co & 31)) * 8 + e] = hi;
+                }
+    for (int t = 0; t < 3; ++t)
+        for (int u = 0; u < 4; ++u)
+            for (int ci = 0; ci < 64; ++ci) {
+                __half hi, lo;
+                split_w(last_w[((size_t)u * 64 + ci) * 3 + t], hi, lo);
+                const size_t c8o = (size_t)(ci >> 3), e = ci & 7;
+                __half *t0 = b2.data() + (size_t)n_mid * KM * mid2 + (size_t)t * last2, *t1 = t0 + rank2;
+                t0[(c8o * 16 + u) * 8 + e] = hi;
+                t0[(c8o * 16 + 8 + u) * 8 + e] = hi;
+                t1[(c8o * 16 + u) * 8 + e] = lo;
+                b2f[(size_t)n_mid * KM * mid2f + (size_t)t * last2f + (c8o * 8 + u) * 8 + e] = hi;
+            }
+    if (!m->tc_w2) STOF_CUDA(cudaMalloc(&m->tc_w2, b2.size() * sizeof(__half)));
+    STOF_CUDA(cudaMemcpy(m->tc_w2, b2.data(), b2.size() * sizeof(__half), cudaMemcpyHostToDevice));
+    if (!m->tc_w2_fast) STOF_CUDA(cudaMalloc(&m->tc_w2_fast, b2f.size() * sizeof(__half)));
+    STOF_CUDA(cudaMemcpy(m->tc_w2_fast, b2f.data(), b2f.size() * sizeof(__half), cudaMemcpyHostToDevice));
+    const __half *base2 = reinterpret_cast<const __half *>(m->tc_w2), *base2f = reinterpret_cast<const __half *>(m->tc_w2_fast);
     const __half *fbase = reinterpret_cast<const __half *>(m->tc_w_fast);
     const __half *base = reinterpret_cast<const __half *>(m->tc_w);
     for (int j = 0; j < n_mid; ++j) {
@@ -132,6 +171,11 @@ static int upload_tc(stof_model *m, const stof_weights *w, const float *last_w /
         l.type = (j == n_mid - 1) ? TC_LONGSKIP : ((j & 1) ? TC_RES : (edsr ? TC_RELU : TC_LEAKY));
         l.stage_bytes = 16384; l.n_out = 64; l.n_stack = 128; l.n_lo = 64; l.lo_row = 0; l.lo_col = 64; l.w_rows = 128; l.n_fast = 64;
         l.w_fast = fbase + (size_t)j * KM * mid_tap_f; l.stage_bytes_fast = 8192; l.w_rows_fast = 64;
+        for (int r = 0; r < 2; ++r) {
+            l.w2[r] = base2 + (size_t)r * rank2 + (size_t)j * KM * mid2;
+            l.w2_fast[r] = base2f + (size_t)r * rank2f + (size_t)j * KM * mid2f;
+        }
+        l.stage_bytes2 = 12288; l.rows2 = 96; l.lo_row2 = 64; l.stage_bytes2_fast = 4096; l.rows2_fast = 32;
     }
     TcLayer &l = m->tc_layer[n_mid];
     l.w = base + (size_t)n_mid * KM * mid_tap;
@@ -139,6 +183,11 @@ static int upload_tc(stof_model *m, const stof_weights *w, const float *last_w /
     l.taps = 3; l.pad = 1; l.type = TC_LAST;
     l.stage_bytes = 4096; l.n_out = 4; l.n_stack = 16; l.n_lo = 16; l.lo_row = 16; l.lo_col = 8; l.w_rows = 32; l.n_fast = 16;
     l.w_fast = fbase + (size_t)n_mid * KM * mid_tap_f; l.stage_bytes_fast = 2048; l.w_rows_fast = 16;
+    for (int r = 0; r < 2; ++r) {
+        l.w2[r] = base2 + (size_t)r * rank2 + (size_t)n_mid * KM * mid2;
+        l.w2_fast[r] = base2f + (size_t)r * rank2f + (size_t)n_mid * KM * mid2f;
+    }
+    l.stage_bytes2 = 2048; l.rows2 = 16; l.lo_row2 = 8; l.stage_bytes2_fast = 1024; l.rows2_fast = 8;
     m->n_tc = n_mid + 1;
     return STOF_OK;
 }
@@ -435,7 +484,8 @@ static int forward_chunk_tc(stof_model *m, const float *x, int n, int L, float *
         if (j + cnt < m->n_tc && m->tc_layer[j + cnt].type == TC_RES) cnt = (cnt > 1) ? cnt - 1 : cnt + 1;
         const bool ends = (j + cnt == m->n_tc);
         ProfScope p(m, ends ? STOF_PROF_LAST : STOF_PROF_MID, st);
-        if ((rc = launch_chain_tc(m->tc_layer + j, cnt, cur, B1, ends ? nullptr : pp[which], ends ? mask : nullptr, n, L, st, fast))) return rc;
+        if ((rc = (m->chain_pair ? launch_chain_tc2 : launch_chain_tc)(m->tc_layer + j, cnt, cur, B1, ends ? nullptr : pp[which],
+                                                                       ends ? mask : nullptr, n, L, st, fast))) return rc;
         cur = pp[which];
         which ^= 1;
         j += cnt;
@@ -557,6 +607,8 @@ extern "C" void stof_model_destroy(stof_model *m) {
     if (m->raw_expand_w) cudaFree(m->raw_expand_w);
     if (m->tc_w) cudaFree(m->tc_w);
     if (m->tc_w_fast) cudaFree(m->tc_w_fast);
+    if (m->tc_w2) cudaFree(m->tc_w2);
+    if (m->tc_w2_fast) cudaFree(m->tc_w2_fast);
     if (m->tc_contract_w) cudaFree(m->tc_contract_w);
     if (m->tc_expand_w) cudaFree(m->tc_expand_w);
     if (m->h_stats) cudaFreeHost(m->h_stats);
@@ -701,6 +753,12 @@ extern "C" int stof_model_set_path(stof_model *m, int path, int layers_per_launc
     return STOF_OK;
 }
 
+extern "C" int stof_model_set_chain_kernel(stof_model *m, int cta_pairs) {
+    STOF_REQUIRE(m != nullptr, STOF_E_INVALID, "stof_model_set_chain_kernel: model is NULL");
+    m->chain_pair = cta_pairs != 0;
+    return STOF_OK;
+}
+
 extern "C" int stof_model_set_host_chunk_rows(stof_model *m, int rows) {
     STOF_REQUIRE(m != nullptr && rows >= 0, STOF_E_INVALID, "stof_model_set_host_chunk_rows: bad arguments");
     m->host_chunk_rows = rows;
@@ -715,9 +773,9 @@ extern "C" int stof_chain_segment(stof_model *m, int first, int count, const voi
                  "stof_chain_segment: layers [%d, %d) of %d", first, first + count, m->n_tc);
     STOF_REQUIRE(in_planes_dev && out_dev && N > 0 && L > 0, STOF_E_INVALID, "stof_chain_segment: bad arguments");
     const bool ends = m->tc_layer[first + count - 1].type == stof::TC_LAST;
-    return stof::launch_chain_tc(m->tc_layer + first, count, in_planes_dev, x0_planes_dev, ends ? nullptr : out_dev,
-                                 ends ? reinterpret_cast<float *>(out_dev) : nullptr, N, L, (cudaStream_t)stream,
-                                 m->path == STOF_PATH_TC_FP16 ? 1 : 0);
+    return (m->chain_pair ? stof::launch_chain_tc2 : stof::launch_chain_tc)(
+        m->tc_layer + first, count, in_planes_dev, x0_planes_dev, ends ? nullptr : out_dev,
+        ends ? reinterpret_cast<float *>(out_dev) : nullptr, N, L, (cudaStream_t)stream, m->path == STOF_PATH_TC_FP16 ? 1 : 0);
 }
 
 extern "C" int stof_sgb_expand(stof_model *m, const float *pooled_dev, int N, int P, float *e_dev, int path, void *stream) {

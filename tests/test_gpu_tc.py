@@ -180,3 +180,27 @@ def test_fp16_one_pass_mode_tolerance(sb, dev, golden):
         a = set(map(tuple, sb.get_maxima_positions(ref, 20, th).cpu().numpy()))
         b = set(map(tuple, sb.get_maxima_positions(fast, 20, th).cpu().numpy()))
         assert len(a & b) >= 0.97 * len(a) and len(a & b) >= 0.97 * len(b), (name, len(a), len(b), len(a & b))
+
+
+@pytest.mark.parametrize("name", ["graceful-snow", "clean-serenity", "proud-cherry"])
+def test_pair_chain_kernel_bit_identical(sb, dev, golden, name):
+    """conv_tc2.cu (2-CTA clusters, tcgen05 cta_group::2, each CTA holding half of every weight tap) against conv_tc.cu: same
+    MMAs in the same order per accumulator, so the masks must be bit-identical - including odd tile counts (the last pair's
+    second CTA runs a phantom tile), both precisions, and EDSR_1D's k3 layers."""
+    from stofnet_b200._lib import lib, check
+    from stofnet_b200.synth import synth_waveforms
+    sd = {k: torch.from_numpy(v) for k, v in golden("weights_%s.npz" % name).items()}
+    model = sb.build_model(sd, dev)
+    for N, L in ((1, 160), (3, 640), (5, 2578), (41, 5120)):
+        x = torch.from_numpy(synth_waveforms(N, L, seed=N, rf=10)).unsqueeze(1).to(dev)
+        for prec in ("fp32", "fp16"):
+            model.set_precision(prec)
+            outs = []
+            for pair in (0, 1):
+                with torch.no_grad():
+                    model(x[:1])                                            # creates / syncs the handle
+                    check(lib.stof_model_set_chain_kernel(model._engine.handle, pair))
+                    outs.append(model(x).clone())
+            check(lib.stof_model_set_chain_kernel(model._engine.handle, 0))
+            assert torch.equal(outs[0], outs[1]), (name, N, L, prec, float((outs[0] - outs[1]).abs().max()))
+    model.set_precision("fp32")
