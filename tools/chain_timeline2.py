@@ -30,12 +30,20 @@ timed = run()
 check(lib.stof_debug_set_timeline(None, 0))
 t = tl.cpu().numpy(); capr = cap // 4
 ev = []
+waits = {}
 for role in range(4):
     for i in range(min(int(t[role]), capr)):
         o = 4 + 2 * (role * capr + i)
-        ev.append((int(t[o + 1]), int(t[o])))
+        code, val = int(t[o]), int(t[o + 1])
+        if (code & 255) in (40, 41):          # per-layer wait cycles of an MMA issuer (activations / weight stages)
+            waits.setdefault((role, (code >> 16) & 255, code & 255), []).append(val)
+        else:
+            ev.append((val, code))
 ev.sort()
 print("precision", prec, "kernel ms plain", plain, "with timeline", timed, "events", len(ev))
+for (role, k, what), v in sorted(waits.items()):
+    v = v[len(v) // 4:]
+    print("# issuer %d layer %d: mean cycles waiting for %s = %.0f (over %d tiles)" % (role - 1, k, "activations" if what == 40 else "weights", sum(v) / max(len(v), 1), len(v)))
 t0 = ev[0][0]
 names = {0: "PROD", 1: "MMA0", 2: "MMA1", 3: "EPI"}
 # skip the first tile: print tiles 3-4 of CTA 0
