@@ -1,0 +1,295 @@
+// ESPCN_1D forward (models/espcn_1d.py:8-36; SURVEY.md 8f row 1, BASELINE config 2's wobbly-sponge) with conv2 on tcgen05:
+//   conv1 (1 -> 64, k5, pad 2) + tanh  ->  conv2 (64 -> 32, k3, pad 1) + tanh  ->  conv3 (32 -> 4, k3, pad 1)
+//   -> SampleShuffle1D(4) -> sigmoid
+// conv2 is 6,144 of the model's 6,848 MACs per position: a dense contraction (K = 3 taps x 64 channels, N = 32) that the fused
+// fp32 kernel (espcn_fused.cu) runs on the FMA pipe.  Here it is an implicit GEMM on the tensor cores, exactly like the chain
+// kernel's layers (conv_tc.cu): M = 128 positions (TMEM lanes), conv1's output written by the producer threads straight into
+// shared memory as split fp16 planes [plane hi/lo][c8][row][8 channels] (the no-swizzle K-major UMMA operand layout, a tap
+// shift = a 16-byte shift of the descriptor), fp32-faithful through the hi/lo split
+//          [D0 | D1] (+)= H1_hi * [W_hi ; W_lo]^T   (N = 64)          D1 += H1_lo * W_hi^T   (N = 32)
+// with conv2's weights (24 KB as packed fp16 taps) resident in shared memory for the whole launch.  conv1 + tanh (producer),
+// tanh + conv3 + shuffle + sigmoid (epilogue) stay on the CUDA cores; HBM traffic is 4 B in + 16 B out per position.
+//
+// One persistent CTA per SM: 16 worker warps + 1 MMA-issuing warp.  Per tile of 124 output positions the workers
+//   (1) drain tile k's accumulator (TMEM -> +bias, tanh -> h2 fp32 in shared memory),
+//   (2) one warp group (rotating per tile) runs conv3 + sigmoid + the shuffled 16-byte stores,
+//   (3) everybody produces tile k+2's conv1 operand (two (row, 8-channel) items per thread) into the A buffer tile k used,
+// while the tensor pipe works on tile k+1 (two A buffers, two accumulators).
+// tanh / sigmoid use ex2.approx + rcp.approx forms (absolute error < 2e-7 on values in (-1, 1)); the fp32 FFMA kernels
+// (STOF_PATH_SIMT) stay as the cross-check (tests/test_gpu_parity.py).
+#include <cuda_fp16.h>
+
+#include "conv_tc_shared.cuh"
+
+namespace stof {
+
+using namespace ptx;
+
+constexpr int ET_WORKER_WARPS = 16;
+constexpr int ET_WORKERS = ET_WORKER_WARPS * 32;       // 512
+constexpr int ET_THREADS = ET_WORKERS + 32;            // + the MMA warp
+constexpr int ET_OUT = 124;                            // output positions per tile
+constexpr int ET_R = 136;                              // rows per (plane, c8) slab of an A buffer (128 produced + tap overhang)
+constexpr int ET_SLAB = ET_R * 16;
+constexpr int ET_PLANE = 8 * ET_SLAB;
+constexpr int ET_ABUF = 2 * ET_PLANE;                  // 34,816 B
+constexpr int ET_W2_TAP = 8 * 64 * 16;                 // one tap: [8 c8][W_hi 32 | W_lo 32][8] fp16 = 8 KB
+constexpr int ET_H2P = 132;                            // pitch of h2 rows (floats)
+
+constexpr int ET_OFF_W2 = 0;
+constexpr int ET_OFF_A = ET_OFF_W2 + 3 * ET_W2_TAP;                    // 24,576
+constexpr int ET_OFF_H2 = ET_OFF_A + 2 * ET_ABUF;                      // 94,208
+constexpr int ET_OFF_W1 = ET_OFF_H2 + 32 * ET_H2P * 4;                 // [5][64] fp32
+constexpr int ET_OFF_B1 = ET_OFF_W1 + 5 * 64 * 4;
+constexpr int ET_OFF_W3 = ET_OFF_B1 + 64 * 4;                          // [32][3][4] fp32
+constexpr int ET_OFF_B2 = ET_OFF_W3 + 32 * 3 * 4 * 4;
+constexpr int ET_OFF_B3 = ET_OFF_B2 + 32 * 4;
+constexpr int ET_OFF_BAR = ET_OFF_B3 + 16;                             // a_full[2] acc_full[2]
+constexpr int ET_OFF_TMEM = ET_OFF_BAR + 4 * 8;
+constexpr int ET_SMEM_BYTES = ET_OFF_TMEM + 16;
+static_assert(ET_OFF_A % 1024 == 0 && ET_SMEM_BYTES <= 232448, "espcn_tc shared-memory map");
+
+// tanh(v) = 1 - 2 / (1 + e^(2 v)) with ex2.approx / rcp.approx: saturates correctly (e -> inf: 1, e -> 0: -1)
+__device__ __forceinline__ float tanh_fast(float v) {
+    float e, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(v * 2.885390081777927f));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e + 1.0f));
+    return fmaf(-2.0f, r, 1.0f);
+}
+__device__ __forceinline__ float sigmoid_fast(float v) {
+    float e, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(v * -1.4426950408889634f));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e + 1.0f));
+    return r;
+}
+
+__device__ __forceinline__ void worker_bar() { asm volatile("bar.sync 1, %0;" ::"n"(ET_WORKERS) : "memory"); }
+
+struct EtParams {
+    const float *x;
+    float *mask;
+    const void *w2p;           // packed conv2 taps (upload_espcn_tc)
+    const float *w1, *b1, *b2, *w3, *b3;
+    int N, L, tiles_per_row, total_tiles;
+};
+
+__global__ void __launch_bounds__(ET_THREADS, 1) espcn_tc_kernel(const EtParams p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const uint32_t sbase = smem_u32(smem);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t bar0 = sbase + ET_OFF_BAR;
+    auto BAR_A_FULL = [&](int b) { return bar0 + 8 * b; };
+    auto BAR_ACC_FULL = [&](int b) { return bar0 + 16 + 8 * b; };
+    volatile uint32_t *s_tmem = reinterpret_cast<volatile uint32_t *>(smem + ET_OFF_TMEM);
+    float *s_h2 = reinterpret_cast<float *>(smem + ET_OFF_H2);
+    const float4 *s_w1 = reinterpret_cast<const float4 *>(smem + ET_OFF_W1);
+    const float4 *s_b1 = reinterpret_cast<const float4 *>(smem + ET_OFF_B1);
+    const float4 *s_w3 = reinterpret_cast<const float4 *>(smem + ET_OFF_W3);
+    const float *s_b2 = reinterpret_cast<const float *>(smem + ET_OFF_B2);
+    const float4 *s_b3 = reinterpret_cast<const float4 *>(smem + ET_OFF_B3);
+
+    // ---- one-time setup: weights to shared memory, zero rows above the produced 128 of both A buffers, barriers, TMEM ----
+    for (int i = tid; i < 3 * ET_W2_TAP / 16; i += ET_THREADS)
+        reinterpret_cast<uint4 *>(smem + ET_OFF_W2)[i] = __ldg(reinterpret_cast<const uint4 *>(p.w2p) + i);
+    for (int i = tid; i < 5 * 64; i += ET_THREADS) reinterpret_cast<float *>(smem + ET_OFF_W1)[i] = __ldg(p.w1 + i);
+    for (int i = tid; i < 64; i += ET_THREADS) reinterpret_cast<float *>(smem + ET_OFF_B1)[i] = __ldg(p.b1 + i);
+    for (int i = tid; i < 32 * 3 * 4; i += ET_THREADS) reinterpret_cast<float *>(smem + ET_OFF_W3)[i] = __ldg(p.w3 + i);
+    for (int i = tid; i < 32; i += ET_THREADS) reinterpret_cast<float *>(smem + ET_OFF_B2)[i] = __ldg(p.b2 + i);
+    if (tid < 4) reinterpret_cast<float *>(smem + ET_OFF_B3)[tid] = __ldg(p.b3 + tid);
+    for (int i = tid; i < 2 * 16 * (ET_R - 128); i += ET_THREADS) {
+        const int slab = i / (ET_R - 128), r = 128 + i % (ET_R - 128);          // slab = buffer * 16 + plane * 8 + c8
+        *reinterpret_cast<uint4 *>(smem + ET_OFF_A + slab * ET_SLAB + r * 16) = make_uint4(0, 0, 0, 0);
+    }
+    if (tid == 0) {
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(BAR_A_FULL(b), ET_WORKER_WARPS);
+            mbar_init(BAR_ACC_FULL(b), 1);
+        }
+        fence_mbar_init();
+    }
+    if (warp == ET_WORKER_WARPS) tmem_alloc(sbase + ET_OFF_TMEM, 128);
+    fence_proxy_async_smem();
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem0 = *s_tmem;
+
+    const int n_my = (p.total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;     // tiles of this CTA
+
+    if (warp == ET_WORKER_WARPS) {
+        // =================================== MMA issuer ==================================================
+        constexpr uint32_t kDescHi = (128u >> 4) | (1u << 14);
+        constexpr uint32_t idesc_a = umma_idesc_f16(128, 64), idesc_b = umma_idesc_f16(128, 32);
+        for (int k = 0; k < n_my; ++k) {
+            const int buf = k & 1;
+            mbar_wait(BAR_A_FULL(buf), (uint32_t)(k >> 1) & 1u);
+            tc_fence_after_sync();
+            if (elect_one()) {
+                const uint32_t a0 = ((sbase + ET_OFF_A + buf * ET_ABUF) >> 4) | ((uint32_t)(ET_SLAB >> 4) << 16);
+                const uint32_t w0 = ((sbase + ET_OFF_W2) >> 4) | (64u << 16);         // LBO = 64 rows of 16 B between c8 chunks
+                const uint32_t d = tmem0 + 64u * (uint32_t)buf;
+#pragma unroll
+                for (int t = 0; t < 3; ++t) {
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks) {
+                        const uint64_t bw = make_desc(w0 + (uint32_t)(t * (ET_W2_TAP >> 4) + 2 * ks * 64), kDescHi);
+                        umma_f16(d, make_desc(a0 + (uint32_t)(t + 2 * ks * ET_R), kDescHi), bw, idesc_a, (t > 0 || ks > 0) ? 1u : 0u);
+                        umma_f16(d + 32u, make_desc(a0 + (uint32_t)(t + (8 + 2 * ks) * ET_R), kDescHi), bw, idesc_b, 1u);
+                    }
+                }
+                umma_commit(BAR_ACC_FULL(buf));
+            }
+            __syncwarp();
+        }
+    } else {
+        // =================================== workers =====================================================
+        const int prow = tid & 127, pcq = tid >> 7;            // producer item: row of the tile, c8 in {pcq, pcq + 4}
+        const int quad = warp & 3, cg = warp >> 2;             // epilogue: TMEM lanes of this warp, channels [8 cg, 8 cg + 8)
+        const int qrow = 32 * quad + lane;
+        const uint32_t lane_addr = (uint32_t)(32 * quad) << 16;
+
+        auto tile_origin = [&](int k, int &n, int &l0) {
+            const int tile = (int)blockIdx.x + k * (int)gridDim.x;
+            n = tile / p.tiles_per_row;
+            l0 = (tile - n * p.tiles_per_row) * ET_OUT;
+        };
+        // the five input samples of this thread's conv1 row: positions l0 - 4 + prow + t (zero outside the waveform)
+        auto load_x = [&](int k, float (&xv)[5]) {
+            int n, l0;
+            tile_origin(k, n, l0);
+            const float *xr = p.x + (size_t)n * p.L;
+#pragma unroll
+            for (int t = 0; t < 5; ++t) {
+                const int g = l0 - 4 + prow + t;
+                xv[t] = (g >= 0 && g < p.L) ? __ldg(xr + g) : 0.0f;
+            }
+        };
+        // conv1 + tanh (espcn_1d.py:12,32) of row prow, 2 x 8 channels -> split planes of A buffer `buf`; bias first, taps ascending
+        // (the sum order of conv_simt.cu / espcn_fused.cu).  Rows outside [0, L) are conv2's zero padding.
+        auto produce = [&](int k, const float (&xv)[5]) {
+            int n, l0;
+            tile_origin(k, n, l0);
+            const int g = l0 - 2 + prow;
+            const bool inside = (g >= 0) && (g < p.L);
+            uint8_t *abuf = smem + ET_OFF_A + (k & 1) * ET_ABUF + prow * 16;
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                const int c8 = pcq + 4 * half;
+                float v[8];
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const float4 bq = s_b1[2 * c8 + h];
+                    float2 a01 = make_float2(bq.x, bq.y), a23 = make_float2(bq.z, bq.w);
+#pragma unroll
+                    for (int t = 0; t < 5; ++t) {
+                        const float4 wv = s_w1[t * 16 + 2 * c8 + h];
+                        const float2 xx = make_float2(xv[t], xv[t]);
+                        a01 = __ffma2_rn(make_float2(wv.x, wv.y), xx, a01);
+                        a23 = __ffma2_rn(make_float2(wv.z, wv.w), xx, a23);
+                    }
+                    v[4 * h + 0] = inside ? tanh_fast(a01.x) : 0.0f;
+                    v[4 * h + 1] = inside ? tanh_fast(a01.y) : 0.0f;
+                    v[4 * h + 2] = inside ? tanh_fast(a23.x) : 0.0f;
+                    v[4 * h + 3] = inside ? tanh_fast(a23.y) : 0.0f;
+                }
+                uint4 uh, ul;
+                split_pair(v[0], v[1], uh.x, ul.x);
+                split_pair(v[2], v[3], uh.y, ul.y);
+                split_pair(v[4], v[5], uh.z, ul.z);
+                split_pair(v[6], v[7], uh.w, ul.w);
+                *reinterpret_cast<uint4 *>(abuf + c8 * ET_SLAB) = uh;
+                *reinterpret_cast<uint4 *>(abuf + ET_PLANE + c8 * ET_SLAB) = ul;
+            }
+            fence_proxy_async_smem();
+            tc_fence_before_sync();                       // orders this thread's earlier tcgen05.ld of the accumulator the MMA will reuse
+            __syncwarp();
+            if (lane == 0) mbar_arrive(BAR_A_FULL(k & 1));
+        };
+
+        float xv[5];
+        for (int k = 0; k < 2 && k < n_my; ++k) {
+            load_x(k, xv);
+            produce(k, xv);
+        }
+        for (int k = 0; k < n_my; ++k) {
+            int n, l0;
+            tile_origin(k, n, l0);
+            if (k + 2 < n_my) load_x(k + 2, xv);          // in flight behind the epilogue of tile k
+            // ---- (1) accumulator -> h2 = tanh(conv2 + bias), zero outside the waveform (espcn_1d.py:13,33) ----------------
+            mbar_wait(BAR_ACC_FULL(k & 1), (uint32_t)(k >> 1) & 1u);
+            tc_fence_after_sync();
+            {
+                const uint32_t d = tmem0 + 64u * (uint32_t)(k & 1) + lane_addr + 8u * (uint32_t)cg;
+                uint32_t d0[8], d1[8];
+                tmem_ld8(d, d0);
+                tmem_ld8(d + 32u, d1);
+                tmem_ld_wait();
+                const int g = l0 - 1 + qrow;
+                const bool inside = (g >= 0) && (g < p.L);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float v = (__uint_as_float(d0[i]) + TC_LO_INV * __uint_as_float(d1[i])) + s_b2[8 * cg + i];
+                    s_h2[(8 * cg + i) * ET_H2P + qrow] = inside ? tanh_fast(v) : 0.0f;
+                }
+            }
+            worker_bar();
+            // ---- (2) conv3 + SampleShuffle1D + sigmoid (espcn_1d.py:14,34-36; utils/sample_shuffle.py:20-26): one warp group ----
+            if (cg == (k & 3)) {
+                const int o = 32 * quad + lane;            // output position of the tile
+                const int l = l0 + o;
+                if (o < ET_OUT && l < p.L) {
+                    const float4 b3 = s_b3[0];
+                    float2 a01 = make_float2(b3.x, b3.y), a23 = make_float2(b3.z, b3.w);
+#pragma unroll 2
+                    for (int c4 = 0; c4 < 8; ++c4) {
+#pragma unroll
+                        for (int t = 0; t < 3; ++t) {
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) {
+                                const float hv = s_h2[(4 * c4 + i) * ET_H2P + o + t];
+                                const float4 wv = s_w3[(4 * c4 + i) * 3 + t];
+                                const float2 xx = make_float2(hv, hv);
+                                a01 = __ffma2_rn(make_float2(wv.x, wv.y), xx, a01);
+                                a23 = __ffma2_rn(make_float2(wv.z, wv.w), xx, a23);
+                            }
+                        }
+                    }
+                    float4 out;
+                    out.x = sigmoid_fast(a01.x); out.y = sigmoid_fast(a01.y);
+                    out.z = sigmoid_fast(a23.x); out.w = sigmoid_fast(a23.y);
+                    reinterpret_cast<float4 *>(p.mask)[(size_t)n * p.L + l] = out;
+                }
+            }
+            // ---- (3) conv1 operand of tile k + 2 into the A buffer tile k's MMAs have released ---------------------------
+            if (k + 2 < n_my) produce(k + 2, xv);
+            worker_bar();                                   // h2 is free again
+        }
+    }
+
+    // ---- teardown --------------------------------------------------------------------------------------
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == ET_WORKER_WARPS) {
+        tc_fence_after_sync();
+        tmem_dealloc(tmem0, 128);
+    }
+}
+
+int launch_espcn_tc(const float *x, float *mask, int N, int L, const float *w1, const float *b1, const void *w2_packed, const float *b2,
+                    const float *w3, const float *b3, cudaStream_t st) {
+    static SmemAttrOnce attr;
+    { const int rc = ensure_dyn_smem(espcn_tc_kernel, ET_SMEM_BYTES, attr); if (rc) return rc; }
+    EtParams p;
+    p.x = x; p.mask = mask; p.w2p = w2_packed; p.w1 = w1; p.b1 = b1; p.b2 = b2; p.w3 = w3; p.b3 = b3;
+    p.N = N; p.L = L;
+    p.tiles_per_row = (L + ET_OUT - 1) / ET_OUT;
+    const long long total = (long long)N * p.tiles_per_row;
+    STOF_REQUIRE(total < (1ll << 31), STOF_E_INVALID, "espcn_tc: too many tiles");
+    p.total_tiles = (int)total;
+    const int grid = (int)(total < kSMs ? total : kSMs);
+    espcn_tc_kernel<<<grid, ET_THREADS, ET_SMEM_BYTES, st>>>(p);
+    STOF_LAUNCH_CHECK();
+    return STOF_OK;
+}
+
+}  // namespace stof

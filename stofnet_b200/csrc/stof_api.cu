@@ -284,6 +284,19 @@ static int set_weights_locked(stof_model *m, const stof_weights *w) {
         if ((rc = upload(m->first, repack_cikco(w->conv1_w, 64, 1, 5), w->conv1_b, 64))) return rc;
         if ((rc = upload(m->mid[0], repack_cikco(w->mid_w[0], 32, 64, 3), w->mid_b[0], 32))) return rc;
         if ((rc = upload(m->last, repack_cikco(w->last_w, 4, 32, 3), w->last_b, 4))) return rc;
+        // tensor-core path (espcn_tc.cu): conv2 (32, 64, 3) as packed fp16 taps [tap][c8][W_hi 32 | W_lo 32][8] (8 KB per tap)
+        std::vector<__half> pk((size_t)3 * 8 * 64 * 8, __float2half_rn(0.0f));
+        for (int t = 0; t < 3; ++t)
+            for (int oc = 0; oc < 32; ++oc)
+                for (int ci = 0; ci < 64; ++ci) {
+                    __half hi, lo;
+                    split_w(w->mid_w[0][((size_t)oc * 64 + ci) * 3 + t], hi, lo);
+                    __half *tap = pk.data() + (size_t)t * 8 * 64 * 8;
+                    tap[((size_t)(ci >> 3) * 64 + oc) * 8 + (ci & 7)] = hi;
+                    tap[((size_t)(ci >> 3) * 64 + 32 + oc) * 8 + (ci & 7)] = lo;
+                }
+        if (!m->tc_w) STOF_CUDA(cudaMalloc(&m->tc_w, pk.size() * sizeof(__half)));
+        STOF_CUDA(cudaMemcpy(m->tc_w, pk.data(), pk.size() * sizeof(__half), cudaMemcpyHostToDevice));
         return STOF_OK;
     }
     m->F = w->num_features; m->n_mid = w->n_mid;
@@ -502,8 +515,13 @@ static int forward_chunk(stof_model *m, const float *x, int n, int L, float *mas
     float *e = reinterpret_cast<float *>(ws + 3 * align256(pl.act * 4) + align256(pl.pooled * 4));
     int rc;
     if (m->kind == STOF_KIND_ESPCN) {
-        // models/espcn_1d.py:31-36: one fused kernel; layers_per_launch == 1 (stof_model_set_path) selects the three
-        // layer-by-layer kernels instead, which give bit-identical masks (kept as the cross-check of the fused kernel)
+        // models/espcn_1d.py:31-36: one fused kernel with conv2 on tcgen05 (default), or - STOF_PATH_SIMT - the fused fp32 FFMA
+        // kernel; there, layers_per_launch == 1 (stof_model_set_path) selects the three layer-by-layer kernels instead, which
+        // give masks bit-identical to the fused FFMA kernel (the cross-checks of the tensor-core kernel)
+        if (m->path != STOF_PATH_SIMT) {
+            ProfScope p(m, STOF_PROF_MID, st);
+            return launch_espcn_tc(x, mask, n, L, m->first.w, m->first.b, m->tc_w, m->mid[0].b, m->last.w, m->last.b, st);
+        }
         if (m->seg_len != 1) {
             ProfScope p(m, STOF_PROF_MID, st);
             return launch_espcn_fused(x, mask, n, L, m->first.w, m->first.b, m->mid[0].w, m->mid[0].b, m->last.w, m->last.b, st);
@@ -742,8 +760,10 @@ extern "C" int stof_model_set_path(stof_model *m, int path, int layers_per_launc
     STOF_REQUIRE(m != nullptr, STOF_E_INVALID, "stof_model_set_path: model is NULL");
     STOF_REQUIRE(path == STOF_PATH_SIMT || path == STOF_PATH_TC || path == STOF_PATH_TC_FP16, STOF_E_INVALID,
                  "stof_model_set_path: path %d", path);
-    STOF_REQUIRE(path == STOF_PATH_SIMT ? m->kind != STOF_KIND_EDSR : m->kind != STOF_KIND_ESPCN, STOF_E_UNSUPPORTED,
-                 "stof_model_set_path: ESPCN_1D runs on the fp32 FFMA path only, EDSR_1D on the tensor-core path only");
+    STOF_REQUIRE(path != STOF_PATH_SIMT || m->kind != STOF_KIND_EDSR, STOF_E_UNSUPPORTED,
+                 "stof_model_set_path: EDSR_1D runs on the tensor-core path only");
+    STOF_REQUIRE(path != STOF_PATH_TC_FP16 || m->kind != STOF_KIND_ESPCN, STOF_E_UNSUPPORTED,
+                 "stof_model_set_path: ESPCN_1D has no one-pass fp16 mode (fp32-faithful tensor-core path or fp32 FFMA path)");
     if (layers_per_launch > 0) {
         STOF_REQUIRE(layers_per_launch <= stof::TC_MAX_LAYERS, STOF_E_INVALID, "stof_model_set_path: at most %d layers per launch",
                      stof::TC_MAX_LAYERS);

@@ -141,6 +141,33 @@ def test_espcn_fused_matches_layer_kernels(sb, dev, golden, name):
         assert torch.equal(fused, layered), (N, L, float((fused - layered).abs().max()))
 
 
+@pytest.mark.parametrize("name", ESPCN_CKPTS)
+def test_espcn_tc_matches_ffma_kernels(sb, dev, golden, name):
+    """The tensor-core ESPCN kernel (espcn_tc.cu: conv2 on tcgen05 through the fp16 hi/lo split, ex2/rcp forms of tanh and
+    sigmoid) against the fused fp32 FFMA kernel: masks (sigmoid outputs in (0, 1)) within 1e-5, identical ToF tables at the
+    checkpoint's threshold; lengths around the 124-position tile, the row ends, and enough tiles for several per CTA."""
+    model = _model(sb, golden, name, dev)
+    eng = model._engine
+    rng = np.random.default_rng(11)
+    worst = 0.0
+    for N, L in ((1, 1), (2, 5), (3, 123), (3, 124), (2, 125), (4, 249), (5, 1000), (37, 2560), (300, 5120)):
+        x = torch.from_numpy(rng.normal(size=(N, 1, L)).astype(np.float32)).to(dev)
+        with torch.no_grad():
+            eng.set_path(sb._lib.PATH_TC, 0)
+            tc = model(x).clone()
+            eng.set_path(sb._lib.PATH_SIMT, 4)
+            ffma = model(x).clone()
+            eng.set_path(sb._lib.PATH_TC, 0)
+        assert tc.shape == (N, 1, 4 * L)
+        err = float((tc - ffma).abs().max())
+        worst = max(worst, err)
+        assert err <= 1e-5, (N, L, err)
+        a = sb.mask2coords(tc, 20, 0.2, upsample_factor=4)
+        b = sb.mask2coords(ffma, 20, 0.2, upsample_factor=4)
+        assert a.shape == b.shape and float((a - b).abs().max()) <= 1e-3, (N, L)
+    print("espcn tc vs ffma: worst abs mask difference %.2e" % worst)
+
+
 @pytest.mark.parametrize("name", EDSR_CKPTS)
 def test_edsr_forward_golden(sb, dev, golden, name):
     """EDSR_1D on the tensor-core chain (k3 layers, ReLU epilogue, shuffle + conv_output folded into conv_last) against the

@@ -2,7 +2,7 @@
 """ESPCN_1D at the C2 shape (BASELINE config 2 names the ESPCN checkpoint wobbly-sponge): waveforms/s of
 forward + mask2coords on device-resident batches, CUDA-event timed.
 
-    python tools/espcn_bench.py [rows] [L] [steps]"""
+    python tools/espcn_bench.py [rows] [L] [steps] [tc|ffma]"""
 import json
 import os
 import sys
@@ -20,6 +20,8 @@ steps = int(sys.argv[3]) if len(sys.argv) > 3 else 5
 dev = torch.device("cuda:0")
 sd = sb.load_checkpoint(os.path.join(ROOT, "tests", "golden", "weights_wobbly-sponge.npz"))
 model = sb.build_model(sd, dev)
+path = sys.argv[4] if len(sys.argv) > 4 else "tc"
+model._engine.set_path(sb._lib.PATH_TC if path == "tc" else sb._lib.PATH_SIMT, 0 if path == "tc" else 4)
 base = torch.from_numpy(synth_waveforms(256, L, seed=3008, rf=20))
 xs = [torch.roll(base.repeat((rows + 255) // 256, 1)[:rows], s, 0).unsqueeze(1).contiguous().to(dev) for s in (0, 7, 13)]
 with torch.no_grad():
@@ -37,5 +39,5 @@ with torch.no_grad():
     e2.record()
     torch.cuda.synchronize()
 fwd, pk = e0.elapsed_time(e1) / steps, e1.elapsed_time(e2) / steps
-print(json.dumps({"model": "ESPCN_1D wobbly-sponge", "rows": rows, "L": L, "forward_ms": round(fwd, 3), "mask2coords_ms": round(pk, 3),
+print(json.dumps({"model": "ESPCN_1D wobbly-sponge", "path": path, "rows": rows, "L": L, "forward_ms": round(fwd, 3), "mask2coords_ms": round(pk, 3),
                   "waveforms_per_s": round(rows / ((fwd + pk) * 1e-3)), "kmax": int(co.shape[-1])}))
