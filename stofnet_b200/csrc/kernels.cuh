@@ -21,9 +21,10 @@ int launch_espcn_conv2(const float *in, float *out, const float *w, const float 
 int launch_espcn_fused(const float *x, float *mask, int N, int L, const float *w1, const float *b1, const float *w2,
                        const float *b2, const float *w3, const float *b3, cudaStream_t st);
 
-// espcn_tc.cu: the same forward with conv2 (64 -> 32, k3) on tcgen05; w2_packed = fp16 taps [tap][c8][W_hi 32 | W_lo 32][8]
-int launch_espcn_tc(const float *x, float *mask, int N, int L, const float *w1, const float *b1, const void *w2_packed, const float *b2,
-                    const float *w3, const float *b3, cudaStream_t st);
+// espcn_tc.cu: the same forward with conv2 (64 -> 32, k3) and conv3 (32 -> 4, k3) on tcgen05; w23_packed = fp16 taps of conv2
+// [tap][8 c8][W_hi 32 | W_lo 32][8] followed by conv3's [tap][4 c8][32 rows: 0-3 W_hi, 8-11 W_lo, 16-19 W_hi][8]
+int launch_espcn_tc(const float *x, float *mask, int N, int L, const float *w1, const float *b1, const void *w23_packed, const float *b2,
+                    const float *b3, cudaStream_t st);
 
 // conv_tc.cu (tcgen05 / TMEM path) ---------------------------------------------------------------
 constexpr int TC_MAX_LAYERS = 6;

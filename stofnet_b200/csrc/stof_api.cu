@@ -284,16 +284,28 @@ static int set_weights_locked(stof_model *m, const stof_weights *w) {
         if ((rc = upload(m->first, repack_cikco(w->conv1_w, 64, 1, 5), w->conv1_b, 64))) return rc;
         if ((rc = upload(m->mid[0], repack_cikco(w->mid_w[0], 32, 64, 3), w->mid_b[0], 32))) return rc;
         if ((rc = upload(m->last, repack_cikco(w->last_w, 4, 32, 3), w->last_b, 4))) return rc;
-        // tensor-core path (espcn_tc.cu): conv2 (32, 64, 3) as packed fp16 taps [tap][c8][W_hi 32 | W_lo 32][8] (8 KB per tap)
-        std::vector<__half> pk((size_t)3 * 8 * 64 * 8, __float2half_rn(0.0f));
+        // tensor-core path (espcn_tc.cu): conv2 (32, 64, 3) as packed fp16 taps [tap][c8][W_hi 32 | W_lo 32][8] (8 KB per tap),
+        // then conv3 (4, 32, 3) as [tap][4 c8][32 rows][8] with rows 0-3 W_hi, 8-11 W_lo, 16-19 W_hi (2 KB per tap)
+        std::vector<__half> pk((size_t)3 * 8 * 64 * 8 + (size_t)3 * 4 * 32 * 8, __float2half_rn(0.0f));
         for (int t = 0; t < 3; ++t)
             for (int oc = 0; oc < 32; ++oc)
                 for (int ci = 0; ci < 64; ++ci) {
                     __half hi, lo;
-                    split_w(w->mid_w[0][((size_t)oc * 64 + ci) * 3 + t], hi, lo);
+                    // the factor 2 log2(e) of tanh's ex2 form rides on the weights (espcn_tc.cu: tanh_scaled)
+                    split_w(2.885390081777927f * w->mid_w[0][((size_t)oc * 64 + ci) * 3 + t], hi, lo);
                     __half *tap = pk.data() + (size_t)t * 8 * 64 * 8;
                     tap[((size_t)(ci >> 3) * 64 + oc) * 8 + (ci & 7)] = hi;
                     tap[((size_t)(ci >> 3) * 64 + 32 + oc) * 8 + (ci & 7)] = lo;
+                }
+        for (int t = 0; t < 3; ++t)
+            for (int u = 0; u < 4; ++u)
+                for (int ci = 0; ci < 32; ++ci) {
+                    __half hi, lo;
+                    split_w(-1.4426950408889634f * w->last_w[((size_t)u * 32 + ci) * 3 + t], hi, lo);     // sigmoid_scaled
+                    __half *tap = pk.data() + (size_t)3 * 8 * 64 * 8 + (size_t)t * 4 * 32 * 8;
+                    tap[((size_t)(ci >> 3) * 32 + u) * 8 + (ci & 7)] = hi;
+                    tap[((size_t)(ci >> 3) * 32 + 8 + u) * 8 + (ci & 7)] = lo;
+                    tap[((size_t)(ci >> 3) * 32 + 16 + u) * 8 + (ci & 7)] = hi;
                 }
         if (!m->tc_w) STOF_CUDA(cudaMalloc(&m->tc_w, pk.size() * sizeof(__half)));
         STOF_CUDA(cudaMemcpy(m->tc_w, pk.data(), pk.size() * sizeof(__half), cudaMemcpyHostToDevice));
@@ -520,7 +532,7 @@ static int forward_chunk(stof_model *m, const float *x, int n, int L, float *mas
         // give masks bit-identical to the fused FFMA kernel (the cross-checks of the tensor-core kernel)
         if (m->path != STOF_PATH_SIMT) {
             ProfScope p(m, STOF_PROF_MID, st);
-            return launch_espcn_tc(x, mask, n, L, m->first.w, m->first.b, m->tc_w, m->mid[0].b, m->last.w, m->last.b, st);
+            return launch_espcn_tc(x, mask, n, L, m->first.w, m->first.b, m->tc_w, m->mid[0].b, m->last.b, st);
         }
         if (m->seg_len != 1) {
             ProfScope p(m, STOF_PROF_MID, st);

@@ -144,12 +144,18 @@ def test_espcn_fused_matches_layer_kernels(sb, dev, golden, name):
 @pytest.mark.parametrize("name", ESPCN_CKPTS)
 def test_espcn_tc_matches_ffma_kernels(sb, dev, golden, name):
     """The tensor-core ESPCN kernel (espcn_tc.cu: conv2 on tcgen05 through the fp16 hi/lo split, ex2/rcp forms of tanh and
-    sigmoid) against the fused fp32 FFMA kernel: masks (sigmoid outputs in (0, 1)) within 1e-5, identical ToF tables at the
-    checkpoint's threshold; lengths around the 124-position tile, the row ends, and enough tiles for several per CTA."""
+    sigmoid) against the fused fp32 FFMA kernel and the reference's fp64 re-run (oracle/torch_port.py on double weights): masks
+    (sigmoid outputs in (0, 1)) within 3e-5 of the fp64 masks on white-noise input 5x the amplitude of a normalised waveform
+    (the fp32 FFMA kernel measures 7.5e-6 there, the tensor-core kernel 2.2e-5: its operands carry 22 significand bits; on the
+    reference-generated goldens both stay under the 2e-5 bar of test_espcn_forward_golden) and within 3e-5 of the FFMA kernel;
+    detections identical or margin-explained;
+    lengths around the 124-position tile, the row ends, and enough tiles for several per CTA."""
+    from oracle import torch_port
+    sd64 = {k: torch.from_numpy(v).double() for k, v in golden("weights_%s.npz" % name).items()}
     model = _model(sb, golden, name, dev)
     eng = model._engine
     rng = np.random.default_rng(11)
-    worst = 0.0
+    worst = worst64 = 0.0
     for N, L in ((1, 1), (2, 5), (3, 123), (3, 124), (2, 125), (4, 249), (5, 1000), (37, 2560), (300, 5120)):
         x = torch.from_numpy(rng.normal(size=(N, 1, L)).astype(np.float32)).to(dev)
         with torch.no_grad():
@@ -161,11 +167,26 @@ def test_espcn_tc_matches_ffma_kernels(sb, dev, golden, name):
         assert tc.shape == (N, 1, 4 * L)
         err = float((tc - ffma).abs().max())
         worst = max(worst, err)
-        assert err <= 1e-5, (N, L, err)
-        a = sb.mask2coords(tc, 20, 0.2, upsample_factor=4)
-        b = sb.mask2coords(ffma, 20, 0.2, upsample_factor=4)
-        assert a.shape == b.shape and float((a - b).abs().max()) <= 1e-3, (N, L)
-    print("espcn tc vs ffma: worst abs mask difference %.2e" % worst)
+        assert err <= 3e-5, (N, L, err)
+        if N * L <= 37 * 2560:
+            with torch.no_grad():
+                ref64 = torch_port.espcn_forward(sd64, x.double().cpu()).float()
+            e_tc, e_ffma = float((tc.cpu() - ref64).abs().max()), float((ffma.cpu() - ref64).abs().max())
+            worst64 = max(worst64, e_tc)
+            assert e_tc <= 3e-5, (N, L, e_tc, e_ffma)
+        # detections: identical, or the differing sample sits within the mask tolerance of a decision boundary (threshold or
+        # the best other score of its 21-window) - white-noise input puts ~800 detections per row next to the threshold
+        ia = set(map(tuple, sb.get_maxima_positions(tc, 20, 0.2).cpu().numpy().tolist()))
+        ib = set(map(tuple, sb.get_maxima_positions(ffma, 20, 0.2).cpu().numpy().tolist()))
+        ref = ffma.squeeze(1).cpu().numpy()
+        for r, pos in sorted(ia ^ ib):
+            row = ref[r]
+            lo, hi = max(0, pos - 10), min(row.shape[0], pos + 11)
+            others = np.delete(row[lo:hi], pos - lo)
+            margin = min(abs(row[pos] - 0.2), abs(row[pos] - others.max()) if others.size else np.inf)
+            assert margin <= 6e-5, (N, L, r, pos, float(margin))
+        assert len(ia ^ ib) <= 1e-3 * max(len(ib), 1) + 2, (N, L, len(ia ^ ib), len(ib))
+    print("espcn tc vs ffma: worst abs mask difference %.2e; tc vs fp64 reference: %.2e" % (worst, worst64))
 
 
 @pytest.mark.parametrize("name", EDSR_CKPTS)
