@@ -12,7 +12,7 @@
 // the conv2 epilogue's split planes of h2.  conv1 + tanh (producer), bias + tanh (conv2 epilogue), bias + shuffle + sigmoid
 // (conv3 epilogue) stay on the CUDA cores; HBM traffic is 4 B in + 16 B out per position.
 //
-// One persistent CTA per SM: 16 worker warps + 1 MMA-issuing warp, synchronised by mbarriers only.  Per tile of 124 output
+// One persistent CTA per SM: 16 worker warps + 3 MMA-issuing warps, synchronised by mbarriers only.  Per tile of 124 output
 // positions the workers
 //   (1) drain tile k's conv2 accumulator (TMEM -> + bias, tanh -> h2 split planes in shared memory),
 //   (2) produce tile k+2's conv1 operand (two (row, 8-channel) items per thread) into the A buffer tile k used, and publish both
@@ -31,7 +31,7 @@ using namespace ptx;
 
 constexpr int ET_WORKER_WARPS = 16;
 constexpr int ET_WORKERS = ET_WORKER_WARPS * 32;       // 512
-constexpr int ET_THREADS = ET_WORKERS + 32;            // + the MMA warp
+constexpr int ET_THREADS = ET_WORKERS + 3 * 32;        // + three MMA-issuing warps (conv2 even / odd K-steps, conv3)
 constexpr int ET_OUT = 124;                            // output positions per tile
 constexpr int ET_R = 136;                              // rows per (plane, c8) slab of an A buffer (128 produced + tap overhang)
 constexpr int ET_SLAB = ET_R * 16;
@@ -51,7 +51,8 @@ constexpr int ET_OFF_B2 = ET_OFF_B1 + 64 * 4;
 constexpr int ET_OFF_B3 = ET_OFF_B2 + 32 * 4;
 constexpr int ET_OFF_BAR = ET_OFF_B3 + 16;                             // a_full[2] acc_full[2] h2_full[2] out_full[2]
 constexpr int ET_OFF_TMEM = ET_OFF_BAR + 8 * 8;
-constexpr uint32_t ET_ACC3_COL = 128;                                  // TMEM: conv2 accumulators at 0 / 64, conv3's at 128 / 160
+// TMEM: conv2 accumulator of A buffer b, issuer j at column 64 (2 b + j); conv3's accumulators at 256 / 288
+constexpr uint32_t ET_ACC3_COL = 256;
 constexpr int ET_SMEM_BYTES = ET_OFF_TMEM + 16;
 static_assert(ET_OFF_A % 1024 == 0 && ET_OFF_W3 % 16 == 0 && ET_SMEM_BYTES <= 232448, "espcn_tc shared-memory map");
 
@@ -66,13 +67,13 @@ constexpr float ET_SIGM_SCALE = -1.4426950408889634f;      // -log2(e)
 // set by the 22-bit hi/lo operands of the two tensor-core convolutions, not by the activations.)
 __device__ __forceinline__ float tanh_scaled(float a) {
     float e, r;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(a));
+    asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(a));
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e + 1.0f));
     return fmaf(-2.0f, r, 1.0f);
 }
 __device__ __forceinline__ float sigmoid_scaled(float a) {
     float e, r;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(a));
+    asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(a));
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e + 1.0f));
     return r;
 }
@@ -118,7 +119,7 @@ __global__ void __launch_bounds__(ET_THREADS, 1) espcn_tc_kernel(const EtParams 
     if (tid == 0) {
         for (int b = 0; b < 2; ++b) {
             mbar_init(BAR_A_FULL(b), ET_WORKER_WARPS);
-            mbar_init(BAR_ACC_FULL(b), 1);
+            mbar_init(BAR_ACC_FULL(b), 2);                 // one commit per conv2 issuer
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(BAR_H2_FULL(b), ET_WORKER_WARPS);
@@ -126,7 +127,7 @@ __global__ void __launch_bounds__(ET_THREADS, 1) espcn_tc_kernel(const EtParams 
         }
         fence_mbar_init();
     }
-    if (warp == ET_WORKER_WARPS) tmem_alloc(sbase + ET_OFF_TMEM, 256);
+    if (warp == ET_WORKER_WARPS) tmem_alloc(sbase + ET_OFF_TMEM, 512);
     fence_proxy_async_smem();
     tc_fence_before_sync();
     __syncthreads();
@@ -135,11 +136,15 @@ __global__ void __launch_bounds__(ET_THREADS, 1) espcn_tc_kernel(const EtParams 
 
     const int n_my = (p.total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;     // tiles of this CTA
 
-    if (warp == ET_WORKER_WARPS) {
-        // =================================== MMA issuer ==================================================
-        // in order: conv2(0), conv2(1), then per tile k: conv3(k), conv2(k + 2)
+    if (warp >= ET_WORKER_WARPS) {
+        // =================================== MMA issuers =================================================
+        // A single thread issues these small MMAs (N = 64 / 32 / 16) at ~90 cycles each, far below the pipe's rate, and 36 of
+        // them per tile would bound the kernel: three issuing warps work in parallel on independent accumulators - conv2's
+        // twelve (tap, K-step) products split even / odd between two of them (the epilogue adds the two partial sums), conv3 on
+        // the third.
         constexpr uint32_t kDescHi = (128u >> 4) | (1u << 14);
         constexpr uint32_t idesc_a = umma_idesc_f16(128, 64), idesc_b = umma_idesc_f16(128, 32), idesc_c = umma_idesc_f16(128, 16);
+        const int role = warp - ET_WORKER_WARPS;            // 0 / 1: conv2 even / odd products, 2: conv3
         auto conv2 = [&](int k) {
             const int buf = k & 1;
             mbar_wait(BAR_A_FULL(buf), (uint32_t)(k >> 1) & 1u);
@@ -147,15 +152,13 @@ __global__ void __launch_bounds__(ET_THREADS, 1) espcn_tc_kernel(const EtParams 
             if (elect_one()) {
                 const uint32_t a0 = ((sbase + ET_OFF_A + buf * ET_ABUF) >> 4) | ((uint32_t)(ET_SLAB >> 4) << 16);
                 const uint32_t w0 = ((sbase + ET_OFF_W2) >> 4) | (64u << 16);         // LBO = 64 rows of 16 B between c8 chunks
-                const uint32_t d = tmem0 + 64u * (uint32_t)buf;
+                const uint32_t d = tmem0 + 64u * (uint32_t)(2 * buf + role);
 #pragma unroll
-                for (int t = 0; t < 3; ++t) {
-#pragma unroll
-                    for (int ks = 0; ks < 4; ++ks) {
-                        const uint64_t bw = make_desc(w0 + (uint32_t)(t * (ET_W2_TAP >> 4) + 2 * ks * 64), kDescHi);
-                        umma_f16(d, make_desc(a0 + (uint32_t)(t + 2 * ks * ET_R), kDescHi), bw, idesc_a, (t > 0 || ks > 0) ? 1u : 0u);
-                        umma_f16(d + 32u, make_desc(a0 + (uint32_t)(t + (8 + 2 * ks) * ET_R), kDescHi), bw, idesc_b, 1u);
-                    }
+                for (int i = 0; i < 6; ++i) {
+                    const int q = 2 * i + role, t = q >> 2, ks = q & 3;
+                    const uint64_t bw = make_desc(w0 + (uint32_t)(t * (ET_W2_TAP >> 4) + 2 * ks * 64), kDescHi);
+                    umma_f16(d, make_desc(a0 + (uint32_t)(t + 2 * ks * ET_R), kDescHi), bw, idesc_a, i > 0 ? 1u : 0u);
+                    umma_f16(d + 32u, make_desc(a0 + (uint32_t)(t + (8 + 2 * ks) * ET_R), kDescHi), bw, idesc_b, 1u);
                 }
                 umma_commit(BAR_ACC_FULL(buf));
             }
@@ -183,10 +186,10 @@ __global__ void __launch_bounds__(ET_THREADS, 1) espcn_tc_kernel(const EtParams 
             }
             __syncwarp();
         };
-        for (int k = 0; k < 2 && k < n_my; ++k) conv2(k);
-        for (int k = 0; k < n_my; ++k) {
-            conv3(k);
-            if (k + 2 < n_my) conv2(k + 2);
+        if (role < 2) {
+            for (int k = 0; k < n_my; ++k) conv2(k);
+        } else {
+            for (int k = 0; k < n_my; ++k) conv3(k);
         }
     } else {
         // =================================== workers =====================================================
@@ -230,10 +233,12 @@ __global__ void __launch_bounds__(ET_THREADS, 1) espcn_tc_kernel(const EtParams 
                         a01 = __ffma2_rn(make_float2(wv.x, wv.y), xx, a01);
                         a23 = __ffma2_rn(make_float2(wv.z, wv.w), xx, a23);
                     }
-                    v[4 * h + 0] = inside ? tanh_scaled(a01.x) : 0.0f;
-                    v[4 * h + 1] = inside ? tanh_scaled(a01.y) : 0.0f;
-                    v[4 * h + 2] = inside ? tanh_scaled(a23.x) : 0.0f;
-                    v[4 * h + 3] = inside ? tanh_scaled(a23.y) : 0.0f;
+                    // evaluated unconditionally, then selected: no branch around the MUFU chains
+                    const float t0 = tanh_scaled(a01.x), t1 = tanh_scaled(a01.y), t2 = tanh_scaled(a23.x), t3 = tanh_scaled(a23.y);
+                    v[4 * h + 0] = inside ? t0 : 0.0f;
+                    v[4 * h + 1] = inside ? t1 : 0.0f;
+                    v[4 * h + 2] = inside ? t2 : 0.0f;
+                    v[4 * h + 3] = inside ? t3 : 0.0f;
                 }
                 uint4 uh, ul;
                 split_pair(v[0], v[1], uh.x, ul.x);
@@ -296,10 +301,12 @@ __global__ void __launch_bounds__(ET_THREADS, 1) espcn_tc_kernel(const EtParams 
             mbar_wait(BAR_ACC_FULL(k & 1), (uint32_t)(k >> 1) & 1u);
             tc_fence_after_sync();
             {
-                const uint32_t d = tmem0 + 64u * (uint32_t)(k & 1) + lane_addr + 8u * (uint32_t)cg;
-                uint32_t d0[8], d1[8];
+                const uint32_t d = tmem0 + 128u * (uint32_t)(k & 1) + lane_addr + 8u * (uint32_t)cg;
+                uint32_t d0[8], d1[8], e0[8], e1[8];                  // the two issuers' partial sums
                 tmem_ld8(d, d0);
                 tmem_ld8(d + 32u, d1);
+                tmem_ld8(d + 64u, e0);
+                tmem_ld8(d + 96u, e1);
                 tmem_ld_wait();
                 const bool inside = (unsigned)(l0 - 1 + qrow) < (unsigned)p.L;
                 const float4 ba = s_b2[2 * cg], bb = s_b2[2 * cg + 1];
@@ -307,8 +314,10 @@ __global__ void __launch_bounds__(ET_THREADS, 1) espcn_tc_kernel(const EtParams 
                 float v[8];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
-                    const float a = (__uint_as_float(d0[i]) + TC_LO_INV * __uint_as_float(d1[i])) + bv[i];
-                    v[i] = inside ? tanh_scaled(a) : 0.0f;
+                    const float a = ((__uint_as_float(d0[i]) + __uint_as_float(e0[i])) +
+                                     TC_LO_INV * (__uint_as_float(d1[i]) + __uint_as_float(e1[i]))) + bv[i];
+                    const float th = tanh_scaled(a);
+                    v[i] = inside ? th : 0.0f;
                 }
                 uint4 uh, ul;
                 split_pair(v[0], v[1], uh.x, ul.x);
@@ -340,7 +349,7 @@ __global__ void __launch_bounds__(ET_THREADS, 1) espcn_tc_kernel(const EtParams 
     __syncthreads();
     if (warp == ET_WORKER_WARPS) {
         tc_fence_after_sync();
-        tmem_dealloc(tmem0, 256);
+        tmem_dealloc(tmem0, 512);
     }
 }
 

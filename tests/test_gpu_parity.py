@@ -145,8 +145,8 @@ def test_espcn_fused_matches_layer_kernels(sb, dev, golden, name):
 def test_espcn_tc_matches_ffma_kernels(sb, dev, golden, name):
     """The tensor-core ESPCN kernel (espcn_tc.cu: conv2 on tcgen05 through the fp16 hi/lo split, ex2/rcp forms of tanh and
     sigmoid) against the fused fp32 FFMA kernel and the reference's fp64 re-run (oracle/torch_port.py on double weights): masks
-    (sigmoid outputs in (0, 1)) within 3e-5 of the fp64 masks on white-noise input 5x the amplitude of a normalised waveform
-    (the fp32 FFMA kernel measures 7.5e-6 there, the tensor-core kernel 2.2e-5: its operands carry 22 significand bits; on the
+    (sigmoid outputs in (0, 1)) within 2e-5 of the fp64 masks on white-noise input 5x the amplitude of a normalised waveform
+    (the fp32 FFMA kernel measures 7.5e-6 there, the tensor-core kernel 1.0e-5: its operands carry 22 significand bits; on the
     reference-generated goldens both stay under the 2e-5 bar of test_espcn_forward_golden) and within 3e-5 of the FFMA kernel;
     detections identical or margin-explained;
     lengths around the 124-position tile, the row ends, and enough tiles for several per CTA."""
@@ -173,7 +173,7 @@ def test_espcn_tc_matches_ffma_kernels(sb, dev, golden, name):
                 ref64 = torch_port.espcn_forward(sd64, x.double().cpu()).float()
             e_tc, e_ffma = float((tc.cpu() - ref64).abs().max()), float((ffma.cpu() - ref64).abs().max())
             worst64 = max(worst64, e_tc)
-            assert e_tc <= 3e-5, (N, L, e_tc, e_ffma)
+            assert e_tc <= 2e-5, (N, L, e_tc, e_ffma)
         # detections: identical, or the differing sample sits within the mask tolerance of a decision boundary (threshold or
         # the best other score of its 21-window) - white-noise input puts ~800 detections per row next to the threshold
         ia = set(map(tuple, sb.get_maxima_positions(tc, 20, 0.2).cpu().numpy().tolist()))
