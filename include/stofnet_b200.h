@@ -77,6 +77,12 @@ int stof_device_count(void);            /* 0 when no CUDA device is visible */
 int stof_model_create(const stof_weights *w, int device, stof_model **out);
 /* Re-upload weights into an existing handle (after an optimizer step).  Synchronous. */
 int stof_model_set_weights(stof_model *m, const stof_weights *w);
+/* The same for a training loop whose optimizer updates the parameters IN DEVICE MEMORY (main.py:246-248 optimizer.step(),
+ * :179 optim.AdamW): `w_dev` holds DEVICE pointers to fp32 tensors in PyTorch's layouts on the model's device; ONE kernel on
+ * `stream` re-derives every device-side layout the fp32 forward / backward kernels read (no host round trip, no
+ * synchronisation; ordered after the optimizer kernel on the same stream).  StofNet only.  The fp16 operand packs of the
+ * tensor-core inference kernels are rebuilt on the next inference call (one device-to-host copy there).                  */
+int stof_model_set_weights_device(stof_model *m, const stof_weights *w_dev, void *stream);
 void stof_model_destroy(stof_model *m);
 
 /* Rows processed per internal chunk and the workspace this needs.  chunk_rows <= 0 picks a default. */

@@ -57,6 +57,7 @@ _SIGS = {
     "stof_launch_count": (C.c_uint64, []),
     "stof_model_create": (_i, [C.POINTER(Weights), _i, C.POINTER(_vp)]),
     "stof_model_set_weights": (_i, [_vp, C.POINTER(Weights)]),
+    "stof_model_set_weights_device": (_i, [_vp, C.POINTER(Weights), _vp]),
     "stof_model_destroy": (None, [_vp]),
     "stof_forward_workspace_bytes": (_i, [_vp, _i, _i, _i, C.POINTER(_sz)]),
     "stof_forward": (_i, [_vp, _vp, _i, _i, _vp, _vp, _sz, _i, _vp]),

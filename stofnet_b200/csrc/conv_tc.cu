@@ -363,6 +363,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                             } else if (type == TC_RELU) {
 #pragma unroll
                                 for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.0f);
+                            } else if (type == TC_NONE) {
+                                // conv + bias only (data gradient of a conv: no activation, no skip)
                             } else if (from_stash) {
                                 // short skip of the segment's last layer: fp32 copy parked in TMEM by the previous layer's epilogue
                                 uint32_t rs[8];
@@ -526,14 +528,24 @@ x0_split_kernel(const float *__restrict__ x, const float *__restrict__ e, int N,
     }
 }
 
-// fp32 C4L4 [n][c/4][l][4]  <->  split planes [n][plane][c8][l][8]
+// fp32 C4L4 [n][c/4][l][4]  <->  split planes [n][plane][c8][l][8], optionally scaled by a power of two derived on the device
+// from the tensor's max |value| (gradients: see kernels.cuh)
+__device__ __forceinline__ float plane_scale(const unsigned *absmax_bits) {
+    if (absmax_bits == nullptr) return 1.0f;
+    const unsigned b = __ldg(absmax_bits);
+    const int e = (int)((b >> 23) & 255u);                       // biased exponent of max |v|: max in [2^(e-127), 2^(e-126))
+    if (e == 0 || e == 255) return 1.0f;                         // all zero (or subnormal) / inf, nan: leave as is
+    return __uint_as_float((unsigned)(127 + 10 - (e - 127)) << 23);    // 2^(10 - (e - 127)): scaled max in [2^10, 2^11)
+}
+
 __global__ void __launch_bounds__(256)
-c4l4_to_planes_kernel(const float4 *__restrict__ act, uint4 *__restrict__ planes, int N, int L) {
+c4l4_to_planes_kernel(const float4 *__restrict__ act, uint4 *__restrict__ planes, int N, int L, const unsigned *__restrict__ absmax_bits) {
     const int n = blockIdx.z, c8 = blockIdx.y;
     const int l = blockIdx.x * 256 + threadIdx.x;
     if (l >= L) return;
+    const float sc = plane_scale(absmax_bits);
     const float4 a0 = act[((size_t)n * 16 + 2 * c8) * L + l], a1 = act[((size_t)n * 16 + 2 * c8 + 1) * L + l];
-    const float v[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+    const float v[8] = {a0.x * sc, a0.y * sc, a0.z * sc, a0.w * sc, a1.x * sc, a1.y * sc, a1.z * sc, a1.w * sc};
     float hi[8], lo[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) split_hi_lo(v[i], hi[i], lo[i]);
@@ -545,18 +557,45 @@ c4l4_to_planes_kernel(const float4 *__restrict__ act, uint4 *__restrict__ planes
 }
 
 __global__ void __launch_bounds__(256)
-planes_to_c4l4_kernel(const uint4 *__restrict__ planes, float4 *__restrict__ act, int N, int L) {
+planes_to_c4l4_kernel(const uint4 *__restrict__ planes, float4 *__restrict__ act, int N, int L, const unsigned *__restrict__ absmax_bits,
+                      int add) {
     const int n = blockIdx.z, c8 = blockIdx.y;
     const int l = blockIdx.x * 256 + threadIdx.x;
     if (l >= L) return;
+    const float inv = 1.0f / plane_scale(absmax_bits);           // exact: a power of two
     float fh[8], fl[8];
     unpack8(planes[((size_t)n * 16 + c8) * L + l], fh);
     unpack8(planes[((size_t)n * 16 + 8 + c8) * L + l], fl);
     float v[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) v[i] = fh[i] + TC_LO_INV * fl[i];
-    act[((size_t)n * 16 + 2 * c8) * L + l] = make_float4(v[0], v[1], v[2], v[3]);
-    act[((size_t)n * 16 + 2 * c8 + 1) * L + l] = make_float4(v[4], v[5], v[6], v[7]);
+    for (int i = 0; i < 8; ++i) v[i] = (fh[i] + TC_LO_INV * fl[i]) * inv;
+    float4 *o0 = act + ((size_t)n * 16 + 2 * c8) * L + l, *o1 = act + ((size_t)n * 16 + 2 * c8 + 1) * L + l;
+    float4 r0 = make_float4(v[0], v[1], v[2], v[3]), r1 = make_float4(v[4], v[5], v[6], v[7]);
+    if (add) {
+        const float4 p0 = *o0, p1 = *o1;
+        r0.x += p0.x; r0.y += p0.y; r0.z += p0.z; r0.w += p0.w;
+        r1.x += p1.x; r1.y += p1.y; r1.z += p1.z; r1.w += p1.w;
+    }
+    *o0 = r0;
+    *o1 = r1;
+}
+
+__global__ void __launch_bounds__(256) absmax_kernel(const float4 *__restrict__ v, size_t n4, unsigned *__restrict__ out_bits) {
+    float m = 0.0f;
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (size_t)gridDim.x * 256) {
+        const float4 a = __ldg(v + i);
+        m = fmaxf(m, fmaxf(fmaxf(fabsf(a.x), fabsf(a.y)), fmaxf(fabsf(a.z), fabsf(a.w))));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    __shared__ float wm[8];
+    if ((threadIdx.x & 31) == 0) wm[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int i = 1; i < 8; ++i) m = fmaxf(m, wm[i]);
+        atomicMax(out_bits, __float_as_uint(m));
+    }
 }
 
 // ------------------------------------------------------------------------------------------------ launchers
@@ -633,16 +672,25 @@ int launch_x0_split(const float *x, const float *e, int N, int L, int P, int sca
     return STOF_OK;
 }
 
-int launch_c4l4_to_planes(const float *act, void *planes, int N, int L, cudaStream_t st) {
+int launch_c4l4_to_planes(const float *act, void *planes, int N, int L, cudaStream_t st, const unsigned *absmax_bits) {
+    STOF_REQUIRE(N <= 65535, STOF_E_INVALID, "c4l4_to_planes: at most 65535 rows per call");
     dim3 grid((L + 255) / 256, 8, N);
-    c4l4_to_planes_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float4 *>(act), reinterpret_cast<uint4 *>(planes), N, L);
+    c4l4_to_planes_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float4 *>(act), reinterpret_cast<uint4 *>(planes), N, L, absmax_bits);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }
 
-int launch_planes_to_c4l4(const void *planes, float *act, int N, int L, cudaStream_t st) {
+int launch_planes_to_c4l4(const void *planes, float *act, int N, int L, cudaStream_t st, const unsigned *absmax_bits, int add) {
+    STOF_REQUIRE(N <= 65535, STOF_E_INVALID, "planes_to_c4l4: at most 65535 rows per call");
     dim3 grid((L + 255) / 256, 8, N);
-    planes_to_c4l4_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const uint4 *>(planes), reinterpret_cast<float4 *>(act), N, L);
+    planes_to_c4l4_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const uint4 *>(planes), reinterpret_cast<float4 *>(act), N, L, absmax_bits, add);
+    STOF_LAUNCH_CHECK();
+    return STOF_OK;
+}
+
+int launch_absmax(const float *v, size_t n4, unsigned *out_bits, cudaStream_t st) {
+    const size_t g = (n4 + 255) / 256;
+    absmax_kernel<<<(unsigned)(g < (size_t)kSMs * 8 ? g : (size_t)kSMs * 8), 256, 0, st>>>(reinterpret_cast<const float4 *>(v), n4, out_bits);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }

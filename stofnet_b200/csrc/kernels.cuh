@@ -28,7 +28,7 @@ int launch_espcn_tc(const float *x, float *mask, int N, int L, const float *w1, 
 
 // conv_tc.cu (tcgen05 / TMEM path) ---------------------------------------------------------------
 constexpr int TC_MAX_LAYERS = 6;
-enum TcLayerType { TC_LEAKY = 0, TC_RES = 1, TC_LONGSKIP = 2, TC_LAST = 3, TC_RELU = 4 };
+enum TcLayerType { TC_LEAKY = 0, TC_RES = 1, TC_LONGSKIP = 2, TC_LAST = 3, TC_RELU = 4, TC_NONE = 5 /* conv + bias only (data gradients) */ };
 
 struct TcLayer {
     const void *w;        // packed fp16 taps: [tap][c8][w_rows][8]
@@ -86,8 +86,13 @@ int launch_contract_pool_tc(const float *x, const void *w, const float *bias, co
                             int N, int L, int P, cudaStream_t st, int fast = 0);
 // expand_tc.cu: E = LeakyReLU(expand_conv(pooled)) on tcgen05 (fp32 in / out, operands split on the fly)
 int launch_expand_tc(const float *pooled, float *e, const void *w_packed, const float *bias, int N, int P, cudaStream_t st);
-// fp32 C4L4 activations <-> split planes (debug / hand-over between the SIMT and tensor paths)
-int launch_c4l4_to_planes(const float *act, void *planes, int N, int L, cudaStream_t st);
-int launch_planes_to_c4l4(const void *planes, float *act, int N, int L, cudaStream_t st);
+// fp32 C4L4 activations <-> split planes (hand-over between the fp32 and tensor paths).  absmax_bits (device, or NULL): bit
+// pattern of max |act| of the tensor; the planes then carry act * 2^k with 2^k max|act| in [2^10, 2^11) - gradients are ~1e-6
+// and would sit in fp16's subnormal range unscaled - and the way back divides by 2^k.  add: act (+)= instead of =.
+int launch_c4l4_to_planes(const float *act, void *planes, int N, int L, cudaStream_t st, const unsigned *absmax_bits = nullptr);
+int launch_planes_to_c4l4(const void *planes, float *act, int N, int L, cudaStream_t st, const unsigned *absmax_bits = nullptr,
+                          int add = 0);
+// *out_bits = max(*out_bits, bits of max |v|) over n4 float4 (non-negative floats order like their bit patterns); zero the slot first
+int launch_absmax(const float *v, size_t n4, unsigned *out_bits, cudaStream_t st);
 
 }  // namespace stof

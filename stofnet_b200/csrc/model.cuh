@@ -44,6 +44,8 @@ struct stof_model {
     // The fp16 hi/lo operand packs above are built on first use after stof_model_set_weights (an optimizer step re-uploads
     // the weights every iteration and its fp32 training kernels never read them): host copies of the tensors they need
     bool tc_dirty = false;
+    // stof_model_set_weights_device: the device layouts are newer than the host copies below (refreshed by ensure_tc)
+    bool host_stale = false;
     std::vector<float> h_mid[STOF_MAX_MID_CONVS], h_last, h_contract, h_expand;
     // training step (train.cu): dgrad weights of the mid convs [co][K-1-t][ci] (a conv with channels swapped and taps
     // flipped), a zero bias vector, and PyTorch-layout copies of conv_last / contract / expand for the backward kernels
@@ -52,6 +54,11 @@ struct stof_model {
     float *raw_last_w = nullptr;                      // (4, 64, 3)
     float *raw_contract_w = nullptr;                  // (512, 64, 5)
     float *raw_expand_w = nullptr;                    // (64, 512, 5)
+    // tensor-core training step (train.cu): fp16 hi/lo taps of the mid convs in the forward and the data-gradient orientation,
+    // packed ON THE DEVICE from mid[].w by the first training call after a weight change (an optimizer step changes them all)
+    void *tr_tc_w = nullptr;
+    stof::TcLayer tr_fwd[STOF_MAX_MID_CONVS], tr_bwd[STOF_MAX_MID_CONVS];
+    bool tr_tc_dirty = true;
     // scratch of stof_infer_host (grow-only)
     static constexpr int kPipe = 2;
     cudaStream_t streams[kPipe] = {nullptr, nullptr};

@@ -335,6 +335,8 @@ static int set_weights_locked(stof_model *m, const stof_weights *w) {
     for (int i = 0; i < w->n_mid; ++i) m->h_mid[i].assign(w->mid_w[i], w->mid_w[i] + (size_t)64 * 64 * 7);
     m->h_last.assign(w->last_w, w->last_w + (size_t)4 * 64 * 3);
     m->tc_dirty = true;
+    m->tr_tc_dirty = true;
+    m->host_stale = false;
     if (w->contract_w) {
         m->sgb_scale = w->sgb_scale; m->sgb_feat = w->sgb_feat; m->sgb_k = w->sgb_k;
         // 8 cout tiles of 64, each [ci][t][co]
@@ -361,6 +363,27 @@ static int ensure_tc(stof_model *m) {
     DeviceGuard guard(m->device);
     STOF_REQUIRE(guard.ok, STOF_E_CUDA, "cudaSetDevice(%d) failed", m->device);
     STOF_CUDA(cudaDeviceSynchronize());               // nothing in flight may still read the packs that are overwritten below
+    if (m->host_stale) {
+        // the weights were last set on the device (stof_model_set_weights_device): fetch the host copies the packs are built
+        // from - conv_last / contract / expand are kept in PyTorch's layout, the mid convs come back from [ci][t][co]
+        std::vector<float> t((size_t)64 * 7 * 64);
+        for (int i = 0; i < m->n_mid; ++i) {
+            STOF_CUDA(cudaMemcpy(t.data(), m->mid[i].w, t.size() * sizeof(float), cudaMemcpyDeviceToHost));
+            m->h_mid[i].resize((size_t)64 * 64 * 7);
+            for (int co = 0; co < 64; ++co)
+                for (int ci = 0; ci < 64; ++ci)
+                    for (int tp = 0; tp < 7; ++tp) m->h_mid[i][((size_t)co * 64 + ci) * 7 + tp] = t[((size_t)ci * 7 + tp) * 64 + co];
+        }
+        m->h_last.resize((size_t)4 * 64 * 3);
+        STOF_CUDA(cudaMemcpy(m->h_last.data(), m->raw_last_w, m->h_last.size() * sizeof(float), cudaMemcpyDeviceToHost));
+        if (m->sgb_scale != 1) {
+            m->h_contract.resize((size_t)512 * 64 * 5);
+            m->h_expand.resize((size_t)64 * 512 * 5);
+            STOF_CUDA(cudaMemcpy(m->h_contract.data(), m->raw_contract_w, m->h_contract.size() * sizeof(float), cudaMemcpyDeviceToHost));
+            STOF_CUDA(cudaMemcpy(m->h_expand.data(), m->raw_expand_w, m->h_expand.size() * sizeof(float), cudaMemcpyDeviceToHost));
+        }
+        m->host_stale = false;
+    }
     stof_weights v;
     memset(&v, 0, sizeof(v));
     v.kind = m->kind; v.n_mid = m->n_mid; v.num_features = m->F; v.upsample_factor = m->r;
@@ -406,6 +429,83 @@ static int ensure_tc(stof_model *m) {
     }
     STOF_CUDA(cudaDeviceSynchronize());               // the packs are complete before any stream's kernel can read them
     m->tc_dirty = false;
+    return STOF_OK;
+}
+
+// ---- device-side weight sync (training loop) -----------------------------------------------------------------------------
+// One launch re-derives every fp32 device layout from PyTorch-layout device tensors: blockIdx.y = job.
+//   mode 0: copy;   mode 1: (Cout, Cin, K) -> [Cin][K][Cout];   mode 2: (Cout, Cin, K) -> [Cout][K-1-t][Cin] (dgrad weights)
+struct RepackJob {
+    const float *src;
+    float *dst;
+    int cout, cin, K, mode;
+};
+constexpr int kMaxRepackJobs = 64;
+struct RepackJobs {
+    RepackJob j[kMaxRepackJobs];
+};
+
+__global__ void __launch_bounds__(256) repack_weights_kernel(const RepackJobs jobs) {
+    const RepackJob jb = jobs.j[blockIdx.y];
+    const int n = jb.cout * jb.cin * jb.K;
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) {
+        int s = i;                                                     // mode 0
+        if (jb.mode == 1) {                                            // i = (ci K + t) Cout + co
+            const int co = i % jb.cout, r = i / jb.cout, t = r % jb.K, ci = r / jb.K;
+            s = (co * jb.cin + ci) * jb.K + t;
+        } else if (jb.mode == 2) {                                     // i = (co K + tp) Cin + ci,  t = K - 1 - tp
+            const int ci = i % jb.cin, r = i / jb.cin, tp = r % jb.K, co = r / jb.K;
+            s = (co * jb.cin + ci) * jb.K + (jb.K - 1 - tp);
+        }
+        jb.dst[i] = __ldg(jb.src + s);
+    }
+}
+
+static int set_weights_device(stof_model *m, const stof_weights *w, cudaStream_t st) {
+    STOF_REQUIRE(m != nullptr && w != nullptr, STOF_E_INVALID, "stof_model_set_weights_device: NULL argument");
+    STOF_REQUIRE(m->kind == STOF_KIND_STOFNET && w->kind == STOF_KIND_STOFNET, STOF_E_UNSUPPORTED,
+                 "stof_model_set_weights_device: StofNet models only (the training step, main.py:217-248)");
+    STOF_REQUIRE(w->n_mid == m->n_mid && (w->contract_w != nullptr) == (m->sgb_scale != 1), STOF_E_INVALID,
+                 "stof_model_set_weights_device: the tensors do not match the model's architecture");
+    STOF_REQUIRE(w->conv1_w && w->conv1_b && w->last_w && w->last_b, STOF_E_INVALID, "stof_model_set_weights_device: missing conv1 / conv_last");
+    STOF_REQUIRE(m->first.w && m->last.w && m->raw_last_w && m->bw_mid[0], STOF_E_INVALID,
+                 "stof_model_set_weights_device: the handle has no device layouts yet (create it from host weights first)");
+    RepackJobs jobs;
+    int n = 0, biggest = 0;
+    auto add = [&](const float *src, float *dst, int cout, int cin, int K, int mode) {
+        jobs.j[n++] = RepackJob{src, dst, cout, cin, K, mode};
+        if (cout * cin * K > biggest) biggest = cout * cin * K;
+    };
+    add(w->conv1_w, m->first.w, 64, 1, 9, 1);
+    add(w->conv1_b, m->first.b, 64, 1, 1, 0);
+    for (int i = 0; i < m->n_mid; ++i) {
+        STOF_REQUIRE(w->mid_w[i] && w->mid_b[i], STOF_E_INVALID, "stof_model_set_weights_device: conv%d missing", i + 2);
+        add(w->mid_w[i], m->mid[i].w, 64, 64, 7, 1);
+        add(w->mid_b[i], m->mid[i].b, 64, 1, 1, 0);
+        add(w->mid_w[i], m->bw_mid[i], 64, 64, 7, 2);
+    }
+    add(w->last_w, m->last.w, 4, 64, 3, 1);
+    add(w->last_b, m->last.b, 4, 1, 1, 0);
+    add(w->last_w, m->raw_last_w, 4, 64, 3, 0);
+    if (m->sgb_scale != 1) {
+        STOF_REQUIRE(w->contract_b && w->expand_w && w->expand_b, STOF_E_INVALID, "stof_model_set_weights_device: incomplete semi-global block");
+        for (int ct = 0; ct < 8; ++ct)                    // 8 cout tiles of 64, each [ci][t][co]
+            add(w->contract_w + (size_t)ct * 64 * 64 * 5, m->contract.w + (size_t)ct * 64 * 64 * 5, 64, 64, 5, 1);
+        add(w->contract_b, m->contract.b, 512, 1, 1, 0);
+        add(w->contract_w, m->raw_contract_w, 512, 64, 5, 0);
+        add(w->expand_w, m->expand.w, 64, 512, 5, 1);
+        add(w->expand_b, m->expand.b, 64, 1, 1, 0);
+        add(w->expand_w, m->raw_expand_w, 64, 512, 5, 0);
+    }
+    STOF_REQUIRE(n <= kMaxRepackJobs, STOF_E_INVALID, "stof_model_set_weights_device: too many tensors");
+    DeviceGuard guard(m->device);
+    STOF_REQUIRE(guard.ok, STOF_E_CUDA, "cudaSetDevice(%d) failed", m->device);
+    dim3 grid((unsigned)((biggest + 255) / 256 < 64 ? (biggest + 255) / 256 : 64), (unsigned)n);
+    repack_weights_kernel<<<grid, 256, 0, st>>>(jobs);
+    STOF_LAUNCH_CHECK();
+    m->tc_dirty = true;
+    m->tr_tc_dirty = true;
+    m->host_stale = true;
     return STOF_OK;
 }
 
@@ -639,6 +739,7 @@ extern "C" void stof_model_destroy(stof_model *m) {
     if (m->tc_w_fast) cudaFree(m->tc_w_fast);
     if (m->tc_w2) cudaFree(m->tc_w2);
     if (m->tc_w2_fast) cudaFree(m->tc_w2_fast);
+    if (m->tr_tc_w) cudaFree(m->tr_tc_w);
     if (m->tc_contract_w) cudaFree(m->tc_contract_w);
     if (m->tc_expand_w) cudaFree(m->tc_expand_w);
     if (m->h_stats) cudaFreeHost(m->h_stats);
@@ -766,6 +867,10 @@ extern "C" int stof_profile_collect(stof_model *m, double *ms_by_class, int64_t 
     }
     m->ev_used = 0;
     return STOF_OK;
+}
+
+extern "C" int stof_model_set_weights_device(stof_model *m, const stof_weights *w_dev, void *stream) {
+    return stof::set_weights_device(m, w_dev, (cudaStream_t)stream);
 }
 
 extern "C" int stof_model_set_path(stof_model *m, int path, int layers_per_launch) {

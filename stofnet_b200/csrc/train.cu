@@ -1,16 +1,22 @@
 // Training step of the StofNet stack (reference main.py:217-248; models/stofnet.py:42-117): a forward pass that keeps every
 // layer's activations, the backward pass (what torch autograd derives from the reference's forward), and a fused AdamW.
 //
-// All fp32 on CUDA cores, activations in the C4L4 layout of conv_simt.cu.  Data gradients of the 64->64 k7 convs reuse the
-// forward conv kernel with channel-swapped, tap-flipped weights (a transposed conv with 'same' padding is a conv); weight
-// gradients are register-tiled outer-product reductions over positions with per-CTA partial sums that a second kernel adds
-// in a fixed order, so gradients are bit-reproducible run to run (no float atomics).
+// fp32 on CUDA cores, activations in the C4L4 layout of conv_simt.cu; data gradients of the 64->64 k7 convs reuse the forward
+// conv with channel-swapped, tap-flipped weights (a transposed conv with 'same' padding is a conv); weight gradients are
+// register-tiled outer-product reductions over positions with per-CTA partial sums that a second kernel adds in a fixed order,
+// so gradients are bit-reproducible run to run (no float atomics).
+// On the tensor-core path (default; STOF_PATH_SIMT keeps the all-fp32 step) the 22 big contractions of a step - forward and
+// data gradient of conv2..conv12, 75 % of its FLOPs - run on the tcgen05 chain kernel (conv_tc.cu), one layer per launch on
+// split fp16 planes: operand packs built on the device from the current weights, gradient planes scaled by a power of two
+// taken from the tensor's max |g| on the device (no host synchronisation), fp32 C4L4 copies kept for the weight gradients.
 //
 //   forward  (saved)   x0r = relu(conv1 x);  pooled, argmax = maxpool80(lrelu(contract x0r));  E = lrelu(expand pooled);
 //                      x0 = x0r + up80(E);  a2 = lrelu(c2 x0);  a3 = x0 + c3 a2;  ...  a12 = x0 + c12 a11;  y = c_last a12
 //   backward           g_y = g_mask (the shuffle is a relabelling);  conv_last, conv12..conv2 (pairs: skip + lrelu'),
 //                      semi-global block (window sum, expand, arg-max scatter through the pool, contract), conv1
+#include <cuda_fp16.h>
 #include <math.h>
+#include <string.h>
 
 #include "model.cuh"
 
@@ -25,6 +31,10 @@ struct TrainPlan {
     size_t off_pooled, off_argmax, off_e, off_ge, off_gpool;
     size_t off_partial;            // float offset of the partial-sum scratch
     size_t partial_floats;
+    // tensor-core path: split planes (same size as an fp32 tensor) of x0 and of every mid conv's output, two gradient planes,
+    // and the max |g| slots (one unsigned per data-gradient call)
+    bool tc;
+    size_t off_px0, off_pa[STOF_MAX_MID_CONVS], off_gp[2], off_absmax;
     size_t total_bytes;
 };
 
@@ -58,6 +68,13 @@ static int make_train_plan(const stof_model *m, int N, int L, TrainPlan *p) {
     // then mid wgrad (WG_MAX_PARTS x WG_MID_LEN)
     p->partial_floats = a64((size_t)WG_MAX_PARTS * WG_MID_LEN);
     p->off_partial = o; o += p->partial_floats;
+    p->tc = (m->path != STOF_PATH_SIMT);
+    if (p->tc) {
+        p->off_px0 = o; o += p->act;
+        for (int j = 0; j < m->n_mid; ++j) { p->off_pa[j] = o; o += p->act; }
+        for (int i = 0; i < 2; ++i) { p->off_gp[i] = o; o += p->act; }
+        p->off_absmax = o; o += 64;
+    }
     p->total_bytes = o * sizeof(float);
     return STOF_OK;
 }
@@ -477,6 +494,72 @@ adamw_kernel(float *__restrict__ p, const float *__restrict__ g, float *__restri
 
 using namespace stof;
 
+// ------------------------------------------------------------------------------------------------ tensor-core operand packs
+// One tap of a 64 -> 64 conv for the chain kernel: [c8 = k/8][W_hi 64 rows | W_lo 64 rows][k%8] fp16 (upload_tc in stof_api.cu).
+// Built here on the device from mid[j].w = [ci][t][co] fp32 (kept current by set_weights / set_weights_device):
+//   forward   tap t : k = ci, row = co              <- W[co][ci][t]
+//   backward  tap t': k = co, row = ci              <- W[co][ci][6 - t']     (dX = conv of dY with swapped channels, flipped taps)
+struct TrainPackJobs {
+    const float *w[STOF_MAX_MID_CONVS];
+    __half *fwd[STOF_MAX_MID_CONVS], *bwd[STOF_MAX_MID_CONVS];
+};
+
+__global__ void __launch_bounds__(256) train_pack_kernel(const TrainPackJobs jobs) {
+    const int j = blockIdx.y;
+    const float *w = jobs.w[j];
+    const int i = blockIdx.x * 256 + threadIdx.x;            // (t, k, row) with row fastest: 7 * 64 * 64
+    if (i >= 7 * 64 * 64) return;
+    const int row = i & 63, k = (i >> 6) & 63, t = i >> 12;
+    {
+        const float v = __ldg(w + ((size_t)k * 7 + t) * 64 + row);                  // W[co = row][ci = k][t]
+        const float c = fminf(fmaxf(v, -65504.0f), 65504.0f);
+        const __half hi = __float2half_rn(c);
+        const __half lo = __float2half_rn((c - __half2float(hi)) * 2048.0f);
+        __half *tap = jobs.fwd[j] + (size_t)t * 8 * 128 * 8;
+        tap[((size_t)(k >> 3) * 128 + row) * 8 + (k & 7)] = hi;
+        tap[((size_t)(k >> 3) * 128 + 64 + row) * 8 + (k & 7)] = lo;
+    }
+    {
+        const float v = __ldg(w + ((size_t)row * 7 + (6 - t)) * 64 + k);            // W[co = k][ci = row][6 - t]
+        const float c = fminf(fmaxf(v, -65504.0f), 65504.0f);
+        const __half hi = __float2half_rn(c);
+        const __half lo = __float2half_rn((c - __half2float(hi)) * 2048.0f);
+        __half *tap = jobs.bwd[j] + (size_t)t * 8 * 128 * 8;
+        tap[((size_t)(k >> 3) * 128 + row) * 8 + (k & 7)] = hi;
+        tap[((size_t)(k >> 3) * 128 + 64 + row) * 8 + (k & 7)] = lo;
+    }
+}
+
+// (re)build the training packs on `st` when the weights changed since the last build
+static int ensure_train_tc(stof_model *m, cudaStream_t st) {
+    const size_t per_layer = (size_t)7 * 8 * 128 * 8;       // halfs
+    if (!m->tr_tc_w) STOF_CUDA(cudaMalloc(&m->tr_tc_w, 2 * (size_t)m->n_mid * per_layer * sizeof(__half)));
+    if (!m->tr_tc_dirty) return STOF_OK;
+    TrainPackJobs jobs;
+    __half *base = reinterpret_cast<__half *>(m->tr_tc_w);
+    for (int j = 0; j < m->n_mid; ++j) {
+        jobs.w[j] = m->mid[j].w;
+        jobs.fwd[j] = base + (size_t)j * per_layer;
+        jobs.bwd[j] = base + (size_t)(m->n_mid + j) * per_layer;
+        for (int dir = 0; dir < 2; ++dir) {
+            TcLayer &l = dir ? m->tr_bwd[j] : m->tr_fwd[j];
+            memset(&l, 0, sizeof(l));
+            l.w = dir ? jobs.bwd[j] : jobs.fwd[j];
+            l.bias = dir ? m->zero_bias : m->mid[j].b;
+            l.taps = 7; l.pad = 3;
+            l.stage_bytes = 16384; l.n_out = 64; l.n_stack = 128; l.n_lo = 64; l.lo_row = 0; l.lo_col = 64; l.w_rows = 128; l.n_fast = 64;
+            // forward (models/stofnet.py:51-62): even index -> LeakyReLU; odd -> skip + conv with the skip read from global
+            // planes (one layer per launch: every output is kept for the backward pass).  backward: set per call.
+            l.type = dir ? TC_NONE : (((j & 1) || j == m->n_mid - 1) ? TC_LONGSKIP : TC_LEAKY);
+        }
+    }
+    dim3 grid((7 * 64 * 64 + 255) / 256, (unsigned)m->n_mid);
+    train_pack_kernel<<<grid, 256, 0, st>>>(jobs);
+    STOF_LAUNCH_CHECK();
+    m->tr_tc_dirty = false;
+    return STOF_OK;
+}
+
 extern "C" int stof_train_workspace_bytes(const stof_model *m, int N, int L, size_t *bytes) {
     STOF_REQUIRE(bytes != nullptr, STOF_E_INVALID, "stof_train_workspace_bytes: bytes is NULL");
     TrainPlan pl;
@@ -508,6 +591,22 @@ extern "C" int stof_forward_train(stof_model *m, const float *x, int N, int L, f
         if ((rc = launch_expand(pooled, e, m->expand.w, m->expand.b, N, pl.P, st))) return rc;
         STOF_CUDA(cudaMemcpyAsync(x0, x0r, (size_t)N * 64 * L * sizeof(float), cudaMemcpyDeviceToDevice, st));
         if ((rc = launch_sgb_add(x0, e, N, L, pl.P, m->sgb_scale, (L - pl.P * m->sgb_scale) / 2, st))) return rc;
+    }
+    if (pl.tc) {
+        // :51-62 on the tensor cores: one chain launch per conv, planes in / planes out (kept), fp32 C4L4 copy for the backward
+        if ((rc = ensure_train_tc(m, st))) return rc;
+        void *px0 = ws + pl.off_px0;
+        if ((rc = launch_c4l4_to_planes(x0, px0, N, L, st))) return rc;
+        const void *curp = px0;
+        for (int j = 0; j < m->n_mid; ++j) {
+            void *outp = ws + pl.off_pa[j];
+            const bool longskip = (j == m->n_mid - 1);
+            const void *skip = (longskip || j < 2) ? px0 : (const void *)(ws + pl.off_pa[j - 2]);
+            if ((rc = launch_chain_tc(&m->tr_fwd[j], 1, curp, ((j & 1) || longskip) ? skip : nullptr, outp, nullptr, N, L, st))) return rc;
+            if ((rc = launch_planes_to_c4l4(outp, ws + pl.off_a[j], N, L, st))) return rc;
+            curp = outp;
+        }
+        return launch_conv_last(ws + pl.off_a[m->n_mid - 1], mask, m->last.w, m->last.b, N, L, 64, 0, st);
     }
     // :51-62  conv index i = j + 2
     const float *cur = x0;
@@ -573,19 +672,36 @@ extern "C" int stof_backward(stof_model *m, const float *x, const float *g_mask,
         reduce_parts_kernel<<<4, 256, 0, st>>>(partial, g2, 772, gr->last_w, 768, gr->last_b);
         STOF_LAUNCH_CHECK();
     }
+    // data gradient of mid conv j: out (+)= dgrad_j(g).  Tensor-core path: max |g| -> power-of-two scale (device side), g -> split
+    // planes, one chain launch with the tap-flipped channel-swapped pack, planes -> fp32 (unscaled, optionally accumulated)
+    int n_dgrad = 0;
+    if (pl.tc) {
+        if ((rc = ensure_train_tc(m, st))) return rc;
+        STOF_CUDA(cudaMemsetAsync(ws + pl.off_absmax, 0, 64 * sizeof(float), st));
+    }
+    auto mid_dgrad = [&](int j, const float *g, float *out, bool accumulate) -> int {
+        if (!pl.tc) return launch_conv_mid_simt(g, accumulate ? out : nullptr, out, m->bw_mid[j], m->zero_bias, N, L, accumulate ? 1 : 2, st);
+        unsigned *slot = reinterpret_cast<unsigned *>(ws + pl.off_absmax) + (n_dgrad++);
+        void *gp0 = ws + pl.off_gp[0], *gp1 = ws + pl.off_gp[1];
+        int r;
+        if ((r = launch_absmax(g, n4, slot, st))) return r;
+        if ((r = launch_c4l4_to_planes(g, gp0, N, L, st, slot))) return r;
+        if ((r = launch_chain_tc(&m->tr_bwd[j], 1, gp0, nullptr, gp1, nullptr, N, L, st))) return r;
+        return launch_planes_to_c4l4(gp1, out, N, L, st, slot, accumulate ? 1 : 0);
+    };
     // ---- conv{nb-1} (long skip): a = x0 + conv(a_prev): g_conv = X;  S = dgrad(X)
     if ((rc = mid_wgrad(X, act(nm - 2), N, L, partial, gr->mid_w[nm - 1], gr->mid_b[nm - 1], st))) return rc;
-    if ((rc = launch_conv_mid_simt(X, nullptr, S, m->bw_mid[nm - 1], m->zero_bias, N, L, 2, st))) return rc;
+    if ((rc = mid_dgrad(nm - 1, X, S, false))) return rc;
     // ---- pairs (RES j, LEAKY j - 1), j = nm-2, nm-4, ..., 1:   S = g wrt a_j
     for (int j = nm - 2; j >= 1; j -= 2) {
         // a_j = a_{j-2} + conv_j(a_{j-1}):  wgrad with input a_{j-1};  T = dgrad_j(S);  skip keeps S
         if ((rc = mid_wgrad(S, act(j - 1), N, L, partial, gr->mid_w[j], gr->mid_b[j], st))) return rc;
-        if ((rc = launch_conv_mid_simt(S, nullptr, T, m->bw_mid[j], m->zero_bias, N, L, 2, st))) return rc;
+        if ((rc = mid_dgrad(j, S, T, false))) return rc;
         // a_{j-1} = lrelu(conv_{j-1}(a_{j-2})):  T *= lrelu'(a_{j-1});  wgrad with input a_{j-2};  S += dgrad_{j-1}(T)
         lrelu_bwd_kernel<<<ew_grid(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(T), reinterpret_cast<const float4 *>(act(j - 1)), n4);
         STOF_LAUNCH_CHECK();
         if ((rc = mid_wgrad(T, act(j - 2), N, L, partial, gr->mid_w[j - 1], gr->mid_b[j - 1], st))) return rc;
-        if ((rc = launch_conv_mid_simt(T, S, S, m->bw_mid[j - 1], m->zero_bias, N, L, 1, st))) return rc;
+        if ((rc = mid_dgrad(j - 1, T, S, true))) return rc;
     }
     // ---- S = g wrt x0 through the chain; add the long skip
     add_kernel<<<ew_grid(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(S), reinterpret_cast<const float4 *>(X), n4);

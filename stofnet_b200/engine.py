@@ -31,7 +31,16 @@ def _host_arrays(sd):
     return out
 
 
+class _DevArray:
+    """Stands in for a numpy array in Engine._pack: .shape and a device pointer."""
+
+    def __init__(self, t):
+        self.t, self.shape = t, tuple(t.shape)
+
+
 def _ptr(a):
+    if isinstance(a, _DevArray):
+        return C.c_void_p(a.t.data_ptr())
     return a.ctypes.data_as(C.c_void_p)
 
 
@@ -70,10 +79,19 @@ class Engine:
             pass
 
     # -- weights ---------------------------------------------------------------------------
-    def _pack(self, sd):
-        """sd: mapping with the reference's state_dict key names -> ctypes struct (+ keep-alive)."""
+    def _pack(self, sd, on_device=False):
+        """sd: mapping with the reference's state_dict key names -> ctypes struct (+ keep-alive).  on_device: the struct
+        carries the DEVICE pointers of the (contiguous fp32 CUDA) tensors instead of host copies."""
         W = _lib.Weights()
-        keep = _host_arrays(sd)
+        if on_device:
+            keep = {}
+            for k, v in sd.items():
+                t = v.detach()
+                if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+                    raise RuntimeError("stofnet_b200: device-side weight sync needs contiguous fp32 CUDA parameters (%s)" % k)
+                keep[k] = _DevArray(t)
+        else:
+            keep = _host_arrays(sd)
         W.kind = self.kind
         if self.kind == _lib.KIND_EDSR:
             # models/edsr_1d.py:22-30
@@ -147,6 +165,17 @@ class Engine:
         self.key = key
         del keep
 
+    def sync_device(self, module, device):
+        """After an in-place optimizer step on the device (Trainer): re-derive the kernels' weight layouts from the
+        parameters where they live, with one kernel on the current stream (stof_model_set_weights_device)."""
+        params = dict(module.state_dict(keep_vars=True))
+        W, keep = self._pack(params, on_device=True)
+        if getattr(module, "semi_global_block", None) is not None:
+            W.sgb_scale = int(module.semi_global_block.sample_scale)
+        with torch.cuda.device(device):
+            check(lib.stof_model_set_weights_device(self.handle, C.byref(W), stream_ptr(device)))
+        del keep
+
     def set_path(self, path, layers_per_launch=0):
         """path: _lib.PATH_TC (tcgen05, fp16 hi/lo split operands) or _lib.PATH_SIMT (fp32 FFMA)."""
         self.path, self.layers_per_launch = path, layers_per_launch
@@ -212,6 +241,7 @@ class Engine:
         N, _, L = x.shape
         with torch.cuda.device(dev):
             self.sync(module, dev)
+            self._apply_path()
             need = C.c_size_t()
             check(lib.stof_train_workspace_bytes(self.handle, N, L, C.byref(need)))
             ws = torch.empty(need.value, dtype=torch.uint8, device=dev)

@@ -18,6 +18,21 @@ from .engine import require_cuda, stream_ptr
 from .utils.gaussian import gaussian_kernel
 
 
+_GAUSS_CACHE = {}
+
+
+def _gauss_on(gauss, dev):
+    """The (tiny) blur kernel as a device tensor, uploaded once per (values, device) - not once per step."""
+    a = np.asarray(gauss, dtype=np.float32).reshape(-1)
+    key = (a.tobytes(), dev.type, dev.index)
+    g = _GAUSS_CACHE.get(key)
+    if g is None:
+        if len(_GAUSS_CACHE) > 64:
+            _GAUSS_CACHE.clear()
+        g = _GAUSS_CACHE[key] = torch.as_tensor(a, device=dev).contiguous()
+    return g
+
+
 def _prep(masks_pred, gt_true):
     require_cuda(masks_pred, "masks_pred")
     require_cuda(gt_true, "gt_true")
@@ -33,7 +48,7 @@ def blur_max(gt_true, m, gauss, device=None):
     n = gt_true.shape[0]
     smp = gt_true.detach().to(torch.int64).reshape(n, -1).contiguous()
     dev = smp.device
-    g = torch.as_tensor(np.asarray(gauss, dtype=np.float32), device=dev).reshape(-1).contiguous()
+    g = _gauss_on(gauss, dev)
     mx = torch.zeros((1,), dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
         check(lib.stof_mask_loss(None, smp.data_ptr(), n, smp.shape[1], int(m), g.data_ptr(), g.numel(), 0.0, 0.0, 1,
@@ -46,7 +61,7 @@ def mask_loss_raw(masks_pred, gt_true, gauss, mask_amplitude=20.0, lambda_value=
     (all-reduced) blur max, or None to compute it over these rows like the single-GPU reference."""
     pred, smp, n, m = _prep(masks_pred, gt_true)
     dev = pred.device
-    g = torch.as_tensor(np.asarray(gauss, dtype=np.float32), device=dev).reshape(-1).contiguous()
+    g = _gauss_on(gauss, dev)
     mx = blur_max_value if blur_max_value is not None else torch.zeros((1,), dtype=torch.float32, device=dev)
     loss = torch.empty((1,), dtype=torch.float64, device=dev)
     grad = torch.empty((n, m), dtype=torch.float32, device=dev) if want_grad else None

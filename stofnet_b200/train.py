@@ -97,6 +97,7 @@ class Trainer:
                                       self.exp_avg_sq.data_ptr(), self.flat.numel(), self.step_count,
                                       float(self.lr if lr is None else lr), float(self.betas[0]), float(self.betas[1]),
                                       float(self.eps), float(self.weight_decay), stream_ptr(self.device)))
-        eng.key = None          # parameters changed in place through the flat buffer: re-upload on the next forward
+        # parameters changed in place through the flat buffer: the kernels' layouts follow on the device, same stream
+        eng.sync_device(model, self.device)
         self.last_grads = grads
         return loss.reshape(())

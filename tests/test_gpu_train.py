@@ -108,3 +108,14 @@ def test_inference_after_training_uses_new_weights(sb, golden):
     assert not torch.equal(before, after)
     sd = model.state_dict()
     assert all(torch.isfinite(v).all() for v in sd.values())
+    # the optimizer step re-derives the kernels' weight layouts on the device (stof_model_set_weights_device) and the
+    # tensor-core packs are rebuilt from a device-to-host copy: a fresh handle created from the state_dict through the
+    # host path must give the same masks bit for bit - on the tensor-core path, the fp32 path and the training forward
+    fresh = sb.build_model({k: v.detach().cpu().clone() for k, v in sd.items()}, dev)
+    with torch.no_grad():
+        assert torch.equal(after, fresh(x))
+        model._engine.set_path(sb._lib.PATH_SIMT)
+        fresh._engine.set_path(sb._lib.PATH_SIMT)
+        assert torch.equal(model(x), fresh(x))
+    model.train(); fresh.train()
+    assert torch.equal(model(x).detach(), fresh(x).detach())
