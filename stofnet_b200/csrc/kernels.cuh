@@ -78,6 +78,12 @@ int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void
 // conv_tc2.cu: the same segment on CTA pairs (2-CTA clusters, tcgen05 cta_group::2: M = 256 per MMA, each CTA reads half of B)
 int launch_chain_tc2(const TcLayer *layers, int count, const void *in, const void *x0, void *out_planes, float *out_mask,
                      int N, int L, cudaStream_t st, int fast = 0);
+// wgrad_tc.cu: weight (and bias) gradient of a 64 -> 64 k7 conv on tcgen05 from the split planes of the output gradient (scaled:
+// absmax_bits as in launch_c4l4_to_planes) and of the conv's input; g_c4l4 = the gradient in fp32 (bias sum); dW in PyTorch's
+// (64, 64, 7) layout; scratch: wgrad_tc_scratch_floats() floats.  Deterministic (fixed-order reduction).
+size_t wgrad_tc_scratch_floats();
+int launch_wgrad_tc(const void *g_planes, const void *a_planes, const float *g_c4l4, const unsigned *absmax_bits, int N, int L,
+                    float *scratch, float *dW, float *db, cudaStream_t st);
 // x (N, L) fp32 -> split planes of x0 = act(conv_first(x)) [+ nearest-upsampled E, centred]  (models/stofnet.py:45,96-115)
 int launch_x0_split(const float *x, const float *e, int N, int L, int P, int scale, int off, const float *w, const float *b,
                     void *planes, cudaStream_t st, int fast = 0, int K = 9);

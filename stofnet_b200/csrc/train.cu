@@ -67,6 +67,7 @@ static int make_train_plan(const stof_model *m, int N, int L, TrainPlan *p) {
     // partial sums: the largest user is the contract wgrad (one partial per row chunk is avoided: it reduces in-kernel),
     // then mid wgrad (WG_MAX_PARTS x WG_MID_LEN)
     p->partial_floats = a64((size_t)WG_MAX_PARTS * WG_MID_LEN);
+    if (m->path != STOF_PATH_SIMT && a64(wgrad_tc_scratch_floats()) > p->partial_floats) p->partial_floats = a64(wgrad_tc_scratch_floats());
     p->off_partial = o; o += p->partial_floats;
     p->tc = (m->path != STOF_PATH_SIMT);
     if (p->tc) {
@@ -672,36 +673,40 @@ extern "C" int stof_backward(stof_model *m, const float *x, const float *g_mask,
         reduce_parts_kernel<<<4, 256, 0, st>>>(partial, g2, 772, gr->last_w, 768, gr->last_b);
         STOF_LAUNCH_CHECK();
     }
-    // data gradient of mid conv j: out (+)= dgrad_j(g).  Tensor-core path: max |g| -> power-of-two scale (device side), g -> split
-    // planes, one chain launch with the tap-flipped channel-swapped pack, planes -> fp32 (unscaled, optionally accumulated)
-    int n_dgrad = 0;
+    // One mid conv j of the backward pass, given g = d loss / d (its output): weight gradient with the conv's input (the output of
+    // conv j - 1, or x0), then out (+)= data gradient.  Tensor-core path: max |g| -> power-of-two scale (device side), g -> split
+    // planes ONCE for both products; wgrad_tc.cu; one chain launch with the tap-flipped channel-swapped pack, planes -> fp32.
+    int n_slots = 0;
     if (pl.tc) {
         if ((rc = ensure_train_tc(m, st))) return rc;
         STOF_CUDA(cudaMemsetAsync(ws + pl.off_absmax, 0, 64 * sizeof(float), st));
     }
-    auto mid_dgrad = [&](int j, const float *g, float *out, bool accumulate) -> int {
-        if (!pl.tc) return launch_conv_mid_simt(g, accumulate ? out : nullptr, out, m->bw_mid[j], m->zero_bias, N, L, accumulate ? 1 : 2, st);
-        unsigned *slot = reinterpret_cast<unsigned *>(ws + pl.off_absmax) + (n_dgrad++);
-        void *gp0 = ws + pl.off_gp[0], *gp1 = ws + pl.off_gp[1];
+    auto pact = [&](int j) -> const void * { return j < 0 ? (const void *)(ws + pl.off_px0) : (const void *)(ws + pl.off_pa[j]); };
+    auto mid_backward = [&](int j, const float *g, float *out, bool accumulate) -> int {
         int r;
+        if (!pl.tc) {
+            if ((r = mid_wgrad(g, act(j - 1), N, L, partial, gr->mid_w[j], gr->mid_b[j], st))) return r;
+            return launch_conv_mid_simt(g, accumulate ? out : nullptr, out, m->bw_mid[j], m->zero_bias, N, L, accumulate ? 1 : 2, st);
+        }
+        STOF_REQUIRE(n_slots < 64, STOF_E_INVALID, "stof_backward: too many mid convs");
+        unsigned *slot = reinterpret_cast<unsigned *>(ws + pl.off_absmax) + (n_slots++);
+        void *gp0 = ws + pl.off_gp[0], *gp1 = ws + pl.off_gp[1];
         if ((r = launch_absmax(g, n4, slot, st))) return r;
         if ((r = launch_c4l4_to_planes(g, gp0, N, L, st, slot))) return r;
+        if ((r = launch_wgrad_tc(gp0, pact(j - 1), g, slot, N, L, partial, gr->mid_w[j], gr->mid_b[j], st))) return r;
         if ((r = launch_chain_tc(&m->tr_bwd[j], 1, gp0, nullptr, gp1, nullptr, N, L, st))) return r;
         return launch_planes_to_c4l4(gp1, out, N, L, st, slot, accumulate ? 1 : 0);
     };
     // ---- conv{nb-1} (long skip): a = x0 + conv(a_prev): g_conv = X;  S = dgrad(X)
-    if ((rc = mid_wgrad(X, act(nm - 2), N, L, partial, gr->mid_w[nm - 1], gr->mid_b[nm - 1], st))) return rc;
-    if ((rc = mid_dgrad(nm - 1, X, S, false))) return rc;
+    if ((rc = mid_backward(nm - 1, X, S, false))) return rc;
     // ---- pairs (RES j, LEAKY j - 1), j = nm-2, nm-4, ..., 1:   S = g wrt a_j
     for (int j = nm - 2; j >= 1; j -= 2) {
         // a_j = a_{j-2} + conv_j(a_{j-1}):  wgrad with input a_{j-1};  T = dgrad_j(S);  skip keeps S
-        if ((rc = mid_wgrad(S, act(j - 1), N, L, partial, gr->mid_w[j], gr->mid_b[j], st))) return rc;
-        if ((rc = mid_dgrad(j, S, T, false))) return rc;
+        if ((rc = mid_backward(j, S, T, false))) return rc;
         // a_{j-1} = lrelu(conv_{j-1}(a_{j-2})):  T *= lrelu'(a_{j-1});  wgrad with input a_{j-2};  S += dgrad_{j-1}(T)
         lrelu_bwd_kernel<<<ew_grid(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(T), reinterpret_cast<const float4 *>(act(j - 1)), n4);
         STOF_LAUNCH_CHECK();
-        if ((rc = mid_wgrad(T, act(j - 2), N, L, partial, gr->mid_w[j - 1], gr->mid_b[j - 1], st))) return rc;
-        if ((rc = mid_dgrad(j - 1, T, S, true))) return rc;
+        if ((rc = mid_backward(j - 1, T, S, true))) return rc;
     }
     // ---- S = g wrt x0 through the chain; add the long skip
     add_kernel<<<ew_grid(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(S), reinterpret_cast<const float4 *>(X), n4);
