@@ -71,11 +71,14 @@ struct ContractParams {
     const float *w1;         // conv1 weights [9][64] fp32
     const float *b1;         // [64]
     float *pooled;           // (N, 512, P)
+    int *argmax;             // (N, 512, P) position of each pooled maximum (training forward), or NULL
     int N, L, P;
     int tiles_per_row, total_tiles;
     int fast;                // 1: one-pass fp16 mode (X_hi W_hi only)
 };
 
+// ARGMAX: also record the position of every pooled maximum (first one on ties, as ATen's max_pool1d) for the backward pass
+template <bool ARGMAX>
 __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const ContractParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     const uint32_t sbase = smem_u32(smem);
@@ -247,6 +250,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
             const int ti = tile - n * p.tiles_per_row;
             const int p0 = 3 * ti;                        // first pooling window of the tile
             float m[3] = {-INFINITY, -INFINITY, -INFINITY};
+            int mi[3] = {0, 0, 0};
 #pragma unroll
             for (int b = 0; b < 2; ++b) {
                 mbar_wait(BAR_ACC_FULL(b), (uint32_t)(it & 1));
@@ -272,9 +276,19 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
                         if (h == 0 || two) {
                             const int w = (128 * b + 16 * (c + h)) / CT_WINDOW;  // compile-time: window of this 16-column chunk
                             float mm = m[w];
+                            if (ARGMAX) {
+                                int ii = mi[w];
 #pragma unroll
-                            for (int i = 0; i < 16; ++i)
-                                mm = fmaxf(mm, fmaf(li, __uint_as_float(d1[16 * h + i]), __uint_as_float(d0[16 * h + i])));
+                                for (int i = 0; i < 16; ++i) {
+                                    const float v = fmaf(li, __uint_as_float(d1[16 * h + i]), __uint_as_float(d0[16 * h + i]));
+                                    if (v > mm) { mm = v; ii = 128 * b + 16 * (c + h) + i; }
+                                }
+                                mi[w] = ii;
+                            } else {
+#pragma unroll
+                                for (int i = 0; i < 16; ++i)
+                                    mm = fmaxf(mm, fmaf(li, __uint_as_float(d1[16 * h + i]), __uint_as_float(d0[16 * h + i])));
+                            }
                             m[w] = mm;
                         }
                     }
@@ -287,7 +301,10 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
             float *dst = p.pooled + ((size_t)n * 512 + co) * p.P + p0;
 #pragma unroll
             for (int w = 0; w < 3; ++w)
-                if (p0 + w < p.P) dst[w] = leaky(m[w] + bias);
+                if (p0 + w < p.P) {
+                    dst[w] = leaky(m[w] + bias);
+                    if (ARGMAX) p.argmax[((size_t)n * 512 + co) * p.P + p0 + w] = CT_TILE * ti + mi[w];
+                }
         }
     }
 
@@ -300,11 +317,12 @@ __global__ void __launch_bounds__(CT_THREADS, 1) contract_tc_kernel(const Contra
 }
 
 int launch_contract_pool_tc(const float *x, const void *w, const float *bias, const float *w1, const float *b1, float *pooled,
-                            int N, int L, int P, cudaStream_t st, int fast) {
-    static SmemAttrOnce attr;
-    { const int rc = ensure_dyn_smem(contract_tc_kernel, CT_SMEM_BYTES, attr); if (rc) return rc; }
+                            int N, int L, int P, cudaStream_t st, int fast, int *argmax) {
+    static SmemAttrOnce attr, attr_arg;
+    { const int rc = argmax ? ensure_dyn_smem(contract_tc_kernel<true>, CT_SMEM_BYTES, attr_arg)
+                            : ensure_dyn_smem(contract_tc_kernel<false>, CT_SMEM_BYTES, attr); if (rc) return rc; }
     ContractParams p;
-    p.x = x; p.w = w; p.bias = bias; p.w1 = w1; p.b1 = b1; p.pooled = pooled;
+    p.x = x; p.w = w; p.bias = bias; p.w1 = w1; p.b1 = b1; p.pooled = pooled; p.argmax = argmax;
     p.N = N; p.L = L; p.P = P; p.fast = fast;
     p.tiles_per_row = (P + 2) / 3;
     const long long total = (long long)N * p.tiles_per_row;
@@ -313,7 +331,8 @@ int launch_contract_pool_tc(const float *x, const void *w, const float *bias, co
     // 4 slices x workers; every slice needs at least one CTA
     long long grid = 4 * total;
     if (grid > kSMs) grid = kSMs;
-    contract_tc_kernel<<<(int)grid, CT_THREADS, CT_SMEM_BYTES, st>>>(p);
+    if (argmax) contract_tc_kernel<true><<<(int)grid, CT_THREADS, CT_SMEM_BYTES, st>>>(p);
+    else contract_tc_kernel<false><<<(int)grid, CT_THREADS, CT_SMEM_BYTES, st>>>(p);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }

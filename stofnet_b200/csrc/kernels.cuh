@@ -88,8 +88,9 @@ int launch_wgrad_tc(const void *g_planes, const void *a_planes, const float *g_c
 int launch_x0_split(const float *x, const float *e, int N, int L, int P, int scale, int off, const float *w, const float *b,
                     void *planes, cudaStream_t st, int fast = 0, int K = 9);
 // contract_tc.cu: pooled = maxpool80(LeakyReLU(contract_conv(relu(conv1 x)))) on tcgen05, conv1 recomputed per tile
+// argmax (or NULL): (N, 512, P) positions of the pooled maxima, for the training step's backward pass
 int launch_contract_pool_tc(const float *x, const void *w, const float *bias, const float *w1, const float *b1, float *pooled,
-                            int N, int L, int P, cudaStream_t st, int fast = 0);
+                            int N, int L, int P, cudaStream_t st, int fast = 0, int *argmax = nullptr);
 // expand_tc.cu: E = LeakyReLU(expand_conv(pooled)) on tcgen05 (fp32 in / out, operands split on the fly)
 int launch_expand_tc(const float *pooled, float *e, const void *w_packed, const float *bias, int N, int P, cudaStream_t st);
 // fp32 C4L4 activations <-> split planes (hand-over between the fp32 and tensor paths).  absmax_bits (device, or NULL): bit

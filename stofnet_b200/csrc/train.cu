@@ -39,6 +39,7 @@ struct TrainPlan {
 };
 
 constexpr int WG_MAX_PARTS = kSMs;                 // persistent wgrad CTAs
+constexpr int SGB_PARTS = 16;                      // row parts of the semi-global block's weight gradients
 constexpr size_t WG_MID_LEN = 64 * 64 * 7 + 64;    // dW + db of one mid conv
 
 static size_t a64(size_t floats) { return (floats + 63) & ~(size_t)63; }
@@ -68,6 +69,7 @@ static int make_train_plan(const stof_model *m, int N, int L, TrainPlan *p) {
     // then mid wgrad (WG_MAX_PARTS x WG_MID_LEN)
     p->partial_floats = a64((size_t)WG_MAX_PARTS * WG_MID_LEN);
     if (m->path != STOF_PATH_SIMT && a64(wgrad_tc_scratch_floats()) > p->partial_floats) p->partial_floats = a64(wgrad_tc_scratch_floats());
+    if (p->sgb && a64((size_t)SGB_PARTS * (512 * 64 * 5 + 512)) > p->partial_floats) p->partial_floats = a64((size_t)SGB_PARTS * (512 * 64 * 5 + 512));
     p->off_partial = o; o += p->partial_floats;
     p->tc = (m->path != STOF_PATH_SIMT);
     if (p->tc) {
@@ -302,14 +304,16 @@ lrelu_bwd1_kernel(float *__restrict__ g, const float *__restrict__ a, size_t n) 
 }
 
 // expand conv (512 -> 64, k5, pad 2 on the pooled axis):  e_pre[n][co][p] = b + sum_ci sum_t We[co][ci][t] pooled[n][ci][p+t-2]
-// wgrad: dWe[co][ci][t] = sum_{n,p} g[n][co][p] pooled[n][ci][p + t - 2];  one CTA per ci, thread = (co, t), fixed (n, p) order
+// wgrad: dWe[co][ci][t] = sum_{n,p} g[n][co][p] pooled[n][ci][p + t - 2];  CTA = (ci, part of the rows), thread = (co, t), fixed
+// (n, p) order; partial [part][(64,512,5)], added in part order by reduce_parts_kernel
 __global__ void __launch_bounds__(320)
 expand_wgrad_kernel(const float *__restrict__ g /*[N][64][P]*/, const float *__restrict__ pooled /*[N][512][P]*/, int N, int P,
-                    float *__restrict__ dW /*(64,512,5)*/) {
+                    float *__restrict__ partial) {
     const int ci = blockIdx.x;
     const int co = threadIdx.x / 5, t = threadIdx.x - 5 * co;
+    float *dW = partial + (size_t)blockIdx.y * (64 * 512 * 5);
     float acc = 0.0f;
-    for (int n = 0; n < N; ++n) {
+    for (int n = blockIdx.y; n < N; n += gridDim.y) {
         const float *gr = g + ((size_t)n * 64 + co) * P;
         const float *pr = pooled + ((size_t)n * 512 + ci) * P;
         for (int p = 0; p < P; ++p) {
@@ -358,14 +362,16 @@ expand_dgrad_kernel(const float *__restrict__ g /*[N][64][P]*/, const float *__r
 }
 
 // contract conv (64 -> 512, k5, pad 2) behind the max-pool: the gradient of c[n][co][.] is gpool[n][co][p] at l* = argmax only.
-// wgrad: dWc[co][ci][t] = sum_{n,p} gpool[n][co][p] x0r[n][ci][l* + t - 2];  dbc[co] = sum gpool.  One CTA per co.
+// wgrad: dWc[co][ci][t] = sum_{n,p} gpool[n][co][p] x0r[n][ci][l* + t - 2];  dbc[co] = sum gpool.  CTA = (co, part of the rows);
+// partial [part][(512,64,5) | (512)], added in part order by reduce_parts_kernel
 __global__ void __launch_bounds__(320)
 contract_wgrad_kernel(const float *__restrict__ gpool, const int *__restrict__ argmax, const float *__restrict__ x0r /*C4L4*/,
-                      int N, int L, int P, float *__restrict__ dW /*(512,64,5)*/, float *__restrict__ db /*(512)*/) {
+                      int N, int L, int P, float *__restrict__ partial) {
     const int co = blockIdx.x;
     const int ci = threadIdx.x / 5, t = threadIdx.x - 5 * ci;
+    float *dW = partial + (size_t)blockIdx.y * (512 * 64 * 5 + 512), *db = dW + 512 * 64 * 5;
     float acc = 0.0f, bs = 0.0f;
-    for (int n = 0; n < N; ++n) {
+    for (int n = blockIdx.y; n < N; n += gridDim.y) {
         const float *xr = x0r + ((size_t)n * 16 + (ci >> 2)) * L * 4 + (ci & 3);
         const size_t base = ((size_t)n * 512 + co) * P;
         for (int p = 0; p < P; ++p) {
@@ -378,37 +384,62 @@ contract_wgrad_kernel(const float *__restrict__ gpool, const int *__restrict__ a
     dW[((size_t)co * 64 + ci) * 5 + t] = acc;
     if (threadIdx.x == 0) db[co] = bs;
 }
-// dgrad (gather form, deterministic): g_x0r[n][ci][l] += sum over (co, p) with |l - l*| <= 2 of Wc[co][ci][l - l* + 2] gpool.
-// One CTA per (row, 80-position tile); it scans the (co, p) entries of the pooling windows that can reach the tile
-// (p in [tile-1, tile+1]); thread = (ci, quarter of the tile) owns its outputs exclusively (shared accumulators, no races).
+// dgrad (deterministic): g_x0r[n][ci][l] += sum over (co, p) with |l - l*| <= 2 of Wc[co][ci][l - l* + 2] gpool[n][co][p].
+// One CTA per (row, 80-position tile).  The (co, p) entries of the pooling windows that can reach the tile (p in [tile-1, tile+1])
+// are compacted IN ORDER to those whose arg-max lies within 2 positions of it (~1/3 of them); thread = (ci, q) then takes every
+// 4th entry and accumulates into its own copy q of the tile's outputs (no races, no atomics); the four copies are added in a
+// fixed order.  Every loop iteration does useful work (the first version scanned all 1,536 candidates in every thread: 3.1 ms
+// of a 16 ms step at 256 x 2560).
 constexpr int CD_T = 80;
+constexpr int CD_SMEM = (4 * 64 * (CD_T + 1)) * 4 + 3 * 512 * (4 + 4 + 4) + 64;
 __global__ void __launch_bounds__(256)
 contract_dgrad_kernel(const float *__restrict__ gpool, const int *__restrict__ argmax, const float *__restrict__ Wc /*(512,64,5)*/,
                       int N, int L, int P, int tiles, float *__restrict__ gx /*C4L4, accumulated into*/) {
-    __shared__ float accs[64][CD_T + 1];
-    __shared__ int e_l[3 * 512];
-    __shared__ float e_g[3 * 512];
+    extern __shared__ __align__(16) uint8_t cd_raw[];
+    float *accs = reinterpret_cast<float *>(cd_raw);                       // [4 q][64 ci][CD_T + 1]
+    int *e_l = reinterpret_cast<int *>(accs + 4 * 64 * (CD_T + 1));        // compacted entries: arg-max position,
+    float *e_g = reinterpret_cast<float *>(e_l + 3 * 512);                 //   pooled gradient,
+    int *e_co = reinterpret_cast<int *>(e_g + 3 * 512);                    //   output channel
+    int *w_cnt = e_co + 3 * 512;                                           // [8 warps] + running total
     const int n = blockIdx.x / tiles, tile = blockIdx.x - n * tiles;
     const int l0 = tile * CD_T;
-    for (int i = threadIdx.x; i < 64 * (CD_T + 1); i += 256) (&accs[0][0])[i] = 0.0f;
-    for (int i = threadIdx.x; i < 3 * 512; i += 256) {
-        const int w = tile - 1 + i / 512, co = i & 511;
-        int l = -1000000; float g = 0.0f;
-        if (w >= 0 && w < P) { l = __ldg(argmax + ((size_t)n * 512 + co) * P + w); g = __ldg(gpool + ((size_t)n * 512 + co) * P + w); }
-        e_l[i] = l; e_g[i] = g;
-    }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < 4 * 64 * (CD_T + 1); i += 256) accs[i] = 0.0f;
+    if (threadIdx.x == 0) w_cnt[8] = 0;
     __syncthreads();
-    const int ci = threadIdx.x >> 2, qt = threadIdx.x & 3;
-    const int lo = l0 + 20 * qt, hi = lo + 20;                 // this thread's positions [lo, hi)
-    for (int i = 0; i < 3 * 512; ++i) {
-        const int ls = e_l[i];
-        if (ls + 2 < lo || ls - 2 >= hi) continue;
-        const float g = e_g[i];
-        const float *wr = Wc + ((size_t)(i & 511) * 64 + ci) * 5;
+    for (int r = 0; r < 6; ++r) {                                          // 1,536 candidates, 256 per round, order preserved
+        const int i = r * 256 + threadIdx.x;
+        const int w = tile - 1 + i / 512, co = i & 511;
+        int l = 0; float g = 0.0f; bool ok = false;
+        if (w >= 0 && w < P) {
+            l = __ldg(argmax + ((size_t)n * 512 + co) * P + w);
+            g = __ldg(gpool + ((size_t)n * 512 + co) * P + w);
+            ok = (l + 2 >= l0) && (l - 2 < l0 + CD_T);
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, ok);
+        if (lane == 0) w_cnt[warp] = __popc(bal);
+        __syncthreads();
+        int off = w_cnt[8];
+        for (int k = 0; k < warp; ++k) off += w_cnt[k];
+        if (ok) {
+            const int d = off + __popc(bal & ((1u << lane) - 1u));
+            e_l[d] = l; e_g[d] = g; e_co[d] = co;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) { int tot = w_cnt[8]; for (int k = 0; k < 8; ++k) tot += w_cnt[k]; w_cnt[8] = tot; }
+        __syncthreads();
+    }
+    const int m = w_cnt[8];
+    const int ci = threadIdx.x >> 2, q = threadIdx.x & 3;
+    float *mine = accs + ((size_t)q * 64 + ci) * (CD_T + 1);
+    for (int k = q; k < m; k += 4) {
+        const int ls = e_l[k] - l0;
+        const float g = e_g[k];
+        const float *wr = Wc + ((size_t)e_co[k] * 64 + ci) * 5;
 #pragma unroll
         for (int t = 0; t < 5; ++t) {
-            const int l = ls + t - 2;                          // c[l*] reads x0r[l* + t - 2]
-            if (l >= lo && l < hi) accs[ci][l - l0] += __ldg(wr + t) * g;
+            const int j = ls + t - 2;                          // c[l*] reads x0r[l* + t - 2]
+            if (j >= 0 && j < CD_T) mine[j] += __ldg(wr + t) * g;
         }
     }
     __syncthreads();
@@ -418,7 +449,13 @@ contract_dgrad_kernel(const float *__restrict__ gpool, const int *__restrict__ a
         if (l >= L) continue;
         float4 *d = reinterpret_cast<float4 *>(gx) + ((size_t)n * 16 + c4) * L + l;
         float4 v = *d;
-        v.x += accs[4 * c4][j]; v.y += accs[4 * c4 + 1][j]; v.z += accs[4 * c4 + 2][j]; v.w += accs[4 * c4 + 3][j];
+        float s4[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const float *a = accs + (size_t)(4 * c4 + c) * (CD_T + 1) + j;
+            s4[c] = ((a[0] + a[64 * (CD_T + 1)]) + a[2 * 64 * (CD_T + 1)]) + a[3 * 64 * (CD_T + 1)];
+        }
+        v.x += s4[0]; v.y += s4[1]; v.z += s4[2]; v.w += s4[3];
         *d = v;
     }
 }
@@ -531,11 +568,47 @@ __global__ void __launch_bounds__(256) train_pack_kernel(const TrainPackJobs job
     }
 }
 
+// semi-global block packs (the layouts of ensure_tc in stof_api.cu) from the PyTorch-layout device copies:
+//   contract (512, 64, 5) -> [4 slices][5 taps][8 c8][W_hi 128 | W_lo 128][8];   expand (64, 512, 5) -> [8 groups][5 taps][8 c8][W_hi 64 | W_lo 64][8]
+__global__ void __launch_bounds__(256)
+train_pack_sgb_kernel(const float *__restrict__ contract_w, const float *__restrict__ expand_w, __half *__restrict__ cpk, __half *__restrict__ epk) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= 512 * 64 * 5) return;
+    const float v = __ldg((blockIdx.y ? expand_w : contract_w) + i);
+    const float c = fminf(fmaxf(v, -65504.0f), 65504.0f);
+    const __half hi = __float2half_rn(c);
+    const __half lo = __float2half_rn((c - __half2float(hi)) * 2048.0f);
+    const int t = i % 5;
+    if (blockIdx.y == 0) {
+        const int ci = (i / 5) & 63, co = i / (5 * 64);
+        const int sl = co >> 7, r = co & 127;
+        __half *tap = cpk + ((size_t)sl * 5 + t) * 8 * 256 * 8;
+        tap[((size_t)(ci >> 3) * 256 + r) * 8 + (ci & 7)] = hi;
+        tap[((size_t)(ci >> 3) * 256 + 128 + r) * 8 + (ci & 7)] = lo;
+    } else {
+        const int cin = (i / 5) & 511, co = i / (5 * 512);
+        const int g = cin >> 6, ci = cin & 63;
+        __half *tap = epk + ((size_t)g * 5 + t) * 8 * 128 * 8;
+        tap[((size_t)(ci >> 3) * 128 + co) * 8 + (ci & 7)] = hi;
+        tap[((size_t)(ci >> 3) * 128 + 64 + co) * 8 + (ci & 7)] = lo;
+    }
+}
+
+constexpr size_t TR_PER_LAYER = (size_t)7 * 8 * 128 * 8;       // halfs of one mid conv pack
+constexpr size_t TR_SGB_PACK = (size_t)512 * 64 * 5 * 2;       // halfs of the contract (and of the expand) pack
+static __half *train_contract_pack(const stof_model *m) { return reinterpret_cast<__half *>(m->tr_tc_w) + 2 * (size_t)m->n_mid * TR_PER_LAYER; }
+static __half *train_expand_pack(const stof_model *m) { return train_contract_pack(m) + TR_SGB_PACK; }
+
 // (re)build the training packs on `st` when the weights changed since the last build
 static int ensure_train_tc(stof_model *m, cudaStream_t st) {
-    const size_t per_layer = (size_t)7 * 8 * 128 * 8;       // halfs
-    if (!m->tr_tc_w) STOF_CUDA(cudaMalloc(&m->tr_tc_w, 2 * (size_t)m->n_mid * per_layer * sizeof(__half)));
+    const size_t per_layer = TR_PER_LAYER;
+    if (!m->tr_tc_w) STOF_CUDA(cudaMalloc(&m->tr_tc_w, (2 * (size_t)m->n_mid * per_layer + 2 * TR_SGB_PACK) * sizeof(__half)));
     if (!m->tr_tc_dirty) return STOF_OK;
+    if (m->sgb_scale != 1) {
+        train_pack_sgb_kernel<<<dim3((512 * 64 * 5 + 255) / 256, 2), 256, 0, st>>>(m->raw_contract_w, m->raw_expand_w, train_contract_pack(m),
+                                                                                  train_expand_pack(m));
+        STOF_LAUNCH_CHECK();
+    }
     TrainPackJobs jobs;
     __half *base = reinterpret_cast<__half *>(m->tr_tc_w);
     for (int j = 0; j < m->n_mid; ++j) {
@@ -584,7 +657,15 @@ extern "C" int stof_forward_train(stof_model *m, const float *x, int N, int L, f
     float *x0r = ws + pl.off_x0r, *x0 = ws + pl.off_x0;
     // models/stofnet.py:45
     if ((rc = launch_conv_first(x, N, L, m->first.w, m->first.b, x0r, 9, 0, st))) return rc;
-    if (pl.sgb) {
+    if (pl.tc && pl.sgb) {
+        // :98-117 on the tensor cores (contract_tc.cu with the arg-max output the backward pass needs, expand_tc.cu); x0 comes
+        // out of the fused conv1 + upsample-add kernel directly as split planes.  x0r (fp32) stays for relu' and the contract wgrad.
+        if ((rc = ensure_train_tc(m, st))) return rc;
+        float *pooled = ws + pl.off_pooled, *e = ws + pl.off_e;
+        int *argmax = reinterpret_cast<int *>(ws + pl.off_argmax);
+        if ((rc = launch_contract_pool_tc(x, train_contract_pack(m), m->contract.b, m->first.w, m->first.b, pooled, N, L, pl.P, st, 0, argmax))) return rc;
+        if ((rc = launch_expand_tc(pooled, e, train_expand_pack(m), m->expand.b, N, pl.P, st))) return rc;
+    } else if (pl.sgb) {
         // :98-117
         float *pooled = ws + pl.off_pooled, *e = ws + pl.off_e;
         int *argmax = reinterpret_cast<int *>(ws + pl.off_argmax);
@@ -597,7 +678,10 @@ extern "C" int stof_forward_train(stof_model *m, const float *x, int N, int L, f
         // :51-62 on the tensor cores: one chain launch per conv, planes in / planes out (kept), fp32 C4L4 copy for the backward
         if ((rc = ensure_train_tc(m, st))) return rc;
         void *px0 = ws + pl.off_px0;
-        if ((rc = launch_c4l4_to_planes(x0, px0, N, L, st))) return rc;
+        if (pl.sgb) {
+            if ((rc = launch_x0_split(x, ws + pl.off_e, N, L, pl.P, m->sgb_scale, (L - pl.P * m->sgb_scale) / 2, m->first.w, m->first.b, px0, st, 0,
+                                      m->k_first))) return rc;
+        } else if ((rc = launch_c4l4_to_planes(x0, px0, N, L, st))) return rc;
         const void *curp = px0;
         for (int j = 0; j < m->n_mid; ++j) {
             void *outp = ws + pl.off_pa[j];
@@ -722,18 +806,26 @@ extern "C" int stof_backward(stof_model *m, const float *x, const float *g_mask,
         const size_t ne = (size_t)N * 64 * P;
         lrelu_bwd1_kernel<<<ew_grid(ne), 256, 0, st>>>(ge, e, ne);
         STOF_LAUNCH_CHECK();
-        expand_wgrad_kernel<<<512, 320, 0, st>>>(ge, pooled, N, P, gr->expand_w);
+        const int parts = N < SGB_PARTS ? N : SGB_PARTS;
+        expand_wgrad_kernel<<<dim3(512, (unsigned)parts), 320, 0, st>>>(ge, pooled, N, P, partial);
+        STOF_LAUNCH_CHECK();
+        reduce_parts_kernel<<<(64 * 512 * 5 + 255) / 256, 256, 0, st>>>(partial, parts, (size_t)64 * 512 * 5, gr->expand_w, (size_t)64 * 512 * 5, nullptr);
         STOF_LAUNCH_CHECK();
         bias_grad_ncl_kernel<<<64, 256, 0, st>>>(ge, N, 64, P, gr->expand_b);
         STOF_LAUNCH_CHECK();
         const long long np = (long long)N * 512 * P;
         expand_dgrad_kernel<<<(unsigned)((np + 255) / 256), 256, 0, st>>>(ge, m->raw_expand_w, pooled, N, P, gpool);
         STOF_LAUNCH_CHECK();
-        contract_wgrad_kernel<<<512, 320, 0, st>>>(gpool, argmax, x0r, N, L, P, gr->contract_w, gr->contract_b);
+        contract_wgrad_kernel<<<dim3(512, (unsigned)parts), 320, 0, st>>>(gpool, argmax, x0r, N, L, P, partial);
+        STOF_LAUNCH_CHECK();
+        reduce_parts_kernel<<<(512 * 64 * 5 + 512 + 255) / 256, 256, 0, st>>>(partial, parts, (size_t)512 * 64 * 5 + 512, gr->contract_w,
+                                                                               (size_t)512 * 64 * 5, gr->contract_b);
         STOF_LAUNCH_CHECK();
         const int tiles = (L + CD_T - 1) / CD_T;
         STOF_REQUIRE((long long)N * tiles < (1ll << 31), STOF_E_INVALID, "stof_backward: batch too large");
-        contract_dgrad_kernel<<<(unsigned)(N * tiles), 256, 0, st>>>(gpool, argmax, m->raw_contract_w, N, L, P, tiles, S);
+        static SmemAttrOnce cd_attr;
+        if ((rc = ensure_dyn_smem(contract_dgrad_kernel, CD_SMEM, cd_attr))) return rc;
+        contract_dgrad_kernel<<<(unsigned)(N * tiles), 256, CD_SMEM, st>>>(gpool, argmax, m->raw_contract_w, N, L, P, tiles, S);
         STOF_LAUNCH_CHECK();
     }
     // ---- conv1: x0r = relu(conv1 x)
