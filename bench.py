@@ -314,6 +314,33 @@ def other_configs(sb, dev, rank, world, cpu):
     if world == 1:
         guarded("C1", c1)
 
+    # ---- C2 with the checkpoint BASELINE.json names literally (wobbly-sponge is an ESPCN_1D checkpoint): 4096 rows x
+    #      L = 5120 per GPU, th = 0.2, forward (espcn_tc.cu: conv2 / conv3 on tcgen05) + mask2coords, device-resident
+    def c2_espcn():
+        from oracle import torch_port
+        sd_e = load_sd("wobbly-sponge")
+        model = sb.build_model(sd_e, dev)
+        x = expand_batch(make_inputs(256, 3008 + rank), ROWS, 0).unsqueeze(1).contiguous().to(dev)
+        step, _ = infer_step(model, x, 0.2, 256)
+        ms = dev_ms(lambda: step(), 2, 5)
+        d = {"config": "C2 with ckpt wobbly-sponge (ESPCN_1D): %d rows x L=%d per GPU, th=0.2, forward + mask2coords" % (ROWS, L),
+             "ms_per_step": ms, "waveforms_per_s": ROWS * world / (ms / 1e3)}
+        if cpu:
+            xs = expand_batch(make_inputs(256, 3008), 256, 0).unsqueeze(1)
+            torch.set_num_threads(threads)
+            torch_port.infer(sd_e, xs[:64], WIN, 0.2, espcn=True)
+            ts = []
+            for _ in range(3):
+                t0 = time.perf_counter()
+                torch_port.infer(sd_e, xs, WIN, 0.2, espcn=True)
+                ts.append(time.perf_counter() - t0)
+            med = float(np.median(ts))
+            d["cpu_port"] = {"waveforms_per_s": 256 / med, "cores": threads, "sample": "256 rows, median of 3 (%.2f s each)" % med}
+        del x
+        model._engine.ws = None
+        return d
+    guarded("C2_espcn", c2_espcn)
+
     # ---- C3: PALA-shaped frames (128 channels folded into rows), 16,000 rows per GPU, th = None, incl. the ToF gather
     def c3():
         rows = 16000

@@ -94,6 +94,32 @@ lrelu_bwd_kernel(float4 *__restrict__ g, const float4 *__restrict__ a, size_t n4
         g[i] = gv;
     }
 }
+// the same with a given as split fp16 planes [n][plane][c8][l][8] (tensor-core path: the forward keeps planes only); a > 0 <=> its
+// hi plane is positive, or zero with a positive lo plane
+__global__ void __launch_bounds__(256)
+lrelu_bwd_planes_kernel(float4 *__restrict__ g /*C4L4*/, const uint4 *__restrict__ planes, int N, int L) {
+    const int n = blockIdx.z, c8 = blockIdx.y;
+    const int l = blockIdx.x * 256 + threadIdx.x;
+    if (l >= L) return;
+    const uint4 h = __ldg(planes + ((size_t)n * 16 + c8) * L + l), lo = __ldg(planes + ((size_t)n * 16 + 8 + c8) * L + l);
+    const uint32_t hw[4] = {h.x, h.y, h.z, h.w}, lw[4] = {lo.x, lo.y, lo.z, lo.w};
+    float f[8];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const uint32_t hv = (hw[i] >> (16 * k)) & 0xffffu, lv = (lw[i] >> (16 * k)) & 0xffffu;
+            // fp16 bit patterns: positive <=> sign bit clear and magnitude non-zero
+            const bool pos = ((hv & 0x7fffu) != 0u) ? ((hv & 0x8000u) == 0u) : (((lv & 0x7fffu) != 0u) && ((lv & 0x8000u) == 0u));
+            f[2 * i + k] = pos ? 1.f : kLeakySlope;
+        }
+    }
+    float4 *g0 = g + ((size_t)n * 16 + 2 * c8) * L + l, *g1 = g + ((size_t)n * 16 + 2 * c8 + 1) * L + l;
+    float4 a = *g0, b = *g1;
+    a.x *= f[0]; a.y *= f[1]; a.z *= f[2]; a.w *= f[3];
+    b.x *= f[4]; b.y *= f[5]; b.z *= f[6]; b.w *= f[7];
+    *g0 = a; *g1 = b;
+}
 // g[i] = (a[i] > 0) ? g[i] : 0     (ReLU backward)
 __global__ void __launch_bounds__(256)
 relu_bwd_kernel(float4 *__restrict__ g, const float4 *__restrict__ a, size_t n4) {
@@ -688,7 +714,8 @@ extern "C" int stof_forward_train(stof_model *m, const float *x, int N, int L, f
             const bool longskip = (j == m->n_mid - 1);
             const void *skip = (longskip || j < 2) ? px0 : (const void *)(ws + pl.off_pa[j - 2]);
             if ((rc = launch_chain_tc(&m->tr_fwd[j], 1, curp, ((j & 1) || longskip) ? skip : nullptr, outp, nullptr, N, L, st))) return rc;
-            if ((rc = launch_planes_to_c4l4(outp, ws + pl.off_a[j], N, L, st))) return rc;
+            // fp32 copy only of the last activation (conv_last forward and weight gradient); lrelu' reads the planes
+            if (longskip && (rc = launch_planes_to_c4l4(outp, ws + pl.off_a[j], N, L, st))) return rc;
             curp = outp;
         }
         return launch_conv_last(ws + pl.off_a[m->n_mid - 1], mask, m->last.w, m->last.b, N, L, 64, 0, st);
@@ -788,7 +815,12 @@ extern "C" int stof_backward(stof_model *m, const float *x, const float *g_mask,
         // a_j = a_{j-2} + conv_j(a_{j-1}):  wgrad with input a_{j-1};  T = dgrad_j(S);  skip keeps S
         if ((rc = mid_backward(j, S, T, false))) return rc;
         // a_{j-1} = lrelu(conv_{j-1}(a_{j-2})):  T *= lrelu'(a_{j-1});  wgrad with input a_{j-2};  S += dgrad_{j-1}(T)
-        lrelu_bwd_kernel<<<ew_grid(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(T), reinterpret_cast<const float4 *>(act(j - 1)), n4);
+        if (pl.tc) {
+            lrelu_bwd_planes_kernel<<<dim3((L + 255) / 256, 8, N), 256, 0, st>>>(reinterpret_cast<float4 *>(T),
+                                                                                 reinterpret_cast<const uint4 *>(pact(j - 1)), N, L);
+        } else {
+            lrelu_bwd_kernel<<<ew_grid(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(T), reinterpret_cast<const float4 *>(act(j - 1)), n4);
+        }
         STOF_LAUNCH_CHECK();
         if ((rc = mid_backward(j - 1, T, S, true))) return rc;
     }
