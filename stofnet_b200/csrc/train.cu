@@ -205,7 +205,8 @@ last_wgrad_kernel(const float4 *__restrict__ gy, const float *__restrict__ a /*C
         const int n = tile / chunks, l0 = (tile - n * chunks) * LW_CHUNK;
         const float *ar = a + ((size_t)n * 16 + (ci >> 2)) * L * 4 + (ci & 3);
         const int l1 = min(L, l0 + LW_CHUNK);
-        for (int l = l0; l < l1; ++l) {
+#pragma unroll 8
+        for (int l = l0; l < l1; ++l) {                      // independent loads: 8 positions in flight per thread
             const float4 g = __ldg(gy + (size_t)n * L + l);
             const int q = l + t - 1;
             const float av = (q >= 0 && q < L) ? __ldg(ar + (size_t)q * 4) : 0.0f;
@@ -330,24 +331,46 @@ lrelu_bwd1_kernel(float *__restrict__ g, const float *__restrict__ a, size_t n) 
 }
 
 // expand conv (512 -> 64, k5, pad 2 on the pooled axis):  e_pre[n][co][p] = b + sum_ci sum_t We[co][ci][t] pooled[n][ci][p+t-2]
-// wgrad: dWe[co][ci][t] = sum_{n,p} g[n][co][p] pooled[n][ci][p + t - 2];  CTA = (ci, part of the rows), thread = (co, t), fixed
-// (n, p) order; partial [part][(64,512,5)], added in part order by reduce_parts_kernel
+// wgrad: dWe[co][ci][t] = sum_{n,p} g[n][co][p] pooled[n][ci][p + t - 2];  CTA = (block of 16 ci, part of the rows), thread =
+// (co, t) with 16 accumulators (one per ci of the block).  Per row and 32-position chunk the CTA stages g (64 x 32) and the 16
+// pooled rows with their +-2 halo (zero outside [0, P)) in shared memory, so every global byte is read once per CTA and the inner
+// loop is one shared-memory read per FMA (the first version re-read both operands from global memory in every thread: 1.5 ms
+// of a 16 ms step at 256 x 2560).  Fixed (n, p) order; partial [part][(64,512,5)], added in part order by reduce_parts_kernel.
+constexpr int EW_CI = 16, EW_PC = 32;
 __global__ void __launch_bounds__(320)
 expand_wgrad_kernel(const float *__restrict__ g /*[N][64][P]*/, const float *__restrict__ pooled /*[N][512][P]*/, int N, int P,
                     float *__restrict__ partial) {
-    const int ci = blockIdx.x;
+    __shared__ float gs[64][EW_PC + 1];
+    __shared__ float ps[EW_CI][EW_PC + 4];
+    const int ci0 = blockIdx.x * EW_CI;
     const int co = threadIdx.x / 5, t = threadIdx.x - 5 * co;
-    float *dW = partial + (size_t)blockIdx.y * (64 * 512 * 5);
-    float acc = 0.0f;
+    float acc[EW_CI];
+#pragma unroll
+    for (int c = 0; c < EW_CI; ++c) acc[c] = 0.0f;
     for (int n = blockIdx.y; n < N; n += gridDim.y) {
-        const float *gr = g + ((size_t)n * 64 + co) * P;
-        const float *pr = pooled + ((size_t)n * 512 + ci) * P;
-        for (int p = 0; p < P; ++p) {
-            const int q = p + t - 2;
-            if (q >= 0 && q < P) acc = fmaf(__ldg(gr + p), __ldg(pr + q), acc);
+        for (int p0 = 0; p0 < P; p0 += EW_PC) {
+            __syncthreads();
+            for (int i = threadIdx.x; i < 64 * EW_PC; i += 320) {
+                const int c = i / EW_PC, j = i - c * EW_PC;
+                gs[c][j] = (p0 + j < P) ? __ldg(g + ((size_t)n * 64 + c) * P + p0 + j) : 0.0f;
+            }
+            for (int i = threadIdx.x; i < EW_CI * (EW_PC + 4); i += 320) {
+                const int c = i / (EW_PC + 4), j = i - c * (EW_PC + 4);
+                const int q = p0 + j - 2;
+                ps[c][j] = (q >= 0 && q < P) ? __ldg(pooled + ((size_t)n * 512 + ci0 + c) * P + q) : 0.0f;
+            }
+            __syncthreads();
+#pragma unroll 4
+            for (int j = 0; j < EW_PC; ++j) {
+                const float gv = gs[co][j];
+#pragma unroll
+                for (int c = 0; c < EW_CI; ++c) acc[c] = fmaf(gv, ps[c][j + t], acc[c]);
+            }
         }
     }
-    dW[((size_t)co * 512 + ci) * 5 + t] = acc;
+    float *dW = partial + (size_t)blockIdx.y * (64 * 512 * 5);
+#pragma unroll
+    for (int c = 0; c < EW_CI; ++c) dW[((size_t)co * 512 + ci0 + c) * 5 + t] = acc[c];
 }
 // db[c] = sum_{n,p} g[n][c][p]     (NCL tensor with C channels; one CTA per channel, fixed-order tree)
 __global__ void __launch_bounds__(256)
@@ -389,10 +412,14 @@ expand_dgrad_kernel(const float *__restrict__ g /*[N][64][P]*/, const float *__r
 
 // contract conv (64 -> 512, k5, pad 2) behind the max-pool: the gradient of c[n][co][.] is gpool[n][co][p] at l* = argmax only.
 // wgrad: dWc[co][ci][t] = sum_{n,p} gpool[n][co][p] x0r[n][ci][l* + t - 2];  dbc[co] = sum gpool.  CTA = (co, part of the rows);
-// partial [part][(512,64,5) | (512)], added in part order by reduce_parts_kernel
+// the row's pooled gradients and arg-max positions are staged in shared memory (one coalesced read) so that the gather from x0r
+// is the only dependent global load; partial [part][(512,64,5) | (512)], added in part order by reduce_parts_kernel
+constexpr int CW_PC = 256;
 __global__ void __launch_bounds__(320)
 contract_wgrad_kernel(const float *__restrict__ gpool, const int *__restrict__ argmax, const float *__restrict__ x0r /*C4L4*/,
                       int N, int L, int P, float *__restrict__ partial) {
+    __shared__ float s_g[CW_PC];
+    __shared__ int s_l[CW_PC];
     const int co = blockIdx.x;
     const int ci = threadIdx.x / 5, t = threadIdx.x - 5 * ci;
     float *dW = partial + (size_t)blockIdx.y * (512 * 64 * 5 + 512), *db = dW + 512 * 64 * 5;
@@ -400,11 +427,18 @@ contract_wgrad_kernel(const float *__restrict__ gpool, const int *__restrict__ a
     for (int n = blockIdx.y; n < N; n += gridDim.y) {
         const float *xr = x0r + ((size_t)n * 16 + (ci >> 2)) * L * 4 + (ci & 3);
         const size_t base = ((size_t)n * 512 + co) * P;
-        for (int p = 0; p < P; ++p) {
-            const float gv = __ldg(gpool + base + p);
-            const int q = __ldg(argmax + base + p) + t - 2;
-            if (q >= 0 && q < L) acc = fmaf(gv, __ldg(xr + (size_t)q * 4), acc);
-            bs += gv;
+        for (int p0 = 0; p0 < P; p0 += CW_PC) {
+            const int np = min(CW_PC, P - p0);
+            __syncthreads();
+            for (int i = threadIdx.x; i < np; i += 320) { s_g[i] = __ldg(gpool + base + p0 + i); s_l[i] = __ldg(argmax + base + p0 + i); }
+            __syncthreads();
+#pragma unroll 4
+            for (int p = 0; p < np; ++p) {
+                const float gv = s_g[p];
+                const int q = s_l[p] + t - 2;
+                if (q >= 0 && q < L) acc = fmaf(gv, __ldg(xr + (size_t)q * 4), acc);
+                bs += gv;
+            }
         }
     }
     dW[((size_t)co * 64 + ci) * 5 + t] = acc;
@@ -415,7 +449,8 @@ contract_wgrad_kernel(const float *__restrict__ gpool, const int *__restrict__ a
 // are compacted IN ORDER to those whose arg-max lies within 2 positions of it (~1/3 of them); thread = (ci, q) then takes every
 // 4th entry and accumulates into its own copy q of the tile's outputs (no races, no atomics); the four copies are added in a
 // fixed order.  Every loop iteration does useful work (the first version scanned all 1,536 candidates in every thread: 3.1 ms
-// of a 16 ms step at 256 x 2560).
+// of a 16 ms step at 256 x 2560; this one 2.0 ms.  A weight-stationary variant - 4 windows per CTA, the 512 channels in 16 staged
+// blocks of 32, thread = (ci, window) - measured 2.7 ms: one CTA per SM and a serial shared-memory read-modify-write chain per thread).
 constexpr int CD_T = 80;
 constexpr int CD_SMEM = (4 * 64 * (CD_T + 1)) * 4 + 3 * 512 * (4 + 4 + 4) + 64;
 __global__ void __launch_bounds__(256)
@@ -839,7 +874,7 @@ extern "C" int stof_backward(stof_model *m, const float *x, const float *g_mask,
         lrelu_bwd1_kernel<<<ew_grid(ne), 256, 0, st>>>(ge, e, ne);
         STOF_LAUNCH_CHECK();
         const int parts = N < SGB_PARTS ? N : SGB_PARTS;
-        expand_wgrad_kernel<<<dim3(512, (unsigned)parts), 320, 0, st>>>(ge, pooled, N, P, partial);
+        expand_wgrad_kernel<<<dim3(512 / EW_CI, (unsigned)parts), 320, 0, st>>>(ge, pooled, N, P, partial);
         STOF_LAUNCH_CHECK();
         reduce_parts_kernel<<<(64 * 512 * 5 + 255) / 256, 256, 0, st>>>(partial, parts, (size_t)64 * 512 * 5, gr->expand_w, (size_t)64 * 512 * 5, nullptr);
         STOF_LAUNCH_CHECK();
