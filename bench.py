@@ -468,8 +468,8 @@ def main():
     torch.cuda.set_device(dev)
     if world > 1:
         # rank 0's stdout carries ONE JSON line: keep NCCL's version banner (NCCL_DEBUG=VERSION on some boxes) off it
-        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "WARN"):
+            os.environ.pop("NCCL_DEBUG")
         dist.init_process_group("nccl", device_id=dev)
 
     sd = load_sd()
