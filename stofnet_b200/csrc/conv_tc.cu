@@ -523,8 +523,9 @@ x0_split_kernel(const float *__restrict__ x, const float *__restrict__ e, int N,
         split_pair(v[2], v[3], uh.y, ul.y);
         split_pair(v[4], v[5], uh.z, ul.z);
         split_pair(v[6], v[7], uh.w, ul.w);
-        dst[(size_t)c8 * L] = uh;
-        if (!fast) dst[(size_t)(8 + c8) * L] = ul;
+        // streaming stores: 256 B per position that nothing re-reads before the tensor has passed through L2 many times over
+        __stcs(dst + (size_t)c8 * L, uh);
+        if (!fast) __stcs(dst + (size_t)(8 + c8) * L, ul);
     }
 }
 

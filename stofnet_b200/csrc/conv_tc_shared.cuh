@@ -32,11 +32,13 @@ __device__ __forceinline__ uint32_t cvt_sat_half2(float a, float b) {
     asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
     return r;
 }
-// (v0, v1) -> packed hi = fp16(v), packed lo = fp16((v - hi) * 2^11)
+// (v0, v1) -> packed hi = fp16(v), packed lo = fp16((v - hi) * 2^11); the subtraction and the scaling run as packed fp32 ops
+// (both steps are exact, so the result equals the scalar form bit for bit)
 __device__ __forceinline__ void split_pair(float v0, float v1, uint32_t &hi, uint32_t &lo) {
     hi = cvt_sat_half2(v0, v1);
     const float2 h = __half22float2(*reinterpret_cast<const __half2 *>(&hi));
-    lo = cvt_sat_half2((v0 - h.x) * TC_LO_SCALE, (v1 - h.y) * TC_LO_SCALE);
+    const float2 d = __fmul2_rn(__ffma2_rn(h, make_float2(-1.0f, -1.0f), make_float2(v0, v1)), make_float2(TC_LO_SCALE, TC_LO_SCALE));
+    lo = cvt_sat_half2(d.x, d.y);
 }
 
 // v -> (hi, lo) with hi = fp16(v) (saturated to the finite range), lo = fp16((v - hi) * 2^11)

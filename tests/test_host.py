@@ -116,6 +116,8 @@ def test_abi_argument_validation():
     sz = C.c_size_t()
     assert _lib.lib.stof_forward_workspace_bytes(None, 4, 160, 0, C.byref(sz)) == _lib.E_INVALID
     assert _lib.lib.stof_peaks(None, 1, 1, 20, 0, 0.5, 4, None, None, 0, None, None, None) == _lib.E_INVALID
+    assert _lib.lib.stof_model_set_weights_device(None, C.byref(W), None) == _lib.E_INVALID
+    assert "NULL" in _lib.last_error()
     with pytest.raises(ValueError):
         _lib.check(_lib.E_INVALID)
     with pytest.raises(RuntimeError):
