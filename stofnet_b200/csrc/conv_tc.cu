@@ -460,72 +460,93 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
 // conv1 (1 -> 64, k9) has K = 9: CUDA-core FMAs, HBM-bound (4 B in, 256 B out per position).
 // (models/stofnet.py:23,45 and :96,108-115; K = 3 without E is EDSR_1D's relu(conv_input(x)), models/edsr_1d.py:33)
 // ------------------------------------------------------------------------------------------------
+// Thread = X0_Q positions (256 apart, so that a warp's 16-byte stores stay contiguous) x all 64 channels: every weight vector read
+// from shared memory feeds X0_Q packed FMAs (with one position per thread the kernel waited on shared-memory loads: short-scoreboard
+// stalls 8.9 per issued instruction, 3.6 TB/s of writes; ncu profiles/r8c).
+constexpr int X0_Q = 4;
 template <int K>
 __global__ void __launch_bounds__(256)
 x0_split_kernel(const float *__restrict__ x, const float *__restrict__ e, int N, int L, int P, int scale, int off,
                 const float *__restrict__ w /*[K][64]*/, const float *__restrict__ b, uint4 *__restrict__ planes, int fast) {
     __shared__ float4 ws[K * 16];
     __shared__ float4 bs[16];
-    // E of the (at most 5) pooled positions this block's 256 samples fall into, [slot][64 channels]: one shared-memory
-    // broadcast read per 4 channels instead of 64 scalar global loads per thread
-    __shared__ float4 es[6 * 16];
+    // E of the pooled positions this block's 1,024 samples fall into (at most 14 windows of 80 + 1), [slot][64 channels]: one
+    // shared-memory broadcast read per 4 channels instead of 64 scalar global loads per thread
+    constexpr int SLOTS = 16;
+    __shared__ float4 es[SLOTS * 16];
     const int n = blockIdx.y;
-    const int l0 = blockIdx.x * 256;
+    const int l0 = blockIdx.x * (256 * X0_Q);
     for (int i = threadIdx.x; i < K * 16; i += 256) ws[i] = reinterpret_cast<const float4 *>(w)[i];
     if (threadIdx.x < 16) bs[threadIdx.x] = reinterpret_cast<const float4 *>(b)[threadIdx.x];
     const int j0 = (l0 - off >= 0) ? (l0 - off) / scale : 0;                 // first pooled slot touched by this block
     if (e != nullptr) {
-        for (int i = threadIdx.x; i < 6 * 64; i += 256) {
+        for (int i = threadIdx.x; i < SLOTS * 64; i += 256) {
             const int slot = i >> 6, c = i & 63;
             const int j = j0 + slot;
             reinterpret_cast<float *>(es)[slot * 64 + c] = (j < P) ? __ldg(e + ((size_t)n * 64 + c) * P + j) : 0.0f;
         }
     }
     __syncthreads();
-    const int l = l0 + threadIdx.x;
-    if (l >= L) return;
     const float *xr = x + (size_t)n * L;
-    float xv[K];
+    float xv[X0_Q][K];
+    bool has_e[X0_Q];
+    const float4 *er[X0_Q];
 #pragma unroll
-    for (int t = 0; t < K; ++t) {
-        const int g = l + t - K / 2;
-        xv[t] = (g >= 0 && g < L) ? __ldg(xr + g) : 0.0f;
+    for (int q = 0; q < X0_Q; ++q) {
+        const int l = l0 + 256 * q + threadIdx.x;
+#pragma unroll
+        for (int t = 0; t < K; ++t) {
+            const int g = l + t - K / 2;
+            xv[q][t] = (g >= 0 && g < L) ? __ldg(xr + g) : 0.0f;
+        }
+        const int j = l - off;
+        has_e[q] = (e != nullptr) && j >= 0 && j < scale * P;
+        er[q] = es + (has_e[q] ? (j / scale - j0) : 0) * 16;
     }
-    const int j = l - off;
-    const bool has_e = (e != nullptr) && j >= 0 && j < scale * P;
-    const float4 *er = es + (has_e ? (j / scale - j0) : 0) * 16;
-    uint4 *dst = planes + (size_t)n * 16 * L + l;
-#pragma unroll 2
+    uint4 *dst = planes + (size_t)n * 16 * L + l0 + threadIdx.x;
+#pragma unroll 1
     for (int c8 = 0; c8 < 8; ++c8) {
-        float v[8];
+        float v[X0_Q][8];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             // packed fp32 FMAs (fma.rn.f32x2, bit-identical to fmaf): half the FMA-pipe instructions of this FMA-bound loop
             const float4 bq = bs[2 * c8 + h];
-            float2 a01 = make_float2(bq.x, bq.y), a23 = make_float2(bq.z, bq.w);
+            float2 a01[X0_Q], a23[X0_Q];
+#pragma unroll
+            for (int q = 0; q < X0_Q; ++q) { a01[q] = make_float2(bq.x, bq.y); a23[q] = make_float2(bq.z, bq.w); }
 #pragma unroll
             for (int t = 0; t < K; ++t) {
                 const float4 wv = ws[t * 16 + 2 * c8 + h];
-                const float2 xx = make_float2(xv[t], xv[t]);
-                a01 = __ffma2_rn(make_float2(wv.x, wv.y), xx, a01);
-                a23 = __ffma2_rn(make_float2(wv.z, wv.w), xx, a23);
+#pragma unroll
+                for (int q = 0; q < X0_Q; ++q) {
+                    const float2 xx = make_float2(xv[q][t], xv[q][t]);
+                    a01[q] = __ffma2_rn(make_float2(wv.x, wv.y), xx, a01[q]);
+                    a23[q] = __ffma2_rn(make_float2(wv.z, wv.w), xx, a23[q]);
+                }
             }
-            v[4 * h + 0] = fmaxf(a01.x, 0.f); v[4 * h + 1] = fmaxf(a01.y, 0.f);
-            v[4 * h + 2] = fmaxf(a23.x, 0.f); v[4 * h + 3] = fmaxf(a23.y, 0.f);
-            if (has_e) {
-                const float4 ev = er[2 * c8 + h];
-                v[4 * h + 0] += ev.x; v[4 * h + 1] += ev.y; v[4 * h + 2] += ev.z; v[4 * h + 3] += ev.w;
+#pragma unroll
+            for (int q = 0; q < X0_Q; ++q) {
+                v[q][4 * h + 0] = fmaxf(a01[q].x, 0.f); v[q][4 * h + 1] = fmaxf(a01[q].y, 0.f);
+                v[q][4 * h + 2] = fmaxf(a23[q].x, 0.f); v[q][4 * h + 3] = fmaxf(a23[q].y, 0.f);
+                if (has_e[q]) {
+                    const float4 ev = er[q][2 * c8 + h];
+                    v[q][4 * h + 0] += ev.x; v[q][4 * h + 1] += ev.y; v[q][4 * h + 2] += ev.z; v[q][4 * h + 3] += ev.w;
+                }
             }
         }
-        // (hi, lo) planes with the packed conversions of the chain kernel's epilogue (same rounding and saturation as split_hi_lo)
-        uint4 uh, ul;
-        split_pair(v[0], v[1], uh.x, ul.x);
-        split_pair(v[2], v[3], uh.y, ul.y);
-        split_pair(v[4], v[5], uh.z, ul.z);
-        split_pair(v[6], v[7], uh.w, ul.w);
-        // streaming stores: 256 B per position that nothing re-reads before the tensor has passed through L2 many times over
-        __stcs(dst + (size_t)c8 * L, uh);
-        if (!fast) __stcs(dst + (size_t)(8 + c8) * L, ul);
+#pragma unroll
+        for (int q = 0; q < X0_Q; ++q) {
+            if (l0 + 256 * q + (int)threadIdx.x >= L) continue;
+            // (hi, lo) planes with the packed conversions of the chain kernel's epilogue (same rounding and saturation as split_hi_lo)
+            uint4 uh, ul;
+            split_pair(v[q][0], v[q][1], uh.x, ul.x);
+            split_pair(v[q][2], v[q][3], uh.y, ul.y);
+            split_pair(v[q][4], v[q][5], uh.z, ul.z);
+            split_pair(v[q][6], v[q][7], uh.w, ul.w);
+            // streaming stores: 256 B per position that nothing re-reads before the tensor has passed through L2 many times over
+            __stcs(dst + (size_t)c8 * L + 256 * q, uh);
+            if (!fast) __stcs(dst + (size_t)(8 + c8) * L + 256 * q, ul);
+        }
     }
 }
 
@@ -665,7 +686,8 @@ int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void
 
 int launch_x0_split(const float *x, const float *e, int N, int L, int P, int scale, int off, const float *w, const float *b,
                     void *planes, cudaStream_t st, int fast, int K) {
-    dim3 grid((L + 255) / 256, N);
+    dim3 grid((L + 256 * X0_Q - 1) / (256 * X0_Q), N);
+    STOF_REQUIRE(e == nullptr || scale >= 72, STOF_E_UNSUPPORTED, "x0_split: upsampling factor %d (the shared-memory slot table is sized for >= 72)", scale);
     STOF_REQUIRE(K == 9 || K == 3, STOF_E_UNSUPPORTED, "x0_split: first conv kernel size %d (built for 9 and 3)", K);
     if (K == 9) x0_split_kernel<9><<<grid, 256, 0, st>>>(x, e, N, L, P, scale, off, w, b, reinterpret_cast<uint4 *>(planes), fast);
     else x0_split_kernel<3><<<grid, 256, 0, st>>>(x, e, N, L, P, scale, off, w, b, reinterpret_cast<uint4 *>(planes), fast);
