@@ -41,7 +41,7 @@ constexpr int TC_OFF_W = 2 * TC_BUF;
 constexpr int TC_OFF_BIAS = TC_OFF_W + TC_STAGES * TC_STAGE_BYTES;          // [TC_MAX_LAYERS][64] fp32
 constexpr int TC_OFF_BAR = TC_OFF_BIAS + TC_MAX_LAYERS * 64 * 4;
 // barriers (8 B each): w_full[STAGES] w_empty[STAGES] acc_full[2] acc_empty[2] act_ready[TC_MAX_LAYERS][2] in_full p_free
-constexpr int TC_NBAR = 2 * TC_MAX_STAGES + 4 + 2 * TC_MAX_LAYERS + 2;
+constexpr int TC_NBAR = 2 * TC_MAX_STAGES + 4 + 2 * TC_MAX_LAYERS + 4;       // ... in_full[2] p_free[2]
 constexpr int TC_OFF_TMEM = TC_OFF_BAR + TC_NBAR * 8;
 constexpr int TC_SMEM_BYTES = TC_OFF_TMEM + 16;
 
@@ -109,7 +109,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
     auto BAR_ACC_FULL = [&](int b) { return bar0 + 8 * (2 * TC_MAX_STAGES + b); };
     auto BAR_ACC_EMPTY = [&](int b) { return bar0 + 8 * (2 * TC_MAX_STAGES + 2 + b); };
     auto BAR_ACT = [&](int k, int b) { return bar0 + 8 * (2 * TC_MAX_STAGES + 4 + 2 * k + b); };
-    const uint32_t BAR_IN_FULL = bar0 + 8 * (2 * TC_MAX_STAGES + 4 + 2 * TC_MAX_LAYERS);
+    // Input buffer(s): a one-layer segment never touches buffer Q, so it alternates its tiles' inputs between P and Q and the next
+    // tile's load runs behind the whole current tile (p.dbl; barriers per buffer: a single one could run two phases ahead of a
+    // parity wait).  Otherwise buffer P only, barrier set 0.
+    const uint32_t BAR_IN_FULL0 = bar0 + 8 * (2 * TC_MAX_STAGES + 4 + 2 * TC_MAX_LAYERS);
+    const bool dbl = (p.dbl != 0);
+    auto in_sel = [&](int j) { return dbl ? (j & 1) : 0; };                         // input buffer / barrier set of this CTA's j-th tile
+    auto in_phase = [&](int j) { return (uint32_t)(dbl ? (j >> 1) : j) & 1u; };     // parity of that buffer's phase for tile j
+    auto BAR_IN_FULL_OF = [&](int sel) { return BAR_IN_FULL0 + 16u * (uint32_t)sel; };
+    auto BAR_P_FREE_OF = [&](int sel) { return BAR_IN_FULL0 + 8u + 16u * (uint32_t)sel; };
+    const uint32_t BAR_IN_FULL = BAR_IN_FULL0;
     constexpr int n_stages = FAST ? TC_MAX_STAGES : TC_STAGES;          // weight ring depth / stage stride
     constexpr uint32_t stage_stride = FAST ? TC_STAGE_BYTES / 2 : TC_STAGE_BYTES;
     const uint32_t BAR_P_FREE = BAR_IN_FULL + 8;
@@ -134,8 +143,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
             mbar_init(BAR_ACT(k, 0), TC_EPI_WARPS);
             mbar_init(BAR_ACT(k, 1), TC_EPI_WARPS);
         }
-        mbar_init(BAR_IN_FULL, 1);
-        mbar_init(BAR_P_FREE, TC_EPI_WARPS);
+        for (int sel = 0; sel < 2; ++sel) {
+            mbar_init(BAR_IN_FULL_OF(sel), 1);
+            mbar_init(BAR_P_FREE_OF(sel), TC_EPI_WARPS);
+        }
         fence_mbar_init();
     }
     if (warp == 1) tmem_alloc(sbase + TC_OFF_TMEM, 512);
@@ -155,14 +166,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
         auto issue_input = [&](int tile, int j) {
             const int n = tile / p.tiles_per_row;
             const int l_org = (tile - n * p.tiles_per_row) * p.t_out - p.l_shift;
-            if (j > 0) mbar_wait(BAR_P_FREE, (uint32_t)(j - 1) & 1u);
+            const int sel = in_sel(j);
+            const uint32_t in_off = sel ? TC_OFF_Q : TC_OFF_P;
+            const uint32_t bar_in = BAR_IN_FULL_OF(sel);
+            // the buffer's previous tile (j - 1, or j - 2 when the tiles alternate) no longer touches it
+            if (dbl) { if (j > 1) mbar_wait(BAR_P_FREE_OF(sel), in_phase(j - 2)); }
+            else if (j > 0) mbar_wait(BAR_P_FREE, (uint32_t)(j - 1) & 1u);
             if (lane == 0) TL(0u, 0, 0, 1);
             const int r_lo = max(0, -l_org), r_hi = min(r_in, p.L - l_org);
             const int nslab = FAST ? 8 : 16;               // one-pass fp16 mode: hi plane only
             // rows outside the waveform are the conv's zero padding (only tiles at the ends of a row have any)
             if (r_lo > 0 || r_hi < r_in) {
                 for (int slab = 0; slab < nslab; ++slab) {
-                    uint8_t *sl = smem + TC_OFF_P + slab * TC_SLAB;
+                    uint8_t *sl = smem + in_off + slab * TC_SLAB;
                     for (int r = lane; r < r_lo; r += 32) *reinterpret_cast<uint4 *>(sl + r * 16) = make_uint4(0, 0, 0, 0);
                     for (int r = r_hi + lane; r < r_in; r += 32) *reinterpret_cast<uint4 *>(sl + r * 16) = make_uint4(0, 0, 0, 0);
                 }
@@ -171,11 +187,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
             __syncwarp();
             if (lane == 0) {
                 const uint32_t bytes = (uint32_t)(r_hi - r_lo) * 16u;
-                mbar_arrive_expect_tx(BAR_IN_FULL, bytes * (uint32_t)nslab);
+                mbar_arrive_expect_tx(bar_in, bytes * (uint32_t)nslab);
                 const __half *src = reinterpret_cast<const __half *>(p.in) + (size_t)n * 16 * p.L * 8;
                 for (int slab = 0; slab < nslab; ++slab)
-                    bulk_g2s(sbase + TC_OFF_P + slab * TC_SLAB + r_lo * 16, src + ((size_t)slab * p.L + l_org + r_lo) * 8, bytes,
-                             BAR_IN_FULL);
+                    bulk_g2s(sbase + in_off + slab * TC_SLAB + r_lo * 16, src + ((size_t)slab * p.L + l_org + r_lo) * 8, bytes, bar_in);
             }
             __syncwarp();
         };
@@ -231,13 +246,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
         int it = 0;
         for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
             if (tl_on) TL(role, 0, b, 1);
-            mbar_wait(BAR_IN_FULL, (uint32_t)(it & 1));
+            mbar_wait(BAR_IN_FULL_OF(in_sel(it)), in_phase(it));
             tc_fence_after_sync();
             if (tl_on) TL(role, 0, b, 2);
             for (int k = 0; k < n_layers; ++k, ++lseq) {
                 const TcLayer &ly = p.layer[k];
                 const int taps = ly.taps;
-                const uint32_t a_base = (((sbase + ((k & 1) ? TC_OFF_Q : TC_OFF_P)) >> 4) | kALoBase) +
+                const uint32_t a_base = (((sbase + (((k & 1) ^ in_sel(it)) ? TC_OFF_Q : TC_OFF_P)) >> 4) | kALoBase) +
                                         (uint32_t)(p.b_row[k] - ly.pad + 128 * b);
                 if (tl_on) TL(role, k, b, 3);
                 mbar_wait(BAR_ACC_EMPTY(b), (lseq & 1u) ^ 1u);
@@ -308,7 +323,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                         // both blocks' MMAs of the last layer that reads buffer P have completed, and this layer's epilogue does
                         // not touch P (its output goes to Q / global, no TMEM stash): hand P to the producer before the epilogue
                         // math, so the next tile's input load overlaps it
-                        if (lane == 0) mbar_arrive(BAR_P_FREE);
+                        if (lane == 0) mbar_arrive(BAR_P_FREE_OF(in_sel(it)));
                     }
                     const uint32_t d_tmem = tmem0 + (uint32_t)b * 128u + lane_addr;
                     const uint32_t stash = tmem0 + 256u + 64u * (uint32_t)b + 32u * (uint32_t)egrp + lane_addr;
@@ -673,6 +688,10 @@ int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void
     // exact mode: the producer asks for the next tile's input after tap STAGES-2 of the last layer (tuned on the timeline);
     // one-pass mode (deep ring): after the tile's last tap
     p.in_tap = (!fast && even && layers[count - 1].taps > TC_STAGES - 1) ? TC_STAGES - 2 : layers[count - 1].taps - 1;
+    // one layer per launch (the training step keeps every activation): buffer Q is idle, so the tiles' inputs alternate between P
+    // and Q; the next tile's load is requested after the current tile's last tap (in_tap above: the producer is then up to a ring
+    // of taps ahead of the MMAs, so the load runs behind the rest of the tile's MMAs and its epilogue)
+    p.dbl = (count == 1) ? 1 : 0;
     for (int k = 0; k < count; ++k)
         STOF_REQUIRE(layers[k].taps >= 1, STOF_E_INVALID, "chain_tc: layer without taps");
     const bool ends_last = layers[count - 1].type == TC_LAST;

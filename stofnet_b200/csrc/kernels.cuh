@@ -58,6 +58,7 @@ struct TcParams {
     int t_out;                  // valid output positions per tile
     int free_layer;             // layer after whose epilogue the input buffer P is no longer touched by the tile
     int stash;                  // 1: the last layer's short skip is parked in TMEM by the epilogue of layer n_layers-2
+    int dbl;                    // 1: one-layer segment, the tiles' inputs alternate between buffers P and Q
     int in_layer, in_tap;       // the producer requests the next tile's input after issuing this weight tap
     int tiles_per_row, total_tiles;
     int N, L;
