@@ -151,3 +151,42 @@ def test_c2_bench_batch_slice(sb, dev, golden):
         assert_index_parity(sd, x, idx, ref_idx, bench.TH, ref_masks32=ref, what="bench batch slice")
     co = sb.mask2coords(m, 20, bench.TH, upsample_factor=4)
     print("bench batch: K_max = %d over %d rows (bench.py widens its table from CAP=%d when needed)" % (co.shape[1], bench.ROWS, bench.CAP))
+
+
+@pytest.mark.parametrize("name,th", [("wobbly-sponge", 0.2), ("vital-puddle", 0.2)])
+def test_espcn_baseline_shape_vs_port(sb, dev, golden, name, th):
+    """ESPCN_1D (the checkpoint BASELINE config 2 names is one) on the tensor-core kernel at the C2 shape, 256 rows x seeds
+    {3008, 0, 1}, against the reference's call sequence on this box's CPU (oracle/torch_port.espcn_forward): masks within 2e-5
+    (sigmoid outputs); index lists identical, or the differing sample within fp32 rounding of a decision boundary when judged by
+    the fp64 re-run (tolerance 4 x the port's own fp32-vs-fp64 distance on that row, as tests/parity_util.py)."""
+    from oracle import torch_port
+    from stofnet_b200.synth import synth_waveforms
+    sd = to_sd(golden("weights_%s.npz" % name))
+    sd64 = {k: v.double() for k, v in sd.items()}
+    model = sb.build_model(sd, dev)
+    total = flips = 0
+    for seed in SEEDS:
+        x = synth_waveforms(ROWS, 5120, seed=seed, rf=20, q15=True)
+        xt = torch.from_numpy(x).unsqueeze(1)
+        with torch.no_grad():
+            got = model(xt.to(dev))
+            ref = torch_port.espcn_forward(sd, xt)
+        assert float((got.cpu() - ref).abs().max()) <= 2e-5
+        idx = sb.get_maxima_positions(got, 20, th).cpu().numpy()
+        ref_idx = torch_port.get_maxima_positions(ref, 20, th).numpy()
+        total += len(ref_idx)
+        diff = sorted(set(map(tuple, idx.tolist())) ^ set(map(tuple, ref_idx.tolist())))
+        if diff:
+            rows = sorted({r for r, _ in diff})
+            with torch.no_grad():
+                m64 = torch_port.espcn_forward(sd64, xt[rows].double()).squeeze(1).numpy()
+            m32 = ref.squeeze(1).numpy()[rows]
+            for r, pos in diff:
+                k = rows.index(r)
+                tol = max(4.0 * float(np.abs(m32[k].astype(np.float64) - m64[k]).max()), 8 * np.finfo(np.float32).eps)
+                lo, hi = max(0, pos - 10), min(m64.shape[1], pos + 11)
+                others = np.delete(m64[k][lo:hi], pos - lo)
+                margin = min(abs(m64[k][pos] - th), abs(m64[k][pos] - others.max()) if others.size else np.inf)
+                assert margin <= tol, (name, seed, r, pos, float(margin), tol)
+            flips += len(diff)
+    print("espcn %s: %d detections over %d rows, %d boundary flips" % (name, total, ROWS * len(SEEDS), flips))
