@@ -64,7 +64,9 @@ constexpr float ET_TANH_SCALE = 2.885390081777927f;        // 2 log2(e)
 constexpr float ET_SIGM_SCALE = -1.4426950408889634f;      // -log2(e)
 // (A tanhf-like variant - polynomial a P(a^2) below |v| = 0.55 for relative accuracy near zero, selected against the ex2 form -
 // was measured: 12 instead of 5 instructions per tanh, forward 1.96 -> 2.53 ms, and NO change of the final mask error, which is
-// set by the 22-bit hi/lo operands of the two tensor-core convolutions, not by the activations.)
+// set by the 22-bit hi/lo operands of the two tensor-core convolutions, not by the activations.  Sharing one reciprocal between
+// two tanh - 1 / (1 + ea) = (1 + eb) / ((1 + ea)(1 + eb)): three MUFU operations instead of four, four more FP32 instructions per
+// pair - was measured too: 1.815 -> 1.795 ms, within noise of a wash between the MUFU and the issue floors; not kept.)
 __device__ __forceinline__ float tanh_scaled(float a) {
     float e, r;
     asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(a));
