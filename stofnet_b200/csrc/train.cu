@@ -55,9 +55,15 @@ static int make_train_plan(const stof_model *m, int N, int L, TrainPlan *p) {
     p->P = p->sgb ? L / m->sgb_scale : 0;
     p->act = a64((size_t)N * 64 * L);
     size_t o = 0;
+    p->tc = (m->path != STOF_PATH_SIMT);
     p->off_x0r = o; o += p->act;
-    if (p->sgb) { p->off_x0 = o; o += p->act; } else p->off_x0 = p->off_x0r;
-    for (int j = 0; j < m->n_mid; ++j) { p->off_a[j] = o; o += p->act; }
+    // the tensor-core path keeps x0 and the mid activations as planes (below); in fp32 it needs x0r and the last activation only
+    if (p->sgb && !p->tc) { p->off_x0 = o; o += p->act; } else p->off_x0 = p->off_x0r;
+    for (int j = 0; j < m->n_mid; ++j) {
+        p->off_a[j] = o;
+        if (!p->tc || j == m->n_mid - 1) o += p->act;
+    }
+    if (p->tc) for (int j = 0; j < m->n_mid - 1; ++j) p->off_a[j] = p->off_a[m->n_mid - 1];     // never read on that path
     for (int i = 0; i < 3; ++i) { p->off_g[i] = o; o += p->act; }
     const size_t np = a64((size_t)N * 512 * p->P), ne = a64((size_t)N * 64 * p->P);
     p->off_pooled = o; o += p->sgb ? np : 0;
@@ -71,7 +77,6 @@ static int make_train_plan(const stof_model *m, int N, int L, TrainPlan *p) {
     if (m->path != STOF_PATH_SIMT && a64(wgrad_tc_scratch_floats()) > p->partial_floats) p->partial_floats = a64(wgrad_tc_scratch_floats());
     if (p->sgb && a64((size_t)SGB_PARTS * (512 * 64 * 5 + 512)) > p->partial_floats) p->partial_floats = a64((size_t)SGB_PARTS * (512 * 64 * 5 + 512));
     p->off_partial = o; o += p->partial_floats;
-    p->tc = (m->path != STOF_PATH_SIMT);
     if (p->tc) {
         p->off_px0 = o; o += p->act;
         for (int j = 0; j < m->n_mid; ++j) { p->off_pa[j] = o; o += p->act; }
