@@ -377,6 +377,11 @@ def other_configs(sb, dev, rank, world, cpu):
             gt = torch.from_numpy(rng.integers(100, 4 * 2560 - 100, size=(rows, 1, 3))).to(dev)
             ms = dev_ms(lambda: tr.step(x, gt), 2, 5)
             res["batch_%d" % rows] = {"ms_per_step": ms, "rows_per_s": rows * world / (ms / 1e3)}
+            if world == 1:
+                # the same step replayed from ONE CUDA graph (Trainer.capture): what is left when the ~140 launches cost no host time
+                tr.capture(x, gt)
+                ms = dev_ms(lambda: tr.step_graph(x, gt), 3, 10)
+                res["batch_%d" % rows]["cuda_graph"] = {"ms_per_step": ms, "rows_per_s": rows / (ms / 1e3)}
             del tr, model
         if cpu:
             res["cpu_port"] = cpu_train_rate(sd_arm, syn, threads)

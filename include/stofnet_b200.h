@@ -83,6 +83,9 @@ int stof_model_set_weights(stof_model *m, const stof_weights *w);
  * synchronisation; ordered after the optimizer kernel on the same stream).  StofNet only.  The fp16 operand packs of the
  * tensor-core inference kernels are rebuilt on the next inference call (one device-to-host copy there).                  */
 int stof_model_set_weights_device(stof_model *m, const stof_weights *w_dev, void *stream);
+/* Host-side bookkeeping of the above without a launch: for a training step replayed from a CUDA graph (the graph holds the
+ * repack kernel; the handle must still learn that the tensor-core inference packs are stale).                             */
+int stof_model_mark_weights_changed(stof_model *m);
 void stof_model_destroy(stof_model *m);
 
 /* Rows processed per internal chunk and the workspace this needs.  chunk_rows <= 0 picks a default. */
@@ -314,6 +317,11 @@ int stof_backward(stof_model *m, const float *x_dev, const float *g_mask_dev, in
  *   p -= lr / (1 - b1^step) * m / (sqrt(v) / sqrt(1 - b2^step) + eps)            step counts from 1                    */
 int stof_adamw_step(float *params_dev, const float *grads_dev, float *exp_avg_dev, float *exp_avg_sq_dev, size_t n, int step,
                     float lr, float beta1, float beta2, float eps, float weight_decay, void *stream);
+/* The same with the scalars in DEVICE memory, hyper_dev[7] = {lr, beta1, beta2, eps, weight_decay, 1 - beta1^step,
+ * sqrt(1 - beta2^step)}: nothing step-dependent is baked into the launch, so the whole training step can be captured once in
+ * a CUDA graph and replayed (copy the seven floats in before each replay).                                                */
+int stof_adamw_step_dev(float *params_dev, const float *grads_dev, float *exp_avg_dev, float *exp_avg_sq_dev, size_t n,
+                        const float *hyper_dev, void *stream);
 
 #ifdef __cplusplus
 }

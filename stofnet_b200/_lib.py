@@ -87,6 +87,8 @@ _SIGS = {
     "stof_forward_train": (_i, [_vp, _vp, _i, _i, _vp, _vp, _sz, _vp]),
     "stof_backward": (_i, [_vp, _vp, _vp, _i, _i, _vp, _sz, C.POINTER(Grads), _vp]),
     "stof_adamw_step": (_i, [_vp, _vp, _vp, _vp, _sz, _i, _f, _f, _f, _f, _f, _vp]),
+    "stof_adamw_step_dev": (_i, [_vp, _vp, _vp, _vp, _sz, _vp, _vp]),
+    "stof_model_mark_weights_changed": (_i, [_vp]),
     "stof_thresholding": (_i, [_vp, _i, _i, _i, _f, _vp, _vp]),
     "stof_get_amplitudes": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "stof_reduce_echoes_pairs": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),

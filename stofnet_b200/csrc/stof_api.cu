@@ -873,6 +873,14 @@ extern "C" int stof_model_set_weights_device(stof_model *m, const stof_weights *
     return stof::set_weights_device(m, w_dev, (cudaStream_t)stream);
 }
 
+extern "C" int stof_model_mark_weights_changed(stof_model *m) {
+    STOF_REQUIRE(m != nullptr, STOF_E_INVALID, "stof_model_mark_weights_changed: model is NULL");
+    m->tc_dirty = true;
+    m->tr_tc_dirty = true;
+    m->host_stale = true;
+    return STOF_OK;
+}
+
 extern "C" int stof_model_set_path(stof_model *m, int path, int layers_per_launch) {
     STOF_REQUIRE(m != nullptr, STOF_E_INVALID, "stof_model_set_path: model is NULL");
     STOF_REQUIRE(path == STOF_PATH_SIMT || path == STOF_PATH_TC || path == STOF_PATH_TC_FP16, STOF_E_INVALID,

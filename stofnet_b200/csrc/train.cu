@@ -594,6 +594,24 @@ adamw_kernel(float *__restrict__ p, const float *__restrict__ g, float *__restri
     }
 }
 
+// the same with the step-dependent scalars in device memory: h = {lr, beta1, beta2, eps, weight_decay, 1 - beta1^step, sqrt(1 - beta2^step)}
+__global__ void __launch_bounds__(256)
+adamw_dev_kernel(float *__restrict__ p, const float *__restrict__ g, float *__restrict__ m, float *__restrict__ v, size_t n,
+                 const float *__restrict__ h) {
+    const float lr = __ldg(h), b1 = __ldg(h + 1), b2 = __ldg(h + 2), eps = __ldg(h + 3), wd = __ldg(h + 4), bc1 = __ldg(h + 5),
+                bc2_sqrt = __ldg(h + 6);
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (size_t)gridDim.x * 256) {
+        const float gi = g[i];
+        float pi = p[i] * (1.0f - lr * wd);
+        const float mi = m[i] + (1.0f - b1) * (gi - m[i]);
+        const float vi = b2 * v[i] + (1.0f - b2) * gi * gi;
+        m[i] = mi; v[i] = vi;
+        const float denom = sqrtf(vi) / bc2_sqrt + eps;
+        pi -= (lr / bc1) * (mi / denom);
+        p[i] = pi;
+    }
+}
+
 }  // namespace stof
 
 using namespace stof;
@@ -923,6 +941,15 @@ extern "C" int stof_adamw_step(float *params_dev, const float *grads_dev, float 
     const double bc2 = 1.0 - pow((double)beta2, (double)step);
     adamw_kernel<<<ew_grid(n), 256, 0, (cudaStream_t)stream>>>(params_dev, grads_dev, exp_avg_dev, exp_avg_sq_dev, n, lr, beta1, beta2, eps,
                                                               weight_decay, (float)bc1, (float)sqrt(bc2));
+    STOF_LAUNCH_CHECK();
+    return STOF_OK;
+}
+
+extern "C" int stof_adamw_step_dev(float *params_dev, const float *grads_dev, float *exp_avg_dev, float *exp_avg_sq_dev, size_t n,
+                                   const float *hyper_dev, void *stream) {
+    STOF_REQUIRE(params_dev && grads_dev && exp_avg_dev && exp_avg_sq_dev && hyper_dev && n > 0, STOF_E_INVALID,
+                 "stof_adamw_step_dev: bad arguments (n=%zu)", n);
+    adamw_dev_kernel<<<ew_grid(n), 256, 0, (cudaStream_t)stream>>>(params_dev, grads_dev, exp_avg_dev, exp_avg_sq_dev, n, hyper_dev);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }

@@ -14,6 +14,7 @@ batch-wide maximum) is MAX-all-reduced first so that every rank sees the single-
 """
 import math
 
+import numpy as np
 import torch
 import torch.distributed as dist
 
@@ -80,6 +81,10 @@ class Trainer:
     def step(self, frame, gt_true, lr=None):
         """One optimisation step on this rank's rows.  frame (N,1,L) fp32 CUDA, gt_true (N,1,G) int64 mask indices
         (main.py:218).  Returns the (global-mean) loss as a 0-dim fp64 CUDA tensor."""
+        self.step_count += 1
+        return self._step_impl(frame, gt_true, float(self.lr if lr is None else lr), None)
+
+    def _step_impl(self, frame, gt_true, lr, hyper_dev):
         model, eng = self.model, self.model._engine
         mask, xc, ws = eng.forward_train(model, frame)
         mx = global_blur_max(blur_max(gt_true, mask.shape[-1], self.gauss), self.group)
@@ -91,13 +96,64 @@ class Trainer:
         if w > 1:
             dist.all_reduce(loss, op=dist.ReduceOp.SUM, group=self.group)
             loss = loss / w
-        self.step_count += 1
         with torch.cuda.device(self.device):
-            check(lib.stof_adamw_step(self.flat.data_ptr(), grads.data_ptr(), self.exp_avg.data_ptr(),
-                                      self.exp_avg_sq.data_ptr(), self.flat.numel(), self.step_count,
-                                      float(self.lr if lr is None else lr), float(self.betas[0]), float(self.betas[1]),
-                                      float(self.eps), float(self.weight_decay), stream_ptr(self.device)))
+            if hyper_dev is None:
+                check(lib.stof_adamw_step(self.flat.data_ptr(), grads.data_ptr(), self.exp_avg.data_ptr(),
+                                          self.exp_avg_sq.data_ptr(), self.flat.numel(), self.step_count, lr,
+                                          float(self.betas[0]), float(self.betas[1]), float(self.eps), float(self.weight_decay),
+                                          stream_ptr(self.device)))
+            else:
+                check(lib.stof_adamw_step_dev(self.flat.data_ptr(), grads.data_ptr(), self.exp_avg.data_ptr(),
+                                              self.exp_avg_sq.data_ptr(), self.flat.numel(), hyper_dev.data_ptr(),
+                                              stream_ptr(self.device)))
         # parameters changed in place through the flat buffer: the kernels' layouts follow on the device, same stream
         eng.sync_device(model, self.device)
         self.last_grads = grads
         return loss.reshape(())
+
+    # -- the whole step as ONE CUDA graph --------------------------------------------------------------------------------
+    def capture(self, frame, gt_true):
+        """Capture forward + loss + backward + AdamW + weight re-layout for batches of this shape in a CUDA graph (single
+        process).  At the reference's batch size of 4 (config.yaml:11) the step is ~140 small launches and launch-bound;
+        replaying the graph removes the per-launch host cost.  Nothing step-dependent is baked in: the inputs are copied
+        into static buffers and the AdamW scalars (lr, bias corrections) into a 7-float device buffer before each replay."""
+        if _world(self.group) > 1:
+            raise RuntimeError("stofnet_b200: Trainer.capture supports single-process training (no collective in the graph)")
+        dev = self.device
+        self._g_frame, self._g_gt = frame.detach().clone(), gt_true.detach().clone()
+        self._g_hyper = torch.zeros((8,), dtype=torch.float32, device=dev)
+        # the warm-up steps are real optimizer steps: snapshot the training state and put it back afterwards
+        snap = (self.flat.clone(), self.exp_avg.clone(), self.exp_avg_sq.clone(), self.step_count)
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):                                    # warm-up: every lazy allocation happens here
+            for _ in range(2):
+                self._fill_hyper(self.lr)
+                self._step_impl(self._g_frame, self._g_gt, self.lr, self._g_hyper)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self._graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._graph):
+            self._g_loss = self._step_impl(self._g_frame, self._g_gt, self.lr, self._g_hyper)
+        self.flat.copy_(snap[0]); self.exp_avg.copy_(snap[1]); self.exp_avg_sq.copy_(snap[2]); self.step_count = snap[3]
+        self.model._engine.sync_device(self.model, dev)
+        return self
+
+    def _fill_hyper(self, lr):
+        self.step_count += 1
+        # the bias corrections exactly as stof_adamw_step forms them: pow() in double of the FLOAT betas
+        b1, b2 = float(np.float32(self.betas[0])), float(np.float32(self.betas[1]))
+        # a fresh pinned block per step: the caching host allocator keeps it alive until the asynchronous copy has run
+        h = torch.tensor([float(lr), b1, b2, float(self.eps), float(self.weight_decay), 1.0 - b1 ** self.step_count,
+                          math.sqrt(1.0 - b2 ** self.step_count), 0.0], dtype=torch.float32).pin_memory()
+        self._g_hyper.copy_(h, non_blocking=True)
+
+    def step_graph(self, frame, gt_true, lr=None):
+        """Replay the captured step on a new batch of the captured shape; returns the loss (a static 0-dim CUDA tensor that
+        the next replay overwrites)."""
+        self._fill_hyper(self.lr if lr is None else lr)
+        self._g_frame.copy_(frame, non_blocking=True)
+        self._g_gt.copy_(gt_true, non_blocking=True)
+        self._graph.replay()
+        check(lib.stof_model_mark_weights_changed(self.model._engine.handle))
+        return self._g_loss
