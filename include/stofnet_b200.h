@@ -229,6 +229,18 @@ size_t stof_loss_scratch_bytes(int N, int M);
 int stof_mask_loss(const float *pred_dev, const int64_t *samples_dev, int N, int G, int M, const float *gauss_dev, int k,
                    float amplitude, float lambda, int mode, float *blur_max_io_dev, double *loss_dev, float *grad_dev,
                    void *scratch_dev, void *stream);
+/* The same loss for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc): no scratch argument - the partial sums live in a 256 KB file-scope device array inside the library (held by
+ * every GPU that loads it until the process exits), and the call performs no cudaMalloc / cudaFree or any allocating
+ * routine.  No counterpart in the reference.
+ *   limit: N * ceil(M / 4096) <= 16384, else STOF_E_UNSUPPORTED (use stof_mask_loss with your own scratch buffer)
+ *   the device that owns the buffers must be current (as for every entry point here); its ordinal must be < 64
+ *   every call on a device shares the array: calls that overlap on the GPU (different streams) race - serialise them.
+ *   Nothing in it needs clearing between calls (every slot the final sum reads is rewritten first).
+ *   Results are bit-identical to stof_mask_loss; all other arguments and the modes are the same.                       */
+int stof_mask_loss_static(const float *pred_dev, const int64_t *samples_dev, int N, int G, int M, const float *gauss_dev,
+                          int k, float amplitude, float lambda, int mode, float *blur_max_io_dev, double *loss_dev,
+                          float *grad_dev, void *stream);
 
 /* Replaces find_threshold (utils/threshold.py:6-28; sklearn.metrics.roc_curve on batch element 0, main.py:330):
  * clamp negatives (or min-max normalise over the WHOLE batch when norm_opt), ROC of row 0 with drop_intermediate,

@@ -80,6 +80,7 @@ _SIGS = {
     "stof_reduce_echoes": (_i, [_vp, _i, _i, _vp, _i, _i, _i, _f, _vp, _vp]),
     "stof_loss_scratch_bytes": (_sz, [_i, _i]),
     "stof_mask_loss": (_i, [_vp, _vp, _i, _i, _i, _vp, _i, _f, _f, _i, _vp, _vp, _vp, _vp, _vp]),
+    "stof_mask_loss_static": (_i, [_vp, _vp, _i, _i, _i, _vp, _i, _f, _f, _i, _vp, _vp, _vp, _vp]),
     "stof_threshold_scratch_bytes": (_sz, [_i, _i]),
     "stof_find_threshold": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "stof_rf_upscale": (_i, [_vp, _vp, _i, _i, _d, _d, _d, _vp, _vp]),

@@ -329,3 +329,50 @@ extern "C" int stof_mask_loss(const float *pred_dev, const int64_t *samples_dev,
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------------
+// stof_mask_loss_static: the mask loss with its per-(row, 4096-column chunk) partial sums in a file-scope device array instead
+// of a caller-provided scratch buffer, for callers that cannot allocate (code under CUDA graph capture, serving loops,
+// harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The array is 256 KB per GPU that loads the library, held until the process exits.  Nothing in it has to start at zero: the
+// loss kernel writes every slot [0, N * chunks) that the final fixed-order sum reads, so the previous call's contents are
+// simply overwritten.  All calls on a device share it: calls that overlap on the GPU (two streams) race.
+constexpr int LOSS_STATIC_MAX_BLOCKS = 16384;                 // N * ceil(M / 4096) of one call
+constexpr int LOSS_STATIC_MAX_DEVICES = 64;
+static __device__ __align__(256) double g_loss_partial_static[2 * LOSS_STATIC_MAX_BLOCKS];
+
+// In host code `g_loss_partial_static` is only a handle for the runtime, not a device address: resolve it once per device, with
+// that device current.  cudaGetSymbolAddress looks the symbol up in the already-loaded module; it allocates nothing.
+static int loss_static_scratch(double **out) {
+    static std::atomic<double *> ptrs[LOSS_STATIC_MAX_DEVICES];
+    int dev = -1;
+    STOF_CUDA(cudaGetDevice(&dev));
+    STOF_REQUIRE(dev >= 0 && dev < LOSS_STATIC_MAX_DEVICES, STOF_E_UNSUPPORTED,
+                 "stof_mask_loss_static: device ordinal %d outside [0, %d)", dev, LOSS_STATIC_MAX_DEVICES);
+    double *p = ptrs[dev].load(std::memory_order_acquire);
+    if (p == nullptr) {
+        void *sym = nullptr;
+        STOF_CUDA(cudaGetSymbolAddress(&sym, g_loss_partial_static));
+        STOF_REQUIRE(sym != nullptr, STOF_E_CUDA, "stof_mask_loss_static: cudaGetSymbolAddress returned NULL on device %d", dev);
+        p = static_cast<double *>(sym);
+        ptrs[dev].store(p, std::memory_order_release);       // two first callers resolve the same address: benign
+    }
+    *out = p;
+    return STOF_OK;
+}
+
+extern "C" int stof_mask_loss_static(const float *pred_dev, const int64_t *samples_dev, int N, int G, int M,
+                                     const float *gauss_dev, int k, float amplitude, float lambda, int mode,
+                                     float *blur_max_io_dev, double *loss_dev, float *grad_dev, void *stream) {
+    STOF_REQUIRE(N > 0 && M > 0, STOF_E_INVALID, "stof_mask_loss_static: bad arguments (N=%d M=%d)", N, M);
+    const long long blocks = (long long)N * ((M + LOSS_CHUNK - 1) / LOSS_CHUNK);
+    STOF_REQUIRE(blocks <= LOSS_STATIC_MAX_BLOCKS, STOF_E_UNSUPPORTED,
+                 "stof_mask_loss_static: N * ceil(M / %d) = %lld exceeds the static scratch of %d blocks (N=%d M=%d); "
+                 "use stof_mask_loss with a caller-provided scratch buffer", LOSS_CHUNK, blocks, LOSS_STATIC_MAX_BLOCKS, N, M);
+    double *scratch = nullptr;
+    const int rc = loss_static_scratch(&scratch);
+    if (rc != STOF_OK) return rc;
+    // same launches as stof_mask_loss (a 4-byte cudaMemsetAsync + three kernels): no cudaMalloc / cudaFree anywhere
+    return stof_mask_loss(pred_dev, samples_dev, N, G, M, gauss_dev, k, amplitude, lambda, mode, blur_max_io_dev, loss_dev,
+                          grad_dev, scratch, stream);
+}
