@@ -593,28 +593,103 @@ c4l4_to_planes_kernel(const float4 *__restrict__ act, uint4 *__restrict__ planes
     planes[((size_t)n * 16 + 8 + c8) * L + l] = ul;
 }
 
+// EX: the gradient hand-over of the training step (train.cu) - v *= lrelu'(a) with a given as split planes (a > 0 <=> its hi plane
+// is positive, or zero with a positive lo plane), and max |written value| folded into *absmax_out (the scale of the NEXT plane
+// conversion of this tensor: saves a pass over it)
+template <bool EX>
 __global__ void __launch_bounds__(256)
 planes_to_c4l4_kernel(const uint4 *__restrict__ planes, float4 *__restrict__ act, int N, int L, const unsigned *__restrict__ absmax_bits,
-                      int add) {
+                      int add, const uint4 *__restrict__ lrelu_planes, unsigned *__restrict__ absmax_out) {
     const int n = blockIdx.z, c8 = blockIdx.y;
     const int l = blockIdx.x * 256 + threadIdx.x;
-    if (l >= L) return;
-    const float inv = 1.0f / plane_scale(absmax_bits);           // exact: a power of two
-    float fh[8], fl[8];
-    unpack8(planes[((size_t)n * 16 + c8) * L + l], fh);
-    unpack8(planes[((size_t)n * 16 + 8 + c8) * L + l], fl);
-    float v[8];
+    float m = 0.0f;
+    if (l < L) {
+        const float inv = 1.0f / plane_scale(absmax_bits);           // exact: a power of two
+        float fh[8], fl[8];
+        unpack8(planes[((size_t)n * 16 + c8) * L + l], fh);
+        unpack8(planes[((size_t)n * 16 + 8 + c8) * L + l], fl);
+        float v[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) v[i] = (fh[i] + TC_LO_INV * fl[i]) * inv;
-    float4 *o0 = act + ((size_t)n * 16 + 2 * c8) * L + l, *o1 = act + ((size_t)n * 16 + 2 * c8 + 1) * L + l;
-    float4 r0 = make_float4(v[0], v[1], v[2], v[3]), r1 = make_float4(v[4], v[5], v[6], v[7]);
-    if (add) {
-        const float4 p0 = *o0, p1 = *o1;
-        r0.x += p0.x; r0.y += p0.y; r0.z += p0.z; r0.w += p0.w;
-        r1.x += p1.x; r1.y += p1.y; r1.z += p1.z; r1.w += p1.w;
+        for (int i = 0; i < 8; ++i) v[i] = (fh[i] + TC_LO_INV * fl[i]) * inv;
+        if (EX && lrelu_planes != nullptr) {
+            const uint4 h = __ldg(lrelu_planes + ((size_t)n * 16 + c8) * L + l), lo = __ldg(lrelu_planes + ((size_t)n * 16 + 8 + c8) * L + l);
+            const uint32_t hw[4] = {h.x, h.y, h.z, h.w}, lw[4] = {lo.x, lo.y, lo.z, lo.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const uint32_t hv = (hw[i >> 1] >> (16 * (i & 1))) & 0xffffu, lv = (lw[i >> 1] >> (16 * (i & 1))) & 0xffffu;
+                // fp16 bit patterns: positive <=> sign bit clear and magnitude non-zero
+                const bool pos = ((hv & 0x7fffu) != 0u) ? ((hv & 0x8000u) == 0u) : (((lv & 0x7fffu) != 0u) && ((lv & 0x8000u) == 0u));
+                v[i] *= pos ? 1.f : kLeakySlope;
+            }
+        }
+        float4 *o0 = act + ((size_t)n * 16 + 2 * c8) * L + l, *o1 = act + ((size_t)n * 16 + 2 * c8 + 1) * L + l;
+        float4 r0 = make_float4(v[0], v[1], v[2], v[3]), r1 = make_float4(v[4], v[5], v[6], v[7]);
+        if (add) {
+            const float4 p0 = *o0, p1 = *o1;
+            r0.x += p0.x; r0.y += p0.y; r0.z += p0.z; r0.w += p0.w;
+            r1.x += p1.x; r1.y += p1.y; r1.z += p1.z; r1.w += p1.w;
+        }
+        *o0 = r0;
+        *o1 = r1;
+        if (EX) m = fmaxf(fmaxf(fmaxf(fabsf(r0.x), fabsf(r0.y)), fmaxf(fabsf(r0.z), fabsf(r0.w))),
+                          fmaxf(fmaxf(fabsf(r1.x), fabsf(r1.y)), fmaxf(fabsf(r1.z), fabsf(r1.w))));
     }
-    *o0 = r0;
-    *o1 = r1;
+    if (EX && absmax_out != nullptr) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        __shared__ float wm[8];
+        if ((threadIdx.x & 31) == 0) wm[threadIdx.x >> 5] = m;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+#pragma unroll
+            for (int i = 1; i < 8; ++i) m = fmaxf(m, wm[i]);
+            if (m > 0.0f) atomicMax(absmax_out, __float_as_uint(m));
+        }
+    }
+}
+
+// fp32 C4L4 gradient -> scaled split planes (as c4l4_to_planes_kernel with absmax_bits), 4 positions per thread, and the bias
+// gradient's partial sums on the way: bias_partial[(n * gridDim.x + blockIdx.x) * 64 + c] = sum of channel c over this block's
+// (up to) 1024 positions, summed in a fixed order (shuffle tree, then the 8 warps in order)
+constexpr int G2P_Q = 4;
+__global__ void __launch_bounds__(256)
+grad_to_planes_kernel(const float4 *__restrict__ act, uint4 *__restrict__ planes, int N, int L, const unsigned *__restrict__ absmax_bits,
+                      float *__restrict__ bias_partial) {
+    const int n = blockIdx.z, c8 = blockIdx.y;
+    const float sc = plane_scale(absmax_bits);
+    float s[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int q = 0; q < G2P_Q; ++q) {
+        const int l = blockIdx.x * (256 * G2P_Q) + q * 256 + threadIdx.x;
+        if (l < L) {
+            const float4 a0 = act[((size_t)n * 16 + 2 * c8) * L + l], a1 = act[((size_t)n * 16 + 2 * c8 + 1) * L + l];
+            const float r[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            float hi[8], lo[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { s[i] += r[i]; split_hi_lo(r[i] * sc, hi[i], lo[i]); }
+            uint4 uh, ul;
+            uh.x = pack_half2(hi[0], hi[1]); uh.y = pack_half2(hi[2], hi[3]); uh.z = pack_half2(hi[4], hi[5]); uh.w = pack_half2(hi[6], hi[7]);
+            ul.x = pack_half2(lo[0], lo[1]); ul.y = pack_half2(lo[2], lo[3]); ul.z = pack_half2(lo[4], lo[5]); ul.w = pack_half2(lo[6], lo[7]);
+            planes[((size_t)n * 16 + c8) * L + l] = uh;
+            planes[((size_t)n * 16 + 8 + c8) * L + l] = ul;
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s[i] += __shfl_xor_sync(0xffffffffu, s[i], o);
+    __shared__ float ws[8][8];
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) ws[threadIdx.x >> 5][i] = s[i];
+    }
+    __syncthreads();
+    if (threadIdx.x < 8) {
+        float t = 0.0f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) t += ws[w][threadIdx.x];
+        bias_partial[((size_t)n * gridDim.x + blockIdx.x) * 64 + 8 * c8 + threadIdx.x] = t;
+    }
 }
 
 __global__ void __launch_bounds__(256) absmax_kernel(const float4 *__restrict__ v, size_t n4, unsigned *__restrict__ out_bits) {
@@ -725,7 +800,28 @@ int launch_c4l4_to_planes(const float *act, void *planes, int N, int L, cudaStre
 int launch_planes_to_c4l4(const void *planes, float *act, int N, int L, cudaStream_t st, const unsigned *absmax_bits, int add) {
     STOF_REQUIRE(N <= 65535, STOF_E_INVALID, "planes_to_c4l4: at most 65535 rows per call");
     dim3 grid((L + 255) / 256, 8, N);
-    planes_to_c4l4_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const uint4 *>(planes), reinterpret_cast<float4 *>(act), N, L, absmax_bits, add);
+    planes_to_c4l4_kernel<false><<<grid, 256, 0, st>>>(reinterpret_cast<const uint4 *>(planes), reinterpret_cast<float4 *>(act), N, L, absmax_bits, add,
+                                                       nullptr, nullptr);
+    STOF_LAUNCH_CHECK();
+    return STOF_OK;
+}
+
+int launch_planes_to_c4l4_ex(const void *planes, float *act, int N, int L, cudaStream_t st, const unsigned *absmax_bits, int add,
+                             const void *lrelu_planes, unsigned *absmax_out) {
+    STOF_REQUIRE(N <= 65535, STOF_E_INVALID, "planes_to_c4l4: at most 65535 rows per call");
+    dim3 grid((L + 255) / 256, 8, N);
+    planes_to_c4l4_kernel<true><<<grid, 256, 0, st>>>(reinterpret_cast<const uint4 *>(planes), reinterpret_cast<float4 *>(act), N, L, absmax_bits, add,
+                                                      reinterpret_cast<const uint4 *>(lrelu_planes), absmax_out);
+    STOF_LAUNCH_CHECK();
+    return STOF_OK;
+}
+
+int grad_to_planes_parts(int N, int L) { return N * ((L + 256 * G2P_Q - 1) / (256 * G2P_Q)); }
+
+int launch_grad_to_planes(const float *g, void *planes, int N, int L, cudaStream_t st, const unsigned *absmax_bits, float *bias_partial) {
+    STOF_REQUIRE(N <= 65535, STOF_E_INVALID, "grad_to_planes: at most 65535 rows per call");
+    dim3 grid((L + 256 * G2P_Q - 1) / (256 * G2P_Q), 8, N);
+    grad_to_planes_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float4 *>(g), reinterpret_cast<uint4 *>(planes), N, L, absmax_bits, bias_partial);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }

@@ -79,12 +79,12 @@ int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void
 // conv_tc2.cu: the same segment on CTA pairs (2-CTA clusters, tcgen05 cta_group::2: M = 256 per MMA, each CTA reads half of B)
 int launch_chain_tc2(const TcLayer *layers, int count, const void *in, const void *x0, void *out_planes, float *out_mask,
                      int N, int L, cudaStream_t st, int fast = 0);
-// wgrad_tc.cu: weight (and bias) gradient of a 64 -> 64 k7 conv on tcgen05 from the split planes of the output gradient (scaled:
-// absmax_bits as in launch_c4l4_to_planes) and of the conv's input; g_c4l4 = the gradient in fp32 (bias sum); dW in PyTorch's
-// (64, 64, 7) layout; scratch: wgrad_tc_scratch_floats() floats.  Deterministic (fixed-order reduction).
+// wgrad_tc.cu: weight gradient of a 64 -> 64 k7 conv on tcgen05 from the split planes of the output gradient (scaled: absmax_bits
+// as in launch_c4l4_to_planes) and of the conv's input; dW in PyTorch's (64, 64, 7) layout; scratch: wgrad_tc_scratch_floats()
+// floats.  Deterministic (fixed-order reduction).  The bias gradient: launch_grad_to_planes + launch_bias_parts_reduce below.
 size_t wgrad_tc_scratch_floats();
-int launch_wgrad_tc(const void *g_planes, const void *a_planes, const float *g_c4l4, const unsigned *absmax_bits, int N, int L,
-                    float *scratch, float *dW, float *db, cudaStream_t st);
+int launch_wgrad_tc(const void *g_planes, const void *a_planes, const unsigned *absmax_bits, int N, int L, float *scratch, float *dW,
+                    cudaStream_t st);
 // x (N, L) fp32 -> split planes of x0 = act(conv_first(x)) [+ nearest-upsampled E, centred]  (models/stofnet.py:45,96-115)
 int launch_x0_split(const float *x, const float *e, int N, int L, int P, int scale, int off, const float *w, const float *b,
                     void *planes, cudaStream_t st, int fast = 0, int K = 9);
@@ -100,6 +100,16 @@ int launch_expand_tc(const float *pooled, float *e, const void *w_packed, const 
 int launch_c4l4_to_planes(const float *act, void *planes, int N, int L, cudaStream_t st, const unsigned *absmax_bits = nullptr);
 int launch_planes_to_c4l4(const void *planes, float *act, int N, int L, cudaStream_t st, const unsigned *absmax_bits = nullptr,
                           int add = 0);
+// The training step's gradient hand-overs with their neighbours fused in (train.cu):
+//   planes -> fp32 with v *= lrelu'(a) (a as split planes, or NULL) before the optional add, and max |written value| folded into
+//   *absmax_out (or NULL) - the scale of this tensor's next plane conversion, without a pass of its own;
+//   fp32 -> scaled planes with the bias gradient's partial sums on the way: bias_partial[part][64], grad_to_planes_parts(N, L)
+//   parts, to be added in order by launch_bias_parts_reduce (wgrad_tc.cu)
+int launch_planes_to_c4l4_ex(const void *planes, float *act, int N, int L, cudaStream_t st, const unsigned *absmax_bits, int add,
+                             const void *lrelu_planes, unsigned *absmax_out);
+int grad_to_planes_parts(int N, int L);
+int launch_grad_to_planes(const float *g, void *planes, int N, int L, cudaStream_t st, const unsigned *absmax_bits, float *bias_partial);
+int launch_bias_parts_reduce(const float *bias_partial, int parts, float *db, cudaStream_t st);
 // *out_bits = max(*out_bits, bits of max |v|) over n4 float4 (non-negative floats order like their bit patterns); zero the slot first
 int launch_absmax(const float *v, size_t n4, unsigned *out_bits, cudaStream_t st);
 

@@ -34,7 +34,7 @@ struct TrainPlan {
     // tensor-core path: split planes (same size as an fp32 tensor) of x0 and of every mid conv's output, two gradient planes,
     // and the max |g| slots (one unsigned per data-gradient call)
     bool tc;
-    size_t off_px0, off_pa[STOF_MAX_MID_CONVS], off_gp[2], off_absmax;
+    size_t off_px0, off_pa[STOF_MAX_MID_CONVS], off_gp[2], off_absmax, off_bpart;
     size_t total_bytes;
 };
 
@@ -82,6 +82,7 @@ static int make_train_plan(const stof_model *m, int N, int L, TrainPlan *p) {
         for (int j = 0; j < m->n_mid; ++j) { p->off_pa[j] = o; o += p->act; }
         for (int i = 0; i < 2; ++i) { p->off_gp[i] = o; o += p->act; }
         p->off_absmax = o; o += 64;
+        p->off_bpart = o; o += a64((size_t)grad_to_planes_parts(N, L) * 64);
     }
     p->total_bytes = o * sizeof(float);
     return STOF_OK;
@@ -98,32 +99,6 @@ lrelu_bwd_kernel(float4 *__restrict__ g, const float4 *__restrict__ a, size_t n4
         gv.z *= av.z > 0.f ? 1.f : kLeakySlope; gv.w *= av.w > 0.f ? 1.f : kLeakySlope;
         g[i] = gv;
     }
-}
-// the same with a given as split fp16 planes [n][plane][c8][l][8] (tensor-core path: the forward keeps planes only); a > 0 <=> its
-// hi plane is positive, or zero with a positive lo plane
-__global__ void __launch_bounds__(256)
-lrelu_bwd_planes_kernel(float4 *__restrict__ g /*C4L4*/, const uint4 *__restrict__ planes, int N, int L) {
-    const int n = blockIdx.z, c8 = blockIdx.y;
-    const int l = blockIdx.x * 256 + threadIdx.x;
-    if (l >= L) return;
-    const uint4 h = __ldg(planes + ((size_t)n * 16 + c8) * L + l), lo = __ldg(planes + ((size_t)n * 16 + 8 + c8) * L + l);
-    const uint32_t hw[4] = {h.x, h.y, h.z, h.w}, lw[4] = {lo.x, lo.y, lo.z, lo.w};
-    float f[8];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            const uint32_t hv = (hw[i] >> (16 * k)) & 0xffffu, lv = (lw[i] >> (16 * k)) & 0xffffu;
-            // fp16 bit patterns: positive <=> sign bit clear and magnitude non-zero
-            const bool pos = ((hv & 0x7fffu) != 0u) ? ((hv & 0x8000u) == 0u) : (((lv & 0x7fffu) != 0u) && ((lv & 0x8000u) == 0u));
-            f[2 * i + k] = pos ? 1.f : kLeakySlope;
-        }
-    }
-    float4 *g0 = g + ((size_t)n * 16 + 2 * c8) * L + l, *g1 = g + ((size_t)n * 16 + 2 * c8 + 1) * L + l;
-    float4 a = *g0, b = *g1;
-    a.x *= f[0]; a.y *= f[1]; a.z *= f[2]; a.w *= f[3];
-    b.x *= f[4]; b.y *= f[5]; b.z *= f[6]; b.w *= f[7];
-    *g0 = a; *g1 = b;
 }
 // g[i] = (a[i] > 0) ? g[i] : 0     (ReLU backward)
 __global__ void __launch_bounds__(256)
@@ -196,34 +171,64 @@ last_dgrad_kernel(const float4 *__restrict__ gy /*[N][L] (4 u)*/, const float *_
     }
 }
 
-// wgrad: dW[u][ci][t] = sum_{n,l} g_y[n][u][l] a[n][ci][l + t - 1];  db[u] = sum g_y.   One CTA per (row, 1024-position chunk):
-// thread = (ci, t) (192 threads) keeps 4 accumulators (u); partial [768 + 4] per CTA.
-constexpr int LW_CHUNK = 1024;
+// wgrad: dW[u][ci][t] = sum_{n,l} g_y[n][u][l] a[n][ci][l + t - 1];  db[u] = sum g_y.   Persistent CTAs over (row, 128-position)
+// tiles staged in shared memory with coalesced 16-byte loads (a: 16 c4 slabs x 130 positions incl. the +-1 halo, zero outside the
+// row; g_y: 128 float4); thread = (ci, t) (192 threads) keeps 4 accumulators (u) and reads one broadcast float4 of g_y and one
+// word of a per position.  (The first version walked global memory position by position from every thread: latency-bound,
+// 0.57 ms of the 256 x 2560 step for 0.5 GMAC.)  partial [768 + 4] per CTA, added in CTA order by reduce_parts_kernel.
+constexpr int LW_TL = 128;
+constexpr int LW_AP = 131;                      // float4 pitch of an a slab: 524 words = 12 mod 32 -> a warp's three c4 groups miss each other
 constexpr int LW_MAX_CTAS = 4 * kSMs;
 __global__ void __launch_bounds__(192)
-last_wgrad_kernel(const float4 *__restrict__ gy, const float *__restrict__ a /*C4L4*/, int N, int L, int chunks,
+last_wgrad_kernel(const float4 *__restrict__ gy, const float4 *__restrict__ a /*C4L4*/, int N, int L, int tiles_per_row,
                   float *__restrict__ partial /*[gridDim.x][772]*/) {
+    __shared__ float4 As[16 * LW_AP];
+    __shared__ float4 Gs[LW_TL];
+    __shared__ float4 red[LW_TL];
     const int ci = threadIdx.x / 3, t = threadIdx.x - 3 * ci;
-    float acc[4] = {0.f, 0.f, 0.f, 0.f}, bs[4] = {0.f, 0.f, 0.f, 0.f};
-    const int total = N * chunks;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    float4 bs = make_float4(0.f, 0.f, 0.f, 0.f);            // thread i < 128: sum of g_y over the positions l0 + i of its tiles
+    const int total = N * tiles_per_row;
     for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
-        const int n = tile / chunks, l0 = (tile - n * chunks) * LW_CHUNK;
-        const float *ar = a + ((size_t)n * 16 + (ci >> 2)) * L * 4 + (ci & 3);
-        const int l1 = min(L, l0 + LW_CHUNK);
+        const int n = tile / tiles_per_row, l0 = (tile - n * tiles_per_row) * LW_TL;
+        __syncthreads();
+        for (int i = threadIdx.x; i < 16 * (LW_TL + 2); i += 192) {
+            const int c4 = i / (LW_TL + 2), j = i - c4 * (LW_TL + 2);
+            const int q = l0 + j - 1;
+            As[c4 * LW_AP + j] = (q >= 0 && q < L) ? __ldg(a + ((size_t)n * 16 + c4) * L + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        if (threadIdx.x < LW_TL) {
+            const int l = l0 + threadIdx.x;
+            const float4 g = (l < L) ? __ldg(gy + (size_t)n * L + l) : make_float4(0.f, 0.f, 0.f, 0.f);
+            Gs[threadIdx.x] = g;
+            bs.x += g.x; bs.y += g.y; bs.z += g.z; bs.w += g.w;
+        }
+        __syncthreads();
+        const float *ar = reinterpret_cast<const float *>(As + (ci >> 2) * LW_AP + t) + (ci & 3);
 #pragma unroll 8
-        for (int l = l0; l < l1; ++l) {                      // independent loads: 8 positions in flight per thread
-            const float4 g = __ldg(gy + (size_t)n * L + l);
-            const int q = l + t - 1;
-            const float av = (q >= 0 && q < L) ? __ldg(ar + (size_t)q * 4) : 0.0f;
+        for (int j = 0; j < LW_TL; ++j) {
+            const float4 g = Gs[j];
+            const float av = ar[4 * j];
             acc[0] = fmaf(g.x, av, acc[0]); acc[1] = fmaf(g.y, av, acc[1]);
             acc[2] = fmaf(g.z, av, acc[2]); acc[3] = fmaf(g.w, av, acc[3]);
-            if (threadIdx.x == 0) { bs[0] += g.x; bs[1] += g.y; bs[2] += g.z; bs[3] += g.w; }
         }
     }
     float *o = partial + (size_t)blockIdx.x * 772;
 #pragma unroll
     for (int u = 0; u < 4; ++u) o[(u * 64 + ci) * 3 + t] = acc[u];
-    if (threadIdx.x == 0) { o[768] = bs[0]; o[769] = bs[1]; o[770] = bs[2]; o[771] = bs[3]; }
+    __syncthreads();
+    if (threadIdx.x < LW_TL) red[threadIdx.x] = bs;
+    __syncthreads();
+    for (int k = LW_TL / 2; k > 0; k >>= 1) {
+        if ((int)threadIdx.x < k) {
+            const float4 y = red[threadIdx.x + k];
+            float4 x = red[threadIdx.x];
+            x.x += y.x; x.y += y.y; x.z += y.z; x.w += y.w;
+            red[threadIdx.x] = x;
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { o[768] = red[0].x; o[769] = red[0].y; o[770] = red[0].z; o[771] = red[0].w; }
 }
 
 // ------------------------------------------------------------------------------------------------ mid conv wgrad
@@ -392,27 +397,60 @@ bias_grad_ncl_kernel(const float *__restrict__ g, int N, int Cn, int P, float *_
     for (int k = 128; k; k >>= 1) { if ((int)threadIdx.x < k) red[threadIdx.x] += red[threadIdx.x + k]; __syncthreads(); }
     if (threadIdx.x == 0) db[c] = red[0];
 }
-// dgrad: g_pooled[n][ci][p] = sum_co sum_t We[co][ci][t] g[n][co][p - t + 2];  then through LeakyReLU of the pooled value
+// dgrad: g_pooled[n][ci][p] = sum_co sum_t We[co][ci][t] g[n][co][p - t + 2];  then through LeakyReLU of the pooled value.
+// CTA = (block of 32 ci, part of the rows): the block's weights (64 co x 32 ci x 5 = 40 KB) stay in shared memory for the whole
+// launch, each row's g (64 co x P with a zero halo of 2 + 4) is staged once; lane = ci, a warp takes 4 consecutive p at a time:
+// per co it reads 5 weights (stride 5: conflict-free) and 8 broadcast g values for 20 FMAs.  (One thread per output reading
+// weights and g from global memory per FMA: 0.41 ms of the 256 x 2560 step.)
+constexpr int ED_CI = 32;
+constexpr int ED_MAXP = 128;                                  // longer pooled rows: chunks of ED_MAXP positions
+constexpr int ED_GP = ED_MAXP + 8;                            // g row pitch: 2 halo words left, >= 6 right, multiple of 4
+constexpr int ED_SMEM = (64 * ED_CI * 5 + 64 * ED_GP) * 4;
 __global__ void __launch_bounds__(256)
 expand_dgrad_kernel(const float *__restrict__ g /*[N][64][P]*/, const float *__restrict__ We /*(64,512,5)*/,
                     const float *__restrict__ pooled, int N, int P, float *__restrict__ gpool /*[N][512][P]*/) {
-    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
-    if (i >= (long long)N * 512 * P) return;
-    const int p = (int)(i % P);
-    const int ci = (int)((i / P) % 512);
-    const int n = (int)(i / ((long long)P * 512));
-    float acc = 0.0f;
-    for (int co = 0; co < 64; ++co) {
-        const float *gr = g + ((size_t)n * 64 + co) * P;
-        const float *wr = We + ((size_t)co * 512 + ci) * 5;
+    extern __shared__ __align__(16) float ed_smem[];
+    float *s_w = ed_smem;                                     // [64 co][32 ci][5]
+    float *s_g = ed_smem + 64 * ED_CI * 5;                    // [64 co][ED_GP]: s_g[co][2 + j] = g[co][p0 + j]
+    const int ci0 = blockIdx.x * ED_CI;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < 64 * ED_CI * 5; i += 256) {
+        const int co = i / (ED_CI * 5), r = i - co * (ED_CI * 5);
+        s_w[i] = __ldg(We + ((size_t)co * 512 + ci0) * 5 + r);
+    }
+    for (int n = blockIdx.y; n < N; n += gridDim.y) {
+        for (int p0 = 0; p0 < P; p0 += ED_MAXP) {
+            const int np = min(ED_MAXP, P - p0);
+            __syncthreads();
+            for (int i = threadIdx.x; i < 64 * ED_GP; i += 256) {
+                const int co = i / ED_GP, j = i - co * ED_GP;
+                const int q = p0 + j - 2;
+                s_g[i] = (q >= 0 && q < P) ? __ldg(g + ((size_t)n * 64 + co) * P + q) : 0.0f;
+            }
+            __syncthreads();
+            for (int pq = warp; 4 * pq < np; pq += 8) {
+                float acc[4] = {0.f, 0.f, 0.f, 0.f};
+                const float *wr = s_w + lane * 5;
+                const float *gr = s_g + 4 * pq;               // gr[k] = g[p0 + 4 pq + k - 2]
+#pragma unroll 4
+                for (int co = 0; co < 64; ++co) {
+                    const float4 ga = *reinterpret_cast<const float4 *>(gr + co * ED_GP), gb = *reinterpret_cast<const float4 *>(gr + co * ED_GP + 4);
+                    const float gv[8] = {ga.x, ga.y, ga.z, ga.w, gb.x, gb.y, gb.z, gb.w};
 #pragma unroll
-        for (int t = 0; t < 5; ++t) {
-            const int q = p - t + 2;
-            if (q >= 0 && q < P) acc = fmaf(__ldg(wr + t), __ldg(gr + q), acc);
+                    for (int t = 0; t < 5; ++t) {
+                        const float w = wr[co * (ED_CI * 5) + t];
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) acc[k] = fmaf(w, gv[k + 4 - t], acc[k]);      // g[p - t + 2]
+                    }
+                }
+                // pooled = lrelu(max + bias): the max-pool routes the gradient to the arg-max position, scaled by lrelu'
+                const size_t o = ((size_t)n * 512 + ci0 + lane) * P + p0 + 4 * pq;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (4 * pq + k < np) gpool[o + k] = acc[k] * ((__ldg(pooled + o + k) > 0.f) ? 1.f : kLeakySlope);
+            }
         }
     }
-    // pooled = lrelu(max + bias): the max-pool routes the gradient to the arg-max position, scaled by lrelu'
-    gpool[i] = acc * ((__ldg(pooled + i) > 0.f) ? 1.f : kLeakySlope);
 }
 
 // contract conv (64 -> 512, k5, pad 2) behind the max-pool: the gradient of c[n][co][.] is gpool[n][co][p] at l* = argmax only.
@@ -450,79 +488,132 @@ contract_wgrad_kernel(const float *__restrict__ gpool, const int *__restrict__ a
     if (threadIdx.x == 0) db[co] = bs;
 }
 // dgrad (deterministic): g_x0r[n][ci][l] += sum over (co, p) with |l - l*| <= 2 of Wc[co][ci][l - l* + 2] gpool[n][co][p].
-// One CTA per (row, 80-position tile).  The (co, p) entries of the pooling windows that can reach the tile (p in [tile-1, tile+1])
-// are compacted IN ORDER to those whose arg-max lies within 2 positions of it (~1/3 of them); thread = (ci, q) then takes every
-// 4th entry and accumulates into its own copy q of the tile's outputs (no races, no atomics); the four copies are added in a
-// fixed order.  Every loop iteration does useful work (the first version scanned all 1,536 candidates in every thread: 3.1 ms
-// of a 16 ms step at 256 x 2560; this one 2.0 ms.  A weight-stationary variant - 4 windows per CTA, the 512 channels in 16 staged
-// blocks of 32, thread = (ci, window) - measured 2.7 ms: one CTA per SM and a serial shared-memory read-modify-write chain per thread).
+// One CTA per (pooling window = 80-position tile, group of 8 rows): an entry (n, co, p) scatters a 64 x 5 patch g * Wc[co] around
+// its arg-max, so the rows of a group SHARE every channel's weights - the 512 channels pass through shared memory in 16 blocks of
+// 32 (40 KB, read from L2 once per CTA, the next block prefetched into registers behind the current one's work).  Thread = (ci,
+// row) keeps its row's 64 x 84 output tile in shared memory (accs[row][ci][85]: lanes = consecutive ci, stride 85 -> conflict-free;
+// 2 halo columns either side) and walks the channels in order.  The window's own entry is branch-free: its 5 taps always land
+// inside the 84 columns (what falls into the halo belongs to the neighbouring tile's CTA and is dropped here).  The neighbouring
+// windows' entries whose arg-max lies within 2 positions of the tile (~2.5 % of them) are compacted in channel order, per row,
+// by the warp that stages that row's entries (ballot + prefix: no atomics), and applied after the block's own entries.
+// One accumulation order per output, no atomics.
+// History at 256 x 2560: every thread scanning all candidates 3.1 ms; compacted entries, one CTA per (row, tile), weights fetched
+// per entry from L2 (5.4 GB of 20-byte reads per step) 2.0 ms; a weight-stationary variant with 4 windows per CTA 2.7 ms; this
+// layout with the three windows' entries tested inline (six divergence-managed branches per channel) 1.46 ms.
 constexpr int CD_T = 80;
-constexpr int CD_SMEM = (4 * 64 * (CD_T + 1)) * 4 + 3 * 512 * (4 + 4 + 4) + 64;
-__global__ void __launch_bounds__(256)
+constexpr int CD_R = 8;                        // rows per CTA
+constexpr int CD_CO = 32;                      // channels per staged block
+constexpr int CD_AP = CD_T + 5;                // accumulator pitch: columns = positions l0 - 2 .. l0 + 81, + 1 pad
+constexpr int CD_THREADS = 64 * CD_R;
+constexpr int CD_SMEM = (CD_R * 64 * CD_AP + CD_CO * 320 + 2 * CD_R * CD_CO + 4 * CD_R * 2 * CD_CO + 16) * 4;
+__global__ void __launch_bounds__(CD_THREADS, 1)
 contract_dgrad_kernel(const float *__restrict__ gpool, const int *__restrict__ argmax, const float *__restrict__ Wc /*(512,64,5)*/,
                       int N, int L, int P, int tiles, float *__restrict__ gx /*C4L4, accumulated into*/) {
     extern __shared__ __align__(16) uint8_t cd_raw[];
-    float *accs = reinterpret_cast<float *>(cd_raw);                       // [4 q][64 ci][CD_T + 1]
-    int *e_l = reinterpret_cast<int *>(accs + 4 * 64 * (CD_T + 1));        // compacted entries: arg-max position,
-    float *e_g = reinterpret_cast<float *>(e_l + 3 * 512);                 //   pooled gradient,
-    int *e_co = reinterpret_cast<int *>(e_g + 3 * 512);                    //   output channel
-    int *w_cnt = e_co + 3 * 512;                                           // [8 warps] + running total
-    const int n = blockIdx.x / tiles, tile = blockIdx.x - n * tiles;
-    const int l0 = tile * CD_T;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int i = threadIdx.x; i < 4 * 64 * (CD_T + 1); i += 256) accs[i] = 0.0f;
-    if (threadIdx.x == 0) w_cnt[8] = 0;
-    __syncthreads();
-    for (int r = 0; r < 6; ++r) {                                          // 1,536 candidates, 256 per round, order preserved
-        const int i = r * 256 + threadIdx.x;
-        const int w = tile - 1 + i / 512, co = i & 511;
-        int l = 0; float g = 0.0f; bool ok = false;
-        if (w >= 0 && w < P) {
-            l = __ldg(argmax + ((size_t)n * 512 + co) * P + w);
-            g = __ldg(gpool + ((size_t)n * 512 + co) * P + w);
-            ok = (l + 2 >= l0) && (l - 2 < l0 + CD_T);
-        }
-        const unsigned bal = __ballot_sync(0xffffffffu, ok);
-        if (lane == 0) w_cnt[warp] = __popc(bal);
-        __syncthreads();
-        int off = w_cnt[8];
-        for (int k = 0; k < warp; ++k) off += w_cnt[k];
-        if (ok) {
-            const int d = off + __popc(bal & ((1u << lane) - 1u));
-            e_l[d] = l; e_g[d] = g; e_co[d] = co;
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) { int tot = w_cnt[8]; for (int k = 0; k < 8; ++k) tot += w_cnt[k]; w_cnt[8] = tot; }
-        __syncthreads();
-    }
-    const int m = w_cnt[8];
-    const int ci = threadIdx.x >> 2, q = threadIdx.x & 3;
-    float *mine = accs + ((size_t)q * 64 + ci) * (CD_T + 1);
-    for (int k = q; k < m; k += 4) {
-        const int ls = e_l[k] - l0;
-        const float g = e_g[k];
-        const float *wr = Wc + ((size_t)e_co[k] * 64 + ci) * 5;
+    float *accs = reinterpret_cast<float *>(cd_raw);                       // [8 rows][64 ci][CD_AP]
+    float *s_w = accs + CD_R * 64 * CD_AP;                                 // [32 co][64 ci][5]
+    int2 *s_e = reinterpret_cast<int2 *>(s_w + CD_CO * 320);               // [8 rows][32 co]: (arg-max - l0, bits of g) of the own window
+    int4 *s_edge = reinterpret_cast<int4 *>(s_e + CD_R * CD_CO);           // [8 rows][64]: (arg-max - l0, bits of g, co in block, -)
+    int *s_cnt = reinterpret_cast<int *>(s_edge + CD_R * 2 * CD_CO);       // [8 rows] edge entries of the block
+    const int group = blockIdx.x / tiles, tile = blockIdx.x - group * tiles;
+    const int n0 = group * CD_R, l0 = tile * CD_T;
+    const int ci = threadIdx.x & 63, row = threadIdx.x >> 6;               // compute role (row is warp-uniform)
+    const int lane = threadIdx.x & 31;
+    const int sr = threadIdx.x >> 5, sn = n0 + sr;                         // staging role of warps 0-7: row sr, lane = co of the block
+    const bool stager = threadIdx.x < 32 * CD_R;
+    for (int i = threadIdx.x; i < CD_R * 64 * CD_AP; i += CD_THREADS) accs[i] = 0.0f;
+    float *mine = accs + ((size_t)row * 64 + ci) * CD_AP;
+    constexpr int W4 = CD_CO * 320 / 4 / CD_THREADS;                       // float4 of a weight block per thread (5)
+    static_assert(W4 * CD_THREADS * 4 == CD_CO * 320, "weight block / thread count");
+    float4 wreg[W4];
+    int pl[3] = {0, 0, 0};
+    float pg[3] = {0.f, 0.f, 0.f};
+    auto prefetch = [&](int c0) {
 #pragma unroll
-        for (int t = 0; t < 5; ++t) {
-            const int j = ls + t - 2;                          // c[l*] reads x0r[l* + t - 2]
-            if (j >= 0 && j < CD_T) mine[j] += __ldg(wr + t) * g;
+        for (int k = 0; k < W4; ++k) wreg[k] = __ldg(reinterpret_cast<const float4 *>(Wc + (size_t)c0 * 320) + threadIdx.x + k * CD_THREADS);
+        if (stager && sn < N) {
+            const size_t base = ((size_t)sn * 512 + c0 + lane) * P;
+#pragma unroll
+            for (int d = 0; d < 3; ++d) {
+                const int w = tile - 1 + d;
+                const bool ok = (w >= 0 && w < P);
+                pl[d] = ok ? __ldg(argmax + base + w) : (1 << 28);
+                pg[d] = ok ? __ldg(gpool + base + w) : 0.0f;
+            }
+        }
+    };
+    prefetch(0);
+    for (int c0 = 0; c0 < 512; c0 += CD_CO) {
+        __syncthreads();                                                    // the previous block's weights / entries are consumed
+#pragma unroll
+        for (int k = 0; k < W4; ++k) reinterpret_cast<float4 *>(s_w)[threadIdx.x + k * CD_THREADS] = wreg[k];
+        if (stager) {
+            int cnt = 0;
+            const bool have = (sn < N);
+            // own window: always inside the tile (col 0..79); absent row / window: a zero entry
+            const bool own = have && tile < P;
+            s_e[sr * CD_CO + lane] = make_int2(own ? pl[1] - l0 : 0, own ? __float_as_int(pg[1]) : 0);
+#pragma unroll
+            for (int d = 0; d < 3; d += 2) {
+                const int rel = pl[d] - l0;                                 // absent: far away
+                const bool ok = have && (d == 0 ? (rel >= -2 && rel < 0) : (rel >= CD_T && rel < CD_T + 2));
+                const unsigned bal = __ballot_sync(0xffffffffu, ok);
+                if (ok) s_edge[sr * 2 * CD_CO + cnt + __popc(bal & ((1u << lane) - 1u))] = make_int4(rel, __float_as_int(pg[d]), lane, 0);
+                cnt += __popc(bal);
+            }
+            if (lane == 0) s_cnt[sr] = cnt;
+        }
+        __syncthreads();
+        if (c0 + CD_CO < 512) prefetch(c0 + CD_CO);                         // in flight behind this block's work
+#pragma unroll 4
+        for (int co = 0; co < CD_CO; ++co) {
+            const float *wr = s_w + ((size_t)co * 64 + ci) * 5;
+            const int2 e = s_e[row * CD_CO + co];
+            const float g = __int_as_float(e.y);
+            float *m = mine + e.x;                                          // columns e.x .. e.x + 4  <->  positions l* - 2 .. l* + 2
+            const float a0 = m[0], a1 = m[1], a2 = m[2], a3 = m[3], a4 = m[4];
+            m[0] = fmaf(wr[0], g, a0); m[1] = fmaf(wr[1], g, a1); m[2] = fmaf(wr[2], g, a2);
+            m[3] = fmaf(wr[3], g, a3); m[4] = fmaf(wr[4], g, a4);
+        }
+        const int ne = s_cnt[row];
+        for (int k = 0; k < ne; ++k) {
+            const int4 e = s_edge[row * 2 * CD_CO + k];
+            const float *wr = s_w + ((size_t)e.z * 64 + ci) * 5;
+            const float g = __int_as_float(e.y);
+#pragma unroll
+            for (int t = 0; t < 5; ++t) {
+                const int c = e.x + t;
+                if (c >= 0 && c < CD_T + 4) mine[c] = fmaf(wr[t], g, mine[c]);
+            }
         }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < 16 * CD_T; i += 256) {
-        const int c4 = i / CD_T, j = i - c4 * CD_T;
-        const int l = l0 + j;
-        if (l >= L) continue;
-        float4 *d = reinterpret_cast<float4 *>(gx) + ((size_t)n * 16 + c4) * L + l;
-        float4 v = *d;
-        float s4[4];
+    // tile position j <-> column j + 2; four independent read-modify-writes in flight per thread
+    constexpr int WO = CD_R * 16 * CD_T;
+    for (int i0 = threadIdx.x; i0 < WO; i0 += 4 * CD_THREADS) {
+        float4 *d[4];
+        float4 v[4];
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            const float *a = accs + (size_t)(4 * c4 + c) * (CD_T + 1) + j;
-            s4[c] = ((a[0] + a[64 * (CD_T + 1)]) + a[2 * 64 * (CD_T + 1)]) + a[3 * 64 * (CD_T + 1)];
+        for (int u = 0; u < 4; ++u) {
+            const int i = i0 + u * CD_THREADS;
+            d[u] = nullptr;
+            if (i < WO) {
+                const int r = i / (16 * CD_T), rem = i - r * (16 * CD_T);
+                const int c4 = rem / CD_T, j = rem - c4 * CD_T;
+                const int l = l0 + j, n = n0 + r;
+                if (l < L && n < N) {
+                    d[u] = reinterpret_cast<float4 *>(gx) + ((size_t)n * 16 + c4) * L + l;
+                    const float *a = accs + ((size_t)r * 64 + 4 * c4) * CD_AP + j + 2;
+                    v[u] = make_float4(a[0], a[CD_AP], a[2 * CD_AP], a[3 * CD_AP]);
+                }
+            }
         }
-        v.x += s4[0]; v.y += s4[1]; v.z += s4[2]; v.w += s4[3];
-        *d = v;
+        float4 o[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) if (d[u]) o[u] = *d[u];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (d[u]) { o[u].x += v[u].x; o[u].y += v[u].y; o[u].z += v[u].z; o[u].w += v[u].w; *d[u] = o[u]; }
     }
 }
 
@@ -834,10 +925,10 @@ extern "C" int stof_backward(stof_model *m, const float *x, const float *g_mask,
         STOF_REQUIRE(N <= 65535, STOF_E_INVALID, "stof_backward: at most 65535 rows per call");
         last_dgrad_kernel<<<grid, 256, 0, st>>>(gy, m->raw_last_w, N, L, reinterpret_cast<float4 *>(X));
         STOF_LAUNCH_CHECK();
-        const int chunks = (L + LW_CHUNK - 1) / LW_CHUNK;
-        const long long total = (long long)N * chunks;
+        const int tpr = (L + LW_TL - 1) / LW_TL;
+        const long long total = (long long)N * tpr;
         const int g2 = (int)(total < LW_MAX_CTAS ? total : LW_MAX_CTAS);
-        last_wgrad_kernel<<<g2, 192, 0, st>>>(gy, act(nm - 1), N, L, chunks, partial);
+        last_wgrad_kernel<<<g2, 192, 0, st>>>(gy, reinterpret_cast<const float4 *>(act(nm - 1)), N, L, tpr, partial);
         STOF_LAUNCH_CHECK();
         reduce_parts_kernel<<<4, 256, 0, st>>>(partial, g2, 772, gr->last_w, 768, gr->last_b);
         STOF_LAUNCH_CHECK();
@@ -851,36 +942,38 @@ extern "C" int stof_backward(stof_model *m, const float *x, const float *g_mask,
         STOF_CUDA(cudaMemsetAsync(ws + pl.off_absmax, 0, 64 * sizeof(float), st));
     }
     auto pact = [&](int j) -> const void * { return j < 0 ? (const void *)(ws + pl.off_px0) : (const void *)(ws + pl.off_pa[j]); };
-    auto mid_backward = [&](int j, const float *g, float *out, bool accumulate) -> int {
+    // lrelu_src (tensor-core path): planes of the activation whose lrelu' multiplies the data gradient on its way back to fp32
+    // (the LEAKY conv below this one).  The hand-overs carry their neighbours: fp32 -> planes also sums the bias gradient's
+    // partials, planes -> fp32 also applies lrelu' and records max |out| in the NEXT slot (the scale of out's own conversion).
+    auto mid_backward = [&](int j, const float *g, float *out, bool accumulate, const void *lrelu_src) -> int {
         int r;
         if (!pl.tc) {
             if ((r = mid_wgrad(g, act(j - 1), N, L, partial, gr->mid_w[j], gr->mid_b[j], st))) return r;
             return launch_conv_mid_simt(g, accumulate ? out : nullptr, out, m->bw_mid[j], m->zero_bias, N, L, accumulate ? 1 : 2, st);
         }
-        STOF_REQUIRE(n_slots < 64, STOF_E_INVALID, "stof_backward: too many mid convs");
+        STOF_REQUIRE(n_slots < 63, STOF_E_INVALID, "stof_backward: too many mid convs");
         unsigned *slot = reinterpret_cast<unsigned *>(ws + pl.off_absmax) + (n_slots++);
         void *gp0 = ws + pl.off_gp[0], *gp1 = ws + pl.off_gp[1];
-        if ((r = launch_absmax(g, n4, slot, st))) return r;
-        if ((r = launch_c4l4_to_planes(g, gp0, N, L, st, slot))) return r;
-        if ((r = launch_wgrad_tc(gp0, pact(j - 1), g, slot, N, L, partial, gr->mid_w[j], gr->mid_b[j], st))) return r;
+        float *bpart = ws + pl.off_bpart;
+        if (n_slots == 1 && (r = launch_absmax(g, n4, slot, st))) return r;          // later slots: written by the previous hand-over
+        if ((r = launch_grad_to_planes(g, gp0, N, L, st, slot, bpart))) return r;
+        if ((r = launch_bias_parts_reduce(bpart, grad_to_planes_parts(N, L), gr->mid_b[j], st))) return r;
+        if ((r = launch_wgrad_tc(gp0, pact(j - 1), slot, N, L, partial, gr->mid_w[j], st))) return r;
         if ((r = launch_chain_tc(&m->tr_bwd[j], 1, gp0, nullptr, gp1, nullptr, N, L, st))) return r;
-        return launch_planes_to_c4l4(gp1, out, N, L, st, slot, accumulate ? 1 : 0);
+        return launch_planes_to_c4l4_ex(gp1, out, N, L, st, slot, accumulate ? 1 : 0, lrelu_src, slot + 1);
     };
     // ---- conv{nb-1} (long skip): a = x0 + conv(a_prev): g_conv = X;  S = dgrad(X)
-    if ((rc = mid_backward(nm - 1, X, S, false))) return rc;
+    if ((rc = mid_backward(nm - 1, X, S, false, nullptr))) return rc;
     // ---- pairs (RES j, LEAKY j - 1), j = nm-2, nm-4, ..., 1:   S = g wrt a_j
     for (int j = nm - 2; j >= 1; j -= 2) {
         // a_j = a_{j-2} + conv_j(a_{j-1}):  wgrad with input a_{j-1};  T = dgrad_j(S);  skip keeps S
-        if ((rc = mid_backward(j, S, T, false))) return rc;
         // a_{j-1} = lrelu(conv_{j-1}(a_{j-2})):  T *= lrelu'(a_{j-1});  wgrad with input a_{j-2};  S += dgrad_{j-1}(T)
-        if (pl.tc) {
-            lrelu_bwd_planes_kernel<<<dim3((L + 255) / 256, 8, N), 256, 0, st>>>(reinterpret_cast<float4 *>(T),
-                                                                                 reinterpret_cast<const uint4 *>(pact(j - 1)), N, L);
-        } else {
+        if ((rc = mid_backward(j, S, T, false, pl.tc ? pact(j - 1) : nullptr))) return rc;
+        if (!pl.tc) {
             lrelu_bwd_kernel<<<ew_grid(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(T), reinterpret_cast<const float4 *>(act(j - 1)), n4);
+            STOF_LAUNCH_CHECK();
         }
-        STOF_LAUNCH_CHECK();
-        if ((rc = mid_backward(j - 1, T, S, true))) return rc;
+        if ((rc = mid_backward(j - 1, T, S, true, nullptr))) return rc;
     }
     // ---- S = g wrt x0 through the chain; add the long skip
     add_kernel<<<ew_grid(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(S), reinterpret_cast<const float4 *>(X), n4);
@@ -903,8 +996,9 @@ extern "C" int stof_backward(stof_model *m, const float *x, const float *g_mask,
         STOF_LAUNCH_CHECK();
         bias_grad_ncl_kernel<<<64, 256, 0, st>>>(ge, N, 64, P, gr->expand_b);
         STOF_LAUNCH_CHECK();
-        const long long np = (long long)N * 512 * P;
-        expand_dgrad_kernel<<<(unsigned)((np + 255) / 256), 256, 0, st>>>(ge, m->raw_expand_w, pooled, N, P, gpool);
+        static SmemAttrOnce ed_attr;
+        if ((rc = ensure_dyn_smem(expand_dgrad_kernel, ED_SMEM, ed_attr))) return rc;
+        expand_dgrad_kernel<<<dim3(512 / ED_CI, (unsigned)(N < 32 ? N : 32)), 256, ED_SMEM, st>>>(ge, m->raw_expand_w, pooled, N, P, gpool);
         STOF_LAUNCH_CHECK();
         contract_wgrad_kernel<<<dim3(512, (unsigned)parts), 320, 0, st>>>(gpool, argmax, x0r, N, L, P, partial);
         STOF_LAUNCH_CHECK();
@@ -915,7 +1009,7 @@ extern "C" int stof_backward(stof_model *m, const float *x, const float *g_mask,
         STOF_REQUIRE((long long)N * tiles < (1ll << 31), STOF_E_INVALID, "stof_backward: batch too large");
         static SmemAttrOnce cd_attr;
         if ((rc = ensure_dyn_smem(contract_dgrad_kernel, CD_SMEM, cd_attr))) return rc;
-        contract_dgrad_kernel<<<(unsigned)(N * tiles), 256, CD_SMEM, st>>>(gpool, argmax, m->raw_contract_w, N, L, P, tiles, S);
+        contract_dgrad_kernel<<<(unsigned)(((N + CD_R - 1) / CD_R) * tiles), CD_THREADS, CD_SMEM, st>>>(gpool, argmax, m->raw_contract_w, N, L, P, tiles, S);
         STOF_LAUNCH_CHECK();
     }
     // ---- conv1: x0r = relu(conv1 x)

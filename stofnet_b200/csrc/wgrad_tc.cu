@@ -163,69 +163,61 @@ __global__ void __launch_bounds__(WT_THREADS, 1) wgrad_tc_kernel(const WtParams 
     }
 }
 
-// dW[co][ci][t] (PyTorch layout) = 2^-k * sum over shares (fixed order) of  hh + 2^-11 (hl + lh)
+// dW[co][ci][t] (PyTorch layout) = 2^-k * sum over shares (fixed order) of  hh + 2^-11 (hl + lh).
+// One block per (tap, co, half of the ci): lane = ci (128-byte coalesced reads of the partials), warp w adds the shares
+// w, w + 8, ... in order, and the eight sub-sums are added in order: as deterministic as a single chain, with an eighth of its
+// dependent-load latency (a lone thread per output walking 74 shares took 42 us per layer: 0.47 ms of the 256-row step)
 __global__ void __launch_bounds__(256)
 wgrad_tc_reduce_kernel(const float *__restrict__ partial, int shares, int tiles, const unsigned *__restrict__ absmax_bits,
                        float *__restrict__ dW) {
-    const int i = blockIdx.x * 256 + threadIdx.x;
-    if (i >= 64 * 64 * 7) return;
-    const int t = i % 7, ci = (i / 7) & 63, co = i / (7 * 64);
+    const int half = blockIdx.x & 1, co = (blockIdx.x >> 1) & 63, t = blockIdx.x >> 7;
+    const int warp = threadIdx.x >> 5, ci = 32 * half + (threadIdx.x & 31);
     const int group = t >> 2, tl = t & 3;
     float hh = 0.0f, x = 0.0f;
     const int used = shares < tiles ? shares : tiles;            // shares beyond the tile count wrote nothing
-    for (int sh = 0; sh < used; ++sh) {
+    for (int sh = warp; sh < used; sh += 8) {
         const float *P = partial + ((size_t)(2 * sh + group) * 4 + tl) * 128 * 128;
-        hh += P[(size_t)co * 128 + ci];
-        x += P[(size_t)co * 128 + 64 + ci] + P[(size_t)(64 + co) * 128 + ci];
+        hh += __ldg(P + (size_t)co * 128 + ci);
+        x += __ldg(P + (size_t)co * 128 + 64 + ci) + __ldg(P + (size_t)(64 + co) * 128 + ci);
     }
+    __shared__ float red[2][8][32];
+    red[0][warp][threadIdx.x & 31] = hh;
+    red[1][warp][threadIdx.x & 31] = x;
+    __syncthreads();
+    if (warp != 0) return;
+    hh = 0.0f; x = 0.0f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) { hh += red[0][w][threadIdx.x]; x += red[1][w][threadIdx.x]; }
     float inv = 1.0f;
     if (absmax_bits != nullptr) {
         const int e = (int)((__ldg(absmax_bits) >> 23) & 255u);
         if (e > 10 && e != 255) inv = __uint_as_float((unsigned)(e - 10) << 23);                     // 1 / plane_scale (conv_tc.cu)
     }
-    dW[i] = (hh + TC_LO_INV * x) * inv;
+    dW[((size_t)co * 64 + ci) * 7 + t] = (hh + TC_LO_INV * x) * inv;
 }
 
-// db[c] = sum over rows and positions of G[n][c][l] (fp32 C4L4): block (c4, part) sums its rows in a fixed order -> partial
-// [part][64]; the caller's reduce adds the parts in order
-__global__ void __launch_bounds__(256)
-bias_grad_c4l4_kernel(const float4 *__restrict__ G, int N, int L, int parts, float *__restrict__ partial /*[parts][64]*/) {
-    const int c4 = blockIdx.x, part = blockIdx.y;
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int n = part; n < N; n += parts) {
-        const float4 *g = G + ((size_t)n * 16 + c4) * L;
-        for (int l = threadIdx.x; l < L; l += 256) {
-            const float4 v = __ldg(g + l);
-            acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
-        }
-    }
-    __shared__ float4 red[256];
-    red[threadIdx.x] = acc;
+// db[c] = sum of bias_partial[q][c] over the parts q (grad_to_planes_kernel): thread t adds q = t, t + 256, ... in order, then a
+// fixed tree
+__global__ void __launch_bounds__(256) bias_parts_reduce_kernel(const float *__restrict__ partial, int parts, float *__restrict__ db) {
+    const int c = blockIdx.x;
+    float s = 0.0f;
+    for (int q = threadIdx.x; q < parts; q += 256) s += __ldg(partial + (size_t)q * 64 + c);
+    __shared__ float red[256];
+    red[threadIdx.x] = s;
     __syncthreads();
     for (int o = 128; o > 0; o >>= 1) {
-        if (threadIdx.x < o) {
-            const float4 b = red[threadIdx.x + o];
-            float4 a = red[threadIdx.x];
-            a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
-            red[threadIdx.x] = a;
-        }
+        if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
         __syncthreads();
     }
-    if (threadIdx.x == 0) *reinterpret_cast<float4 *>(partial + (size_t)part * 64 + 4 * c4) = red[0];
+    if (threadIdx.x == 0) db[c] = red[0];
 }
 
-__global__ void __launch_bounds__(64) bias_grad_reduce_kernel(const float *__restrict__ partial, int parts, float *__restrict__ db) {
-    float s = 0.0f;
-    for (int q = 0; q < parts; ++q) s += partial[(size_t)q * 64 + threadIdx.x];
-    db[threadIdx.x] = s;
-}
+size_t wgrad_tc_scratch_floats() { return (size_t)2 * WT_SHARES * WT_PART; }
 
-size_t wgrad_tc_scratch_floats() { return (size_t)2 * WT_SHARES * WT_PART + 64 * 64; }
-
-// g_planes / a_planes: split planes of the layer's output gradient (scaled, see absmax_bits) and of its input; g_c4l4: the same
-// gradient in fp32 (bias gradient); scratch: wgrad_tc_scratch_floats() floats
-int launch_wgrad_tc(const void *g_planes, const void *a_planes, const float *g_c4l4, const unsigned *absmax_bits, int N, int L,
-                    float *scratch, float *dW, float *db, cudaStream_t st) {
+// g_planes / a_planes: split planes of the layer's output gradient (scaled, see absmax_bits) and of its input; scratch:
+// wgrad_tc_scratch_floats() floats.  (The bias gradient comes from the partial sums of launch_grad_to_planes, conv_tc.cu.)
+int launch_wgrad_tc(const void *g_planes, const void *a_planes, const unsigned *absmax_bits, int N, int L, float *scratch, float *dW,
+                    cudaStream_t st) {
     static SmemAttrOnce attr;
     { const int rc = ensure_dyn_smem(wgrad_tc_kernel, WT_SMEM_BYTES, attr); if (rc) return rc; }
     WtParams p;
@@ -238,13 +230,13 @@ int launch_wgrad_tc(const void *g_planes, const void *a_planes, const float *g_c
     p.shares = (int)(total < WT_SHARES ? total : WT_SHARES);
     wgrad_tc_kernel<<<2 * p.shares, WT_THREADS, WT_SMEM_BYTES, st>>>(p);
     STOF_LAUNCH_CHECK();
-    wgrad_tc_reduce_kernel<<<(64 * 64 * 7 + 255) / 256, 256, 0, st>>>(scratch, p.shares, p.total_tiles, absmax_bits, dW);
+    wgrad_tc_reduce_kernel<<<7 * 64 * 2, 256, 0, st>>>(scratch, p.shares, p.total_tiles, absmax_bits, dW);
     STOF_LAUNCH_CHECK();
-    float *bpart = scratch + (size_t)2 * WT_SHARES * WT_PART;
-    const int parts = N < 64 ? N : 64;
-    bias_grad_c4l4_kernel<<<dim3(16, (unsigned)parts), 256, 0, st>>>(reinterpret_cast<const float4 *>(g_c4l4), N, L, parts, bpart);
-    STOF_LAUNCH_CHECK();
-    bias_grad_reduce_kernel<<<1, 64, 0, st>>>(bpart, parts, db);
+    return STOF_OK;
+}
+
+int launch_bias_parts_reduce(const float *bias_partial, int parts, float *db, cudaStream_t st) {
+    bias_parts_reduce_kernel<<<64, 256, 0, st>>>(bias_partial, parts, db);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }
