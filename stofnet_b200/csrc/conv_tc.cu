@@ -599,7 +599,7 @@ c4l4_to_planes_kernel(const float4 *__restrict__ act, uint4 *__restrict__ planes
 template <bool EX>
 __global__ void __launch_bounds__(256)
 planes_to_c4l4_kernel(const uint4 *__restrict__ planes, float4 *__restrict__ act, int N, int L, const unsigned *__restrict__ absmax_bits,
-                      int add, const uint4 *__restrict__ lrelu_planes, unsigned *__restrict__ absmax_out) {
+                      int add, const uint4 *__restrict__ lrelu_planes, unsigned *__restrict__ absmax_out, const float4 *__restrict__ add2) {
     const int n = blockIdx.z, c8 = blockIdx.y;
     const int l = blockIdx.x * 256 + threadIdx.x;
     float m = 0.0f;
@@ -628,6 +628,11 @@ planes_to_c4l4_kernel(const uint4 *__restrict__ planes, float4 *__restrict__ act
             const float4 p0 = *o0, p1 = *o1;
             r0.x += p0.x; r0.y += p0.y; r0.z += p0.z; r0.w += p0.w;
             r1.x += p1.x; r1.y += p1.y; r1.z += p1.z; r1.w += p1.w;
+        }
+        if (EX && add2 != nullptr) {                                 // a second addend (the long skip's gradient at the end of the chain)
+            const float4 q0 = __ldg(add2 + ((size_t)n * 16 + 2 * c8) * L + l), q1 = __ldg(add2 + ((size_t)n * 16 + 2 * c8 + 1) * L + l);
+            r0.x += q0.x; r0.y += q0.y; r0.z += q0.z; r0.w += q0.w;
+            r1.x += q1.x; r1.y += q1.y; r1.z += q1.z; r1.w += q1.w;
         }
         *o0 = r0;
         *o1 = r1;
@@ -801,17 +806,17 @@ int launch_planes_to_c4l4(const void *planes, float *act, int N, int L, cudaStre
     STOF_REQUIRE(N <= 65535, STOF_E_INVALID, "planes_to_c4l4: at most 65535 rows per call");
     dim3 grid((L + 255) / 256, 8, N);
     planes_to_c4l4_kernel<false><<<grid, 256, 0, st>>>(reinterpret_cast<const uint4 *>(planes), reinterpret_cast<float4 *>(act), N, L, absmax_bits, add,
-                                                       nullptr, nullptr);
+                                                       nullptr, nullptr, nullptr);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }
 
 int launch_planes_to_c4l4_ex(const void *planes, float *act, int N, int L, cudaStream_t st, const unsigned *absmax_bits, int add,
-                             const void *lrelu_planes, unsigned *absmax_out) {
+                             const void *lrelu_planes, unsigned *absmax_out, const float *add2) {
     STOF_REQUIRE(N <= 65535, STOF_E_INVALID, "planes_to_c4l4: at most 65535 rows per call");
     dim3 grid((L + 255) / 256, 8, N);
     planes_to_c4l4_kernel<true><<<grid, 256, 0, st>>>(reinterpret_cast<const uint4 *>(planes), reinterpret_cast<float4 *>(act), N, L, absmax_bits, add,
-                                                      reinterpret_cast<const uint4 *>(lrelu_planes), absmax_out);
+                                                      reinterpret_cast<const uint4 *>(lrelu_planes), absmax_out, reinterpret_cast<const float4 *>(add2));
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }

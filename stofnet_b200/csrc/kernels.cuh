@@ -101,12 +101,13 @@ int launch_c4l4_to_planes(const float *act, void *planes, int N, int L, cudaStre
 int launch_planes_to_c4l4(const void *planes, float *act, int N, int L, cudaStream_t st, const unsigned *absmax_bits = nullptr,
                           int add = 0);
 // The training step's gradient hand-overs with their neighbours fused in (train.cu):
-//   planes -> fp32 with v *= lrelu'(a) (a as split planes, or NULL) before the optional add, and max |written value| folded into
+//   planes -> fp32 with v *= lrelu'(a) (a as split planes, or NULL) before the optional add (and a second addend add2, fp32 C4L4,
+//   or NULL), and max |written value| folded into
 //   *absmax_out (or NULL) - the scale of this tensor's next plane conversion, without a pass of its own;
 //   fp32 -> scaled planes with the bias gradient's partial sums on the way: bias_partial[part][64], grad_to_planes_parts(N, L)
 //   parts, to be added in order by launch_bias_parts_reduce (wgrad_tc.cu)
 int launch_planes_to_c4l4_ex(const void *planes, float *act, int N, int L, cudaStream_t st, const unsigned *absmax_bits, int add,
-                             const void *lrelu_planes, unsigned *absmax_out);
+                             const void *lrelu_planes, unsigned *absmax_out, const float *add2 = nullptr);
 int grad_to_planes_parts(int N, int L);
 int launch_grad_to_planes(const float *g, void *planes, int N, int L, cudaStream_t st, const unsigned *absmax_bits, float *bias_partial);
 int launch_bias_parts_reduce(const float *bias_partial, int parts, float *db, cudaStream_t st);

@@ -39,7 +39,7 @@ struct TrainPlan {
 };
 
 constexpr int WG_MAX_PARTS = kSMs;                 // persistent wgrad CTAs
-constexpr int SGB_PARTS = 16;                      // row parts of the semi-global block's weight gradients
+constexpr int CWG_MAX_PARTS = 37;                  // parts of the semi-global block's weight gradients: 8 channel blocks x 37 = 2 x 148 CTAs
 constexpr size_t WG_MID_LEN = 64 * 64 * 7 + 64;    // dW + db of one mid conv
 
 static size_t a64(size_t floats) { return (floats + 63) & ~(size_t)63; }
@@ -75,7 +75,7 @@ static int make_train_plan(const stof_model *m, int N, int L, TrainPlan *p) {
     // then mid wgrad (WG_MAX_PARTS x WG_MID_LEN)
     p->partial_floats = a64((size_t)WG_MAX_PARTS * WG_MID_LEN);
     if (m->path != STOF_PATH_SIMT && a64(wgrad_tc_scratch_floats()) > p->partial_floats) p->partial_floats = a64(wgrad_tc_scratch_floats());
-    if (p->sgb && a64((size_t)SGB_PARTS * (512 * 64 * 5 + 512)) > p->partial_floats) p->partial_floats = a64((size_t)SGB_PARTS * (512 * 64 * 5 + 512));
+    if (p->sgb && a64((size_t)CWG_MAX_PARTS * (512 * 64 * 5)) > p->partial_floats) p->partial_floats = a64((size_t)CWG_MAX_PARTS * (512 * 64 * 5));
     p->off_partial = o; o += p->partial_floats;
     if (p->tc) {
         p->off_px0 = o; o += p->act;
@@ -341,46 +341,65 @@ lrelu_bwd1_kernel(float *__restrict__ g, const float *__restrict__ a, size_t n) 
 }
 
 // expand conv (512 -> 64, k5, pad 2 on the pooled axis):  e_pre[n][co][p] = b + sum_ci sum_t We[co][ci][t] pooled[n][ci][p+t-2]
-// wgrad: dWe[co][ci][t] = sum_{n,p} g[n][co][p] pooled[n][ci][p + t - 2];  CTA = (block of 16 ci, part of the rows), thread =
-// (co, t) with 16 accumulators (one per ci of the block).  Per row and 32-position chunk the CTA stages g (64 x 32) and the 16
-// pooled rows with their +-2 halo (zero outside [0, P)) in shared memory, so every global byte is read once per CTA and the inner
-// loop is one shared-memory read per FMA (the first version re-read both operands from global memory in every thread: 1.5 ms
-// of a 16 ms step at 256 x 2560).  Fixed (n, p) order; partial [part][(64,512,5)], added in part order by reduce_parts_kernel.
-constexpr int EW_CI = 16, EW_PC = 32;
-__global__ void __launch_bounds__(320)
+// wgrad: dWe[co][ci][t] = sum_{n,p} g[n][co][p] pooled[n][ci][p + t - 2];  CTA = (block of 64 ci, part of the rows); thread =
+// (co group, ci group) owns 4 co x 4 ci x 5 taps = 80 accumulators (co = cog + 16 a, ci = cig + 16 b: a warp's 16 ci rows sit in
+// distinct banks, its two co rows are broadcasts).  Per row and 32-position chunk the CTA stages g (64 x 32) and the block's 64
+// pooled rows with their +-2 halo (zero outside [0, P)); per position a thread reads 4 g values and the 4 x 5 window (the
+// unrolled loop keeps the overlapping window values in registers): ~0.2 shared-memory reads per FMA.
+// (History at 256 x 2560: both operands from global memory in every thread 1.49 ms; thread = (co, t) with 16 ci accumulators and
+// one shared-memory read per FMA 0.23 ms.)  Fixed (n, p) order; partial [part][(64,512,5)], added in part order by reduce_parts_kernel.
+constexpr int EW_CB = 64, EW_PC = 32;
+constexpr int EW_GP = EW_PC + 1, EW_PP = EW_PC + 5;
+__global__ void __launch_bounds__(256, 2)
 expand_wgrad_kernel(const float *__restrict__ g /*[N][64][P]*/, const float *__restrict__ pooled /*[N][512][P]*/, int N, int P,
                     float *__restrict__ partial) {
-    __shared__ float gs[64][EW_PC + 1];
-    __shared__ float ps[EW_CI][EW_PC + 4];
-    const int ci0 = blockIdx.x * EW_CI;
-    const int co = threadIdx.x / 5, t = threadIdx.x - 5 * co;
-    float acc[EW_CI];
+    __shared__ float gs[64][EW_GP];
+    __shared__ float ps[EW_CB][EW_PP];
+    const int ci0 = blockIdx.x * EW_CB;
+    const int cog = threadIdx.x >> 4, cig = threadIdx.x & 15;
+    float acc[4][4][5];
 #pragma unroll
-    for (int c = 0; c < EW_CI; ++c) acc[c] = 0.0f;
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+#pragma unroll
+            for (int t = 0; t < 5; ++t) acc[a][b][t] = 0.0f;
     for (int n = blockIdx.y; n < N; n += gridDim.y) {
         for (int p0 = 0; p0 < P; p0 += EW_PC) {
             __syncthreads();
-            for (int i = threadIdx.x; i < 64 * EW_PC; i += 320) {
+            for (int i = threadIdx.x; i < 64 * EW_PC; i += 256) {
                 const int c = i / EW_PC, j = i - c * EW_PC;
                 gs[c][j] = (p0 + j < P) ? __ldg(g + ((size_t)n * 64 + c) * P + p0 + j) : 0.0f;
             }
-            for (int i = threadIdx.x; i < EW_CI * (EW_PC + 4); i += 320) {
+            for (int i = threadIdx.x; i < EW_CB * (EW_PC + 4); i += 256) {
                 const int c = i / (EW_PC + 4), j = i - c * (EW_PC + 4);
                 const int q = p0 + j - 2;
                 ps[c][j] = (q >= 0 && q < P) ? __ldg(pooled + ((size_t)n * 512 + ci0 + c) * P + q) : 0.0f;
             }
             __syncthreads();
-#pragma unroll 4
+#pragma unroll 8
             for (int j = 0; j < EW_PC; ++j) {
-                const float gv = gs[co][j];
+                float gv[4];
 #pragma unroll
-                for (int c = 0; c < EW_CI; ++c) acc[c] = fmaf(gv, ps[c][j + t], acc[c]);
+                for (int a = 0; a < 4; ++a) gv[a] = gs[cog + 16 * a][j];
+#pragma unroll
+                for (int b = 0; b < 4; ++b)
+#pragma unroll
+                    for (int t = 0; t < 5; ++t) {
+                        const float x = ps[cig + 16 * b][j + t];
+#pragma unroll
+                        for (int a = 0; a < 4; ++a) acc[a][b][t] = fmaf(gv[a], x, acc[a][b][t]);
+                    }
             }
         }
     }
     float *dW = partial + (size_t)blockIdx.y * (64 * 512 * 5);
 #pragma unroll
-    for (int c = 0; c < EW_CI; ++c) dW[((size_t)co * 512 + ci0 + c) * 5 + t] = acc[c];
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+#pragma unroll
+            for (int t = 0; t < 5; ++t) dW[((size_t)(cog + 16 * a) * 512 + ci0 + cig + 16 * b) * 5 + t] = acc[a][b][t];
 }
 // db[c] = sum_{n,p} g[n][c][p]     (NCL tensor with C channels; one CTA per channel, fixed-order tree)
 __global__ void __launch_bounds__(256)
@@ -454,38 +473,104 @@ expand_dgrad_kernel(const float *__restrict__ g /*[N][64][P]*/, const float *__r
 }
 
 // contract conv (64 -> 512, k5, pad 2) behind the max-pool: the gradient of c[n][co][.] is gpool[n][co][p] at l* = argmax only.
-// wgrad: dWc[co][ci][t] = sum_{n,p} gpool[n][co][p] x0r[n][ci][l* + t - 2];  dbc[co] = sum gpool.  CTA = (co, part of the rows);
-// the row's pooled gradients and arg-max positions are staged in shared memory (one coalesced read) so that the gather from x0r
-// is the only dependent global load; partial [part][(512,64,5) | (512)], added in part order by reduce_parts_kernel
-constexpr int CW_PC = 256;
-__global__ void __launch_bounds__(320)
-contract_wgrad_kernel(const float *__restrict__ gpool, const int *__restrict__ argmax, const float *__restrict__ x0r /*C4L4*/,
+// wgrad: dWc[co][ci][t] = sum_{n,p} gpool[n][co][p] x0r[n][ci][l* + t - 2]  (dbc[co] = sum gpool: bias_grad_ncl_kernel).
+// Every arg-max of pooling window p lies inside that window, so all the x0r values its 512 channels gather come from one
+// 64 x 84 tile of row n (80 positions + 2 either side, zero outside the row).  CTA = (block of 64 co, part of the (n, p) tiles):
+// the tile is staged in shared memory once (C4L4 order kept: float4 per (c4, position), pitch 85 -> the 8 c4 groups of a warp hit
+// disjoint banks) by 16-byte cp.async through a 4-stage ring (three tiles in flight behind the current one: the work on a
+// tile is much shorter than a trip to L2 / HBM); thread = (ci, one of 8 co groups) keeps 8 x 5 accumulators and reads, per entry, one broadcast (column, g) pair and the 5 tap values of its ci.
+// (One CTA per co gathering from global memory per entry: 6.4 GB of L2 sector reads, 0.79 ms of the 256 x 2560 step.)
+// Fixed tile order per part; partial [part][(512,64,5)], added in part order by reduce_parts_kernel.
+constexpr int CWG_COB = 64;
+constexpr int CWG_AP = 85;
+constexpr int CWG_THREADS = 512;
+constexpr int CWG_K = CWG_COB / (CWG_THREADS / 64);                   // entries per thread and tile (8)
+constexpr int CWG_STAGES = 4;                                         // tiles in the cp.async ring (3 in flight behind the current one)
+constexpr int CWG_STAGE_BYTES = 16 * CWG_AP * 16 + 2 * CWG_COB * 4;   // tile + the block's (arg-max, g) entries
+constexpr int CWG_SMEM = CWG_STAGES * CWG_STAGE_BYTES;
+__global__ void __launch_bounds__(CWG_THREADS, 1)
+contract_wgrad_kernel(const float *__restrict__ gpool, const int *__restrict__ argmax, const float4 *__restrict__ x0r /*C4L4*/,
                       int N, int L, int P, float *__restrict__ partial) {
-    __shared__ float s_g[CW_PC];
-    __shared__ int s_l[CW_PC];
-    const int co = blockIdx.x;
-    const int ci = threadIdx.x / 5, t = threadIdx.x - 5 * ci;
-    float *dW = partial + (size_t)blockIdx.y * (512 * 64 * 5 + 512), *db = dW + 512 * 64 * 5;
-    float acc = 0.0f, bs = 0.0f;
-    for (int n = blockIdx.y; n < N; n += gridDim.y) {
-        const float *xr = x0r + ((size_t)n * 16 + (ci >> 2)) * L * 4 + (ci & 3);
-        const size_t base = ((size_t)n * 512 + co) * P;
-        for (int p0 = 0; p0 < P; p0 += CW_PC) {
-            const int np = min(CW_PC, P - p0);
-            __syncthreads();
-            for (int i = threadIdx.x; i < np; i += 320) { s_g[i] = __ldg(gpool + base + p0 + i); s_l[i] = __ldg(argmax + base + p0 + i); }
-            __syncthreads();
-#pragma unroll 4
-            for (int p = 0; p < np; ++p) {
-                const float gv = s_g[p];
-                const int q = s_l[p] + t - 2;
-                if (q >= 0 && q < L) acc = fmaf(gv, __ldg(xr + (size_t)q * 4), acc);
-                bs += gv;
+    extern __shared__ __align__(16) uint8_t cw_raw[];
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(cw_raw);
+    const int co0 = blockIdx.x * CWG_COB;
+    const int ci = threadIdx.x & 63, cg = threadIdx.x >> 6;           // co = co0 + cg + 8 k
+    float acc[CWG_K][5];
+#pragma unroll
+    for (int k = 0; k < CWG_K; ++k)
+#pragma unroll
+        for (int t = 0; t < 5; ++t) acc[k][t] = 0.0f;
+    constexpr int PRE = (16 * 84 + CWG_THREADS - 1) / CWG_THREADS;    // 3 16-byte copies of a tile per thread
+    const int total = N * P;
+    // this thread's share of a tile copy does not depend on the tile: (c4, column) of its PRE chunks, as source / destination offsets
+    int src_off[PRE], col_of[PRE];
+    uint32_t dst_off[PRE];
+#pragma unroll
+    for (int k = 0; k < PRE; ++k) {
+        const int i = threadIdx.x + k * CWG_THREADS;
+        const int c4 = i / 84, c = i - c4 * 84;
+        col_of[k] = (i < 16 * 84) ? c - 2 : (1 << 30);                  // position relative to l0; beyond the tile: never copied
+        src_off[k] = c4 * L;
+        dst_off[k] = (uint32_t)(c4 * CWG_AP + c) * 16u;
+    }
+    const int step_n = gridDim.y / P, step_w = gridDim.y - step_n * P;  // tile cursor increments (tile = n * P + w)
+    int in_ = blockIdx.y / P, iw = blockIdx.y - in_ * P, itl = blockIdx.y;     // cursor of the copies
+    // one cp.async group per tile (empty past the end): x0r positions l0 - 2 .. l0 + 81 of the 16 c4 slabs, zero-filled outside the row
+    auto issue = [&](int stage) {
+        if (itl < total) {
+            const int l0 = iw * 80;
+            const uint32_t dst0 = sbase + stage * CWG_STAGE_BYTES;
+            const float4 *row = x0r + (size_t)in_ * 16 * L;
+#pragma unroll
+            for (int k = 0; k < PRE; ++k) {
+                const int pos = l0 + col_of[k];
+                if (col_of[k] < 84) {
+                    const bool ok = (pos >= 0 && pos < L);
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst0 + dst_off[k]), "l"(row + src_off[k] + (ok ? pos : 0)),
+                                 "r"(ok ? 16u : 0u) : "memory");
+                }
+            }
+            if (threadIdx.x < CWG_COB) {
+                const size_t e = ((size_t)in_ * 512 + co0 + threadIdx.x) * P + iw;
+                const uint32_t d = dst0 + 16 * CWG_AP * 16 + threadIdx.x * 4;
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(argmax + e) : "memory");
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + CWG_COB * 4), "l"(gpool + e) : "memory");
             }
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        itl += gridDim.y; in_ += step_n; iw += step_w;
+        if (iw >= P) { iw -= P; ++in_; }
+    };
+#pragma unroll
+    for (int s = 0; s < CWG_STAGES - 1; ++s) issue(s);
+    int stage = 0, w = blockIdx.y % P;                                  // cursor of the work
+    for (int tl = blockIdx.y; tl < total; tl += gridDim.y) {
+        asm volatile("cp.async.wait_group %0;" ::"n"(CWG_STAGES - 2) : "memory");
+        __syncthreads();                  // this tile has landed for everyone; everyone is done with the previous one, whose stage is refilled now
+        issue(stage == 0 ? CWG_STAGES - 1 : stage - 1);
+        const uint8_t *st = cw_raw + stage * CWG_STAGE_BYTES;
+        const float *xr = reinterpret_cast<const float *>(st) + ((ci >> 2) * CWG_AP) * 4 + (ci & 3);
+        const int *s_l = reinterpret_cast<const int *>(st + 16 * CWG_AP * 16);
+        const float *s_g = reinterpret_cast<const float *>(s_l + CWG_COB);
+        const int l0 = w * 80;
+#pragma unroll
+        for (int k = 0; k < CWG_K; ++k) {
+            const int kk = cg + (CWG_THREADS / 64) * k;
+            const float g = s_g[kk];
+            const float *x = xr + 4 * (s_l[kk] - l0);                    // x[4 t] = x0r[ci][l* + t - 2]
+#pragma unroll
+            for (int t = 0; t < 5; ++t) acc[k][t] = fmaf(g, x[4 * t], acc[k][t]);
+        }
+        stage = (stage + 1 == CWG_STAGES) ? 0 : stage + 1;
+        w += step_w;
+        if (w >= P) w -= P;
     }
-    dW[((size_t)co * 64 + ci) * 5 + t] = acc;
-    if (threadIdx.x == 0) db[co] = bs;
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    float *dW = partial + (size_t)blockIdx.y * (512 * 64 * 5);
+#pragma unroll
+    for (int k = 0; k < CWG_K; ++k)
+#pragma unroll
+        for (int t = 0; t < 5; ++t) dW[((size_t)(co0 + cg + (CWG_THREADS / 64) * k) * 64 + ci) * 5 + t] = acc[k][t];
 }
 // dgrad (deterministic): g_x0r[n][ci][l] += sum over (co, p) with |l - l*| <= 2 of Wc[co][ci][l - l* + 2] gpool[n][co][p].
 // One CTA per (pooling window = 80-position tile, group of 8 rows): an entry (n, co, p) scatters a 64 x 5 patch g * Wc[co] around
@@ -508,7 +593,8 @@ constexpr int CD_THREADS = 64 * CD_R;
 constexpr int CD_SMEM = (CD_R * 64 * CD_AP + CD_CO * 320 + 2 * CD_R * CD_CO + 4 * CD_R * 2 * CD_CO + 16) * 4;
 __global__ void __launch_bounds__(CD_THREADS, 1)
 contract_dgrad_kernel(const float *__restrict__ gpool, const int *__restrict__ argmax, const float *__restrict__ Wc /*(512,64,5)*/,
-                      int N, int L, int P, int tiles, float *__restrict__ gx /*C4L4, accumulated into*/) {
+                      int N, int L, int P, int tiles, float *__restrict__ gx /*C4L4, accumulated into*/,
+                      const float4 *__restrict__ relu_src /*C4L4 or NULL: gx = (gx + ...) * (relu_src > 0), conv1's ReLU backward*/) {
     extern __shared__ __align__(16) uint8_t cd_raw[];
     float *accs = reinterpret_cast<float *>(cd_raw);                       // [8 rows][64 ci][CD_AP]
     float *s_w = accs + CD_R * 64 * CD_AP;                                 // [32 co][64 ci][5]
@@ -608,12 +694,22 @@ contract_dgrad_kernel(const float *__restrict__ gpool, const int *__restrict__ a
                 }
             }
         }
-        float4 o[4];
+        float4 o[4], a[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) if (d[u]) o[u] = *d[u];
+        for (int u = 0; u < 4; ++u) {
+            if (d[u]) o[u] = *d[u];
+            if (d[u] && relu_src) a[u] = __ldg(relu_src + (d[u] - reinterpret_cast<float4 *>(gx)));
+        }
 #pragma unroll
         for (int u = 0; u < 4; ++u)
-            if (d[u]) { o[u].x += v[u].x; o[u].y += v[u].y; o[u].z += v[u].z; o[u].w += v[u].w; *d[u] = o[u]; }
+            if (d[u]) {
+                o[u].x += v[u].x; o[u].y += v[u].y; o[u].z += v[u].z; o[u].w += v[u].w;
+                if (relu_src) {
+                    o[u].x = a[u].x > 0.f ? o[u].x : 0.f; o[u].y = a[u].y > 0.f ? o[u].y : 0.f;
+                    o[u].z = a[u].z > 0.f ? o[u].z : 0.f; o[u].w = a[u].w > 0.f ? o[u].w : 0.f;
+                }
+                *d[u] = o[u];
+            }
     }
 }
 
@@ -945,7 +1041,7 @@ extern "C" int stof_backward(stof_model *m, const float *x, const float *g_mask,
     // lrelu_src (tensor-core path): planes of the activation whose lrelu' multiplies the data gradient on its way back to fp32
     // (the LEAKY conv below this one).  The hand-overs carry their neighbours: fp32 -> planes also sums the bias gradient's
     // partials, planes -> fp32 also applies lrelu' and records max |out| in the NEXT slot (the scale of out's own conversion).
-    auto mid_backward = [&](int j, const float *g, float *out, bool accumulate, const void *lrelu_src) -> int {
+    auto mid_backward = [&](int j, const float *g, float *out, bool accumulate, const void *lrelu_src, const float *extra) -> int {
         int r;
         if (!pl.tc) {
             if ((r = mid_wgrad(g, act(j - 1), N, L, partial, gr->mid_w[j], gr->mid_b[j], st))) return r;
@@ -960,24 +1056,27 @@ extern "C" int stof_backward(stof_model *m, const float *x, const float *g_mask,
         if ((r = launch_bias_parts_reduce(bpart, grad_to_planes_parts(N, L), gr->mid_b[j], st))) return r;
         if ((r = launch_wgrad_tc(gp0, pact(j - 1), slot, N, L, partial, gr->mid_w[j], st))) return r;
         if ((r = launch_chain_tc(&m->tr_bwd[j], 1, gp0, nullptr, gp1, nullptr, N, L, st))) return r;
-        return launch_planes_to_c4l4_ex(gp1, out, N, L, st, slot, accumulate ? 1 : 0, lrelu_src, slot + 1);
+        return launch_planes_to_c4l4_ex(gp1, out, N, L, st, slot, accumulate ? 1 : 0, lrelu_src, slot + 1, extra);
     };
     // ---- conv{nb-1} (long skip): a = x0 + conv(a_prev): g_conv = X;  S = dgrad(X)
-    if ((rc = mid_backward(nm - 1, X, S, false, nullptr))) return rc;
+    // (tensor-core path: the long skip's gradient X is added by the LAST hand-over of the chain instead of a pass of its own)
+    if ((rc = mid_backward(nm - 1, X, S, false, nullptr, (pl.tc && nm - 2 < 1) ? X : nullptr))) return rc;
     // ---- pairs (RES j, LEAKY j - 1), j = nm-2, nm-4, ..., 1:   S = g wrt a_j
     for (int j = nm - 2; j >= 1; j -= 2) {
         // a_j = a_{j-2} + conv_j(a_{j-1}):  wgrad with input a_{j-1};  T = dgrad_j(S);  skip keeps S
         // a_{j-1} = lrelu(conv_{j-1}(a_{j-2})):  T *= lrelu'(a_{j-1});  wgrad with input a_{j-2};  S += dgrad_{j-1}(T)
-        if ((rc = mid_backward(j, S, T, false, pl.tc ? pact(j - 1) : nullptr))) return rc;
+        if ((rc = mid_backward(j, S, T, false, pl.tc ? pact(j - 1) : nullptr, nullptr))) return rc;
         if (!pl.tc) {
             lrelu_bwd_kernel<<<ew_grid(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(T), reinterpret_cast<const float4 *>(act(j - 1)), n4);
             STOF_LAUNCH_CHECK();
         }
-        if ((rc = mid_backward(j - 1, T, S, true, nullptr))) return rc;
+        if ((rc = mid_backward(j - 1, T, S, true, nullptr, (pl.tc && j - 2 < 1) ? X : nullptr))) return rc;
     }
     // ---- S = g wrt x0 through the chain; add the long skip
-    add_kernel<<<ew_grid(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(S), reinterpret_cast<const float4 *>(X), n4);
-    STOF_LAUNCH_CHECK();
+    if (!pl.tc) {
+        add_kernel<<<ew_grid(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(S), reinterpret_cast<const float4 *>(X), n4);
+        STOF_LAUNCH_CHECK();
+    }
     // ---- semi-global block: x0 = x0r + pad(up(E))
     if (pl.sgb) {
         float *pooled = ws + pl.off_pooled, *e = ws + pl.off_e, *ge = ws + pl.off_ge, *gpool = ws + pl.off_gpool;
@@ -989,8 +1088,8 @@ extern "C" int stof_backward(stof_model *m, const float *x, const float *g_mask,
         const size_t ne = (size_t)N * 64 * P;
         lrelu_bwd1_kernel<<<ew_grid(ne), 256, 0, st>>>(ge, e, ne);
         STOF_LAUNCH_CHECK();
-        const int parts = N < SGB_PARTS ? N : SGB_PARTS;
-        expand_wgrad_kernel<<<dim3(512 / EW_CI, (unsigned)parts), 320, 0, st>>>(ge, pooled, N, P, partial);
+        const int parts = N < CWG_MAX_PARTS ? N : CWG_MAX_PARTS;
+        expand_wgrad_kernel<<<dim3(512 / EW_CB, (unsigned)parts), 256, 0, st>>>(ge, pooled, N, P, partial);
         STOF_LAUNCH_CHECK();
         reduce_parts_kernel<<<(64 * 512 * 5 + 255) / 256, 256, 0, st>>>(partial, parts, (size_t)64 * 512 * 5, gr->expand_w, (size_t)64 * 512 * 5, nullptr);
         STOF_LAUNCH_CHECK();
@@ -1000,21 +1099,28 @@ extern "C" int stof_backward(stof_model *m, const float *x, const float *g_mask,
         if ((rc = ensure_dyn_smem(expand_dgrad_kernel, ED_SMEM, ed_attr))) return rc;
         expand_dgrad_kernel<<<dim3(512 / ED_CI, (unsigned)(N < 32 ? N : 32)), 256, ED_SMEM, st>>>(ge, m->raw_expand_w, pooled, N, P, gpool);
         STOF_LAUNCH_CHECK();
-        contract_wgrad_kernel<<<dim3(512, (unsigned)parts), 320, 0, st>>>(gpool, argmax, x0r, N, L, P, partial);
+        const int cparts = (long long)N * P < CWG_MAX_PARTS ? N * P : CWG_MAX_PARTS;
+        static SmemAttrOnce cw_attr;
+        if ((rc = ensure_dyn_smem(contract_wgrad_kernel, CWG_SMEM, cw_attr))) return rc;
+        contract_wgrad_kernel<<<dim3(512 / CWG_COB, (unsigned)cparts), CWG_THREADS, CWG_SMEM, st>>>(gpool, argmax, reinterpret_cast<const float4 *>(x0r), N, L, P, partial);
         STOF_LAUNCH_CHECK();
-        reduce_parts_kernel<<<(512 * 64 * 5 + 512 + 255) / 256, 256, 0, st>>>(partial, parts, (size_t)512 * 64 * 5 + 512, gr->contract_w,
-                                                                               (size_t)512 * 64 * 5, gr->contract_b);
+        reduce_parts_kernel<<<(512 * 64 * 5 + 255) / 256, 256, 0, st>>>(partial, cparts, (size_t)512 * 64 * 5, gr->contract_w, (size_t)512 * 64 * 5, nullptr);
+        STOF_LAUNCH_CHECK();
+        bias_grad_ncl_kernel<<<512, 256, 0, st>>>(gpool, N, 512, P, gr->contract_b);
         STOF_LAUNCH_CHECK();
         const int tiles = (L + CD_T - 1) / CD_T;
         STOF_REQUIRE((long long)N * tiles < (1ll << 31), STOF_E_INVALID, "stof_backward: batch too large");
         static SmemAttrOnce cd_attr;
         if ((rc = ensure_dyn_smem(contract_dgrad_kernel, CD_SMEM, cd_attr))) return rc;
-        contract_dgrad_kernel<<<(unsigned)(((N + CD_R - 1) / CD_R) * tiles), CD_THREADS, CD_SMEM, st>>>(gpool, argmax, m->raw_contract_w, N, L, P, tiles, S);
+        contract_dgrad_kernel<<<(unsigned)(((N + CD_R - 1) / CD_R) * tiles), CD_THREADS, CD_SMEM, st>>>(gpool, argmax, m->raw_contract_w, N, L, P, tiles, S,
+                                                                                                        reinterpret_cast<const float4 *>(x0r));
         STOF_LAUNCH_CHECK();
     }
     // ---- conv1: x0r = relu(conv1 x)
-    relu_bwd_kernel<<<ew_grid(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(S), reinterpret_cast<const float4 *>(x0r), n4);
-    STOF_LAUNCH_CHECK();
+    if (!pl.sgb) {                                    // with the semi-global block: applied by contract_dgrad's write-out
+        relu_bwd_kernel<<<ew_grid(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(S), reinterpret_cast<const float4 *>(x0r), n4);
+        STOF_LAUNCH_CHECK();
+    }
     {
         const int chunks = (L + C1_CHUNK - 1) / C1_CHUNK;
         const long long total = (long long)N * chunks;
