@@ -97,7 +97,7 @@ __device__ __forceinline__ void issue_layer_taps(uint32_t a_base, uint32_t w_bas
     umma_commit(bar_acc_full);
 }
 
-template <bool FAST>
+template <bool FAST, bool GRAD>
 __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     const uint32_t sbase = smem_u32(smem);
@@ -288,6 +288,30 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
         const uint32_t lane_addr = (uint32_t)(32 * quad) << 16;
         const bool tl_on = (warp == 3) && (lane == 0);
         const bool free_early = (p.stash == 0);     // free_layer has an even index: it reads P as operand only
+        // gradient mode (training step, one TC_NONE layer per launch): out_stored = (conv(in_stored) * g_sk [+ aux_stored * g_ss])
+        // [* lrelu'(aux)], the powers of two chosen so that a bound of max |out| lands in [2^10, 2^11)
+        float g_sk = 1.0f, g_ss = 1.0f, g_amax = 0.0f;
+        float g_bsum[32];
+        int g_mode = 0;
+        if (GRAD) {
+            g_mode = p.grad.mode;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) g_bsum[i] = 0.0f;
+            const unsigned in_bits = __ldg(&p.grad.g_in->amax_bits);
+            const int e_in = __ldg(&p.grad.g_in->E);
+            auto pow2 = [](int d) { d = d < -126 ? -126 : (d > 127 ? 127 : d); return __uint_as_float((unsigned)(d + 127) << 23); };
+            float bound = __uint_as_float(in_bits) * pow2(-e_in);
+            int e_aux = 0;
+            if (g_mode == 2) {
+                e_aux = __ldg(&p.grad.g_aux->E);
+                bound += __uint_as_float(__ldg(&p.grad.g_aux->amax_bits)) * pow2(-e_aux);
+            }
+            const int eb = (int)((__float_as_uint(bound) >> 23) & 255u);
+            const int e_out = (eb == 0 || eb == 255) ? e_in : 10 - (eb - 127);
+            g_sk = pow2(e_out - e_in);
+            g_ss = pow2(e_out - e_aux);
+            if (blockIdx.x == 0 && warp == 3 && lane == 0) p.grad.g_out->E = e_out;
+        }
         uint32_t lseq = 0;
         int it = 0;
         for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
@@ -308,8 +332,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                     // long skip (res1 = x0 planes in global memory): issue the loads before waiting for the accumulator so
                     // that their latency hides behind the block's MMAs (the producer has pulled the rows into L2)
                     uint4 xs_h[4], xs_l[4];
-                    if (type == TC_LONGSKIP) {
-                        const uint4 *x0 = reinterpret_cast<const uint4 *>(p.x0) + (size_t)n * 16 * p.L;
+                    if (type == TC_LONGSKIP || (GRAD && g_mode >= 2)) {
+                        const uint4 *x0 = reinterpret_cast<const uint4 *>(GRAD ? p.grad.aux : p.x0) + (size_t)n * 16 * p.L;
 #pragma unroll
                         for (int h = 0; h < 4; ++h) {
                             xs_h[h] = inside ? __ldg(x0 + (size_t)(4 * egrp + h) * p.L + l) : make_uint4(0, 0, 0, 0);
@@ -380,6 +404,32 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
                                 for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.0f);
                             } else if (type == TC_NONE) {
                                 // conv + bias only (data gradient of a conv: no activation, no skip)
+                                if (GRAD) {
+#pragma unroll
+                                    for (int i = 0; i < 8; ++i) v[i] *= g_sk;
+                                    if (g_mode == 2) {
+                                        float fh[8], fl[8];
+                                        unpack8(xs_h[h], fh);
+                                        unpack8(xs_l[h], fl);
+#pragma unroll
+                                        for (int i = 0; i < 8; ++i) v[i] = fmaf(fh[i] + TC_LO_INV * fl[i], g_ss, v[i]);
+                                    } else if (g_mode == 3) {
+                                        const uint32_t hw[4] = {xs_h[h].x, xs_h[h].y, xs_h[h].z, xs_h[h].w};
+                                        const uint32_t lw[4] = {xs_l[h].x, xs_l[h].y, xs_l[h].z, xs_l[h].w};
+#pragma unroll
+                                        for (int i = 0; i < 8; ++i) {
+                                            const uint32_t hv = (hw[i >> 1] >> (16 * (i & 1))) & 0xffffu, lv = (lw[i >> 1] >> (16 * (i & 1))) & 0xffffu;
+                                            // a > 0 <=> its hi plane is positive, or zero with a positive lo plane
+                                            const bool pos = ((hv & 0x7fffu) != 0u) ? ((hv & 0x8000u) == 0u)
+                                                                                    : (((lv & 0x7fffu) != 0u) && ((lv & 0x8000u) == 0u));
+                                            v[i] *= pos ? 1.0f : kLeakySlope;
+                                        }
+                                    }
+                                    if (store_global) {
+#pragma unroll
+                                        for (int i = 0; i < 8; ++i) { g_amax = fmaxf(g_amax, fabsf(v[i])); g_bsum[8 * h + i] += v[i]; }
+                                    }
+                                }
                             } else if (from_stash) {
                                 // short skip of the segment's last layer: fp32 copy parked in TMEM by the previous layer's epilogue
                                 uint32_t rs[8];
@@ -459,6 +509,38 @@ __global__ void __launch_bounds__(TC_THREADS, 1) chain_tc_kernel(const TcParams 
             }
         }
         if (tl_on) TL_FLUSH(3u);
+        if (GRAD) {
+            // max |stored output| of this launch; bias-gradient sums of this CTA: lanes (rows) by shuffle tree, then the four
+            // quadrant warps of each channel half in order (after the CTA-wide barrier below: the operand buffers are free then)
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) g_amax = fmaxf(g_amax, __shfl_xor_sync(0xffffffffu, g_amax, o));
+            if (lane == 0 && g_amax > 0.0f) atomicMax(&p.grad.g_out->amax_bits, __float_as_uint(g_amax));
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) g_bsum[i] += __shfl_xor_sync(0xffffffffu, g_bsum[i], o);
+            tc_fence_before_sync();
+            __syncthreads();
+            float *red = reinterpret_cast<float *>(smem + TC_OFF_P);                   // [8 epilogue warps][32]
+            float mine = 0.0f;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) if (lane == i) mine = g_bsum[i];
+            red[(warp - 3) * 32 + lane] = mine;
+        }
+    }
+    if (GRAD) {
+        if (warp < 3) { tc_fence_before_sync(); __syncthreads(); }
+        __syncthreads();
+        if (p.grad.bias_partial != nullptr && threadIdx.x < 64) {
+            const int egrp = threadIdx.x >> 5, c = threadIdx.x & 31;
+            const float *red = reinterpret_cast<const float *>(smem + TC_OFF_P) + (4 * egrp) * 32 + c;
+            p.grad.bias_partial[(size_t)blockIdx.x * 64 + threadIdx.x] = ((red[0] + red[32]) + red[64]) + red[96];
+        }
+        if (warp == 1) {
+            tc_fence_after_sync();
+            tmem_dealloc(tmem0, 512);
+        }
+        return;
     }
 
     // ---- teardown --------------------------------------------------------------------------------------
@@ -593,64 +675,41 @@ c4l4_to_planes_kernel(const float4 *__restrict__ act, uint4 *__restrict__ planes
     planes[((size_t)n * 16 + 8 + c8) * L + l] = ul;
 }
 
-// EX: the gradient hand-over of the training step (train.cu) - v *= lrelu'(a) with a given as split planes (a > 0 <=> its hi plane
-// is positive, or zero with a positive lo plane), and max |written value| folded into *absmax_out (the scale of the NEXT plane
-// conversion of this tensor: saves a pass over it)
+// EX: the end of the training step's gradient chain (train.cu) - planes written by the chain kernel's gradient mode (g * 2^E, E
+// in the tensor's slot) back to fp32, plus a second addend (the long skip's gradient)
 template <bool EX>
 __global__ void __launch_bounds__(256)
 planes_to_c4l4_kernel(const uint4 *__restrict__ planes, float4 *__restrict__ act, int N, int L, const unsigned *__restrict__ absmax_bits,
-                      int add, const uint4 *__restrict__ lrelu_planes, unsigned *__restrict__ absmax_out, const float4 *__restrict__ add2) {
+                      int add, const float4 *__restrict__ add2, const GradSlot *__restrict__ slot) {
     const int n = blockIdx.z, c8 = blockIdx.y;
     const int l = blockIdx.x * 256 + threadIdx.x;
-    float m = 0.0f;
-    if (l < L) {
-        const float inv = 1.0f / plane_scale(absmax_bits);           // exact: a power of two
-        float fh[8], fl[8];
-        unpack8(planes[((size_t)n * 16 + c8) * L + l], fh);
-        unpack8(planes[((size_t)n * 16 + 8 + c8) * L + l], fl);
-        float v[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) v[i] = (fh[i] + TC_LO_INV * fl[i]) * inv;
-        if (EX && lrelu_planes != nullptr) {
-            const uint4 h = __ldg(lrelu_planes + ((size_t)n * 16 + c8) * L + l), lo = __ldg(lrelu_planes + ((size_t)n * 16 + 8 + c8) * L + l);
-            const uint32_t hw[4] = {h.x, h.y, h.z, h.w}, lw[4] = {lo.x, lo.y, lo.z, lo.w};
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const uint32_t hv = (hw[i >> 1] >> (16 * (i & 1))) & 0xffffu, lv = (lw[i >> 1] >> (16 * (i & 1))) & 0xffffu;
-                // fp16 bit patterns: positive <=> sign bit clear and magnitude non-zero
-                const bool pos = ((hv & 0x7fffu) != 0u) ? ((hv & 0x8000u) == 0u) : (((lv & 0x7fffu) != 0u) && ((lv & 0x8000u) == 0u));
-                v[i] *= pos ? 1.f : kLeakySlope;
-            }
-        }
-        float4 *o0 = act + ((size_t)n * 16 + 2 * c8) * L + l, *o1 = act + ((size_t)n * 16 + 2 * c8 + 1) * L + l;
-        float4 r0 = make_float4(v[0], v[1], v[2], v[3]), r1 = make_float4(v[4], v[5], v[6], v[7]);
-        if (add) {
-            const float4 p0 = *o0, p1 = *o1;
-            r0.x += p0.x; r0.y += p0.y; r0.z += p0.z; r0.w += p0.w;
-            r1.x += p1.x; r1.y += p1.y; r1.z += p1.z; r1.w += p1.w;
-        }
-        if (EX && add2 != nullptr) {                                 // a second addend (the long skip's gradient at the end of the chain)
-            const float4 q0 = __ldg(add2 + ((size_t)n * 16 + 2 * c8) * L + l), q1 = __ldg(add2 + ((size_t)n * 16 + 2 * c8 + 1) * L + l);
-            r0.x += q0.x; r0.y += q0.y; r0.z += q0.z; r0.w += q0.w;
-            r1.x += q1.x; r1.y += q1.y; r1.z += q1.z; r1.w += q1.w;
-        }
-        *o0 = r0;
-        *o1 = r1;
-        if (EX) m = fmaxf(fmaxf(fmaxf(fabsf(r0.x), fabsf(r0.y)), fmaxf(fabsf(r0.z), fabsf(r0.w))),
-                          fmaxf(fmaxf(fabsf(r1.x), fabsf(r1.y)), fmaxf(fabsf(r1.z), fabsf(r1.w))));
+    if (l >= L) return;
+    float inv = 1.0f / plane_scale(absmax_bits);                     // exact: a power of two
+    if (EX && slot != nullptr) {
+        int d = -__ldg(&slot->E);
+        d = d < -126 ? -126 : (d > 127 ? 127 : d);
+        inv = __uint_as_float((unsigned)(d + 127) << 23);
     }
-    if (EX && absmax_out != nullptr) {
+    float fh[8], fl[8];
+    unpack8(planes[((size_t)n * 16 + c8) * L + l], fh);
+    unpack8(planes[((size_t)n * 16 + 8 + c8) * L + l], fl);
+    float v[8];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-        __shared__ float wm[8];
-        if ((threadIdx.x & 31) == 0) wm[threadIdx.x >> 5] = m;
-        __syncthreads();
-        if (threadIdx.x == 0) {
-#pragma unroll
-            for (int i = 1; i < 8; ++i) m = fmaxf(m, wm[i]);
-            if (m > 0.0f) atomicMax(absmax_out, __float_as_uint(m));
-        }
+    for (int i = 0; i < 8; ++i) v[i] = (fh[i] + TC_LO_INV * fl[i]) * inv;
+    float4 *o0 = act + ((size_t)n * 16 + 2 * c8) * L + l, *o1 = act + ((size_t)n * 16 + 2 * c8 + 1) * L + l;
+    float4 r0 = make_float4(v[0], v[1], v[2], v[3]), r1 = make_float4(v[4], v[5], v[6], v[7]);
+    if (add) {
+        const float4 p0 = *o0, p1 = *o1;
+        r0.x += p0.x; r0.y += p0.y; r0.z += p0.z; r0.w += p0.w;
+        r1.x += p1.x; r1.y += p1.y; r1.z += p1.z; r1.w += p1.w;
     }
+    if (EX && add2 != nullptr) {
+        const float4 q0 = __ldg(add2 + ((size_t)n * 16 + 2 * c8) * L + l), q1 = __ldg(add2 + ((size_t)n * 16 + 2 * c8 + 1) * L + l);
+        r0.x += q0.x; r0.y += q0.y; r0.z += q0.z; r0.w += q0.w;
+        r1.x += q1.x; r1.y += q1.y; r1.z += q1.z; r1.w += q1.w;
+    }
+    *o0 = r0;
+    *o1 = r1;
 }
 
 // fp32 C4L4 gradient -> scaled split planes (as c4l4_to_planes_kernel with absmax_bits), 4 positions per thread, and the bias
@@ -659,9 +718,14 @@ planes_to_c4l4_kernel(const uint4 *__restrict__ planes, float4 *__restrict__ act
 constexpr int G2P_Q = 4;
 __global__ void __launch_bounds__(256)
 grad_to_planes_kernel(const float4 *__restrict__ act, uint4 *__restrict__ planes, int N, int L, const unsigned *__restrict__ absmax_bits,
-                      float *__restrict__ bias_partial) {
+                      float *__restrict__ bias_partial, GradSlot *__restrict__ slot_out) {
     const int n = blockIdx.z, c8 = blockIdx.y;
     const float sc = plane_scale(absmax_bits);
+    if (slot_out != nullptr && blockIdx.x == 0 && c8 == 0 && n == 0 && threadIdx.x == 0) {
+        // the planes' slot for the chain kernel's gradient mode: E = log2 of the scale, max |stored| = max |g| * scale
+        slot_out->E = (int)((__float_as_uint(sc) >> 23) & 255u) - 127;
+        slot_out->amax_bits = __float_as_uint(__uint_as_float(__ldg(absmax_bits)) * sc);
+    }
     float s[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
     for (int q = 0; q < G2P_Q; ++q) {
@@ -720,12 +784,25 @@ static unsigned long long *g_timeline = nullptr;
 static int g_timeline_cap = 0;
 void set_chain_timeline(void *dev_buf, int cap) { g_timeline = reinterpret_cast<unsigned long long *>(dev_buf); g_timeline_cap = cap; }
 
-int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void *x0, void *out_planes, float *out_mask,
-                    int N, int L, cudaStream_t st, int fast) {
+int chain_tc_grid(int count, const TcLayer *layers, int N, int L) {
+    int Sp = 0;
+    for (int k = 1; k < count; ++k) Sp += layers[k].pad;
+    const int t_out = 256 - 2 * Sp;
+    const long long total = (long long)N * ((L + t_out - 1) / t_out);
+    return (int)(total < kSMs ? total : kSMs);
+}
+
+static int launch_chain_impl(const TcLayer *layers, int count, const void *in, const void *x0, void *out_planes, float *out_mask,
+                             int N, int L, cudaStream_t st, int fast, const TcGrad *grad) {
     STOF_REQUIRE(count >= 1 && count <= TC_MAX_LAYERS, STOF_E_INVALID, "chain_tc: %d layers per segment (max %d)", count, TC_MAX_LAYERS);
     static SmemAttrOnce attr_exact, attr_fast;
-    { const int rc = fast ? ensure_dyn_smem(chain_tc_kernel<true>, TC_SMEM_BYTES, attr_fast)
-                          : ensure_dyn_smem(chain_tc_kernel<false>, TC_SMEM_BYTES, attr_exact); if (rc) return rc; }
+    static SmemAttrOnce attr_grad;
+    STOF_REQUIRE(grad == nullptr || (!fast && count == 1 && layers[0].type == TC_NONE && grad->mode >= 1 && grad->mode <= 3 && grad->g_in &&
+                                     grad->g_out && (grad->mode == 1 || grad->aux) && (grad->mode != 2 || grad->g_aux)),
+                 STOF_E_INVALID, "chain_tc: gradient mode needs one TC_NONE layer, exact arithmetic and its slots");
+    { const int rc = grad ? ensure_dyn_smem(chain_tc_kernel<false, true>, TC_SMEM_BYTES, attr_grad)
+                   : fast ? ensure_dyn_smem(chain_tc_kernel<true, false>, TC_SMEM_BYTES, attr_fast)
+                          : ensure_dyn_smem(chain_tc_kernel<false, false>, TC_SMEM_BYTES, attr_exact); if (rc) return rc; }
     TcParams p;
     memset(&p, 0, sizeof(p));
     int S = 0, Sp = 0;
@@ -777,10 +854,19 @@ int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void
     const bool ends_last = layers[count - 1].type == TC_LAST;
     STOF_REQUIRE(ends_last ? out_mask != nullptr : out_planes != nullptr, STOF_E_INVALID, "chain_tc: missing output buffer");
     const int grid = (int)(total < kSMs ? total : kSMs);
-    if (fast) chain_tc_kernel<true><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(p);
-    else chain_tc_kernel<false><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(p);
+    if (grad) { p.grad = *grad; chain_tc_kernel<false, true><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(p); }
+    else if (fast) chain_tc_kernel<true, false><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(p);
+    else chain_tc_kernel<false, false><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(p);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
+}
+
+int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void *x0, void *out_planes, float *out_mask,
+                    int N, int L, cudaStream_t st, int fast) {
+    return launch_chain_impl(layers, count, in, x0, out_planes, out_mask, N, L, st, fast, nullptr);
+}
+int launch_chain_tc_grad(const TcLayer *layer, const void *in, void *out_planes, int N, int L, cudaStream_t st, const TcGrad &grad) {
+    return launch_chain_impl(layer, 1, in, nullptr, out_planes, nullptr, N, L, st, 0, &grad);
 }
 
 int launch_x0_split(const float *x, const float *e, int N, int L, int P, int scale, int off, const float *w, const float *b,
@@ -806,27 +892,28 @@ int launch_planes_to_c4l4(const void *planes, float *act, int N, int L, cudaStre
     STOF_REQUIRE(N <= 65535, STOF_E_INVALID, "planes_to_c4l4: at most 65535 rows per call");
     dim3 grid((L + 255) / 256, 8, N);
     planes_to_c4l4_kernel<false><<<grid, 256, 0, st>>>(reinterpret_cast<const uint4 *>(planes), reinterpret_cast<float4 *>(act), N, L, absmax_bits, add,
-                                                       nullptr, nullptr, nullptr);
+                                                       nullptr, nullptr);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }
 
-int launch_planes_to_c4l4_ex(const void *planes, float *act, int N, int L, cudaStream_t st, const unsigned *absmax_bits, int add,
-                             const void *lrelu_planes, unsigned *absmax_out, const float *add2) {
+int launch_grad_planes_to_c4l4(const void *planes, float *act, int N, int L, cudaStream_t st, const GradSlot *slot, const float *add2) {
     STOF_REQUIRE(N <= 65535, STOF_E_INVALID, "planes_to_c4l4: at most 65535 rows per call");
     dim3 grid((L + 255) / 256, 8, N);
-    planes_to_c4l4_kernel<true><<<grid, 256, 0, st>>>(reinterpret_cast<const uint4 *>(planes), reinterpret_cast<float4 *>(act), N, L, absmax_bits, add,
-                                                      reinterpret_cast<const uint4 *>(lrelu_planes), absmax_out, reinterpret_cast<const float4 *>(add2));
+    planes_to_c4l4_kernel<true><<<grid, 256, 0, st>>>(reinterpret_cast<const uint4 *>(planes), reinterpret_cast<float4 *>(act), N, L, nullptr, 0,
+                                                      reinterpret_cast<const float4 *>(add2), slot);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }
 
 int grad_to_planes_parts(int N, int L) { return N * ((L + 256 * G2P_Q - 1) / (256 * G2P_Q)); }
 
-int launch_grad_to_planes(const float *g, void *planes, int N, int L, cudaStream_t st, const unsigned *absmax_bits, float *bias_partial) {
+int launch_grad_to_planes(const float *g, void *planes, int N, int L, cudaStream_t st, const unsigned *absmax_bits, float *bias_partial,
+                          GradSlot *slot_out) {
     STOF_REQUIRE(N <= 65535, STOF_E_INVALID, "grad_to_planes: at most 65535 rows per call");
     dim3 grid((L + 256 * G2P_Q - 1) / (256 * G2P_Q), 8, N);
-    grad_to_planes_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float4 *>(g), reinterpret_cast<uint4 *>(planes), N, L, absmax_bits, bias_partial);
+    grad_to_planes_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float4 *>(g), reinterpret_cast<uint4 *>(planes), N, L, absmax_bits, bias_partial,
+                                                slot_out);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }

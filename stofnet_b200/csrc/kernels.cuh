@@ -49,6 +49,21 @@ struct TcLayer {
     int stage_bytes2_fast, rows2_fast;
 };
 
+// Training step: a gradient tensor kept as split planes holds g * 2^E; its slot records E and the bit pattern of max |stored value|
+// (non-negative floats order like their bit patterns: atomicMax).  The chain kernel's gradient mode (TcGrad) reads the slots of
+// its operands, chooses the output's E from them on the device, and records the output's slot - no pass over a gradient tensor
+// just to find its scale.
+struct GradSlot { unsigned amax_bits; int E; };
+struct TcGrad {
+    int mode;                   // 1: out = conv(in);  2: out = conv(in) + aux (aux = gradient planes with their own slot);
+                                // 3: out = conv(in) * lrelu'(aux) (aux = activation planes)
+    const void *aux;
+    const GradSlot *g_in, *g_aux;
+    GradSlot *g_out;            // amax_bits zeroed by the caller
+    float *bias_partial;        // [gridDim][64]: per-CTA sums of the stored output over its valid rows (bias gradient of the conv
+                                // whose output gradient this is), or NULL
+};
+
 struct TcParams {
     TcLayer layer[TC_MAX_LAYERS];
     int n_layers;
@@ -70,20 +85,24 @@ struct TcParams {
     float *out_mask;            // (N, 4L) when the segment ends with TC_LAST
     unsigned long long *timeline;   // debug: [0] = event count, then (code, clock64) pairs written by CTA 0; or NULL
     int timeline_cap;
+    TcGrad grad;                // gradient mode of the training step (chain_tc_kernel<false, true> only; mode 0 otherwise)
 };
 void set_chain_timeline(void *dev_buf, int cap);
 
 // layers[first .. first+count) of the spec list; returns STOF_E_* on error
 int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void *x0, void *out_planes, float *out_mask,
                     int N, int L, cudaStream_t st, int fast = 0);
+// one TC_NONE layer in gradient mode (the training step's data gradients; see TcGrad)
+int launch_chain_tc_grad(const TcLayer *layer, const void *in, void *out_planes, int N, int L, cudaStream_t st, const TcGrad &grad);
+int chain_tc_grid(int count, const TcLayer *layers, int N, int L);       // CTAs of that launch (= parts of TcGrad::bias_partial)
 // conv_tc2.cu: the same segment on CTA pairs (2-CTA clusters, tcgen05 cta_group::2: M = 256 per MMA, each CTA reads half of B)
 int launch_chain_tc2(const TcLayer *layers, int count, const void *in, const void *x0, void *out_planes, float *out_mask,
                      int N, int L, cudaStream_t st, int fast = 0);
-// wgrad_tc.cu: weight gradient of a 64 -> 64 k7 conv on tcgen05 from the split planes of the output gradient (scaled: absmax_bits
-// as in launch_c4l4_to_planes) and of the conv's input; dW in PyTorch's (64, 64, 7) layout; scratch: wgrad_tc_scratch_floats()
+// wgrad_tc.cu: weight gradient of a 64 -> 64 k7 conv on tcgen05 from the split planes of the output gradient (g * 2^E, E in its
+// slot) and of the conv's input; dW in PyTorch's (64, 64, 7) layout; scratch: wgrad_tc_scratch_floats()
 // floats.  Deterministic (fixed-order reduction).  The bias gradient: launch_grad_to_planes + launch_bias_parts_reduce below.
 size_t wgrad_tc_scratch_floats();
-int launch_wgrad_tc(const void *g_planes, const void *a_planes, const unsigned *absmax_bits, int N, int L, float *scratch, float *dW,
+int launch_wgrad_tc(const void *g_planes, const void *a_planes, const GradSlot *slot, int N, int L, float *scratch, float *dW,
                     cudaStream_t st);
 // x (N, L) fp32 -> split planes of x0 = act(conv_first(x)) [+ nearest-upsampled E, centred]  (models/stofnet.py:45,96-115)
 int launch_x0_split(const float *x, const float *e, int N, int L, int P, int scale, int off, const float *w, const float *b,
@@ -100,17 +119,16 @@ int launch_expand_tc(const float *pooled, float *e, const void *w_packed, const 
 int launch_c4l4_to_planes(const float *act, void *planes, int N, int L, cudaStream_t st, const unsigned *absmax_bits = nullptr);
 int launch_planes_to_c4l4(const void *planes, float *act, int N, int L, cudaStream_t st, const unsigned *absmax_bits = nullptr,
                           int add = 0);
-// The training step's gradient hand-overs with their neighbours fused in (train.cu):
-//   planes -> fp32 with v *= lrelu'(a) (a as split planes, or NULL) before the optional add (and a second addend add2, fp32 C4L4,
-//   or NULL), and max |written value| folded into
-//   *absmax_out (or NULL) - the scale of this tensor's next plane conversion, without a pass of its own;
-//   fp32 -> scaled planes with the bias gradient's partial sums on the way: bias_partial[part][64], grad_to_planes_parts(N, L)
-//   parts, to be added in order by launch_bias_parts_reduce (wgrad_tc.cu)
-int launch_planes_to_c4l4_ex(const void *planes, float *act, int N, int L, cudaStream_t st, const unsigned *absmax_bits, int add,
-                             const void *lrelu_planes, unsigned *absmax_out, const float *add2 = nullptr);
+// The training step's gradient hand-overs (train.cu):
+//   fp32 -> scaled planes with the bias gradient's partial sums on the way (bias_partial[part][64], grad_to_planes_parts(N, L)
+//   parts, added in order by launch_bias_parts_reduce, wgrad_tc.cu) and the planes' slot for the chain kernel's gradient mode;
+//   planes of a slot (g * 2^E) -> fp32, plus a second fp32 addend (or NULL)
+int launch_grad_planes_to_c4l4(const void *planes, float *act, int N, int L, cudaStream_t st, const GradSlot *slot, const float *add2);
 int grad_to_planes_parts(int N, int L);
-int launch_grad_to_planes(const float *g, void *planes, int N, int L, cudaStream_t st, const unsigned *absmax_bits, float *bias_partial);
-int launch_bias_parts_reduce(const float *bias_partial, int parts, float *db, cudaStream_t st);
+int launch_grad_to_planes(const float *g, void *planes, int N, int L, cudaStream_t st, const unsigned *absmax_bits, float *bias_partial,
+                          GradSlot *slot_out = nullptr);
+// slot (or NULL): the partial sums are of stored values g * 2^E - db = 2^-E * sum
+int launch_bias_parts_reduce(const float *bias_partial, int parts, float *db, cudaStream_t st, const GradSlot *slot = nullptr);
 // *out_bits = max(*out_bits, bits of max |v|) over n4 float4 (non-negative floats order like their bit patterns); zero the slot first
 int launch_absmax(const float *v, size_t n4, unsigned *out_bits, cudaStream_t st);
 

@@ -82,7 +82,8 @@ static int make_train_plan(const stof_model *m, int N, int L, TrainPlan *p) {
         for (int j = 0; j < m->n_mid; ++j) { p->off_pa[j] = o; o += p->act; }
         for (int i = 0; i < 2; ++i) { p->off_gp[i] = o; o += p->act; }
         p->off_absmax = o; o += 64;
-        p->off_bpart = o; o += a64((size_t)grad_to_planes_parts(N, L) * 64);
+        { const size_t parts = (size_t)grad_to_planes_parts(N, L) > (size_t)kSMs ? (size_t)grad_to_planes_parts(N, L) : (size_t)kSMs;
+          p->off_bpart = o; o += a64(parts * 64); }
     }
     p->total_bytes = o * sizeof(float);
     return STOF_OK;
@@ -1029,51 +1030,76 @@ extern "C" int stof_backward(stof_model *m, const float *x, const float *g_mask,
         reduce_parts_kernel<<<4, 256, 0, st>>>(partial, g2, 772, gr->last_w, 768, gr->last_b);
         STOF_LAUNCH_CHECK();
     }
-    // One mid conv j of the backward pass, given g = d loss / d (its output): weight gradient with the conv's input (the output of
-    // conv j - 1, or x0), then out (+)= data gradient.  Tensor-core path: max |g| -> power-of-two scale (device side), g -> split
-    // planes ONCE for both products; wgrad_tc.cu; one chain launch with the tap-flipped channel-swapped pack, planes -> fp32.
-    int n_slots = 0;
-    if (pl.tc) {
-        if ((rc = ensure_train_tc(m, st))) return rc;
-        STOF_CUDA(cudaMemsetAsync(ws + pl.off_absmax, 0, 64 * sizeof(float), st));
-    }
     auto pact = [&](int j) -> const void * { return j < 0 ? (const void *)(ws + pl.off_px0) : (const void *)(ws + pl.off_pa[j]); };
-    // lrelu_src (tensor-core path): planes of the activation whose lrelu' multiplies the data gradient on its way back to fp32
-    // (the LEAKY conv below this one).  The hand-overs carry their neighbours: fp32 -> planes also sums the bias gradient's
-    // partials, planes -> fp32 also applies lrelu' and records max |out| in the NEXT slot (the scale of out's own conversion).
-    auto mid_backward = [&](int j, const float *g, float *out, bool accumulate, const void *lrelu_src, const float *extra) -> int {
-        int r;
-        if (!pl.tc) {
+    if (pl.tc) {
+        // ---- mid convs, tensor-core path: the gradients stay in split planes from X to the gradient of x0.
+        // A planes tensor holds g * 2^E with its GradSlot {max |stored|, E} in device memory.  X is converted once (max |X| ->
+        // E, bias partial sums on the way); after that every data gradient is ONE launch of the chain kernel in gradient mode
+        // (conv_tc.cu: the tap-flipped channel-swapped pack, then * lrelu' of the activation planes or + the skip gradient's
+        // planes in the epilogue, the output's E chosen on the device from the operands' slots, max |out| and the bias
+        // gradient's per-CTA sums recorded on the way), and every weight gradient one launch of wgrad_tc on the same planes.
+        if ((rc = ensure_train_tc(m, st))) return rc;
+        STOF_REQUIRE(nm + 2 <= 31, STOF_E_INVALID, "stof_backward: too many mid convs");
+        STOF_CUDA(cudaMemsetAsync(ws + pl.off_absmax, 0, 64 * sizeof(float), st));
+        unsigned *raw_amax = reinterpret_cast<unsigned *>(ws + pl.off_absmax);
+        GradSlot *slots = reinterpret_cast<GradSlot *>(ws + pl.off_absmax + 2);
+        void *buf[3] = {ws + pl.off_gp[0], ws + pl.off_gp[1], ws + pl.off_g[2]};       // planes (the fp32 T buffer is not used on this path)
+        float *bpart = ws + pl.off_bpart;
+        int n_slot = 0;
+        const int cgrid = chain_tc_grid(1, &m->tr_bwd[0], N, L);
+        // X -> planes
+        if ((rc = launch_absmax(X, n4, raw_amax, st))) return rc;
+        if ((rc = launch_grad_to_planes(X, buf[0], N, L, st, raw_amax, bpart, &slots[0]))) return rc;
+        if ((rc = launch_bias_parts_reduce(bpart, grad_to_planes_parts(N, L), gr->mid_b[nm - 1], st))) return rc;
+        // g (planes, slot) = gradient wrt the output of conv j: dW_j; out = dgrad_j(g) [* lrelu'(a) | + skip] with its slot and the
+        // bias gradient of the conv below (db_below, whose output gradient `out` is)
+        auto step = [&](int j, int gi, int gslot, int oi, int mode, const void *aux, int aux_slot, float *db_below) -> int {
+            int r;
+            if ((r = launch_wgrad_tc(buf[gi], pact(j - 1), &slots[gslot], N, L, partial, gr->mid_w[j], st))) return r;
+            TcGrad g;
+            g.mode = mode; g.aux = aux;
+            g.g_in = &slots[gslot]; g.g_aux = aux_slot >= 0 ? &slots[aux_slot] : nullptr;
+            g.g_out = &slots[++n_slot];
+            g.bias_partial = db_below ? bpart : nullptr;
+            if ((r = launch_chain_tc_grad(&m->tr_bwd[j], buf[gi], buf[oi], N, L, st, g))) return r;
+            if (db_below && (r = launch_bias_parts_reduce(bpart, cgrid, db_below, st, g.g_out))) return r;
+            return STOF_OK;
+        };
+        // conv{nm-1} (long skip): a = x0 + conv(a_prev): g_conv = X;  S = dgrad(X) = gradient wrt a_{nm-2}
+        int si = 1, s_slot;
+        if ((rc = step(nm - 1, 0, 0, si, 1, nullptr, -1, nm >= 2 ? gr->mid_b[nm - 2] : nullptr))) return rc;
+        s_slot = n_slot;
+        // pairs (RES j, LEAKY j - 1), j = nm-2, nm-4, ..., 1
+        for (int j = nm - 2; j >= 1; j -= 2) {
+            // a_j = a_{j-2} + conv_j(a_{j-1}):  T = dgrad_j(S) * lrelu'(a_{j-1}) = gradient wrt the output of conv j-1; the skip keeps S
+            const int ti = (si + 1) % 3, s2 = (si + 2) % 3;
+            if ((rc = step(j, si, s_slot, ti, 3, pact(j - 1), -1, gr->mid_b[j - 1]))) return rc;
+            const int t_slot = n_slot;
+            // a_{j-1} = lrelu(conv_{j-1}(a_{j-2})):  S' = S + dgrad_{j-1}(T) = gradient wrt a_{j-2} (the output of conv j-2, or x0)
+            if ((rc = step(j - 1, ti, t_slot, s2, 2, buf[si], s_slot, j - 2 >= 0 ? gr->mid_b[j - 2] : nullptr))) return rc;
+            si = s2; s_slot = n_slot;
+        }
+        // S (planes) = gradient wrt x0 through the chain: back to fp32, + the long skip's X
+        if ((rc = launch_grad_planes_to_c4l4(buf[si], S, N, L, st, &slots[s_slot], X))) return rc;
+    } else {
+        // ---- mid convs, fp32 path: weight gradient with the conv's input (the output of conv j - 1, or x0), then out (+)= data gradient
+        auto mid_backward = [&](int j, const float *g, float *out, bool accumulate) -> int {
+            int r;
             if ((r = mid_wgrad(g, act(j - 1), N, L, partial, gr->mid_w[j], gr->mid_b[j], st))) return r;
             return launch_conv_mid_simt(g, accumulate ? out : nullptr, out, m->bw_mid[j], m->zero_bias, N, L, accumulate ? 1 : 2, st);
-        }
-        STOF_REQUIRE(n_slots < 63, STOF_E_INVALID, "stof_backward: too many mid convs");
-        unsigned *slot = reinterpret_cast<unsigned *>(ws + pl.off_absmax) + (n_slots++);
-        void *gp0 = ws + pl.off_gp[0], *gp1 = ws + pl.off_gp[1];
-        float *bpart = ws + pl.off_bpart;
-        if (n_slots == 1 && (r = launch_absmax(g, n4, slot, st))) return r;          // later slots: written by the previous hand-over
-        if ((r = launch_grad_to_planes(g, gp0, N, L, st, slot, bpart))) return r;
-        if ((r = launch_bias_parts_reduce(bpart, grad_to_planes_parts(N, L), gr->mid_b[j], st))) return r;
-        if ((r = launch_wgrad_tc(gp0, pact(j - 1), slot, N, L, partial, gr->mid_w[j], st))) return r;
-        if ((r = launch_chain_tc(&m->tr_bwd[j], 1, gp0, nullptr, gp1, nullptr, N, L, st))) return r;
-        return launch_planes_to_c4l4_ex(gp1, out, N, L, st, slot, accumulate ? 1 : 0, lrelu_src, slot + 1, extra);
-    };
-    // ---- conv{nb-1} (long skip): a = x0 + conv(a_prev): g_conv = X;  S = dgrad(X)
-    // (tensor-core path: the long skip's gradient X is added by the LAST hand-over of the chain instead of a pass of its own)
-    if ((rc = mid_backward(nm - 1, X, S, false, nullptr, (pl.tc && nm - 2 < 1) ? X : nullptr))) return rc;
-    // ---- pairs (RES j, LEAKY j - 1), j = nm-2, nm-4, ..., 1:   S = g wrt a_j
-    for (int j = nm - 2; j >= 1; j -= 2) {
-        // a_j = a_{j-2} + conv_j(a_{j-1}):  wgrad with input a_{j-1};  T = dgrad_j(S);  skip keeps S
-        // a_{j-1} = lrelu(conv_{j-1}(a_{j-2})):  T *= lrelu'(a_{j-1});  wgrad with input a_{j-2};  S += dgrad_{j-1}(T)
-        if ((rc = mid_backward(j, S, T, false, pl.tc ? pact(j - 1) : nullptr, nullptr))) return rc;
-        if (!pl.tc) {
+        };
+        // conv{nb-1} (long skip): a = x0 + conv(a_prev): g_conv = X;  S = dgrad(X)
+        if ((rc = mid_backward(nm - 1, X, S, false))) return rc;
+        // pairs (RES j, LEAKY j - 1), j = nm-2, nm-4, ..., 1:   S = g wrt a_j
+        for (int j = nm - 2; j >= 1; j -= 2) {
+            // a_j = a_{j-2} + conv_j(a_{j-1}):  wgrad with input a_{j-1};  T = dgrad_j(S);  skip keeps S
+            if ((rc = mid_backward(j, S, T, false))) return rc;
+            // a_{j-1} = lrelu(conv_{j-1}(a_{j-2})):  T *= lrelu'(a_{j-1});  wgrad with input a_{j-2};  S += dgrad_{j-1}(T)
             lrelu_bwd_kernel<<<ew_grid(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(T), reinterpret_cast<const float4 *>(act(j - 1)), n4);
             STOF_LAUNCH_CHECK();
+            if ((rc = mid_backward(j - 1, T, S, true))) return rc;
         }
-        if ((rc = mid_backward(j - 1, T, S, true, nullptr, (pl.tc && j - 2 < 1) ? X : nullptr))) return rc;
-    }
-    // ---- S = g wrt x0 through the chain; add the long skip
-    if (!pl.tc) {
+        // S = g wrt x0 through the chain; add the long skip
         add_kernel<<<ew_grid(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(S), reinterpret_cast<const float4 *>(X), n4);
         STOF_LAUNCH_CHECK();
     }

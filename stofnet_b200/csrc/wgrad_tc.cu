@@ -39,7 +39,7 @@ constexpr int WT_SHARES = kSMs / 2;              // position shares per tap grou
 constexpr size_t WT_PART = (size_t)4 * 128 * 128; // floats of one CTA's partial: [tap of the group][lane][column]
 
 struct WtParams {
-    const void *g_planes;      // [N][2][8][L][8] fp16, scaled by the power of two derived from *absmax_bits
+    const void *g_planes;      // [N][2][8][L][8] fp16, the gradient times 2^E (E in its GradSlot)
     const void *a_planes;      // [N][2][8][L][8] fp16, the conv's input
     float *partial;            // [gridDim.x][4][128][128]
     int N, L, tiles_per_row, total_tiles, shares;
@@ -168,7 +168,7 @@ __global__ void __launch_bounds__(WT_THREADS, 1) wgrad_tc_kernel(const WtParams 
 // w, w + 8, ... in order, and the eight sub-sums are added in order: as deterministic as a single chain, with an eighth of its
 // dependent-load latency (a lone thread per output walking 74 shares took 42 us per layer: 0.47 ms of the 256-row step)
 __global__ void __launch_bounds__(256)
-wgrad_tc_reduce_kernel(const float *__restrict__ partial, int shares, int tiles, const unsigned *__restrict__ absmax_bits,
+wgrad_tc_reduce_kernel(const float *__restrict__ partial, int shares, int tiles, const GradSlot *__restrict__ slot,
                        float *__restrict__ dW) {
     const int half = blockIdx.x & 1, co = (blockIdx.x >> 1) & 63, t = blockIdx.x >> 7;
     const int warp = threadIdx.x >> 5, ci = 32 * half + (threadIdx.x & 31);
@@ -189,16 +189,18 @@ wgrad_tc_reduce_kernel(const float *__restrict__ partial, int shares, int tiles,
 #pragma unroll
     for (int w = 0; w < 8; ++w) { hh += red[0][w][threadIdx.x]; x += red[1][w][threadIdx.x]; }
     float inv = 1.0f;
-    if (absmax_bits != nullptr) {
-        const int e = (int)((__ldg(absmax_bits) >> 23) & 255u);
-        if (e > 10 && e != 255) inv = __uint_as_float((unsigned)(e - 10) << 23);                     // 1 / plane_scale (conv_tc.cu)
+    if (slot != nullptr) {                                           // the gradient planes hold g * 2^E
+        int d = -__ldg(&slot->E);
+        d = d < -126 ? -126 : (d > 127 ? 127 : d);
+        inv = __uint_as_float((unsigned)(d + 127) << 23);
     }
     dW[((size_t)co * 64 + ci) * 7 + t] = (hh + TC_LO_INV * x) * inv;
 }
 
 // db[c] = sum of bias_partial[q][c] over the parts q (grad_to_planes_kernel): thread t adds q = t, t + 256, ... in order, then a
 // fixed tree
-__global__ void __launch_bounds__(256) bias_parts_reduce_kernel(const float *__restrict__ partial, int parts, float *__restrict__ db) {
+__global__ void __launch_bounds__(256) bias_parts_reduce_kernel(const float *__restrict__ partial, int parts, float *__restrict__ db,
+                                                                const GradSlot *__restrict__ slot) {
     const int c = blockIdx.x;
     float s = 0.0f;
     for (int q = threadIdx.x; q < parts; q += 256) s += __ldg(partial + (size_t)q * 64 + c);
@@ -209,14 +211,22 @@ __global__ void __launch_bounds__(256) bias_parts_reduce_kernel(const float *__r
         if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
         __syncthreads();
     }
-    if (threadIdx.x == 0) db[c] = red[0];
+    if (threadIdx.x == 0) {
+        float inv = 1.0f;
+        if (slot != nullptr) {
+            int d = -__ldg(&slot->E);
+            d = d < -126 ? -126 : (d > 127 ? 127 : d);
+            inv = __uint_as_float((unsigned)(d + 127) << 23);
+        }
+        db[c] = red[0] * inv;
+    }
 }
 
 size_t wgrad_tc_scratch_floats() { return (size_t)2 * WT_SHARES * WT_PART; }
 
-// g_planes / a_planes: split planes of the layer's output gradient (scaled, see absmax_bits) and of its input; scratch:
+// g_planes / a_planes: split planes of the layer's output gradient (g * 2^E, slot) and of its input; scratch:
 // wgrad_tc_scratch_floats() floats.  (The bias gradient comes from the partial sums of launch_grad_to_planes, conv_tc.cu.)
-int launch_wgrad_tc(const void *g_planes, const void *a_planes, const unsigned *absmax_bits, int N, int L, float *scratch, float *dW,
+int launch_wgrad_tc(const void *g_planes, const void *a_planes, const GradSlot *slot, int N, int L, float *scratch, float *dW,
                     cudaStream_t st) {
     static SmemAttrOnce attr;
     { const int rc = ensure_dyn_smem(wgrad_tc_kernel, WT_SMEM_BYTES, attr); if (rc) return rc; }
@@ -230,13 +240,13 @@ int launch_wgrad_tc(const void *g_planes, const void *a_planes, const unsigned *
     p.shares = (int)(total < WT_SHARES ? total : WT_SHARES);
     wgrad_tc_kernel<<<2 * p.shares, WT_THREADS, WT_SMEM_BYTES, st>>>(p);
     STOF_LAUNCH_CHECK();
-    wgrad_tc_reduce_kernel<<<7 * 64 * 2, 256, 0, st>>>(scratch, p.shares, p.total_tiles, absmax_bits, dW);
+    wgrad_tc_reduce_kernel<<<7 * 64 * 2, 256, 0, st>>>(scratch, p.shares, p.total_tiles, slot, dW);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }
 
-int launch_bias_parts_reduce(const float *bias_partial, int parts, float *db, cudaStream_t st) {
-    bias_parts_reduce_kernel<<<64, 256, 0, st>>>(bias_partial, parts, db);
+int launch_bias_parts_reduce(const float *bias_partial, int parts, float *db, cudaStream_t st, const GradSlot *slot) {
+    bias_parts_reduce_kernel<<<64, 256, 0, st>>>(bias_partial, parts, db, slot);
     STOF_LAUNCH_CHECK();
     return STOF_OK;
 }

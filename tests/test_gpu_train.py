@@ -65,6 +65,26 @@ def test_backward_is_deterministic(sb, golden, name):
 
 
 @pytest.mark.parametrize("name", CASES)
+def test_backward_is_homogeneous_in_the_loss_scale(sb, golden, name):
+    """The tensor-core backward keeps its gradients as fp16 hi/lo planes times a power of two that each kernel derives on the
+    device from its operands' recorded maxima.  Scaling the loss by 2^k scales every stored maximum and nothing else, so the
+    gradients must come out scaled by exactly 2^k - bit for bit - from 2^-20 (far below fp16's range unscaled) to 2^16."""
+    dev = torch.device("cuda:0")
+    g = golden("train_%s.npz" % name)
+    model = _model(sb, golden, name, dev).train()
+    x = torch.from_numpy(g["x"]).unsqueeze(1).to(dev)
+    gt = torch.from_numpy(g["gt"]).to(dev)
+    grads = {}
+    for k in (0, -20, 16):
+        model.zero_grad()
+        (sb.mask_loss(model(x), gt, 7, 1.0, 20.0, float(g["lambda"])) * (2.0 ** k)).backward()
+        grads[k] = torch.cat([p.grad.reshape(-1) for p in model.parameters()]).clone()
+    assert float(grads[0].abs().max()) > 0
+    for k in (-20, 16):
+        assert torch.equal(grads[k] * (2.0 ** -k), grads[0]), k
+
+
+@pytest.mark.parametrize("name", CASES)
 def test_three_adamw_steps(sb, golden, name):
     dev = torch.device("cuda:0")
     g = golden("train_%s.npz" % name)
