@@ -7,17 +7,13 @@
 // (conv_tc.cu): 16-byte vectors of 8 channels, positions 16 bytes apart - which is exactly the no-swizzle MN-MAJOR UMMA operand
 // layout (core matrix = 8 positions x 8 channels = 128 contiguous bytes; next 8 channels = next slab (SBO), next 8 positions =
 // + 128 bytes (LBO)); a tap shift of the activation operand is a 16-byte shift of its descriptor.  The hi and lo planes are
-// stacked along M and N, so ONE MMA per (tap, 16 positions) yields all four hi/lo products
+// stacked along M and N, so ONE M = 128, N = 128, K = 16 MMA per (tap, 16 positions) yields all four hi/lo products
 //     [G_hi; G_lo] * [A_hi; A_lo]^T = [[hh, hl], [lh, ll]]        dW = hh + 2^-11 (hl + lh)      (ll, 2^-22, is dropped)
-// with fp32 accumulation in TMEM over the whole launch.  What bounds the kernel is what an SM can take in (~20 B/clk of bulk copies
-// under MMA load), so the split over CTAs is chosen for the fewest bytes per MMA: a CTA owns ALL 7 taps of HALF of the input
-// channels - its B operand is [A_hi (32 ci); A_lo (32 ci)], N = 64, 64 TMEM columns per tap (448 of 512) - and streams, per tile
-// of 128 positions of one row, the 32 KB of G planes and the 17 KB of its half of the A planes (incl. the 6-position halo, zero
-// outside the row) through a three-stage bulk-copy ring: 49 KB for 56 MMAs.  (The first version gave a CTA 4 taps of all 64 ci:
-// N = 128, 66.5 KB for 32 MMAs, every tile fetched by two CTAs - 139 us per layer at 256 x 2560 with the tensor pipe 58 % busy.)
-// The grid is two channel halves x 74 position shares; each CTA writes its accumulators once at the end; a second kernel adds the
-// shares in a fixed order (bit-reproducible, no float atomics), folds the hi/lo terms and removes the power of two the gradient
-// planes carry.
+// with fp32 accumulation in TMEM over the whole launch: 128 columns per tap, so a CTA owns 4 taps (taps 0-3 or 4-6) and the
+// grid is two tap groups x 74 position shares.  Each CTA streams its tiles (128 positions of one row: 32 KB of G planes, 34 KB
+// of A planes incl. the 6-position halo, zero outside the row) through a two-stage bulk-copy ring, issues 8 MMAs per tap and
+// tile, and writes its accumulators once at the end; a second kernel adds the shares in a fixed order (bit-reproducible, no
+// float atomics), folds the hi/lo terms and removes the power-of-two scale the gradient planes carry.
 #include <cuda_fp16.h>
 #include <string.h>
 
@@ -31,22 +27,25 @@ constexpr int WT_TK = 128;                       // positions per tile
 constexpr int WT_AR = 136;                       // rows of an activation slab: 128 + 6 halo (+ 2 pad)
 constexpr int WT_GSLAB = WT_TK * 16;
 constexpr int WT_ASLAB = WT_AR * 16;
-constexpr int WT_GBUF = 16 * WT_GSLAB;           // 32,768 B: [G_hi 8 slabs; G_lo 8 slabs]
-constexpr int WT_ABUF = 8 * WT_ASLAB;            // 17,408 B: [A_hi 4 slabs; A_lo 4 slabs] of this CTA's 32 input channels
+constexpr int WT_GBUF = 16 * WT_GSLAB;           // 32,768 B
+constexpr int WT_ABUF = 16 * WT_ASLAB;           // 34,816 B
 constexpr int WT_STAGE = WT_GBUF + WT_ABUF;
-constexpr int WT_STAGES = 3;
+constexpr int WT_STAGES = 2;                       // 3 stages measured no faster (1.52 ms per 11 layers either way): ingest-bound, not latency-bound
+// (Also measured: a CTA owning ALL 7 taps of HALF of the input channels - B = [A_hi (32 ci); A_lo (32 ci)], N = 64, 448 TMEM
+// columns, 49 KB per tile for 56 MMAs instead of 66.5 KB for 32.  147 us per layer instead of 139: an M = 128, K = 16 MMA with
+// MN-major operands takes ~63 cycles whether N is 64 or 128 - the transposed A-operand read sets its time - so halving N halves
+// the work per MMA for nothing; profiles/r11b_wgrad_nhalf_ncu_summary.txt.)
 constexpr int WT_OFF_BAR = WT_STAGES * WT_STAGE;  // full[stages] empty[stages] acc_full
 constexpr int WT_OFF_TMEM = WT_OFF_BAR + (2 * WT_STAGES + 1) * 8;
 constexpr int WT_SMEM_BYTES = WT_OFF_TMEM + 16;
 constexpr int WT_THREADS = 6 * 32;               // producer, MMA issuer, 4 epilogue warps
-constexpr int WT_SHARES = kSMs / 2;              // position shares per channel half
-constexpr int WT_TAPS = 7;
-constexpr size_t WT_PART = (size_t)WT_TAPS * 128 * 64; // floats of one CTA's partial: [tap][lane][column]
+constexpr int WT_SHARES = kSMs / 2;              // position shares per tap group
+constexpr size_t WT_PART = (size_t)4 * 128 * 128; // floats of one CTA's partial: [tap of the group][lane][column]
 
 struct WtParams {
     const void *g_planes;      // [N][2][8][L][8] fp16, the gradient times 2^E (E in its GradSlot)
     const void *a_planes;      // [N][2][8][L][8] fp16, the conv's input
-    float *partial;            // [gridDim.x][7][128][64]
+    float *partial;            // [gridDim.x][4][128][128]
     int N, L, tiles_per_row, total_tiles, shares;
 };
 
@@ -73,7 +72,8 @@ __global__ void __launch_bounds__(WT_THREADS, 1) wgrad_tc_kernel(const WtParams 
     tc_fence_after_sync();
     const uint32_t tmem0 = *s_tmem;
 
-    const int half = blockIdx.x & 1, share = blockIdx.x >> 1;          // input channels 32 half .. 32 half + 31
+    const int group = blockIdx.x & 1, share = blockIdx.x >> 1;
+    const int t0 = 4 * group, ntaps = group ? 3 : 4;
     const int n_my = (p.total_tiles - share + p.shares - 1) / p.shares;        // tiles share, share + shares, ...
 
     if (warp == 0) {
@@ -88,9 +88,8 @@ __global__ void __launch_bounds__(WT_THREADS, 1) wgrad_tc_kernel(const WtParams 
             const int a_lo = max(0, 3 - l0), a_hi = min(WT_TK + 6, p.L - l0 + 3);   // valid A rows: position l0 - 3 + row in [0, L)
             if (gv < WT_TK || a_lo > 0 || a_hi < WT_TK + 6) {
                 // rows outside the waveform: zero (the conv's padding for A; no contribution for G)
-                for (int slab = 0; slab < 16; ++slab)
+                for (int slab = 0; slab < 16; ++slab) {
                     for (int r = gv + lane; r < WT_TK; r += 32) *reinterpret_cast<uint4 *>(gb + slab * WT_GSLAB + r * 16) = make_uint4(0, 0, 0, 0);
-                for (int slab = 0; slab < 8; ++slab) {
                     for (int r = lane; r < a_lo; r += 32) *reinterpret_cast<uint4 *>(ab + slab * WT_ASLAB + r * 16) = make_uint4(0, 0, 0, 0);
                     for (int r = a_hi + lane; r < WT_TK + 6; r += 32) *reinterpret_cast<uint4 *>(ab + slab * WT_ASLAB + r * 16) = make_uint4(0, 0, 0, 0);
                 }
@@ -99,14 +98,12 @@ __global__ void __launch_bounds__(WT_THREADS, 1) wgrad_tc_kernel(const WtParams 
             __syncwarp();
             if (lane == 0) {
                 const uint32_t gbytes = (uint32_t)gv * 16u, abytes = (uint32_t)(a_hi - a_lo) * 16u;
-                mbar_arrive_expect_tx(BAR_FULL(s), 16u * gbytes + 8u * abytes);
+                mbar_arrive_expect_tx(BAR_FULL(s), 16u * (gbytes + abytes));
                 const __half *gsrc = reinterpret_cast<const __half *>(p.g_planes) + (size_t)n * 16 * p.L * 8;
                 const __half *asrc = reinterpret_cast<const __half *>(p.a_planes) + (size_t)n * 16 * p.L * 8;
-                for (int slab = 0; slab < 16; ++slab)
+                for (int slab = 0; slab < 16; ++slab) {
                     bulk_g2s(sbase + s * WT_STAGE + slab * WT_GSLAB, gsrc + ((size_t)slab * p.L + l0) * 8, gbytes, BAR_FULL(s));
-                for (int i = 0; i < 8; ++i) {                               // smem slab i <- plane i / 4, c8 = 4 half + i % 4
-                    const int slab = 8 * (i >> 2) + 4 * half + (i & 3);
-                    bulk_g2s(sbase + s * WT_STAGE + WT_GBUF + i * WT_ASLAB + a_lo * 16, asrc + ((size_t)slab * p.L + l0 - 3 + a_lo) * 8,
+                    bulk_g2s(sbase + s * WT_STAGE + WT_GBUF + slab * WT_ASLAB + a_lo * 16, asrc + ((size_t)slab * p.L + l0 - 3 + a_lo) * 8,
                              abytes, BAR_FULL(s));
                 }
             }
@@ -115,7 +112,7 @@ __global__ void __launch_bounds__(WT_THREADS, 1) wgrad_tc_kernel(const WtParams 
     } else if (warp == 1) {
         // =================================== MMA issuer ==================================================
         // descriptor: start address, LBO = 128 B (next 8 positions = next K core block), SBO = slab (next 8 channels)
-        constexpr uint32_t idesc = umma_idesc_f16_mn(128, 64);
+        constexpr uint32_t idesc = umma_idesc_f16_mn(128, 128);
         constexpr uint32_t kLbo = (128u >> 4) << 16;
         constexpr uint32_t kGHi = ((uint32_t)WT_GSLAB >> 4) | (1u << 14), kAHi = ((uint32_t)WT_ASLAB >> 4) | (1u << 14);
         for (int k = 0; k < n_my; ++k) {
@@ -125,11 +122,11 @@ __global__ void __launch_bounds__(WT_THREADS, 1) wgrad_tc_kernel(const WtParams 
             if (elect_one()) {
                 const uint32_t g0 = ((sbase + s * WT_STAGE) >> 4) | kLbo;
                 const uint32_t a0 = ((sbase + s * WT_STAGE + WT_GBUF) >> 4) | kLbo;
-                for (int t = 0; t < WT_TAPS; ++t) {
+                for (int tl = 0; tl < ntaps; ++tl) {
 #pragma unroll
                     for (int ks = 0; ks < WT_TK / 16; ++ks)
-                        umma_f16(tmem0 + 64u * (uint32_t)t, make_desc(g0 + (uint32_t)(16 * ks), kGHi),
-                                 make_desc(a0 + (uint32_t)(t + 16 * ks), kAHi), idesc, (k > 0 || ks > 0) ? 1u : 0u);
+                        umma_f16(tmem0 + 128u * (uint32_t)tl, make_desc(g0 + (uint32_t)(16 * ks), kGHi),
+                                 make_desc(a0 + (uint32_t)(t0 + tl + 16 * ks), kAHi), idesc, (k > 0 || ks > 0) ? 1u : 0u);
                 }
                 umma_commit(BAR_EMPTY(s));
                 if (k == n_my - 1) umma_commit(BAR_ACC);
@@ -138,7 +135,7 @@ __global__ void __launch_bounds__(WT_THREADS, 1) wgrad_tc_kernel(const WtParams 
         }
     } else {
         // =================================== epilogue (once) =============================================
-        // lane = row of [G_hi (64 co); G_lo (64 co)], column = [A_hi (32 ci) | A_lo (32 ci)]; the lo x lo quadrant is not stored
+        // lane = row of [G_hi (64 co); G_lo (64 co)], column = [A_hi (64 ci) | A_lo (64 ci)]; the lo x lo quadrant is not stored
         const int quad = warp & 3;
         const int row = 32 * quad + lane;
         const uint32_t lane_addr = (uint32_t)(32 * quad) << 16;
@@ -146,13 +143,13 @@ __global__ void __launch_bounds__(WT_THREADS, 1) wgrad_tc_kernel(const WtParams 
         if (n_my > 0) {
             mbar_wait(BAR_ACC, 0u);
             tc_fence_after_sync();
-            const int ncol = (row < 64) ? 64 : 32;
-            for (int tl = 0; tl < WT_TAPS; ++tl) {
-                float4 *dst = reinterpret_cast<float4 *>(out + ((size_t)tl * 128 + row) * 64);
+            const int ncol = (row < 64) ? 128 : 64;
+            for (int tl = 0; tl < ntaps; ++tl) {
+                float4 *dst = reinterpret_cast<float4 *>(out + ((size_t)tl * 128 + row) * 128);
 #pragma unroll 1
                 for (int c = 0; c < ncol; c += 16) {
                     uint32_t d[16];
-                    tmem_ld16(tmem0 + 64u * (uint32_t)tl + lane_addr + (uint32_t)c, d);
+                    tmem_ld16(tmem0 + 128u * (uint32_t)tl + lane_addr + (uint32_t)c, d);
                     tmem_ld_wait();
 #pragma unroll
                     for (int i = 0; i < 4; ++i)
@@ -171,20 +168,21 @@ __global__ void __launch_bounds__(WT_THREADS, 1) wgrad_tc_kernel(const WtParams 
 }
 
 // dW[co][ci][t] (PyTorch layout) = 2^-k * sum over shares (fixed order) of  hh + 2^-11 (hl + lh).
-// One block per (tap, co, half of the ci = the CTAs of that half): lane = ci (coalesced reads of the partials), warp w adds the shares
+// One block per (tap, co, half of the ci): lane = ci (128-byte coalesced reads of the partials), warp w adds the shares
 // w, w + 8, ... in order, and the eight sub-sums are added in order: as deterministic as a single chain, with an eighth of its
 // dependent-load latency (a lone thread per output walking 74 shares took 42 us per layer: 0.47 ms of the 256-row step)
 __global__ void __launch_bounds__(256)
 wgrad_tc_reduce_kernel(const float *__restrict__ partial, int shares, int tiles, const GradSlot *__restrict__ slot,
                        float *__restrict__ dW) {
     const int half = blockIdx.x & 1, co = (blockIdx.x >> 1) & 63, t = blockIdx.x >> 7;
-    const int warp = threadIdx.x >> 5, cl = threadIdx.x & 31, ci = 32 * half + cl;
+    const int warp = threadIdx.x >> 5, ci = 32 * half + (threadIdx.x & 31);
+    const int group = t >> 2, tl = t & 3;
     float hh = 0.0f, x = 0.0f;
     const int used = shares < tiles ? shares : tiles;            // shares beyond the tile count wrote nothing
     for (int sh = warp; sh < used; sh += 8) {
-        const float *P = partial + ((size_t)(2 * sh + half) * WT_TAPS + t) * 128 * 64;       // the CTA of this channel half
-        hh += __ldg(P + (size_t)co * 64 + cl);
-        x += __ldg(P + (size_t)co * 64 + 32 + cl) + __ldg(P + (size_t)(64 + co) * 64 + cl);
+        const float *P = partial + ((size_t)(2 * sh + group) * 4 + tl) * 128 * 128;
+        hh += __ldg(P + (size_t)co * 128 + ci);
+        x += __ldg(P + (size_t)co * 128 + 64 + ci) + __ldg(P + (size_t)(64 + co) * 128 + ci);
     }
     __shared__ float red[2][8][32];
     red[0][warp][threadIdx.x & 31] = hh;
