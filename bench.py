@@ -376,9 +376,11 @@ def other_configs(sb, dev, rank, world, cpu):
             rng = np.random.default_rng(5 + rank)
             gt = torch.from_numpy(rng.integers(100, 4 * 2560 - 100, size=(rows, 1, 3))).to(dev)
             ms = dev_ms(lambda: tr.step(x, gt), 2, 5)
-            res["batch_%d" % rows] = {"ms_per_step": ms, "rows_per_s": rows * world / (ms / 1e3)}
+            # forward + data gradient + weight gradient of every conv: 3 x the forward's algorithmic FLOPs
+            res["batch_%d" % rows] = {"ms_per_step": ms, "rows_per_s": rows * world / (ms / 1e3),
+                                      "algorithmic_tflops": 3 * flops_row(2560) * rows * world / (ms / 1e3) / 1e12}
             if world == 1:
-                # the same step replayed from ONE CUDA graph (Trainer.capture): what is left when the ~140 launches cost no host time
+                # the same step replayed from ONE CUDA graph (Trainer.capture): what is left when the ~100 launches cost no host time
                 tr.capture(x, gt)
                 ms = dev_ms(lambda: tr.step_graph(x, gt), 3, 10)
                 res["batch_%d" % rows]["cuda_graph"] = {"ms_per_step": ms, "rows_per_s": rows / (ms / 1e3)}
