@@ -34,7 +34,9 @@ constexpr int WT_STAGES = 2;                       // 3 stages measured no faste
 // (Also measured: a CTA owning ALL 7 taps of HALF of the input channels - B = [A_hi (32 ci); A_lo (32 ci)], N = 64, 448 TMEM
 // columns, 49 KB per tile for 56 MMAs instead of 66.5 KB for 32.  147 us per layer instead of 139: an M = 128, K = 16 MMA with
 // MN-major operands takes ~63 cycles whether N is 64 or 128 - the transposed A-operand read sets its time - so halving N halves
-// the work per MMA for nothing; profiles/r11b_wgrad_nhalf_ncu_summary.txt.)
+// the work per MMA for nothing; profiles/r11b_wgrad_nhalf_ncu_summary.txt.  And CTA pairs - one cta_group::2 MMA computing two
+// taps, the peer's G operand one position earlier, each CTA holding half of B: 49 KB per tile, every tile fetched once - verified
+// against all training tests and slower still, 154 us: tools/experiments/wgrad_tc_pair.cu, profiles/r11d_wgrad_pair_ncu_summary.txt.)
 constexpr int WT_OFF_BAR = WT_STAGES * WT_STAGE;  // full[stages] empty[stages] acc_full
 constexpr int WT_OFF_TMEM = WT_OFF_BAR + (2 * WT_STAGES + 1) * 8;
 constexpr int WT_SMEM_BYTES = WT_OFF_TMEM + 16;
