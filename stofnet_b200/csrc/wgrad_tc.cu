@@ -36,7 +36,9 @@ constexpr int WT_STAGES = 2;                       // 3 stages measured no faste
 // MN-major operands takes ~63 cycles whether N is 64 or 128 - the transposed A-operand read sets its time - so halving N halves
 // the work per MMA for nothing; profiles/r11b_wgrad_nhalf_ncu_summary.txt.  And CTA pairs - one cta_group::2 MMA computing two
 // taps, the peer's G operand one position earlier, each CTA holding half of B: 49 KB per tile, every tile fetched once - verified
-// against all training tests and slower still, 154 us: tools/experiments/wgrad_tc_pair.cu, profiles/r11d_wgrad_pair_ncu_summary.txt.)
+// against all training tests and slower still, 154 us: tools/experiments/wgrad_tc_pair.cu, profiles/r11d_wgrad_pair_ncu_summary.txt.
+// Slab strides of 16 bytes mod 128 instead of 0 mod 128 (in case one position's vectors of the 16 slabs collide in one bank
+// group): 138 vs 139.5 us - no.)
 constexpr int WT_OFF_BAR = WT_STAGES * WT_STAGE;  // full[stages] empty[stages] acc_full
 constexpr int WT_OFF_TMEM = WT_OFF_BAR + (2 * WT_STAGES + 1) * 8;
 constexpr int WT_SMEM_BYTES = WT_OFF_TMEM + 16;
