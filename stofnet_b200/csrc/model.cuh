@@ -59,6 +59,11 @@ struct stof_model {
     void *tr_tc_w = nullptr;
     stof::TcLayer tr_fwd[STOF_MAX_MID_CONVS], tr_bwd[STOF_MAX_MID_CONVS];
     bool tr_tc_dirty = true;
+    // backward pass: the weight / bias gradients of the mid convs run on a side stream next to the data-gradient chain (they only
+    // read what the chain has produced); events fork and join it, also under CUDA-graph capture
+    cudaStream_t tr_side = nullptr;
+    static constexpr int kTrainEvents = 2 * STOF_MAX_MID_CONVS + 4;
+    cudaEvent_t tr_ev[kTrainEvents] = {};
     // scratch of stof_infer_host (grow-only)
     static constexpr int kPipe = 2;
     cudaStream_t streams[kPipe] = {nullptr, nullptr};

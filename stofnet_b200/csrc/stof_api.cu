@@ -740,6 +740,8 @@ extern "C" void stof_model_destroy(stof_model *m) {
     if (m->tc_w2) cudaFree(m->tc_w2);
     if (m->tc_w2_fast) cudaFree(m->tc_w2_fast);
     if (m->tr_tc_w) cudaFree(m->tr_tc_w);
+    if (m->tr_side) cudaStreamDestroy(m->tr_side);
+    for (cudaEvent_t e : m->tr_ev) if (e) cudaEventDestroy(e);
     if (m->tc_contract_w) cudaFree(m->tc_contract_w);
     if (m->tc_expand_w) cudaFree(m->tc_expand_w);
     if (m->h_stats) cudaFreeHost(m->h_stats);

@@ -34,7 +34,7 @@ struct TrainPlan {
     // tensor-core path: split planes (same size as an fp32 tensor) of x0 and of every mid conv's output, two gradient planes,
     // and the max |g| slots (one unsigned per data-gradient call)
     bool tc;
-    size_t off_px0, off_pa[STOF_MAX_MID_CONVS], off_gp[2], off_absmax, off_bpart;
+    size_t off_px0, off_pa[STOF_MAX_MID_CONVS], off_gp[2], off_absmax, off_bpart, off_bparts, off_wpart;
     size_t total_bytes;
 };
 
@@ -82,8 +82,9 @@ static int make_train_plan(const stof_model *m, int N, int L, TrainPlan *p) {
         for (int j = 0; j < m->n_mid; ++j) { p->off_pa[j] = o; o += p->act; }
         for (int i = 0; i < 2; ++i) { p->off_gp[i] = o; o += p->act; }
         p->off_absmax = o; o += 64;
-        { const size_t parts = (size_t)grad_to_planes_parts(N, L) > (size_t)kSMs ? (size_t)grad_to_planes_parts(N, L) : (size_t)kSMs;
-          p->off_bpart = o; o += a64(parts * 64); }
+        p->off_bpart = o; o += a64((size_t)grad_to_planes_parts(N, L) * 64);          // bias partials of the first gradient tensor
+        p->off_bparts = o; o += a64((size_t)kSMs * 64) * m->n_mid;                     // ... of each chain launch (read on the side stream)
+        p->off_wpart = o; o += a64(wgrad_tc_scratch_floats());                         // wgrad_tc's partials (side stream)
     }
     p->total_bytes = o * sizeof(float);
     return STOF_OK;
@@ -875,6 +876,10 @@ static __half *train_expand_pack(const stof_model *m) { return train_contract_pa
 static int ensure_train_tc(stof_model *m, cudaStream_t st) {
     const size_t per_layer = TR_PER_LAYER;
     if (!m->tr_tc_w) STOF_CUDA(cudaMalloc(&m->tr_tc_w, (2 * (size_t)m->n_mid * per_layer + 2 * TR_SGB_PACK) * sizeof(__half)));
+    if (!m->tr_side) {
+        STOF_CUDA(cudaStreamCreateWithFlags(&m->tr_side, cudaStreamNonBlocking));
+        for (cudaEvent_t &e : m->tr_ev) STOF_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
     if (!m->tr_tc_dirty) return STOF_OK;
     if (m->sgb_scale != 1) {
         train_pack_sgb_kernel<<<dim3((512 * 64 * 5 + 255) / 256, 2), 256, 0, st>>>(m->raw_contract_w, m->raw_expand_w, train_contract_pack(m),
@@ -1047,40 +1052,60 @@ extern "C" int stof_backward(stof_model *m, const float *x, const float *g_mask,
         float *bpart = ws + pl.off_bpart;
         int n_slot = 0;
         const int cgrid = chain_tc_grid(1, &m->tr_bwd[0], N, L);
-        // X -> planes
-        if ((rc = launch_absmax(X, n4, raw_amax, st))) return rc;
-        if ((rc = launch_grad_to_planes(X, buf[0], N, L, st, raw_amax, bpart, &slots[0]))) return rc;
-        if ((rc = launch_bias_parts_reduce(bpart, grad_to_planes_parts(N, L), gr->mid_b[nm - 1], st))) return rc;
-        // g (planes, slot) = gradient wrt the output of conv j: dW_j; out = dgrad_j(g) [* lrelu'(a) | + skip] with its slot and the
-        // bias gradient of the conv below (db_below, whose output gradient `out` is)
-        auto step = [&](int j, int gi, int gslot, int oi, int mode, const void *aux, int aux_slot, float *db_below) -> int {
+        const size_t bp_stride = ((size_t)kSMs * 64 + 63) / 64 * 64;
+        auto bparts = [&](int slot) { return ws + pl.off_bparts + (size_t)(slot - 1) * bp_stride; };     // of the chain launch that wrote `slot`
+        // The weight and bias gradients only READ what the data-gradient chain produces, so they run on a side stream next to
+        // it (forked and joined with events - also under CUDA-graph capture): at the reference's batch size the backward is a
+        // chain of ~50 tiny dependent kernels, and this halves its critical path.
+        cudaStream_t side = m->tr_side;
+        float *wpart = ws + pl.off_wpart;
+        int ev_i = 0;
+        cudaEvent_t buf_free[3] = {nullptr, nullptr, nullptr}, last_side = nullptr;      // side-stream work that last read buf[i]
+        // dW_j, db_j from g = buf[gi] (gradient wrt the output of conv j, just produced on the main stream with its bias partials)
+        auto side_grads = [&](int j, int gi, int gslot, const float *bp, int parts, const GradSlot *bslot) -> int {
             int r;
-            if ((r = launch_wgrad_tc(buf[gi], pact(j - 1), &slots[gslot], N, L, partial, gr->mid_w[j], st))) return r;
+            cudaEvent_t ready = m->tr_ev[ev_i++], done = m->tr_ev[ev_i++];
+            STOF_CUDA(cudaEventRecord(ready, st));
+            STOF_CUDA(cudaStreamWaitEvent(side, ready, 0));
+            if ((r = launch_wgrad_tc(buf[gi], pact(j - 1), &slots[gslot], N, L, wpart, gr->mid_w[j], side))) return r;
+            if ((r = launch_bias_parts_reduce(bp, parts, gr->mid_b[j], side, bslot))) return r;
+            STOF_CUDA(cudaEventRecord(done, side));
+            buf_free[gi] = done; last_side = done;
+            return STOF_OK;
+        };
+        // main stream: buf[oi] = dgrad_j(buf[gi]) [* lrelu'(aux) | + aux], with the new tensor's slot and bias partial sums
+        auto step = [&](int j, int gi, int gslot, int oi, int mode, const void *aux, int aux_slot, bool want_bias) -> int {
+            if (buf_free[oi]) STOF_CUDA(cudaStreamWaitEvent(st, buf_free[oi], 0));      // its last reader on the side stream is done
             TcGrad g;
             g.mode = mode; g.aux = aux;
             g.g_in = &slots[gslot]; g.g_aux = aux_slot >= 0 ? &slots[aux_slot] : nullptr;
             g.g_out = &slots[++n_slot];
-            g.bias_partial = db_below ? bpart : nullptr;
-            if ((r = launch_chain_tc_grad(&m->tr_bwd[j], buf[gi], buf[oi], N, L, st, g))) return r;
-            if (db_below && (r = launch_bias_parts_reduce(bpart, cgrid, db_below, st, g.g_out))) return r;
-            return STOF_OK;
+            g.bias_partial = want_bias ? bparts(n_slot) : nullptr;
+            return launch_chain_tc_grad(&m->tr_bwd[j], buf[gi], buf[oi], N, L, st, g);
         };
+        // X -> planes
+        if ((rc = launch_absmax(X, n4, raw_amax, st))) return rc;
+        if ((rc = launch_grad_to_planes(X, buf[0], N, L, st, raw_amax, bpart, &slots[0]))) return rc;
         // conv{nm-1} (long skip): a = x0 + conv(a_prev): g_conv = X;  S = dgrad(X) = gradient wrt a_{nm-2}
         int si = 1, s_slot;
-        if ((rc = step(nm - 1, 0, 0, si, 1, nullptr, -1, nm >= 2 ? gr->mid_b[nm - 2] : nullptr))) return rc;
+        if ((rc = side_grads(nm - 1, 0, 0, bpart, grad_to_planes_parts(N, L), nullptr))) return rc;
+        if ((rc = step(nm - 1, 0, 0, si, 1, nullptr, -1, nm >= 2))) return rc;
         s_slot = n_slot;
         // pairs (RES j, LEAKY j - 1), j = nm-2, nm-4, ..., 1
         for (int j = nm - 2; j >= 1; j -= 2) {
             // a_j = a_{j-2} + conv_j(a_{j-1}):  T = dgrad_j(S) * lrelu'(a_{j-1}) = gradient wrt the output of conv j-1; the skip keeps S
             const int ti = (si + 1) % 3, s2 = (si + 2) % 3;
-            if ((rc = step(j, si, s_slot, ti, 3, pact(j - 1), -1, gr->mid_b[j - 1]))) return rc;
+            if ((rc = side_grads(j, si, s_slot, bparts(s_slot), cgrid, &slots[s_slot]))) return rc;
+            if ((rc = step(j, si, s_slot, ti, 3, pact(j - 1), -1, true))) return rc;
             const int t_slot = n_slot;
             // a_{j-1} = lrelu(conv_{j-1}(a_{j-2})):  S' = S + dgrad_{j-1}(T) = gradient wrt a_{j-2} (the output of conv j-2, or x0)
-            if ((rc = step(j - 1, ti, t_slot, s2, 2, buf[si], s_slot, j - 2 >= 0 ? gr->mid_b[j - 2] : nullptr))) return rc;
+            if ((rc = side_grads(j - 1, ti, t_slot, bparts(t_slot), cgrid, &slots[t_slot]))) return rc;
+            if ((rc = step(j - 1, ti, t_slot, s2, 2, buf[si], s_slot, j - 2 >= 0))) return rc;
             si = s2; s_slot = n_slot;
         }
         // S (planes) = gradient wrt x0 through the chain: back to fp32, + the long skip's X
         if ((rc = launch_grad_planes_to_c4l4(buf[si], S, N, L, st, &slots[s_slot], X))) return rc;
+        if (last_side) STOF_CUDA(cudaStreamWaitEvent(st, last_side, 0));                // join: everything after sees dW / db
     } else {
         // ---- mid convs, fp32 path: weight gradient with the conv's input (the output of conv j - 1, or x0), then out (+)= data gradient
         auto mid_backward = [&](int j, const float *g, float *out, bool accumulate) -> int {
