@@ -66,7 +66,10 @@ constexpr float ET_SIGM_SCALE = -1.4426950408889634f;      // -log2(e)
 // was measured: 12 instead of 5 instructions per tanh, forward 1.96 -> 2.53 ms, and NO change of the final mask error, which is
 // set by the 22-bit hi/lo operands of the two tensor-core convolutions, not by the activations.  Sharing one reciprocal between
 // two tanh - 1 / (1 + ea) = (1 + eb) / ((1 + ea)(1 + eb)): three MUFU operations instead of four, four more FP32 instructions per
-// pair - was measured too: 1.815 -> 1.795 ms, within noise of a wash between the MUFU and the issue floors; not kept.)
+// pair - was measured too: 1.815 -> 1.795 ms, within noise of a wash between the MUFU and the issue floors; not kept.
+// Also measured (r11e, with an ncu opcode histogram: 96 FSEL per position for the zero padding, 16 FADD + two TMEM loads per
+// conv2 item for the second issuer's partial sums): zero rows by a branch around the item instead of selects, and ONE conv2 issuer
+// with one accumulator - 9 % fewer instructions, 1.815 -> 1.836 ms: the kernel is not short of issue slots; not kept.)
 __device__ __forceinline__ float tanh_scaled(float a) {
     float e, r;
     asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(a));
