@@ -320,7 +320,10 @@ int stof_forward_train(stof_model *m, const float *x_dev, int N, int L, float *m
 
 /* `loss.backward()` (main.py:247) for the StofNet stack: g_mask_dev (N, r*L) = d loss / d masks_pred -> every parameter's
  * gradient (overwritten, not accumulated: the reference calls optimizer.zero_grad() before every backward, main.py:246).
- * Must follow stof_forward_train on the same x_dev / ws_dev with unchanged weights.                                      */
+ * Must follow stof_forward_train on the same x_dev / ws_dev with unchanged weights.
+ * Stream-ordered on `stream`: on the tensor-core path the weight / bias gradients of the conv stack run on a side stream of
+ * the model, forked from and joined back into `stream` with events before the call returns (safe under CUDA-graph capture
+ * once a first, uncaptured call has created that stream).  Deterministic: bit-identical gradients run to run.            */
 int stof_backward(stof_model *m, const float *x_dev, const float *g_mask_dev, int N, int L, void *ws_dev, size_t ws_bytes,
                   const stof_grads *grads, void *stream);
 
