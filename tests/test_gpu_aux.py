@@ -157,6 +157,32 @@ def test_attention_block(sb, dev, golden):
     assert not torch.equal(blk(x, seed=1), blk(x, seed=2)) and torch.equal(blk(x, seed=3), blk(x, seed=3))
 
 
+def test_attention_block_at_its_intended_shape(sb, dev):
+    """utils/attention_block.py is dead code in the reference (it raises NameError as shipped: parity unpinned); the
+    shape it was written for is a frame of 512 positions x ~1288 features.  Checker here: the same formula
+    softmax(q k^T / sqrt(H)) v in torch float64 on the GPU (test-only), dropout off; fp32 kernel within 2e-5 of the output range."""
+    torch.manual_seed(5)
+    B, S, D, H = 2, 512, 1288, 1288
+    blk = sb.AttentionBlock(D, H, dropout_p=0.0).to(dev)
+    x = torch.randn(B, S, D, device=dev)
+    y = blk(x)
+    with torch.no_grad():
+        xd = x.double()
+        q, k, v = (torch.nn.functional.linear(xd, getattr(blk, n).weight.double(), getattr(blk, n).bias.double())
+                   for n in ("query", "key", "value"))
+        ref = torch.softmax(q @ k.transpose(1, 2) / (H ** 0.5), dim=-1) @ v
+    assert y.shape == ref.shape
+    assert float((y.double() - ref).abs().max()) <= 2e-5 * float(ref.abs().max())
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(5):
+        blk(x)
+    e1.record()
+    torch.cuda.synchronize()
+    print("AttentionBlock (2, 512, 1288) -> 1288: %.3f ms per call" % (e0.elapsed_time(e1) / 5))
+
+
 def test_surface_thresholding(sb, dev, golden):
     """thresholding (utils/mask2samples.py:14-23) as stof_thresholding: bit-exact, in place for a float threshold."""
     g = golden("surface_cases.npz")
