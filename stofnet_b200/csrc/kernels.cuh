@@ -95,6 +95,12 @@ int launch_chain_tc(const TcLayer *layers, int count, const void *in, const void
 // one TC_NONE layer in gradient mode (the training step's data gradients; see TcGrad)
 int launch_chain_tc_grad(const TcLayer *layer, const void *in, void *out_planes, int N, int L, cudaStream_t st, const TcGrad &grad);
 int chain_tc_grid(int count, const TcLayer *layers, int N, int L);       // CTAs of that launch (= parts of TcGrad::bias_partial)
+// conv1l_tc.cu: ONE 64 -> 64 k7 layer per launch with the layer's taps resident in shared memory (the training step keeps every
+// activation and cannot fuse layers).  type: TC_LEAKY, TC_LONGSKIP (aux = skip planes) or TC_NONE; grad (or NULL): gradient mode,
+// TcGrad::bias_partial with conv1l_tc_grid(N, L) parts.  Results equal launch_chain_tc's one-layer launch bit for bit.
+int conv1l_tc_grid(int N, int L);
+int launch_conv1l_tc(const TcLayer *layer, int type, const void *in, const void *aux, void *out, int N, int L, cudaStream_t st,
+                     const TcGrad *grad = nullptr);
 // conv_tc2.cu: the same segment on CTA pairs (2-CTA clusters, tcgen05 cta_group::2: M = 256 per MMA, each CTA reads half of B)
 int launch_chain_tc2(const TcLayer *layers, int count, const void *in, const void *x0, void *out_planes, float *out_mask,
                      int N, int L, cudaStream_t st, int fast = 0);

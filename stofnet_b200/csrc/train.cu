@@ -16,6 +16,7 @@
 //                      semi-global block (window sum, expand, arg-max scatter through the pool, contract), conv1
 #include <cuda_fp16.h>
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "model.cuh"
@@ -873,6 +874,13 @@ static __half *train_contract_pack(const stof_model *m) { return reinterpret_cas
 static __half *train_expand_pack(const stof_model *m) { return train_contract_pack(m) + TR_SGB_PACK; }
 
 // (re)build the training packs on `st` when the weights changed since the last build
+// The mid convs of the training step: the weight-stationary one-layer kernel (conv1l_tc.cu), or - STOF_TRAIN_CONV1L=0, kept for
+// A/B measurements - one-layer launches of the inference chain kernel; bit-identical results
+static bool train_conv1l() {
+    static const bool on = [] { const char *e = getenv("STOF_TRAIN_CONV1L"); return !(e != nullptr && e[0] == '0'); }();
+    return on;
+}
+
 static int ensure_train_tc(stof_model *m, cudaStream_t st) {
     const size_t per_layer = TR_PER_LAYER;
     if (!m->tr_tc_w) STOF_CUDA(cudaMalloc(&m->tr_tc_w, (2 * (size_t)m->n_mid * per_layer + 2 * TR_SGB_PACK) * sizeof(__half)));
@@ -964,7 +972,12 @@ extern "C" int stof_forward_train(stof_model *m, const float *x, int N, int L, f
             void *outp = ws + pl.off_pa[j];
             const bool longskip = (j == m->n_mid - 1);
             const void *skip = (longskip || j < 2) ? px0 : (const void *)(ws + pl.off_pa[j - 2]);
-            if ((rc = launch_chain_tc(&m->tr_fwd[j], 1, curp, ((j & 1) || longskip) ? skip : nullptr, outp, nullptr, N, L, st))) return rc;
+            const bool add_skip = (j & 1) || longskip;
+            if (train_conv1l())
+                rc = launch_conv1l_tc(&m->tr_fwd[j], add_skip ? TC_LONGSKIP : TC_LEAKY, curp, add_skip ? skip : nullptr, outp, N, L, st);
+            else
+                rc = launch_chain_tc(&m->tr_fwd[j], 1, curp, add_skip ? skip : nullptr, outp, nullptr, N, L, st);
+            if (rc) return rc;
             // fp32 copy only of the last activation (conv_last forward and weight gradient); lrelu' reads the planes
             if (longskip && (rc = launch_planes_to_c4l4(outp, ws + pl.off_a[j], N, L, st))) return rc;
             curp = outp;
@@ -1051,7 +1064,7 @@ extern "C" int stof_backward(stof_model *m, const float *x, const float *g_mask,
         void *buf[3] = {ws + pl.off_gp[0], ws + pl.off_gp[1], ws + pl.off_g[2]};       // planes (the fp32 T buffer is not used on this path)
         float *bpart = ws + pl.off_bpart;
         int n_slot = 0;
-        const int cgrid = chain_tc_grid(1, &m->tr_bwd[0], N, L);
+        const int cgrid = train_conv1l() ? conv1l_tc_grid(N, L) : chain_tc_grid(1, &m->tr_bwd[0], N, L);
         const size_t bp_stride = ((size_t)kSMs * 64 + 63) / 64 * 64;
         auto bparts = [&](int slot) { return ws + pl.off_bparts + (size_t)(slot - 1) * bp_stride; };     // of the chain launch that wrote `slot`
         // The weight and bias gradients only READ what the data-gradient chain produces, so they run on a side stream next to
@@ -1081,6 +1094,7 @@ extern "C" int stof_backward(stof_model *m, const float *x, const float *g_mask,
             g.g_in = &slots[gslot]; g.g_aux = aux_slot >= 0 ? &slots[aux_slot] : nullptr;
             g.g_out = &slots[++n_slot];
             g.bias_partial = want_bias ? bparts(n_slot) : nullptr;
+            if (train_conv1l()) return launch_conv1l_tc(&m->tr_bwd[j], TC_NONE, buf[gi], nullptr, buf[oi], N, L, st, &g);
             return launch_chain_tc_grad(&m->tr_bwd[j], buf[gi], buf[oi], N, L, st, g);
         };
         // X -> planes
