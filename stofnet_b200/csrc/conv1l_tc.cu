@@ -192,8 +192,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv1l_tc_kernel(const C1Params
             if (use_aux) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
-                    xs_h[q] = inside ? __ldg(aux + (size_t)q * p.L) : make_uint4(0, 0, 0, 0);
-                    xs_l[q] = inside ? __ldg(aux + (size_t)(8 + q) * p.L) : make_uint4(0, 0, 0, 0);
+                    xs_h[q] = inside ? aux[(size_t)q * p.L] : make_uint4(0, 0, 0, 0);     // plain loads: the skip may be updated in place (out == aux)
+                    xs_l[q] = inside ? aux[(size_t)(8 + q) * p.L] : make_uint4(0, 0, 0, 0);
                 }
             }
             mbar_wait(BAR_ACC_FULL(a), (uint32_t)(i >> 2) & 1u);
@@ -272,8 +272,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv1l_tc_kernel(const C1Params
                     // the second pass's vectors (their latency hides behind the TMEM loads and the first chunk's math of that pass)
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
-                        xs_h[q] = inside ? __ldg(aux + (size_t)(4 + q) * p.L) : make_uint4(0, 0, 0, 0);
-                        xs_l[q] = inside ? __ldg(aux + (size_t)(12 + q) * p.L) : make_uint4(0, 0, 0, 0);
+                        xs_h[q] = inside ? aux[(size_t)(4 + q) * p.L] : make_uint4(0, 0, 0, 0);
+                        xs_l[q] = inside ? aux[(size_t)(12 + q) * p.L] : make_uint4(0, 0, 0, 0);
                     }
                 }
             }

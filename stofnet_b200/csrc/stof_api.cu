@@ -599,6 +599,39 @@ static int forward_chunk_tc(stof_model *m, const float *x, int n, int L, float *
     // x0 = relu(conv1 x) + upsample(E) as split planes (:45,108-115); also the long skip res1 (:51,62)
     { ProfScope p(m, STOF_PROF_SGB_ADD, st);
       if ((rc = launch_x0_split(x, sgb ? e : nullptr, n, L, pl.P, m->sgb_scale, off, m->first.w, m->first.b, B1, st, fast, m->k_first))) return rc; }
+    // EXPERIMENT (STOF_INFER_CONV1L=1): the mid convs layer by layer on the weight-stationary kernel (conv1l_tc.cu) instead of
+    // fused segments: no halo recompute and no weight re-streaming, but 512 B of HBM traffic per position and layer
+    static const bool by_layer = [] { const char *e = getenv("STOF_INFER_CONV1L"); return e != nullptr && e[0] == '1'; }();
+    if (by_layer && !fast && m->kind == STOF_KIND_STOFNET && m->tc_layer[0].taps == 7) {
+        // a_j: LEAKY layers write the free buffer; short-skip layers add onto their skip IN PLACE (a thread reads its skip vector
+        // before it writes the same vector, nobody else reads that buffer); B1 = x0 stays for the long skip
+        const void *in = B1, *prev = B1;               // a_{j-1}, a_{j-2}
+        void *fr = B2, *other = B0;
+        for (int j = 0; j + 1 < m->n_tc; ++j) {
+            const int type = m->tc_layer[j].type;
+            ProfScope p(m, STOF_PROF_MID, st);
+            if (type == TC_LEAKY) {
+                void *out = (in == fr) ? other : fr;
+                if ((rc = launch_conv1l_tc(m->tc_layer + j, TC_LEAKY, in, nullptr, out, n, L, st))) return rc;
+                prev = in; in = out;
+            } else if (type == TC_RES) {
+                if (prev == B1) {                          // the first short skip is x0 itself: keep it, write the third buffer
+                    void *out = (in == fr) ? other : fr;
+                    if ((rc = launch_conv1l_tc(m->tc_layer + j, TC_LONGSKIP, in, prev, out, n, L, st))) return rc;
+                    prev = in; in = out;
+                } else {
+                    if ((rc = launch_conv1l_tc(m->tc_layer + j, TC_LONGSKIP, in, prev, const_cast<void *>(prev), n, L, st))) return rc;
+                    const void *t = prev; prev = in; in = t;
+                }
+            } else {                                       // long skip (x0)
+                void *out = (in == fr) ? other : fr;
+                if ((rc = launch_conv1l_tc(m->tc_layer + j, TC_LONGSKIP, in, B1, out, n, L, st))) return rc;
+                prev = in; in = out;
+            }
+        }
+        ProfScope p(m, STOF_PROF_LAST, st);
+        return launch_chain_tc(m->tc_layer + m->n_tc - 1, 1, in, B1, nullptr, mask, n, L, st, 0);
+    }
     const void *cur = B1;
     void *pp[2] = {B2, B0};
     int which = 0;
