@@ -34,8 +34,8 @@ constexpr int C1_NBUF = 3;
 constexpr int C1_OFF_W = 0;                                 // 7 taps x 16 KB, resident
 constexpr int C1_OFF_IN = 7 * TC_STAGE_BYTES;               // 114,688
 constexpr int C1_OFF_BIAS = C1_OFF_IN + C1_NBUF * C1_HBUF;  // 219,136
-constexpr int C1_OFF_BAR = C1_OFF_BIAS + 64 * 4;            // w_full, in_full[3], in_empty[3], acc_full[4], acc_empty[4]
-constexpr int C1_NBAR = 1 + 2 * C1_NBUF + 8;
+constexpr int C1_OFF_BAR = C1_OFF_BIAS + 64 * 4;            // w_full[7], in_full[3], in_empty[3], acc_full[4], acc_empty[4]
+constexpr int C1_NBAR = 7 + 2 * C1_NBUF + 8;
 constexpr int C1_OFF_TMEM = C1_OFF_BAR + C1_NBAR * 8;
 constexpr int C1_SMEM_BYTES = C1_OFF_TMEM + 16;
 static_assert(C1_SMEM_BYTES <= 232448, "conv1l kernel exceeds the 227 KB shared-memory limit");
@@ -57,17 +57,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv1l_tc_kernel(const C1Params
     const uint32_t sbase = smem_u32(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t bar0 = sbase + C1_OFF_BAR;
-    const uint32_t BAR_W_FULL = bar0;
-    auto BAR_IN_FULL = [&](int b) { return bar0 + 8 * (1 + b); };
-    auto BAR_IN_EMPTY = [&](int b) { return bar0 + 8 * (1 + C1_NBUF + b); };
-    auto BAR_ACC_FULL = [&](int a) { return bar0 + 8 * (1 + 2 * C1_NBUF + a); };
-    auto BAR_ACC_EMPTY = [&](int a) { return bar0 + 8 * (1 + 2 * C1_NBUF + 4 + a); };
+    auto BAR_W_FULL = [&](int t) { return bar0 + 8 * t; };           // one per tap: the first MMAs start behind tap 0, not behind all 112 KB
+    auto BAR_IN_FULL = [&](int b) { return bar0 + 8 * (7 + b); };
+    auto BAR_IN_EMPTY = [&](int b) { return bar0 + 8 * (7 + C1_NBUF + b); };
+    auto BAR_ACC_FULL = [&](int a) { return bar0 + 8 * (7 + 2 * C1_NBUF + a); };
+    auto BAR_ACC_EMPTY = [&](int a) { return bar0 + 8 * (7 + 2 * C1_NBUF + 4 + a); };
     float *s_bias = reinterpret_cast<float *>(smem + C1_OFF_BIAS);
     volatile uint32_t *s_tmem = reinterpret_cast<volatile uint32_t *>(smem + C1_OFF_TMEM);
 
     if (threadIdx.x < 64) s_bias[threadIdx.x] = __ldg(p.bias + threadIdx.x);
     if (threadIdx.x == 0) {
-        mbar_init(BAR_W_FULL, 1);
+        for (int t = 0; t < 7; ++t) mbar_init(BAR_W_FULL(t), 1);
         for (int b = 0; b < C1_NBUF; ++b) { mbar_init(BAR_IN_FULL(b), 1); mbar_init(BAR_IN_EMPTY(b), 1); }
         for (int a = 0; a < 4; ++a) { mbar_init(BAR_ACC_FULL(a), 1); mbar_init(BAR_ACC_EMPTY(a), 4); }   // four epilogue warps drain it
         fence_mbar_init();
@@ -86,10 +86,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv1l_tc_kernel(const C1Params
     if (warp == 0) {
         // =================================== producer ===================================================
         if (lane == 0) {
-            mbar_arrive_expect_tx(BAR_W_FULL, 7u * TC_STAGE_BYTES);
-            for (int t = 0; t < 7; ++t)
+            for (int t = 0; t < 7; ++t) {
+                mbar_arrive_expect_tx(BAR_W_FULL(t), TC_STAGE_BYTES);
                 bulk_g2s(sbase + C1_OFF_W + t * TC_STAGE_BYTES, reinterpret_cast<const uint8_t *>(p.w) + (size_t)t * TC_STAGE_BYTES,
-                         TC_STAGE_BYTES, BAR_W_FULL);
+                         TC_STAGE_BYTES, BAR_W_FULL(t));
+            }
         }
         for (int i = 0; i < n_my; ++i) {
             const int b = i % C1_NBUF;
@@ -122,7 +123,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv1l_tc_kernel(const C1Params
         const int cls = warp - 1;
         constexpr uint32_t kDescHi = (128u >> 4) | (1u << 14);
         constexpr uint32_t idesc_a = umma_idesc_f16(128, 128), idesc_b = umma_idesc_f16(128, 64);
-        mbar_wait(BAR_W_FULL, 0u);
         for (int i = cls; i < n_my; i += 2) {
             const int b = i % C1_NBUF, a = acc_of(i);
             mbar_wait(BAR_IN_FULL(b), (uint32_t)(i / C1_NBUF) & 1u);
@@ -133,6 +133,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv1l_tc_kernel(const C1Params
                 const uint32_t w_base = ((sbase + C1_OFF_W) >> 4) | (128u << 16);
                 const uint32_t d = tmem0 + 128u * (uint32_t)a;
                 for (int t = 0; t < 7; ++t) {
+                    if (i < 2) { mbar_wait(BAR_W_FULL(t), 0u); tc_fence_after_sync(); }     // this issuer's first half-tile: tap by tap
                     const uint32_t a_lo = a_base + (uint32_t)t;
                     const uint32_t w_lo = w_base + (uint32_t)t * (TC_STAGE_BYTES >> 4);
 #pragma unroll
