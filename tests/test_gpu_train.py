@@ -5,9 +5,13 @@ Tolerances (fp32, different summation orders): forward mask 1e-4 of its range (a
 parameter gradient within 2e-4 of that tensor's max |grad| (+ a 1e-7 absolute floor); loss within 1e-4 relative;
 parameters after three AdamW steps within 3e-5 absolute (lr = 5e-4: a sign flip of a ~zero gradient moves a weight
 by up to lr per step, so elementwise agreement is checked at the 99.9th percentile and the max is bounded by 3 lr)."""
+import os
+
 import numpy as np
 import pytest
 import torch
+
+ROOT_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 pytestmark = pytest.mark.gpu
 
@@ -208,6 +212,49 @@ def test_training_paths_agree_on_a_multi_tile_batch(sb, golden):
     for k in g_fp:
         rel = float((g_tc[k] - g_fp[k]).abs().max()) / max(float(g_fp[k].abs().max()), 1e-30)
         assert rel <= (1e-4 if k.startswith("conv12.") or k.startswith("conv_last.") else 3e-3), (k, rel)
+
+
+def test_one_layer_kernel_equals_the_chain_kernel_bit_for_bit(sb, golden, tmp_path):
+    """conv1l_tc.cu (weights resident in shared memory, the training step's default) against one-layer launches of the inference
+    chain kernel (STOF_TRAIN_CONV1L=0): same operands, same accumulation order - the training forward's mask and every parameter
+    gradient must be IDENTICAL (the mid convs' bias gradients, sums over per-CTA partials, to 2e-6).  The switch is read once per process, so each variant runs in a process of its own."""
+    import subprocess
+    import sys
+    script = r"""
+import os, sys, numpy as np, torch
+sys.path.insert(0, %r)
+import stofnet_b200 as sb
+from stofnet_b200.synth import synth_waveforms
+dev = torch.device("cuda:0")
+sd = sb.load_checkpoint(os.path.join(%r, "tests", "golden", "weights_different-armadillo.npz"))
+model = sb.build_model(sd, dev).train()
+N, L = 6, 2578
+x = torch.from_numpy(synth_waveforms(N, L, seed=29, rf=10)).unsqueeze(1).to(dev)
+gt = torch.from_numpy(np.random.default_rng(4).integers(50, 4 * L - 50, size=(N, 1, 4))).to(dev)
+mask = model(x)
+sb.mask_loss(mask, gt, 7, 1.0, 20.0, 1e-2).backward()
+out = {"mask": mask.detach().cpu().numpy()}
+for k, p in model.named_parameters():
+    out["g/" + k] = p.grad.cpu().numpy()
+np.savez(sys.argv[1], **out)
+""" % (ROOT_DIR, ROOT_DIR)
+    res = {}
+    for v in ("0", "1"):
+        f = str(tmp_path / ("v%s.npz" % v))
+        env = dict(os.environ, STOF_TRAIN_CONV1L=v)
+        r = subprocess.run([sys.executable, "-c", script, f], env=env, capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-2000:]
+        res[v] = dict(np.load(f))
+    assert set(res["0"]) == set(res["1"]) and len(res["0"]) > 20
+    for k in res["0"]:
+        a, b = res["0"][k], res["1"][k]
+        if k.startswith("g/") and k.endswith(".bias") and k[2:6] == "conv" and k not in ("g/conv1.bias", "g/conv_last.bias") \
+                and not k.endswith("conv12.bias"):
+            # bias gradients of conv2..conv11 are sums of the data-gradient kernels' per-CTA partials: the two kernels cut the
+            # batch into CTAs differently, so these (and only these) differ in the summation order
+            assert np.abs(a - b).max() <= 2e-6 * np.abs(b).max(), k
+        else:
+            assert np.array_equal(a, b), k
 
 
 def test_graphed_step_reproduces_the_eager_trajectory(sb, golden):
