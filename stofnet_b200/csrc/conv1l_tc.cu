@@ -15,6 +15,10 @@
 // accumulation are those of conv_tc.cu (fp16 hi/lo split, [D0 | D1] += X_hi [W_hi; W_lo]^T, D1 += X_lo W_hi^T; result D0 +
 // 2^-11 D1), so the results equal the chain kernel's one-layer launch bit for bit.
 //
+// (Measured and not kept: an L2 prefetch of the half-tile that takes a buffer next - 92 vs 90 us per forward layer at 256 x 2560:
+// the input copies are not what the MMAs wait for; fetching the activation's lo plane only when a hi value is zero in the lrelu'
+// mode - within noise.)
+//
 // Epilogue variants: bias + LeakyReLU, bias + skip (split planes from global memory), and the gradient mode of kernels.cuh
 // (TcGrad: rescale by a power of two chosen from the operands' slots, + skip gradient or * lrelu'(activation), max |out| and
 // per-CTA bias-gradient sums recorded on the way).
