@@ -165,16 +165,22 @@ class Engine:
         self.key = key
         del keep
 
-    def sync_device(self, module, device):
+    def sync_device(self, module, device, cache_key=None):
         """After an in-place optimizer step on the device (Trainer): re-derive the kernels' weight layouts from the
-        parameters where they live, with one kernel on the current stream (stof_model_set_weights_device)."""
-        params = dict(module.state_dict(keep_vars=True))
-        W, keep = self._pack(params, on_device=True)
-        if getattr(module, "semi_global_block", None) is not None:
-            W.sgb_scale = int(module.semi_global_block.sample_scale)
+        parameters where they live, with one kernel on the current stream (stof_model_set_weights_device).
+        cache_key (Trainer: the address of its flat parameter buffer, which every parameter is a view of): the pointer table
+        is built once and reused while the key is the same - the walk over the state_dict was ~10 % of a batch-4 step."""
+        cached = getattr(self, "_dev_pack", None)
+        if cache_key is not None and cached is not None and cached[0] == (cache_key, id(module)):
+            W = cached[1]
+        else:
+            params = dict(module.state_dict(keep_vars=True))
+            W, keep = self._pack(params, on_device=True)
+            if getattr(module, "semi_global_block", None) is not None:
+                W.sgb_scale = int(module.semi_global_block.sample_scale)
+            self._dev_pack = ((cache_key, id(module)), W, keep) if cache_key is not None else None
         with torch.cuda.device(device):
             check(lib.stof_model_set_weights_device(self.handle, C.byref(W), stream_ptr(device)))
-        del keep
 
     def set_path(self, path, layers_per_launch=0):
         """path: _lib.PATH_TC (tcgen05, fp16 hi/lo split operands) or _lib.PATH_SIMT (fp32 FFMA)."""
@@ -231,8 +237,9 @@ class Engine:
         return out
 
     # -- training step -------------------------------------------------------------------
-    def forward_train(self, module, x):
-        """Forward that keeps the activations in a workspace for backward(); returns (mask, x_contig, workspace)."""
+    def forward_train(self, module, x, synced=False):
+        """Forward that keeps the activations in a workspace for backward(); returns (mask, x_contig, workspace).
+        synced: the caller vouches that the handle holds the module's current parameters (Trainer, which tracks their versions)."""
         require_cuda(x, "input")
         if x.dim() != 3 or x.shape[1] != 1:
             raise RuntimeError("stofnet_b200: expected input of shape (N, 1, L), got %s" % (tuple(x.shape),))
@@ -240,7 +247,8 @@ class Engine:
         x = x.detach().to(torch.float32).contiguous()
         N, _, L = x.shape
         with torch.cuda.device(dev):
-            self.sync(module, dev)
+            if not (synced and self.handle is not None):
+                self.sync(module, dev)
             self._apply_path()
             need = C.c_size_t()
             check(lib.stof_train_workspace_bytes(self.handle, N, L, C.byref(need)))
@@ -250,21 +258,29 @@ class Engine:
                                          stream_ptr(dev)))
         return out, x, ws
 
-    def backward(self, module, x, g_mask, ws, names):
-        """d loss / d masks_pred -> one flat fp32 gradient buffer; returns (flat, [view per name in `names`])."""
+    def backward(self, module, x, g_mask, ws, names, reuse=False):
+        """d loss / d masks_pred -> one flat fp32 gradient buffer; returns (flat, [view per name in `names`]).
+        reuse (Trainer only): the same gradient bucket, views and pointer table on every call - the kernels overwrite every
+        gradient, so nothing needs clearing; the autograd path must NOT reuse (torch may keep the returned views as .grad)."""
         dev = x.device
         N, _, L = x.shape
         g_mask = g_mask.detach().to(torch.float32).contiguous()
-        params = dict(module.named_parameters())
-        sizes = [params[k].numel() for k in names]
-        pad = [(-s) % 4 for s in sizes]                     # keep every view 16-byte aligned
-        flat = torch.zeros((sum(sizes) + sum(pad),), dtype=torch.float32, device=dev)
-        views, G, o = [], _lib.Grads(), 0
-        for k, s, p in zip(names, sizes, pad):
-            v = flat[o:o + s].view(params[k].shape)
-            views.append(v)
-            o += s + p
-            self._set_grad_ptr(G, k, v.data_ptr())
+        cached = getattr(self, "_grad_bucket", None) if reuse else None
+        if cached is not None and cached[0] == (id(module), tuple(names), dev):
+            _, flat, views, G = cached
+        else:
+            params = dict(module.named_parameters())
+            sizes = [params[k].numel() for k in names]
+            pad = [(-s) % 4 for s in sizes]                     # keep every view 16-byte aligned
+            flat = torch.zeros((sum(sizes) + sum(pad),), dtype=torch.float32, device=dev)
+            views, G, o = [], _lib.Grads(), 0
+            for k, s, p in zip(names, sizes, pad):
+                v = flat[o:o + s].view(params[k].shape)
+                views.append(v)
+                o += s + p
+                self._set_grad_ptr(G, k, v.data_ptr())
+            if reuse:
+                self._grad_bucket = ((id(module), tuple(names), dev), flat, views, G)
         with torch.cuda.device(dev):
             check(lib.stof_backward(self.handle, x.data_ptr(), g_mask.data_ptr(), N, L, ws.data_ptr(), ws.numel(),
                                     C.byref(G), stream_ptr(dev)))

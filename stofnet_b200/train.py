@@ -74,6 +74,7 @@ class Trainer:
                 self.flat[o:o + s].copy_(p.detach().reshape(-1))
                 p.data = self.flat[o:o + s].view(p.shape)        # same layout as Engine.backward's gradient bucket
                 o += s + pd
+        self._params = params
         self.exp_avg = torch.zeros_like(self.flat)
         self.exp_avg_sq = torch.zeros_like(self.flat)
         self.step_count = 0
@@ -86,11 +87,16 @@ class Trainer:
 
     def _step_impl(self, frame, gt_true, lr, hyper_dev):
         model, eng = self.model, self.model._engine
-        mask, xc, ws = eng.forward_train(model, frame)
+        # the handle follows the parameters through sync_device below; a full sync is needed only when somebody else wrote them
+        # (load_state_dict, a manual edit: torch bumps the tensors' version counters)
+        ver = tuple(p._version for p in self._params)
+        synced = (ver == getattr(self, "_seen_versions", None))
+        mask, xc, ws = eng.forward_train(model, frame, synced=synced)
+        self._seen_versions = ver
         mx = global_blur_max(blur_max(gt_true, mask.shape[-1], self.gauss), self.group)
         loss, g_mask = mask_loss_raw(mask, gt_true, self.gauss, self.mask_amplitude, self.lambda_value, want_grad=True,
                                      blur_max_value=mx)
-        grads, _ = eng.backward(model, xc, g_mask, ws, self.names)
+        grads, _ = eng.backward(model, xc, g_mask, ws, self.names, reuse=True)
         average_gradients(grads, self.group)
         w = _world(self.group)
         if w > 1:
@@ -107,8 +113,8 @@ class Trainer:
                                               self.exp_avg_sq.data_ptr(), self.flat.numel(), hyper_dev.data_ptr(),
                                               stream_ptr(self.device)))
         # parameters changed in place through the flat buffer: the kernels' layouts follow on the device, same stream
-        eng.sync_device(model, self.device)
-        self.last_grads = grads
+        eng.sync_device(model, self.device, cache_key=self.flat.data_ptr())
+        self.last_grads = grads                      # the Trainer's gradient bucket: overwritten by the next step
         return loss.reshape(())
 
     # -- the whole step as ONE CUDA graph --------------------------------------------------------------------------------
