@@ -515,7 +515,43 @@ def gen_surface_cases():
     np.savez_compressed(os.path.join(HERE, "surface_cases.npz"), **out)
     print("surface cases done")
 
+def gen_train_b4():
+    """The reference's own training configuration (config.yaml:11 batch_size 4, rf 10: L = 2560) for one step of
+    main.py:217-248: loss, mask and every parameter's gradient from the reference model and torch autograd."""
+    import torch.nn.functional as F
+    from utils.gaussian import gaussian_kernel
+    gk = torch.tensor(gaussian_kernel(size=7, sigma=1), dtype=torch.float32).unsqueeze(0).unsqueeze(0)
+    name, N, L, lam = "different-armadillo", 4, 2560, 1e-2
+    sd = load_sd(name)
+    torch.manual_seed(1)
+    model = StofNet(upsample_factor=4, semi_global_scale=80)
+    model.load_state_dict(sd)
+    model.train()
+    x = torch.from_numpy(synth_waveforms(N, L, seed=91, rf=10)).unsqueeze(1)
+    rng = np.random.default_rng(17)
+    gt = torch.from_numpy(np.sort(rng.integers(40, 4 * L - 40, size=(N, 1, 3)), axis=-1))
+    gt[1, 0, 2] = 0
+    gt[3, 0, 1:] = 0                                              # absent echoes, as the batches pad them
+    masks_pred = model(x)
+    mt = coords2mask(gt.clone(), masks_pred)
+    blur = F.conv1d(mt, gk, padding=3)
+    blur /= blur.max()
+    blur *= 20
+    loss = torch.nn.MSELoss()(masks_pred.squeeze(1), blur.squeeze(1).float()) + \
+        torch.nn.L1Loss()(masks_pred.squeeze(1), torch.zeros_like(masks_pred.squeeze(1))) * lam
+    loss.backward()
+    out = {"x": x.squeeze(1).numpy(), "gt": gt.numpy(), "lambda": np.float64(lam), "loss": np.float64(loss.item()),
+           "mask0": masks_pred.detach().squeeze(1).numpy(), "names": np.array([k for k, _ in model.named_parameters()])}
+    for k, p in model.named_parameters():
+        out["grad0/" + k] = p.grad.detach().numpy().copy()
+    np.savez_compressed(os.path.join(HERE, "train_b4_%s.npz" % name), **out)
+    print("train b4 case", name, loss.item())
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "train_b4":
+        gen_train_b4()
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "scale":
         gen_scale()
         sys.exit(0)
@@ -541,6 +577,7 @@ if __name__ == "__main__":
     gen_metrics_cases()
     gen_aux_cases()
     gen_train_cases()
+    gen_train_b4()
     gen_scale()
     gen_surface_cases()
     print("done")

@@ -53,6 +53,28 @@ def test_backward_matches_reference_autograd(sb, golden, name):
         assert err <= 2e-4 * np.abs(ref).max() + 1e-7, (k, err, np.abs(ref).max())
 
 
+def test_backward_matches_reference_autograd_at_the_reference_batch(sb, golden):
+    """The reference's own training shape (config.yaml:11 batch_size 4, rf 10: 4 x 2560; BASELINE config 4): mask, loss and every
+    parameter's gradient against the reference model + torch autograd (tests/golden/make_golden.py train_b4).  Here every
+    persistent kernel of the step has real tiles to walk (40 chain half-tiles per row group, 32 pooling windows per row)."""
+    dev = torch.device("cuda:0")
+    g = golden("train_b4_different-armadillo.npz")
+    model = _model(sb, golden, "different-armadillo", dev).train()
+    x = torch.from_numpy(g["x"]).unsqueeze(1).to(dev)
+    gt = torch.from_numpy(g["gt"]).to(dev)
+    masks_pred = model(x)
+    ref_mask = g["mask0"]
+    assert np.abs(masks_pred.detach().squeeze(1).cpu().numpy() - ref_mask).max() <= 1e-4 * np.abs(ref_mask).max()
+    loss = sb.mask_loss(masks_pred, gt, 7, 1.0, 20.0, float(g["lambda"]))
+    assert abs(float(loss.detach()) - float(g["loss"])) <= 1e-4 * abs(float(g["loss"]))
+    loss.backward()
+    assert [str(k) for k in g["names"]] == [k for k, _ in model.named_parameters()]
+    for k, p in model.named_parameters():
+        ref = g["grad0/" + k]
+        err = np.abs(p.grad.cpu().numpy() - ref).max()
+        assert err <= 2e-4 * np.abs(ref).max() + 1e-7, (k, err, np.abs(ref).max())
+
+
 @pytest.mark.parametrize("name", CASES)
 def test_backward_is_deterministic(sb, golden, name):
     dev = torch.device("cuda:0")
