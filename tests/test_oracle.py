@@ -205,3 +205,33 @@ def test_surface_ops_port(golden):
         with torch.no_grad():
             y = torch_port.semi_global_block(sd, x)
         assert np.abs(y.numpy() - g[key + "_y"]).max() <= 2e-5 * np.abs(g[key + "_y"]).max(), key
+
+
+def test_port_training_step_matches_reference_autograd(golden):
+    """The CPU baseline of the training step (bench.py cpu_train_rate: oracle/torch_port.stofnet_forward + torch autograd) against
+    the reference model's own autograd at the reference's batch shape (train_b4 golden: 4 x 2560): same ATen kernels in the same
+    order, so loss, mask and every gradient agree to fp32 noise."""
+    import torch.nn.functional as F
+    g = golden("train_b4_different-armadillo.npz")
+    sd = golden("weights_different-armadillo.npz")
+    torch.manual_seed(0)
+    params = {k: torch.from_numpy(np.ascontiguousarray(v)).clone().requires_grad_(True) for k, v in sd.items()}
+    x = torch.from_numpy(g["x"]).unsqueeze(1)
+    gt = torch.from_numpy(g["gt"]).clone()
+    pred = torch_port.stofnet_forward(params, x)
+    assert np.abs(pred.detach().squeeze(1).numpy() - g["mask0"]).max() <= 1e-6 * np.abs(g["mask0"]).max()
+    mask = torch.zeros_like(pred)
+    gt[gt < 0] = 0
+    mask.scatter_(2, gt, 1)
+    mask[..., :1] = 0                                               # utils/mask2samples.py:139-148
+    gk = torch.tensor([0.00443185, 0.05399097, 0.24197072, 0.39894228, 0.24197072, 0.05399097, 0.00443185]).view(1, 1, -1)
+    blur = F.conv1d(mask, gk, padding=3)
+    blur = blur / blur.max() * 20
+    loss = F.mse_loss(pred.squeeze(1), blur.squeeze(1)) + float(g["lambda"]) * pred.abs().mean()
+    assert abs(float(loss.detach()) - float(g["loss"])) <= 1e-5 * abs(float(g["loss"]))
+    loss.backward()
+    for k in g["names"]:
+        k = str(k)
+        ref = g["grad0/" + k]
+        err = np.abs(params[k].grad.numpy() - ref).max()
+        assert err <= 2e-5 * np.abs(ref).max() + 1e-9, (k, err)
